@@ -1,0 +1,1 @@
+#include "cnf2_refshim.hpp"
