@@ -1,0 +1,316 @@
+#!/usr/bin/env python
+"""Benchmark of the cnF2freq hot path (forward-backward + posterior statistics, the E-step of one EM
+iteration) on B200: individual-marker-states per second.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    torchrun --nproc-per-node N bench.py --gpus N ...          (one rank per GPU, NCCL)
+
+A "step" is one E-step pass over every chromosome of the workload.  Workload (BASELINE.json configs[2], the
+largest configuration that one GPU finishes in seconds at the current kernel speed): synthetic F2 intercross,
+2,000 analysed individuals x 10,000 markers (10 chromosomes x 1,000), 20 % missing genotypes, PER GPU (weak
+scaling: every rank holds its own 2,000 F2s of the same cross; the two founders' statistics rows are
+all-reduced over NCCL once per chromosome).
+
+value      inputs resident in HBM; CUDA events on the engine's stream around the K steps; max over ranks.
+e2e        through the C ABI with pinned HOST buffers: every step copies the parameters host->device
+           (cnf2_set_params) and the statistics device->host (cnf2_get_stats).
+roofline   fp64-pipe and HBM bounds from the algorithmic work of SURVEY.md 8(d): 67,584 flop and
+           694 B per individual-marker; peaks: fp64 measured in this run (register-resident DFMA kernel,
+           MEASURED_PEAKS.json has no fp64 figure), HBM from MEASURED_PEAKS.json.
+cpu_baseline / --impl reference: the reference's own code (oracle/_ref/cnf2ref_fast, built from
+           /root/reference by oracle/build_ref.sh with demo.sh's flags) on all host cores, on a bounded sample
+           of the same workload; it times the reference's whole doit() (E-step + M-step).
+"""
+import argparse
+import json
+import os
+import re
+import statistics
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+NUMTYPES = 64
+FLOP_PER_INDMARKER = 8448 * 8      # 8,448 flop per (individual-marker, shift mode), 8 shift modes
+BYTES_PER_INDMARKER = 238 + 8 + 448  # 34 B x 7 relatives read, 8 B interval, 64 B x 7 accumulated
+METRIC = "individual-marker-states/sec fwd-bwd+EM"
+UNIT = "individual-marker-states/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--individuals", type=int, default=2000, help="analysed F2 individuals per GPU")
+    ap.add_argument("--chroms", type=int, default=10)
+    ap.add_argument("--markers-per-chrom", type=int, default=1000)
+    ap.add_argument("--cpu-sample-individuals", type=int, default=64)
+    ap.add_argument("--cpu-sample-markers", type=int, default=500)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def workload_name(a):
+    return (f"synthetic F2 intercross, {a.individuals} individuals x {a.chroms * a.markers_per_chrom} markers "
+            f"({a.chroms} chromosomes x {a.markers_per_chrom}) per GPU, 20% missing")
+
+
+# ---------------------------------------------------------------------------------------------------------
+# the reference's CPU build on a bounded sample
+def run_reference_cpu(a, iterations, warm):
+    """Times oracle/_ref/cnf2ref_fast (reference code, -O2 -ffast-math -fopenmp as demo.sh:6) on the first
+    cpu-sample-individuals x cpu-sample-markers of the workload.  Returns (rate, seconds per iteration list,
+    cores, sample description) or (None, reason)."""
+    from cnf2freq_b200 import synth
+    binary = os.path.join(ROOT, "oracle", "_ref", "cnf2ref_fast")
+    if not os.path.exists(binary):
+        return None, f"{binary} not built (oracle/build_ref.sh needs /root/reference)"
+    cores = os.cpu_count() or 1
+    n, m = a.cpu_sample_individuals, a.cpu_sample_markers
+    sim = synth.simulate_f2(n_f2=n, n_chrom=1, markers_per_chrom=m, spacing_cM=0.1, missing=0.2, seed=3)
+    with tempfile.TemporaryDirectory() as tmp:
+        synth.write_alpha_files(tmp + "/s", sim)
+        env = dict(os.environ, OMP_NUM_THREADS=str(cores), OMP_STACKSIZE="128M")
+        cmd = [binary, "--mapfile", tmp + "/s.map", "--pedfile", tmp + "/s.ped", "--genfile", tmp + "/s.gen", "--count",
+               str(1 + warm + iterations), "--mode", "time"]
+        res = subprocess.run(cmd, env=env, capture_output=True, text=True)
+    times = [float(x) for x in re.findall(r"TIME iter \d+ seconds (\S+)", res.stdout)]
+    if res.returncode != 0 or len(times) < warm + iterations:
+        return None, f"reference binary failed (rc {res.returncode}): {res.stderr[-200:]}"
+    times = times[warm:]
+    states = n * m * NUMTYPES
+    sample = (f"first {n} individuals x {m} markers of chromosome 1 of the workload; reference doit() = E-step + "
+              f"M-step per iteration; {len(times)} iterations after {warm} warm-up")
+    return (states / statistics.median(times), times, cores, sample), None
+
+
+def reference_arm(a, rank):
+    if rank != 0:
+        return
+    r, why = run_reference_cpu(a, a.steps, a.warmup)
+    if r is None:
+        print(json.dumps({"impl": "reference", "unavailable": why}))
+        return
+    rate, times, cores, sample = r
+    line = {
+        "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
+        "warmup": a.warmup, "ms_per_step": 1e3 * statistics.median(times), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload_name(a), "timing": "host wall clock inside the reference binary (omp_get_wtime)"},
+        "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
+        "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+# ---------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks and throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.thread = [], None, None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        self.thread.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) < 7:
+                continue
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except (OSError, ValueError):
+        return None
+
+
+def ours(a, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    from cnf2freq_b200 import synth
+    from cnf2freq_b200.engine import Engine
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the engine has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def pinned(shape, dtype):
+        t = torch.zeros(tuple(shape), dtype={np.uint8: torch.uint8, np.float64: torch.float64}[dtype], pin_memory=True)
+        return t.numpy()
+
+    d = synth.f2_flat(a.individuals, a.chroms, a.markers_per_chrom, spacing_cM=0.1, missing=0.2, seed=3 + rank, pinned=pinned)
+    K, M, C = d["par"].shape[0], d["markerpos"].shape[0], a.chroms
+    eng = Engine(device=local_rank)
+    eng.set_map(d["markerpos"], d["chromstarts"], d["genrec"])
+    eng.set_shared_rows(d["shared"])
+    if world > 1:
+        class DevBuf:  # zero-copy view of the engine's shared statistics block for torch.distributed
+            def __init__(self, ptr, n):
+                self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f8", "data": (ptr, False), "version": 2}
+
+        def allreduce(ptr, count, stream):
+            with torch.cuda.stream(torch.cuda.ExternalStream(stream)):
+                t = torch.as_tensor(DevBuf(ptr, count), device=torch.device("cuda", local_rank))
+                dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        eng.set_allreduce(allreduce)
+    eng.set_pedigree(d["par"], d["empty"], d["founder"], d["gen"], d["descendants"], d["dous"])
+    out = dict(haplobase=pinned((K, M), np.float64), haplocount=pinned((K, M), np.float64),
+               infprobs=pinned((K, M, 2, 2), np.float64), homozyg=pinned((K, M, 2), np.float64),
+               loglik=np.zeros((len(d["dous"]), C, 2)))
+
+    def barrier():
+        eng.sync()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    def maxranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def e2e_step():
+        for c in range(C):
+            eng.set_params(c, d["alleles"], d["sure"], d["haploweight"])
+            eng.estep(c)
+            eng.get_stats(c, out["haplobase"], out["haplocount"], out["infprobs"], out["homozyg"], out["loglik"])
+
+    def resident_step():
+        for c in range(C):
+            eng.estep(c)
+
+    # warm-up: the e2e steps also leave every chromosome's parameters resident for the device-timed region
+    for _ in range(max(1, a.warmup)):
+        e2e_step()
+    barrier()
+    ind_markers = len(d["dous"]) * M
+    states_per_step = ind_markers * NUMTYPES * world
+
+    # ---- e2e: host buffers, copies inside the timed region ----
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        e2e_step()
+    barrier()
+    e2e_s = maxranks(time.perf_counter() - t0) / a.steps
+    n_rows = int((np.unique(np.concatenate([d["dous"], d["par"][d["dous"]].ravel(), [1, 2]])) > 0).sum())
+    h2d = n_rows * M * 26 + 2 * M * 8
+    d2h = n_rows * M * 64 + len(d["dous"]) * C * 16
+
+    # ---- value: inputs resident in HBM, CUDA events on the launching stream ----
+    for _ in range(a.warmup):
+        resident_step()
+    barrier()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    eng.mark(0)
+    kernel_ms = []
+    for _ in range(a.steps):
+        resident_step()
+    eng.mark(1)
+    barrier()
+    step_ms = maxranks(eng.elapsed_ms(0, 1)) / a.steps
+    clocks = sampler.stop() if sampler else None
+    # per-launch duration of the dominant kernel (CUDA events around each launch, engine stream)
+    for c in range(C):
+        eng.estep(c)
+        kernel_ms.append(eng.last_estep_ms())
+    barrier()
+    launch_ms = statistics.mean(kernel_ms)
+
+    if rank == 0:
+        dfma_tflops, copy_gbs = eng.measure_peaks()
+        peaks = measured_peaks()
+        hbm_peak = peaks["hbm_gbs"] if peaks else 6650.0
+        per_launch_im = len(d["dous"]) * a.markers_per_chrom
+        fl = per_launch_im * FLOP_PER_INDMARKER / (launch_ms * 1e-3) * 1e-12
+        by = per_launch_im * BYTES_PER_INDMARKER / (launch_ms * 1e-3) * 1e-9
+        t_fp64 = per_launch_im * FLOP_PER_INDMARKER / (dfma_tflops * 1e12)
+        t_hbm = per_launch_im * BYTES_PER_INDMARKER / (hbm_peak * 1e9)
+        roof = {"bound": "fp64" if t_fp64 >= t_hbm else "hbm", "kernel": "cnf2::estep_kernel",
+                "achieved": fl if t_fp64 >= t_hbm else by, "peak": dfma_tflops if t_fp64 >= t_hbm else hbm_peak,
+                "unit": "TFLOP/s" if t_fp64 >= t_hbm else "GB/s",
+                "frac": (fl / dfma_tflops) if t_fp64 >= t_hbm else by / hbm_peak, "traffic": None,
+                "launch_ms": launch_ms,
+                "peak_source": "fp64: register-resident DFMA kernel measured in this run (MEASURED_PEAKS.json has no fp64 "
+                               "figure); hbm: MEASURED_PEAKS.json" + ("" if peaks else " absent -> fallback 6650 GB/s"),
+                "hbm": {"achieved": by, "peak": hbm_peak, "unit": "GB/s", "frac": by / hbm_peak, "copy_gbs_this_run": copy_gbs},
+                "fp64": {"achieved": fl, "peak": dfma_tflops, "unit": "TFLOP/s", "frac": fl / dfma_tflops}}
+        cpu = None
+        if not a.no_cpu_baseline:
+            r, why = run_reference_cpu(a, 2, 0)
+            cpu = ({"value": r[0], "unit": UNIT, "cores": r[2], "kind": "reference", "sample": r[3]} if r else
+                   {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "reference", "sample": "unavailable: " + why})
+        line = {
+            "metric": METRIC, "value": states_per_step / (step_ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_name(a), "parallelism": f"individuals sharded over {world} GPU(s)",
+                       "l2": "inputs + statistics per launch (%.0f MB) exceed the 126 MB L2" % ((h2d + d2h) / C / 1e6),
+                       "step": "E-step of all chromosomes: fwd/bwd sweeps for 8 shift modes + posterior scatter into EM statistics"},
+            "e2e": {"value": states_per_step / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": e2e_s * 1e3},
+            "gpu_launches": a.steps * C, "roofline": roof, "cpu_baseline": cpu, "clocks": clocks,
+        }
+        print(json.dumps(line))
+    eng.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    a = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if a.impl == "reference":
+        reference_arm(a, rank)
+        return
+    if world != a.gpus:
+        raise SystemExit(f"bench.py: --gpus {a.gpus} needs {a.gpus} ranks (launch with torch.distributed.run); WORLD_SIZE={world}")
+    ours(a, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

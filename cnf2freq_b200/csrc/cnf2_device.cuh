@@ -1,0 +1,197 @@
+// Device-side data model and the emission routine of the cnF2freq hot path, for sm_100a.
+//
+// State space (settings.h:19-42 at HEAD): 64 inheritance states g (6 meiosis bits), 128 orientations
+// flag2 (7 focus-tree slots), 8 shift modes.  Slots: 0 root, 1 parent 0, 2/3 its parents, 4 parent 1,
+// 5/6 its parents (fixtrees, cnF2freq.cpp:3124, 3146).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace cnf2
+{
+constexpr int NUMTYPES = 64;   // settings.h:27
+constexpr int NUMPATHS = 128;  // settings.h:32
+constexpr int NUMSHIFTS = 8;   // settings.h:35
+constexpr int NSLOTS = 7;      // TURNBITS, settings.h:40
+constexpr int TILE = 32;       // markers staged in shared memory at a time
+constexpr int NTHREADS = NUMSHIFTS * 32;  // one warp per shift mode, two states per lane
+
+constexpr int U_HAPLOS = 1, U_GENOS = 2, U_HOMOZYGOUS = 4, U_GENOSPROBE = 8;  // cnF2freq.cpp:792-795
+constexpr int UNKNOWN = 0;    // cnF2freq.cpp:225
+constexpr int SEXMARKER = 9;  // cnF2freq.cpp:226
+
+// Per-thread accumulator columns in shared memory (the reference's thread-local haplos / infprobs,
+// cnF2freq.cpp:379-380, keyed by focus-tree slot instead of individual id):
+//   [0,14)   haplos[slot][f2n]
+//   [14,42)  infprobs[slot][realf2n][allele-1]
+//   [42,44)  homozyg[allele-1]
+constexpr int ACC_HAPLOS = 0, ACC_INF = 14, ACC_HZ = 42, NACC = 44;
+constexpr int STATS_PER_CELL = 8;  // haplobase, haplocount, infprobs[2][2], homozyg[2]
+
+// One analysed individual = one focus tree (what fixtrees leaves in reltree / reltreeordered / relmap /
+// relmapshift, cnF2freq.cpp:3099-3187), built on the host by cnf2_set_pedigree.
+struct Unit
+{
+	int32_t row[NSLOTS];         // slot -> row of the compact parameter arrays; -1 = null parent pointer
+	int32_t relrow[NSLOTS];      // distinct tree members (reltree, empty ones included) -> statistics row
+	uint8_t slotrel[NSLOTS];     // slot -> index into relrow
+	uint8_t founder[NSLOTS];     // individ::founder of the slot's occupant
+	uint8_t relfilter[NSLOTS];   // relmap[rel]: slots the (non-empty) relative occupies; 0 = not in relmap
+	uint8_t relshift[NSLOTS];    // relmapshift[rel]
+	uint8_t relhalvings[NSLOTS]; // number of reltreeordered slots equal to rel (moveinfprobs, :3584-3588)
+	uint8_t nrel;
+	uint8_t flag2ignore;
+	uint8_t shiftignore;
+	uint8_t shiftend;            // NUMSHIFTS, or 2 when gen < 2 (:5359)
+	int32_t out;                 // row of the loglik output
+	double descendants;
+};
+
+// Shared-memory view handed to the emission routine.
+struct Ctx
+{
+	const uchar2* A;         // [NSLOTS][TILE] allele pair
+	const double2* S;        // [NSLOTS][TILE] markersure pair
+	const double* HW;        // [NSLOTS][TILE] haploweight
+	const int32_t* row;      // [NSLOTS]
+	const uint8_t* founder;  // [NSLOTS]
+	double* acc;             // this thread's accumulator column; stride NTHREADS
+};
+
+// upflagit, cnF2freq.cpp:321-329
+template <int GW>
+__device__ __forceinline__ int upflagit(int flag, int parnum)
+{
+	if (flag < 0) return flag;
+	return (flag >> (parnum * (GW - 1))) & ((1 << (GW - 1)) - 1);
+}
+
+template <int UPD, int GW>
+__device__ double track(const Ctx& c, int slot, int inval, double second, int t, unsigned flag, int flag99,
+                        int localshift, double updateval);
+
+// recursetrackpossible, cnF2freq.cpp:955-1058 (DOIMPOSSIBLE false).  GW is the CALLER's genwidth.
+template <int UPD, int GW>
+__device__ __forceinline__ double up(const Ctx& c, int slot, int par, int val, double second, int t, int upflag,
+                                     int upflag2, int upshift, double updateval)
+{
+	const int child = (GW == 4) ? 1 + 3 * par : slot + 1 + par;
+	if (c.row[child] < 0) return 1.0 + second;  // :1043-1046
+	const int f = upflagit<GW>(upflag, par);
+	const int f2 = upflagit<GW>(upflag2, par);          // NUMGEN - NUMFLAG2GEN = 0, :985
+	const int sh = upflagit<(GW >> 1)>(upshift, par);   // NUMGEN - NUMSHIFTGEN = 1, :986
+	return track<UPD, (GW >> 1)>(c, child, val, second, t, (unsigned)f, f2, sh, updateval);
+}
+
+// trackpossible<update, zeropropagate = 0>, cnF2freq.cpp:1075-1359: probability of the observed alleles
+// of the focus tree below `slot` given inheritance flag, orientation flag99 (-1 = both) and shift mode;
+// in the update modes it also scatters updateval into the accumulator columns.
+template <int UPD, int GW>
+__device__ double track(const Ctx& c, int slot, int inval, double second, int t, unsigned flag, int flag99,
+                        int localshift, double updateval)
+{
+	const bool attopnow = !(UPD & U_HOMOZYGOUS) && (GW == 1 || c.founder[slot]);  // :1120
+	const uchar2 a = c.A[slot * TILE + t];
+	const double2 s = c.S[slot * TILE + t];
+	const double hw = c.HW[slot * TILE + t];
+
+	int upflag2 = -1;
+	const int upflag = flag >> 1;
+	const int upshift = localshift >> 1;
+	int f2s = 0, f2end = 2;
+	if (flag99 != -1)  // :1141
+	{
+		upflag2 = flag99 >> 1;
+		f2s = flag99 & 1;
+		f2end = f2s + 1;
+	}
+	const int firstpar = flag & 1;  // :1156
+	const bool allthesame = a.x == a.y;
+	double ok = 0;
+
+	for (int f2 = f2s; f2 < f2end; f2++)
+	{
+		int f2n = f2;
+		const int realf2n = f2;
+		const int Af = f2 ? a.y : a.x, Ao = f2 ? a.x : a.y;
+		const double Sf = f2 ? s.y : s.x, So = f2 ? s.x : s.y;
+		int val = inval;
+		double base, main2 = 0;
+		bool miss;  // markermiss<0>, :303-316
+		if (val == UNKNOWN)
+		{
+			val = Af;
+			miss = false;
+		}
+		else if (Af == UNKNOWN && val != SEXMARKER) miss = false;
+		else miss = val != Af;
+
+		if (miss)  // :1198-1203
+		{
+			base = Sf;
+			if (Sf != 0 && second != 0) main2 = (1.0 - Sf) * second;
+		}
+		else  // :1204-1210
+		{
+			const double eff2 = (inval == UNKNOWN && val != UNKNOWN) ? 1.0 : second;
+			base = 1.0 - Sf;
+			main2 = (Af == UNKNOWN ? 1.0 : Sf) * eff2;
+		}
+		if (attopnow || (UPD & 1))  // `update & (GENOS || GENOSPROBE)` is `update & 1`, :1213
+		{
+			base += main2;
+			main2 = 0;
+		}
+		else if (main2 != 0) main2 /= base;
+
+		bool doupd = true;
+		f2n ^= (firstpar ^ localshift) & 1;  // :1227
+		if (allthesame && s.x == s.y)        // :1235 (CORRECTIONINFERENCE false inside doit)
+		{
+			base *= f2n ? 1.0 : 0.0;
+			doupd = false;
+		}
+		else base *= fabs((f2n ? 1.0 : 0.0) - hw);  // :1245
+
+		if constexpr (GW > 1)
+		{
+			if (base != 0 && !attopnow)  // :1271-1341
+			{
+				if (!(UPD & U_GENOS))  // :1291
+				{
+					double sec2 = 0;
+					int secmark = Ao;
+					if (!(UPD & U_HOMOZYGOUS))
+					{
+						if (So != 0)  // :1298-1302
+						{
+							base *= 1.0 - So;
+							sec2 = So / (1.0 - So);
+						}
+					}
+					else if (val != secmark)  // :1306-1314
+					{
+						if (secmark != UNKNOWN) base *= So;
+						secmark = val;
+					}
+					else base *= 1.0 - So;  // :1315-1319
+					base *= up<(UPD & ~U_HOMOZYGOUS), GW>(c, slot, !firstpar, secmark, sec2, t, upflag, upflag2, upshift,
+					                                      updateval);
+				}
+				if (base != 0)
+					base *= up<(UPD & ~U_HOMOZYGOUS), GW>(c, slot, firstpar, val, main2, t, upflag, upflag2, upshift,
+					                                      updateval);
+			}
+		}
+
+		if (base != 0)  // :1343-1355
+		{
+			ok += base;
+			if ((UPD & U_HAPLOS) && doupd) c.acc[(ACC_HAPLOS + slot * 2 + f2n) * NTHREADS] += updateval;
+			if ((UPD & U_GENOS) && (val == 1 || val == 2))
+				c.acc[(ACC_INF + (slot * 2 + realf2n) * 2 + (val - 1)) * NTHREADS] += updateval;
+		}
+	}
+	return ok;
+}
+}  // namespace cnf2

@@ -1,0 +1,677 @@
+// C-ABI implementation of include/cnf2_engine.h: host-side tables (the port of what fixtrees,
+// cnF2freq.cpp:3099-3187, leaves behind), device memory, launches.  No CPU compute path exists here:
+// every entry point that would compute needs the CUDA device.
+#include "../../include/cnf2_engine.h"
+#include "cnf2_estep_kernel.cuh"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+using namespace cnf2;
+
+namespace
+{
+std::string g_create_error;
+
+struct Run  // consecutive rows holding consecutive individual ids: one 2-D copy
+{
+	int32_t row0, id0, n;
+};
+
+template <typename T>
+struct DevBuf
+{
+	T* p = nullptr;
+	size_t n = 0;
+	cudaError_t ensure(size_t want)
+	{
+		if (want <= n && p) return cudaSuccess;
+		if (p) cudaFree(p);
+		p = nullptr;
+		n = 0;
+		cudaError_t e = cudaMalloc(&p, std::max<size_t>(want, 1) * sizeof(T));
+		if (e == cudaSuccess) n = want;
+		return e;
+	}
+	void release()
+	{
+		if (p) cudaFree(p);
+		p = nullptr;
+		n = 0;
+	}
+};
+}  // namespace
+
+struct cnf2_engine
+{
+	cnf2_settings settings{};
+	std::string error;
+	cudaStream_t stream = nullptr;
+	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+	int n_sm = 0;
+	int n_ctas = 0;
+
+	// map
+	std::vector<double> markerpos;
+	std::vector<uint32_t> chromstarts;
+	double genrec[3] = { 0, 0, 0 };
+	int max_mc = 0;
+
+	// pedigree
+	int32_t n_ind = 0;
+	std::vector<int32_t> shared_ids;
+	std::vector<int32_t> rowof;   // individual id -> row, -1 = not touched by this engine
+	std::vector<int32_t> rowid;   // row -> individual id
+	std::vector<Run> runs;
+	int32_t n_rows = 0, n_shared = 0;
+	std::vector<Unit> units;
+
+	// device
+	DevBuf<uchar2> d_alleles;
+	DevBuf<double2> d_sure;
+	DevBuf<double> d_hw, d_rec, d_alpha, d_alphafac, d_stats, d_loglik;
+	DevBuf<Unit> d_units;
+	DevBuf<unsigned int> d_counter;
+	std::vector<double> h_loglik;
+
+	// parameters stay resident for every chromosome when they fit (resident), else one chromosome at a time
+	bool resident = false;
+	size_t ld = 0;
+	std::vector<uint8_t> have_params;
+	int estep_chrom = -1;
+	cudaEvent_t marks[4] = { nullptr, nullptr, nullptr, nullptr };
+	int last_launches = 0;
+	cnf2_allreduce_fn allreduce = nullptr;
+	void* allreduce_ctx = nullptr;
+
+	int fail(int code, const std::string& msg)
+	{
+		error = msg;
+		return code;
+	}
+	int cuda(cudaError_t e, const char* what)
+	{
+		if (e == cudaSuccess) return 0;
+		return fail(CNF2_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+	}
+	int mc(int chrom) const { return (int)(chromstarts[chrom + 1] - chromstarts[chrom]); }
+	double* stats_shared() { return d_stats.p; }
+	double* stats_local(int Mc) { return d_stats.p + (size_t)n_shared * Mc * STATS_PER_CELL; }
+};
+
+#define CU(call)                                      \
+	do                                                \
+	{                                                 \
+		int rc_ = e->cuda((call), #call);             \
+		if (rc_) return rc_;                          \
+	} while (0)
+
+extern "C" void cnf2_default_settings(cnf2_settings* s)
+{
+	if (!s) return;
+	std::memset(s, 0, sizeof(*s));
+	s->numgen = 3;         // settings.h:19
+	s->selfing = 0;        // settings.h:14
+	s->relskewstates = 0;  // settings.h:16
+	s->haplotyping = 1;    // settings.h:36
+	s->doinfprobs = 1;     // settings.h:12
+	s->device = 0;
+	s->ctas_per_sm = 0;
+}
+
+extern "C" const char* cnf2_last_error(const cnf2_engine* e)
+{
+	return e ? e->error.c_str() : g_create_error.c_str();
+}
+
+extern "C" int cnf2_create(cnf2_engine** out, const cnf2_settings* settings)
+{
+	if (!out || !settings)
+	{
+		g_create_error = "cnf2_create: null argument";
+		return CNF2_ERR_BAD_ARG;
+	}
+	*out = nullptr;
+	if (settings->numgen != 3 || settings->selfing || settings->relskewstates || !settings->haplotyping ||
+	    !settings->doinfprobs)
+	{
+		g_create_error =
+		    "cnf2_create: kernels are built for NUMGEN 3, SELFING false, RELSKEWSTATES false, HAPLOTYPING true, "
+		    "DOINFPROBS true";
+		return CNF2_ERR_UNSUPPORTED;
+	}
+	int ndev = 0;
+	cudaError_t ce = cudaGetDeviceCount(&ndev);
+	if (ce != cudaSuccess || ndev <= 0 || settings->device < 0 || settings->device >= ndev)
+	{
+		g_create_error = std::string("cnf2_create: no usable CUDA device (") +
+		                 (ce != cudaSuccess ? cudaGetErrorString(ce) : "device ordinal out of range") +
+		                 "); this engine has no CPU path";
+		return CNF2_ERR_NO_DEVICE;
+	}
+	cnf2_engine* e = new cnf2_engine;
+	e->settings = *settings;
+	auto bail = [&](cudaError_t err, const char* what) {
+		g_create_error = std::string("cnf2_create: ") + what + ": " + cudaGetErrorString(err);
+		delete e;
+		return (int)CNF2_ERR_CUDA;
+	};
+	if ((ce = cudaSetDevice(settings->device)) != cudaSuccess) return bail(ce, "cudaSetDevice");
+	cudaDeviceProp prop;
+	if ((ce = cudaGetDeviceProperties(&prop, settings->device)) != cudaSuccess) return bail(ce, "cudaGetDeviceProperties");
+	e->n_sm = prop.multiProcessorCount;
+	if ((ce = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(ce, "cudaStreamCreate");
+	if ((ce = cudaEventCreate(&e->ev0)) != cudaSuccess) return bail(ce, "cudaEventCreate");
+	if ((ce = cudaEventCreate(&e->ev1)) != cudaSuccess) return bail(ce, "cudaEventCreate");
+	if ((ce = cudaFuncSetAttribute(estep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem))) != cudaSuccess)
+		return bail(ce, "cudaFuncSetAttribute(estep_kernel)");
+	int per_sm = 0;
+	if ((ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, estep_kernel, NTHREADS, sizeof(Smem))) != cudaSuccess)
+		return bail(ce, "occupancy query");
+	if (per_sm < 1) per_sm = 1;
+	if (settings->ctas_per_sm > 0) per_sm = std::min(per_sm, settings->ctas_per_sm);
+	e->n_ctas = per_sm * e->n_sm;
+	*out = e;
+	return CNF2_OK;
+}
+
+extern "C" void cnf2_destroy(cnf2_engine* e)
+{
+	if (!e) return;
+	cudaSetDevice(e->settings.device);
+	if (e->stream) cudaStreamSynchronize(e->stream);
+	e->d_alleles.release();
+	e->d_sure.release();
+	e->d_hw.release();
+	e->d_rec.release();
+	e->d_alpha.release();
+	e->d_alphafac.release();
+	e->d_stats.release();
+	e->d_loglik.release();
+	e->d_units.release();
+	e->d_counter.release();
+	for (cudaEvent_t m : e->marks)
+		if (m) cudaEventDestroy(m);
+	if (e->ev0) cudaEventDestroy(e->ev0);
+	if (e->ev1) cudaEventDestroy(e->ev1);
+	if (e->stream) cudaStreamDestroy(e->stream);
+	delete e;
+}
+
+extern "C" int cnf2_set_map(cnf2_engine* e, const double* markerpos, int32_t n_markers, const uint32_t* chromstarts,
+                            int32_t n_chrom, const double genrec[3])
+{
+	if (!e) return CNF2_ERR_BAD_ARG;
+	if (!markerpos || !chromstarts || !genrec || n_markers <= 0 || n_chrom <= 0)
+		return e->fail(CNF2_ERR_BAD_ARG, "cnf2_set_map: null or empty argument");
+	if (chromstarts[0] != 0 || chromstarts[n_chrom] != (uint32_t)n_markers)
+		return e->fail(CNF2_ERR_BAD_ARG, "cnf2_set_map: chromstarts must run from 0 to n_markers");
+	for (int c = 0; c < n_chrom; c++)
+		if (chromstarts[c + 1] <= chromstarts[c]) return e->fail(CNF2_ERR_BAD_ARG, "cnf2_set_map: empty chromosome");
+	e->markerpos.assign(markerpos, markerpos + n_markers);
+	e->chromstarts.assign(chromstarts, chromstarts + n_chrom + 1);
+	for (int i = 0; i < 3; i++) e->genrec[i] = genrec[i];
+	e->max_mc = 0;
+	for (int c = 0; c < n_chrom; c++) e->max_mc = std::max(e->max_mc, e->mc(c));
+	e->have_params.assign(n_chrom, 0);
+	e->estep_chrom = -1;
+	return CNF2_OK;
+}
+
+extern "C" int cnf2_set_shared_rows(cnf2_engine* e, const int32_t* ids, int32_t n_ids)
+{
+	if (!e) return CNF2_ERR_BAD_ARG;
+	if (n_ids < 0 || (n_ids > 0 && !ids)) return e->fail(CNF2_ERR_BAD_ARG, "cnf2_set_shared_rows: bad list");
+	e->shared_ids.assign(ids, ids + n_ids);
+	return CNF2_OK;
+}
+
+extern "C" int cnf2_set_allreduce(cnf2_engine* e, cnf2_allreduce_fn fn, void* ctx)
+{
+	if (!e) return CNF2_ERR_BAD_ARG;
+	e->allreduce = fn;
+	e->allreduce_ctx = ctx;
+	return CNF2_OK;
+}
+
+extern "C" int cnf2_set_pedigree(cnf2_engine* e, int32_t n_ind, const int32_t* parents, const uint8_t* empty,
+                                 const uint8_t* founder_in, const int32_t* gen, const int32_t* descendants,
+                                 const int32_t* dous, int32_t n_dous, const int32_t* all_dous, int32_t n_all_dous)
+{
+	if (!e) return CNF2_ERR_BAD_ARG;
+	if (!parents || !empty || !founder_in || !gen || !descendants || n_ind <= 0 || n_dous < 0 || (n_dous && !dous))
+		return e->fail(CNF2_ERR_BAD_ARG, "cnf2_set_pedigree: null or empty argument");
+	if (!all_dous)
+	{
+		all_dous = dous;
+		n_all_dous = n_dous;
+	}
+	auto valid = [&](int32_t id) { return id > 0 && id < n_ind; };
+	for (int i = 0; i < n_ind * 2; i++)
+		if (parents[i] < 0 || parents[i] >= n_ind) return e->fail(CNF2_ERR_BAD_ARG, "cnf2_set_pedigree: parent id out of range");
+	for (int j = 0; j < n_dous; j++)
+		if (!valid(dous[j])) return e->fail(CNF2_ERR_BAD_ARG, "cnf2_set_pedigree: analysed id out of range");
+	for (int j = 0; j < n_all_dous; j++)
+		if (!valid(all_dous[j])) return e->fail(CNF2_ERR_BAD_ARG, "cnf2_set_pedigree: analysed id out of range");
+	for (int32_t id : e->shared_ids)
+		if (!valid(id)) return e->fail(CNF2_ERR_BAD_ARG, "cnf2_set_pedigree: shared id out of range");
+	cudaSetDevice(e->settings.device);
+
+	// fixtrees' sticky founder flag in its steady state (cnF2freq.cpp:3170-3177)
+	std::vector<uint8_t> founder(founder_in, founder_in + n_ind);
+	auto anylev1 = [&](int ind) {
+		bool any = false;
+		for (int lev1 = 0; lev1 < 2; lev1++)
+		{
+			const int l1 = parents[ind * 2 + lev1];
+			if (!l1) continue;
+			bool anypars = false;
+			for (int lev2 = 0; lev2 < 2; lev2++)
+			{
+				const int l2 = parents[l1 * 2 + lev2];
+				if (l2 && !empty[l2]) anypars = true;
+			}
+			if (anypars || !empty[l1]) any = true;
+		}
+		return any;
+	};
+	for (int j = 0; j < n_all_dous; j++)
+		if (!anylev1(all_dous[j])) founder[all_dous[j]] = 1;
+
+	// rows: shared individuals first (same order on every rank), then the other touched ones by id
+	e->n_ind = n_ind;
+	e->rowof.assign(n_ind, -1);
+	e->rowid.clear();
+	for (int32_t id : e->shared_ids)
+	{
+		if (e->rowof[id] >= 0) return e->fail(CNF2_ERR_BAD_ARG, "cnf2_set_pedigree: duplicate shared id");
+		e->rowof[id] = (int32_t)e->rowid.size();
+		e->rowid.push_back(id);
+	}
+	e->n_shared = (int32_t)e->rowid.size();
+	std::vector<uint8_t> touched(n_ind, 0);
+	auto slot_ids = [&](int ind, int32_t ids[NSLOTS]) {
+		for (int k = 0; k < NSLOTS; k++) ids[k] = 0;
+		ids[0] = ind;
+		for (int lev1 = 0; lev1 < 2; lev1++)
+		{
+			const int l1 = parents[ind * 2 + lev1];
+			if (!l1) continue;
+			const int base = 1 + lev1 * 3;  // :3124
+			ids[base] = l1;
+			for (int lev2 = 0; lev2 < 2; lev2++) ids[base + 1 + lev2] = parents[l1 * 2 + lev2];
+		}
+	};
+	for (int j = 0; j < n_dous; j++)
+	{
+		int32_t ids[NSLOTS];
+		slot_ids(dous[j], ids);
+		for (int k = 0; k < NSLOTS; k++)
+			if (ids[k]) touched[ids[k]] = 1;
+	}
+	for (int id = 1; id < n_ind; id++)
+		if (touched[id] && e->rowof[id] < 0)
+		{
+			e->rowof[id] = (int32_t)e->rowid.size();
+			e->rowid.push_back(id);
+		}
+	e->n_rows = (int32_t)e->rowid.size();
+	e->runs.clear();
+	for (int r = 0; r < e->n_rows; r++)
+	{
+		const bool boundary = r == e->n_shared;  // a run never straddles the two statistics blocks
+		if (!e->runs.empty() && !boundary && e->runs.back().id0 + e->runs.back().n == e->rowid[r]) e->runs.back().n++;
+		else e->runs.push_back(Run{ r, e->rowid[r], 1 });
+	}
+
+	// focus trees (fixtrees, :3099-3187)
+	e->units.assign(n_dous, Unit{});
+	for (int j = 0; j < n_dous; j++)
+	{
+		Unit& u = e->units[j];
+		const int ind = dous[j];
+		int32_t ids[NSLOTS];
+		slot_ids(ind, ids);
+		int32_t ordered[NSLOTS] = { 0 };
+		std::map<int32_t, int> relmap, relmapshift;
+		ordered[0] = ind;
+		relmap[ind] = 1;
+		relmapshift[ind] = 1;
+		int flag2ignore = 1, shiftignore = 0;
+		bool any1 = false;
+		for (int lev1 = 0; lev1 < 2; lev1++)
+		{
+			const int l1 = parents[ind * 2 + lev1];
+			if (!l1) continue;
+			const int flag2index = 1 + lev1 * 3;  // :3124
+			const int shiftval = 2 << lev1;       // :3125
+			if (!empty[l1])
+			{
+				flag2ignore |= 1 << flag2index;
+				relmap[l1] |= 1 << flag2index;
+				relmapshift[l1] |= shiftval;
+				ordered[flag2index] = l1;
+			}
+			bool anypars = false;
+			for (int lev2 = 0; lev2 < 2; lev2++)
+			{
+				const int l2 = parents[l1 * 2 + lev2];
+				if (!l2 || empty[l2]) continue;
+				flag2ignore |= 1 << (flag2index + lev2 + 1);
+				relmap[l2] |= 1 << (flag2index + lev2 + 1);
+				relmapshift[l2] |= 0;
+				ordered[flag2index + lev2 + 1] = l2;
+				anypars = true;
+			}
+			if (anypars) shiftignore |= shiftval;
+			if (anypars || !empty[l1]) any1 = true;
+		}
+		if (any1) shiftignore |= 1;
+		u.flag2ignore = (uint8_t)(flag2ignore ^ (NUMPATHS - 1));
+		u.shiftignore = (uint8_t)(shiftignore ^ (NUMSHIFTS - 1));
+		u.shiftend = (uint8_t)(gen[ind] < 2 ? 2 : NUMSHIFTS);  // :5359
+		u.out = j;
+		u.descendants = (double)descendants[ind];
+		std::vector<int32_t> rel;  // reltree: distinct members, empty ones included, sorted (:3179-3181)
+		for (int k = 0; k < NSLOTS; k++)
+			if (ids[k]) rel.push_back(ids[k]);
+		std::sort(rel.begin(), rel.end());
+		rel.erase(std::unique(rel.begin(), rel.end()), rel.end());
+		u.nrel = (uint8_t)rel.size();
+		for (int k = 0; k < NSLOTS; k++)
+		{
+			u.row[k] = ids[k] ? e->rowof[ids[k]] : -1;
+			u.founder[k] = ids[k] ? founder[ids[k]] : 0;
+			u.slotrel[k] = ids[k] ? (uint8_t)(std::lower_bound(rel.begin(), rel.end(), ids[k]) - rel.begin()) : 0xff;
+			u.relrow[k] = -1;
+		}
+		for (size_t r = 0; r < rel.size(); r++)
+		{
+			u.relrow[r] = e->rowof[rel[r]];
+			auto it = relmap.find(rel[r]);
+			u.relfilter[r] = it == relmap.end() ? 0 : (uint8_t)it->second;
+			u.relshift[r] = it == relmap.end() ? 0 : (uint8_t)relmapshift[rel[r]];
+			int halvings = 0;
+			for (int k = 0; k < NSLOTS; k++)
+				if (ordered[k] == rel[r]) halvings++;
+			u.relhalvings[r] = (uint8_t)halvings;
+		}
+	}
+	CU(e->d_units.ensure(e->units.size()));
+	if (!e->units.empty())
+		CU(cudaMemcpyAsync(e->d_units.p, e->units.data(), e->units.size() * sizeof(Unit), cudaMemcpyHostToDevice, e->stream));
+	CU(e->d_loglik.ensure(e->units.size() * 2));
+	e->h_loglik.assign(e->units.size() * 2, 0.0);
+	CU(e->d_counter.ensure(1));
+	CU(cudaStreamSynchronize(e->stream));
+	std::fill(e->have_params.begin(), e->have_params.end(), 0);
+	e->estep_chrom = -1;
+	// 26 bytes of parameters per (row, marker): keep all chromosomes on the device when that is a small part of HBM
+	size_t free_b = 0, total_b = 0;
+	CU(cudaMemGetInfo(&free_b, &total_b));
+	const size_t M = e->markerpos.size();
+	e->resident = !e->markerpos.empty() && (double)e->n_rows * M * 26.0 < 0.4 * (double)free_b;
+	e->ld = e->resident ? M : (size_t)e->max_mc;
+	return CNF2_OK;
+}
+
+extern "C" int cnf2_set_params(cnf2_engine* e, int32_t chrom, const uint8_t* alleles, const double* sure,
+                               const double* haploweight)
+{
+	if (!e) return CNF2_ERR_BAD_ARG;
+	if (e->chromstarts.empty() || e->rowof.empty()) return e->fail(CNF2_ERR_STATE, "cnf2_set_params: set_map and set_pedigree first");
+	if (chrom < 0 || chrom + 1 >= (int)e->chromstarts.size() || !alleles || !sure || !haploweight)
+		return e->fail(CNF2_ERR_BAD_ARG, "cnf2_set_params: bad argument");
+	cudaSetDevice(e->settings.device);
+	const size_t M = e->markerpos.size();
+	const size_t c0 = e->chromstarts[chrom];
+	const size_t Mc = e->mc(chrom), ld = e->ld;
+	const size_t col0 = e->resident ? c0 : 0;
+	CU(e->d_alleles.ensure((size_t)e->n_rows * ld));
+	CU(e->d_sure.ensure((size_t)e->n_rows * ld));
+	CU(e->d_hw.ensure((size_t)e->n_rows * ld));
+	for (const Run& r : e->runs)
+	{
+		const size_t src = (size_t)r.id0 * M + c0, dst = (size_t)r.row0 * ld + col0;
+		CU(cudaMemcpy2DAsync(e->d_alleles.p + dst, ld * 2, alleles + src * 2, M * 2, Mc * 2, r.n, cudaMemcpyHostToDevice, e->stream));
+		CU(cudaMemcpy2DAsync(e->d_sure.p + dst, ld * 16, sure + src * 2, M * 16, Mc * 16, r.n, cudaMemcpyHostToDevice, e->stream));
+		CU(cudaMemcpy2DAsync(e->d_hw.p + dst, ld * 8, haploweight + src, M * 8, Mc * 8, r.n, cudaMemcpyHostToDevice, e->stream));
+	}
+	// recombination fractions towards the next marker (:2286; getactrec :777-780 ignores sex and marker)
+	std::vector<double> rec(2 * Mc, 0.0);
+	for (size_t m = 0; m + 1 < Mc; m++)
+	{
+		const double dist = e->markerpos[c0 + m + 1] - e->markerpos[c0 + m];
+		if (!(dist > 0)) continue;  // same position: no transition (:2273)
+		rec[m] = 0.5 * (1.0 - std::exp(e->genrec[0] * dist));
+		rec[Mc + m] = 0.5 * (1.0 - std::exp(e->genrec[1] * dist));
+	}
+	CU(e->d_rec.ensure(2 * (e->resident ? M : (size_t)e->max_mc)));
+	CU(cudaMemcpyAsync(e->d_rec.p + 2 * col0, rec.data(), rec.size() * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+	CU(cudaStreamSynchronize(e->stream));  // rec is a stack-lifetime buffer; caller buffers may be reused after return
+	if (!e->resident) std::fill(e->have_params.begin(), e->have_params.end(), 0);
+	e->have_params[chrom] = 1;
+	return CNF2_OK;
+}
+
+extern "C" int cnf2_estep(cnf2_engine* e, int32_t chrom)
+{
+	if (!e) return CNF2_ERR_BAD_ARG;
+	if (chrom < 0 || chrom >= (int)e->have_params.size() || !e->have_params[chrom])
+		return e->fail(CNF2_ERR_STATE, "cnf2_estep: cnf2_set_params for this chromosome first");
+	cudaSetDevice(e->settings.device);
+	const int Mc = e->mc(chrom);
+	const int n_units = (int)e->units.size();
+	const int n_ctas = std::max(1, std::min(e->n_ctas, n_units));
+	CU(e->d_alpha.ensure((size_t)n_ctas * e->max_mc * NUMSHIFTS * NUMTYPES));
+	CU(e->d_alphafac.ensure((size_t)n_ctas * e->max_mc * NUMSHIFTS));
+	CU(e->d_stats.ensure((size_t)e->n_rows * e->max_mc * STATS_PER_CELL));
+	CU(cudaEventRecord(e->ev0, e->stream));
+	CU(cudaMemsetAsync(e->d_stats.p, 0, (size_t)e->n_rows * Mc * STATS_PER_CELL * sizeof(double), e->stream));
+	CU(cudaMemsetAsync(e->d_counter.p, 0, sizeof(unsigned int), e->stream));
+	e->last_launches = 0;
+	if (n_units > 0)
+	{
+		EstepArgs a{};
+		const size_t col0 = e->resident ? e->chromstarts[chrom] : 0;
+		a.alleles = e->d_alleles.p + col0;
+		a.sure = e->d_sure.p + col0;
+		a.hw = e->d_hw.p + col0;
+		a.rec0 = e->d_rec.p + 2 * col0;
+		a.rec1 = e->d_rec.p + 2 * col0 + Mc;
+		a.units = e->d_units.p;
+		a.n_units = n_units;
+		a.Mc = Mc;
+		a.ld = (int32_t)e->ld;
+		a.counter = e->d_counter.p;
+		a.alpha = e->d_alpha.p;
+		a.alphafac = e->d_alphafac.p;
+		a.stats_shared = e->stats_shared();
+		a.stats_local = e->stats_local(Mc);
+		a.n_shared = e->n_shared;
+		a.n_local = e->n_rows - e->n_shared;
+		a.loglik = e->d_loglik.p;
+		estep_kernel<<<n_ctas, NTHREADS, sizeof(Smem), e->stream>>>(a);
+		CU(cudaGetLastError());
+		e->last_launches = 1;
+	}
+	CU(cudaEventRecord(e->ev1, e->stream));
+	if (e->allreduce && e->n_shared > 0)
+	{
+		const int rc = e->allreduce(e->allreduce_ctx, e->stats_shared(), (size_t)e->n_shared * Mc * STATS_PER_CELL, (void*)e->stream);
+		if (rc) return e->fail(CNF2_ERR_CUDA, "cnf2_estep: all-reduce hook failed");
+	}
+	e->estep_chrom = chrom;
+	return CNF2_OK;
+}
+
+extern "C" int cnf2_sync(cnf2_engine* e)
+{
+	if (!e) return CNF2_ERR_BAD_ARG;
+	cudaSetDevice(e->settings.device);
+	CU(cudaStreamSynchronize(e->stream));
+	CU(cudaGetLastError());
+	return CNF2_OK;
+}
+
+extern "C" int cnf2_get_stats(cnf2_engine* e, int32_t chrom, double* haplobase, double* haplocount, double* infprobs,
+                              double* homozyg, double* loglik)
+{
+	if (!e) return CNF2_ERR_BAD_ARG;
+	if (e->estep_chrom != chrom || chrom < 0) return e->fail(CNF2_ERR_STATE, "cnf2_get_stats: cnf2_estep for this chromosome first");
+	cudaSetDevice(e->settings.device);
+	const size_t M = e->markerpos.size(), c0 = e->chromstarts[chrom], Mc = e->mc(chrom);
+	for (const Run& r : e->runs)
+	{
+		const bool sh = r.row0 < e->n_shared;
+		const StatsCell src = sh ? stats_cell(e->stats_shared(), e->n_shared, Mc, r.row0, 0)
+		                         : stats_cell(e->stats_local((int)Mc), e->n_rows - e->n_shared, Mc, r.row0 - e->n_shared, 0);
+		const size_t dst = (size_t)r.id0 * M + c0;
+		if (haplobase)
+			CU(cudaMemcpy2DAsync(haplobase + dst, M * 8, src.haplobase, Mc * 8, Mc * 8, r.n, cudaMemcpyDeviceToHost, e->stream));
+		if (haplocount)
+			CU(cudaMemcpy2DAsync(haplocount + dst, M * 8, src.haplocount, Mc * 8, Mc * 8, r.n, cudaMemcpyDeviceToHost, e->stream));
+		if (infprobs)
+			CU(cudaMemcpy2DAsync(infprobs + dst * 4, M * 32, src.infprobs, Mc * 32, Mc * 32, r.n, cudaMemcpyDeviceToHost, e->stream));
+		if (homozyg)
+			CU(cudaMemcpy2DAsync(homozyg + dst * 2, M * 16, src.homozyg, Mc * 16, Mc * 16, r.n, cudaMemcpyDeviceToHost, e->stream));
+	}
+	if (loglik && !e->units.empty())
+		CU(cudaMemcpyAsync(e->h_loglik.data(), e->d_loglik.p, e->units.size() * 2 * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+	CU(cudaStreamSynchronize(e->stream));
+	CU(cudaGetLastError());
+	if (loglik)
+	{
+		const size_t C = e->chromstarts.size() - 1;
+		for (size_t j = 0; j < e->units.size(); j++)
+		{
+			loglik[(j * C + chrom) * 2 + 0] = e->h_loglik[j * 2 + 0];
+			loglik[(j * C + chrom) * 2 + 1] = e->h_loglik[j * 2 + 1];
+		}
+	}
+	return CNF2_OK;
+}
+
+extern "C" int cnf2_last_estep_ms(cnf2_engine* e, float* ms)
+{
+	if (!e || !ms) return CNF2_ERR_BAD_ARG;
+	cudaSetDevice(e->settings.device);
+	CU(cudaEventSynchronize(e->ev1));
+	CU(cudaEventElapsedTime(ms, e->ev0, e->ev1));
+	return CNF2_OK;
+}
+
+extern "C" int cnf2_last_estep_launches(cnf2_engine* e, int32_t* n)
+{
+	if (!e || !n) return CNF2_ERR_BAD_ARG;
+	*n = e->last_launches;
+	return CNF2_OK;
+}
+
+extern "C" int cnf2_mark(cnf2_engine* e, int32_t slot)
+{
+	if (!e || slot < 0 || slot >= 4) return CNF2_ERR_BAD_ARG;
+	cudaSetDevice(e->settings.device);
+	if (!e->marks[slot]) CU(cudaEventCreate(&e->marks[slot]));
+	CU(cudaEventRecord(e->marks[slot], e->stream));
+	return CNF2_OK;
+}
+
+extern "C" int cnf2_elapsed_ms(cnf2_engine* e, int32_t from, int32_t to, float* ms)
+{
+	if (!e || !ms || from < 0 || from >= 4 || to < 0 || to >= 4 || !e->marks[from] || !e->marks[to]) return CNF2_ERR_BAD_ARG;
+	cudaSetDevice(e->settings.device);
+	CU(cudaEventSynchronize(e->marks[to]));
+	CU(cudaEventElapsedTime(ms, e->marks[from], e->marks[to]));
+	return CNF2_OK;
+}
+
+extern "C" void* cnf2_stream(cnf2_engine* e)
+{
+	return e ? (void*)e->stream : nullptr;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Roofline denominators measured on the box itself: fp64 FMA issue rate and a device copy.
+namespace
+{
+__global__ void dfma_peak_kernel(double* out, int iters, double a, double b)
+{
+	double x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+	for (int i = 0; i < iters; i++)
+	{
+		x0 = fma(x0, a, b);
+		x1 = fma(x1, a, b);
+		x2 = fma(x2, a, b);
+		x3 = fma(x3, a, b);
+		x4 = fma(x4, a, b);
+		x5 = fma(x5, a, b);
+		x6 = fma(x6, a, b);
+		x7 = fma(x7, a, b);
+	}
+	out[blockIdx.x * blockDim.x + threadIdx.x] = x0 + x1 + x2 + x3 + x4 + x5 + x6 + x7;
+}
+
+__global__ void copy_peak_kernel(const double2* __restrict__ src, double2* __restrict__ dst, size_t n)
+{
+	for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) dst[i] = src[i];
+}
+}  // namespace
+
+extern "C" int cnf2_measure_peaks(cnf2_engine* e, double* dfma_tflops, double* copy_gbs)
+{
+	if (!e) return CNF2_ERR_BAD_ARG;
+	cudaSetDevice(e->settings.device);
+	cudaEvent_t t0, t1;
+	CU(cudaEventCreate(&t0));
+	CU(cudaEventCreate(&t1));
+	float ms = 0;
+	if (dfma_tflops)
+	{
+		const int blocks = e->n_sm * 8, threads = 256, iters = 1 << 14;
+		double* out = nullptr;
+		CU(cudaMalloc(&out, (size_t)blocks * threads * sizeof(double)));
+		double best = 0;
+		for (int rep = 0; rep < 4; rep++)
+		{
+			CU(cudaEventRecord(t0, e->stream));
+			dfma_peak_kernel<<<blocks, threads, 0, e->stream>>>(out, iters, 0.999999, 1e-9);
+			CU(cudaEventRecord(t1, e->stream));
+			CU(cudaEventSynchronize(t1));
+			CU(cudaEventElapsedTime(&ms, t0, t1));
+			const double flops = 2.0 * 8 * (double)iters * blocks * threads;
+			if (rep) best = std::max(best, flops / (ms * 1e-3) * 1e-12);
+		}
+		cudaFree(out);
+		*dfma_tflops = best;
+	}
+	if (copy_gbs)
+	{
+		const size_t n = (size_t)1 << 26;  // 2 x 1 GiB
+		double2 *a = nullptr, *b = nullptr;
+		CU(cudaMalloc(&a, n * sizeof(double2)));
+		CU(cudaMalloc(&b, n * sizeof(double2)));
+		CU(cudaMemsetAsync(a, 0, n * sizeof(double2), e->stream));
+		double best = 0;
+		for (int rep = 0; rep < 5; rep++)
+		{
+			CU(cudaEventRecord(t0, e->stream));
+			copy_peak_kernel<<<e->n_sm * 16, 512, 0, e->stream>>>(a, b, n);
+			CU(cudaEventRecord(t1, e->stream));
+			CU(cudaEventSynchronize(t1));
+			CU(cudaEventElapsedTime(&ms, t0, t1));
+			if (rep) best = std::max(best, 2.0 * n * sizeof(double2) / (ms * 1e-3) * 1e-9);
+		}
+		cudaFree(a);
+		cudaFree(b);
+		*copy_gbs = best;
+	}
+	cudaEventDestroy(t0);
+	cudaEventDestroy(t1);
+	return CNF2_OK;
+}

@@ -1,0 +1,384 @@
+// The E-step kernel: one persistent CTA per resident slot, each looping over (analysed individual,
+// chromosome) units.  One warp per shift mode, two inheritance states per lane (bits 0-4 of the state
+// across lanes, bit 5 inside the thread), so the Kronecker transition R(r)^{(x)6} (cnF2freq.cpp:2270-2367)
+// is five __shfl_xor butterfly stages plus one in-register stage.
+#pragma once
+#include "cnf2_device.cuh"
+
+namespace cnf2
+{
+struct EstepArgs
+{
+	const uchar2* alleles;   // [n_rows][ld]
+	const double2* sure;     // [n_rows][ld]
+	const double* hw;        // [n_rows][ld]
+	const double* rec0;      // [Mc] recombination fraction towards the next marker, genrec[0] (0 = same position)
+	const double* rec1;      // [Mc] same with genrec[1]
+	const Unit* units;
+	int32_t n_units;
+	int32_t Mc;              // markers of this chromosome
+	int32_t ld;              // row stride of the parameter arrays (markers)
+	unsigned int* counter;   // work queue head
+	double* alpha;           // scratch [n_ctas][Mc][NUMSHIFTS][NUMTYPES]: alpha before the emission at each marker
+	double* alphafac;        // scratch [n_ctas][Mc][NUMSHIFTS]: its log-factor
+	double* stats_shared;    // statistics block of the rows shared between ranks (layout: StatsBlock)
+	double* stats_local;     // statistics block of the other rows
+	int32_t n_shared;        // rows [0, n_shared) live in stats_shared
+	int32_t n_local;
+	double* loglik;          // [n_units][2]
+};
+
+// Statistics of nr rows x Mc markers, one array per statistic so that each can be copied straight into
+// the caller's per-individual vectors: haplobase [nr][Mc], haplocount [nr][Mc], infprobs [nr][Mc][2][2],
+// homozyg [nr][Mc][2]  (8 doubles per cell in total).
+struct StatsCell
+{
+	double *haplobase, *haplocount, *infprobs, *homozyg;
+};
+__host__ __device__ __forceinline__ StatsCell stats_cell(double* base, size_t nr, size_t Mc, size_t idx, size_t m)
+{
+	const size_t cell = idx * Mc + m, plane = nr * Mc;
+	return StatsCell{ base + cell, base + plane + cell, base + 2 * plane + cell * 4, base + 6 * plane + cell * 2 };
+}
+
+struct __align__(16) Smem
+{
+	double acc[NACC * NTHREADS];
+	double2 S[NSLOTS * TILE];
+	double HW[NSLOTS * TILE];
+	double tot[NACC];
+	double Ls[NUMSHIFTS];
+	uchar2 A[NSLOTS * TILE];
+	Unit unit;
+	int32_t unit_index;
+};
+
+__device__ __forceinline__ double warp_sum(double v)
+{
+#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+	return v;
+}
+
+// Transition part of realanalyze (cnF2freq.cpp:2270-2367): p'[to] = sum_from p[from] * prod_t (bit_t(from^to) ? r_t : 1-r_t).
+// TYPEGENS = {1,0,0,1,0,0} (settings.h:23) picks genrec[1] for the two child meioses (bits 0 and 3).
+__device__ __forceinline__ void transition(double& p0, double& p1, double r0, double r1)
+{
+	if (!(r0 > 0) && !(r1 > 0)) return;  // same position: identity (:2273)
+#pragma unroll
+	for (int b = 0; b < 5; b++)
+	{
+		const double r = (b == 0 || b == 3) ? r1 : r0;
+		const double q0 = __shfl_xor_sync(0xffffffffu, p0, 1 << b);
+		const double q1 = __shfl_xor_sync(0xffffffffu, p1, 1 << b);
+		p0 = (1.0 - r) * p0 + r * q0;
+		p1 = (1.0 - r) * p1 + r * q1;
+	}
+	const double n0 = (1.0 - r0) * p0 + r0 * p1;
+	const double n1 = (1.0 - r0) * p1 + r0 * p0;
+	p0 = n0;
+	p1 = n1;
+}
+
+constexpr double MINFACTOR_D = (double)(float)-1e15;  // settings.h:29, a float constant
+
+// adjustprobs (cnF2freq.cpp:1579-1670) for one warp = one shift mode, all orientations summed (flag2 = -1).
+__device__ __forceinline__ void emit_step(const Ctx& c, int t, int lane, int shift, double& p0, double& p1, double& F)
+{
+	if (p0 < 1e-300) p0 = 0;
+	else p0 *= track<0, 4>(c, 0, UNKNOWN, 0.0, t, (unsigned)(lane * 2), -1, shift, 0.0);
+	if (p1 < 1e-300) p1 = 0;
+	else p1 *= track<0, 4>(c, 0, UNKNOWN, 0.0, t, (unsigned)((lane + 32) * 2), -1, shift, 0.0);
+	const double sum = warp_sum(p0 + p1);
+	if (sum <= 0) F = MINFACTOR_D;
+	else
+	{
+		p0 /= sum;
+		p1 /= sum;
+		F += log(sum);
+	}
+}
+
+__device__ __forceinline__ void load_tile(Smem& sm, const EstepArgs& a, int m0, int tid)
+{
+	for (int i = tid; i < NSLOTS * TILE; i += NTHREADS)
+	{
+		const int slot = i / TILE, t = i % TILE;
+		const int row = sm.unit.row[slot];
+		const int m = m0 + t;
+		uchar2 al = make_uchar2(0, 0);
+		double2 su = make_double2(0, 0);
+		double h = 0;
+		if (row >= 0 && m < a.Mc)
+		{
+			const size_t o = (size_t)row * a.ld + m;
+			al = a.alleles[o];
+			su = a.sure[o];
+			h = a.hw[o];
+		}
+		sm.A[i] = al;
+		sm.S[i] = su;
+		sm.HW[i] = h;
+	}
+}
+
+// ignoreflag2, cnF2freq.cpp:3462-3496, rules 2 and 3 (rule 1 is applied by enumerating only the
+// orientations outside flag2ignore).  hom bit i = relative i is "homozygous with equal sureness" here.
+__device__ __forceinline__ bool ignored(const Unit& u, int hom, int flag2, int g, int shift)
+{
+	const int x = flag2 ^ (g << 1);
+	for (int i = 0; i < u.nrel; i++)
+	{
+		const int filt = u.relfilter[i];
+		if (!filt) continue;
+		const int filtered = x & filt;
+		if (filtered && filtered != filt) return true;
+		if (((hom >> i) & 1) && !((filtered != 0) ^ ((shift & u.relshift[i]) != 0))) return true;
+	}
+	return false;
+}
+
+__global__ void __launch_bounds__(NTHREADS, 1) estep_kernel(EstepArgs a)
+{
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
+	const int tid = threadIdx.x, lane = tid & 31, shift = tid >> 5;
+	double* const alpha = a.alpha + (size_t)blockIdx.x * a.Mc * (NUMSHIFTS * NUMTYPES);
+	double* const alphafac = a.alphafac + (size_t)blockIdx.x * a.Mc * NUMSHIFTS;
+	Ctx c{ sm.A, sm.S, sm.HW, sm.unit.row, sm.unit.founder, sm.acc + tid };
+	const int Mc = a.Mc, E = Mc - 1;
+	const int ntiles = (Mc + TILE - 1) / TILE;
+
+	for (int i = tid; i < NACC * NTHREADS; i += NTHREADS) sm.acc[i] = 0;
+
+	for (;;)
+	{
+		__syncthreads();
+		if (tid == 0) sm.unit_index = (int)atomicAdd(a.counter, 1u);
+		__syncthreads();
+		const int ui = sm.unit_index;
+		if (ui >= a.n_units) break;
+		{
+			const int* src = reinterpret_cast<const int*>(a.units + ui);
+			int* dst = reinterpret_cast<int*>(&sm.unit);
+			for (int i = tid; i < (int)(sizeof(Unit) / 4); i += NTHREADS) dst[i] = src[i];
+		}
+		__syncthreads();
+		const Unit& u = sm.unit;
+		const bool active = shift < u.shiftend && !(shift & u.shiftignore);
+
+		// ---- forward sweep: initfwbw + realanalyze<STORE|FORWARD> (cnF2freq.cpp:2086-2107) ----
+		double p0 = 1.0 / NUMTYPES, p1 = 1.0 / NUMTYPES, F = 0;  // EVENGEN, :2100-2104
+		double L = 0;
+		for (int tile = 0; tile < ntiles; tile++)
+		{
+			__syncthreads();
+			load_tile(sm, a, tile * TILE, tid);
+			__syncthreads();
+			if (!active) continue;
+			const int tend = min(TILE, Mc - tile * TILE);
+			for (int t = 0; t < tend; t++)
+			{
+				const int m = tile * TILE + t;
+				double* dst = alpha + ((size_t)m * NUMSHIFTS + shift) * NUMTYPES;
+				dst[lane] = p0;
+				dst[lane + 32] = p1;
+				if (lane == 0) alphafac[(size_t)m * NUMSHIFTS + shift] = F;
+				emit_step(c, t, lane, shift, p0, p1, F);
+				if (m < E) transition(p0, p1, a.rec0[m], a.rec1[m]);
+			}
+		}
+		if (active)
+		{
+			// doanalyze/quickanalyze with NONESTOP (:1984-2018): alpha+ at the last marker against beta = 1
+			L = F;
+			const double sum = warp_sum(p0 + p1);
+			if (sum <= 0) L = MINFACTOR_D;
+			else L -= log(1.0 / sum);
+			if (lane == 0) sm.Ls[shift] = L;
+		}
+		__syncthreads();
+		// :5373-5403
+		double factor = -1e15, realfactor = 0;
+		for (int s = 0; s < u.shiftend; s++)
+		{
+			const double f = (s & u.shiftignore) ? -1e30 : sm.Ls[s];
+			factor = fmax(factor, f);
+		}
+		for (int s = 0; s < u.shiftend; s++)
+		{
+			if (s & u.shiftignore) continue;
+			realfactor += exp(sm.Ls[s] - factor);
+		}
+		const double maxfactor = factor;
+		factor += log(realfactor);
+		if (tid == 0)
+		{
+			a.loglik[(size_t)u.out * 2 + 0] = maxfactor;
+			a.loglik[(size_t)u.out * 2 + 1] = factor;
+		}
+		if (isnan(factor) || factor < MINFACTOR_D) continue;  // :5403
+		const bool contributing = active && !(factor - L > 40);  // :5421
+		const float minfactor = (float)(-200.0 + factor);         // unusualstate + factor as a float, :1936
+		const int allowed = (NUMPATHS - 1) & ~u.flag2ignore;
+
+		// ---- backward sweep fused with the posterior enumeration (cnF2freq.cpp:2109-2116, 5406-5583) ----
+		double b0 = 1.0, b1 = 1.0, B = 0;  // :2111-2114
+		for (int tile = ntiles - 1; tile >= 0; tile--)
+		{
+			__syncthreads();
+			load_tile(sm, a, tile * TILE, tid);
+			__syncthreads();
+			const int tend = min(TILE, Mc - tile * TILE);
+			for (int t = tend - 1; t >= 0; t--)
+			{
+				const int m = tile * TILE + t;
+				if (contributing)
+				{
+					int hom = 0;
+					for (int i = 0; i < u.nrel; i++)
+					{
+						if (!u.relfilter[i]) continue;
+						// any slot of the relative holds the same individual's data
+						const int slot = __ffs(u.relfilter[i]) - 1;
+						const uchar2 al = sm.A[slot * TILE + t];
+						const double2 su = sm.S[slot * TILE + t];
+						if (al.x == al.y && su.x == su.y) hom |= 1 << i;
+					}
+					const double* src = alpha + ((size_t)m * NUMSHIFTS + shift) * NUMTYPES;
+					const double Fm = alphafac[(size_t)m * NUMSHIFTS + shift];
+					for (int gi = 0; gi < 2; gi++)
+					{
+						const int g = lane + 32 * gi;
+						const double am = src[g];
+						const double bm = gi ? b1 : b0;
+						for (int flag2 = allowed;; flag2 = (flag2 - 1) & allowed)
+						{
+							if (!ignored(u, hom, flag2, g, shift))
+							{
+								// doanalyze with classicstop(marker, g) and orientation flag2 (:1963-2018, 2229-2266)
+								double lp = Fm;
+								double e = 0;
+								if (!(lp < minfactor))
+								{
+									double v = 0;
+									if (!(am < 1e-300))
+									{
+										e = track<0, 4>(c, 0, UNKNOWN, 0.0, t, (unsigned)(g * 2), flag2, shift, 0.0);
+										v = am * e;
+									}
+									double inner = (v <= 0) ? MINFACTOR_D : log(v);
+									lp += inner;
+									if (!(lp < minfactor))
+									{
+										lp += B;
+										if (bm <= 0) lp = MINFACTOR_D;
+										else lp -= log(1.0 / bm);
+									}
+								}
+								double val = lp - factor;
+								if (isfinite(val) && val > -200.0)
+								{
+									val = exp(val);
+									double sv[2][2], svs[2], hz[2];
+#pragma unroll
+									for (int side = 0; side < 2; side++)  // :5519-5529
+									{
+										sv[side][0] = track<U_GENOSPROBE, 4>(c, 0, 1, 0.0, t, (unsigned)(g * 2 + side), flag2 ^ side, shift, 0.0);
+										sv[side][1] = track<U_GENOSPROBE, 4>(c, 0, 2, 0.0, t, (unsigned)(g * 2 + side), flag2 ^ side, shift, 0.0);
+										svs[side] = sv[side][0] + sv[side][1];
+									}
+#pragma unroll
+									for (int al = 0; al < 2; al++)  // :5532-5537
+										hz[al] = track<U_HOMOZYGOUS, 4>(c, 0, al + 1, 0.0, t, (unsigned)(g * 2), flag2, shift, 0.0);
+									// updatehaplo, :1561-1575 (its first, update-free call is the emission above)
+									if (e != 0) track<U_HAPLOS, 4>(c, 0, UNKNOWN, 0.0, t, (unsigned)(g * 2), flag2, shift, val);
+#pragma unroll
+									for (int side = 0; side < 2; side++)  // :5560-5568
+#pragma unroll
+										for (int al = 0; al < 2; al++)
+											track<U_GENOS, 4>(c, 0, al + 1, 0.0, t, (unsigned)(g * 2 + side), flag2 ^ side, shift,
+											                  val * sv[side][al] / svs[side]);
+#pragma unroll
+									for (int al = 0; al < 2; al++)  // :5571-5575
+										c.acc[(ACC_HZ + al) * NTHREADS] += val * hz[al] / svs[0];
+								}
+							}
+							if (flag2 == 0) break;
+						}
+					}
+				}
+				__syncthreads();
+				// block-level reduction of the accumulator columns; the reader clears what it read
+				for (int k = shift; k < NACC; k += NUMSHIFTS)
+				{
+					double v = 0;
+#pragma unroll
+					for (int j = 0; j < NTHREADS / 32; j++)
+					{
+						double* p = &sm.acc[k * NTHREADS + j * 32 + lane];
+						v += *p;
+						*p = 0;
+					}
+					v = warp_sum(v);
+					if (lane == 0) sm.tot[k] = v;
+				}
+				__syncthreads();
+				// transfer into the EM sufficient statistics (:5875-5904, moveinfprobs :3577-3597, movehaplos :3599-3616)
+				if (tid < u.nrel)
+				{
+					const int r = tid;
+					const int rootrel = u.slotrel[0];
+					double rootsum = 0, h0 = 0, h1 = 0, ip[4] = { 0, 0, 0, 0 };
+					for (int slot = 0; slot < NSLOTS; slot++)
+					{
+						if (u.row[slot] < 0) continue;
+						const int rel = u.slotrel[slot];
+						if (rel == rootrel) rootsum += sm.tot[ACC_INF + slot * 4 + 0] + sm.tot[ACC_INF + slot * 4 + 1];
+						if (rel == r)
+						{
+							h0 += sm.tot[ACC_HAPLOS + slot * 2 + 0];
+							h1 += sm.tot[ACC_HAPLOS + slot * 2 + 1];
+							for (int q = 0; q < 4; q++) ip[q] += sm.tot[ACC_INF + slot * 4 + q];
+						}
+					}
+					const double sum = 1.0 / rootsum;
+					const int srow = u.relrow[r];
+					const StatsCell cell = srow < a.n_shared ? stats_cell(a.stats_shared, a.n_shared, Mc, srow, m)
+					                                         : stats_cell(a.stats_local, a.n_local, Mc, srow - a.n_shared, m);
+					double norm = sum * 2;
+					for (int k = 0; k < u.relhalvings[r]; k++) norm /= 2;
+					norm *= u.descendants;
+					for (int q = 0; q < 4; q++)
+						if (ip[q] != 0) atomicAdd(cell.infprobs + q, ip[q] * norm);
+					if (h0 != 0 || h1 != 0)
+					{
+						// the relative's own haploweight at this marker; any of its slots holds it
+						int slot = 0;
+						while (u.slotrel[slot] != r || u.row[slot] < 0) slot++;
+						const double w = sm.HW[slot * TILE + t];
+						if (fabs(w - 0.5) < 0.5 - 1e-12)
+						{
+							const double eps = exp(-400.0) * (double)(0.000005f) * (double)(0.000005f) * 0.5;  // maxdiff, :228
+							const double x1 = h0 + eps, x2 = h1 + eps;
+							atomicAdd(cell.haplobase, x1 / (x1 + x2) * u.descendants);
+							atomicAdd(cell.haplocount, u.descendants);
+						}
+					}
+					if (r == rootrel)
+					{
+						atomicAdd(cell.homozyg + 0, sm.tot[ACC_HZ + 0] * sum);
+						atomicAdd(cell.homozyg + 1, sm.tot[ACC_HZ + 1] * sum);
+					}
+				}
+				// beta for the previous marker: adjustprobs at m, then the transition (:2390-2396)
+				if (active && m > 0)
+				{
+					emit_step(c, t, lane, shift, b0, b1, B);
+					transition(b0, b1, a.rec0[m - 1], a.rec1[m - 1]);
+				}
+			}
+		}
+	}
+}
+}  // namespace cnf2

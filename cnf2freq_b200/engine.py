@@ -1,0 +1,186 @@
+"""Host-side binding of the C ABI in include/cnf2_engine.h (ctypes; no torch types cross the boundary).
+
+This is the Python mirror of what a C++ host does around the cut in doit() (cnF2freq.cpp:5283-5907):
+per chromosome, hand the engine the current parameters, run the E-step, take the EM sufficient
+statistics back.  There is no CPU path: if the CUDA library is missing or no GPU is present the calls
+raise.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG, "lib", "libcnf2_engine.so")
+
+SYMBOLS = [
+    "cnf2_default_settings", "cnf2_create", "cnf2_destroy", "cnf2_last_error", "cnf2_set_map", "cnf2_set_pedigree",
+    "cnf2_set_params", "cnf2_estep", "cnf2_set_allreduce", "cnf2_set_shared_rows", "cnf2_get_stats", "cnf2_sync",
+    "cnf2_last_estep_ms", "cnf2_last_estep_launches", "cnf2_stream", "cnf2_measure_peaks", "cnf2_mark",
+    "cnf2_elapsed_ms",
+]
+
+
+class Settings(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_int32) for n in
+                ("numgen", "selfing", "relskewstates", "haplotyping", "doinfprobs", "device", "ctas_per_sm", "reserved")]
+
+
+ALLREDUCE_FN = ctypes.CFUNCTYPE(ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p)
+
+
+class EngineError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load_library():
+    """Loads libcnf2_engine.so; raises (never falls back) when it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise EngineError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                              "(the engine has no CPU fallback)")
+        lib = ctypes.CDLL(LIB_PATH)
+        lib.cnf2_last_error.restype = ctypes.c_char_p
+        lib.cnf2_last_error.argtypes = [ctypes.c_void_p]
+        lib.cnf2_stream.restype = ctypes.c_void_p
+        lib.cnf2_stream.argtypes = [ctypes.c_void_p]
+        lib.cnf2_destroy.restype = None
+        lib.cnf2_destroy.argtypes = [ctypes.c_void_p]
+        lib.cnf2_default_settings.restype = None
+        _lib = lib
+    return _lib
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(ctypes.c_void_p)
+
+
+class Engine:
+    """One engine = one GPU (one rank).  Method names follow the C ABI."""
+
+    def __init__(self, device=0, ctas_per_sm=0):
+        self.lib = load_library()
+        s = Settings()
+        self.lib.cnf2_default_settings(ctypes.byref(s))
+        s.device = device
+        s.ctas_per_sm = ctas_per_sm
+        self.h = ctypes.c_void_p()
+        rc = self.lib.cnf2_create(ctypes.byref(self.h), ctypes.byref(s))
+        if rc != 0:
+            raise EngineError(f"cnf2_create failed ({rc}): {self.lib.cnf2_last_error(None).decode()}")
+        self._keep = []
+        self.n_markers = self.n_chrom = self.n_ind = self.n_dous = 0
+        self.chromstarts = None
+
+    def _check(self, rc):
+        if rc != 0:
+            raise EngineError(f"cnf2 error {rc}: {self.lib.cnf2_last_error(self.h).decode()}")
+
+    def close(self):
+        if self.h:
+            self.lib.cnf2_destroy(self.h)
+            self.h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_map(self, markerpos, chromstarts, genrec):
+        markerpos = np.ascontiguousarray(markerpos, np.float64)
+        chromstarts = np.ascontiguousarray(chromstarts, np.uint32)
+        genrec = np.ascontiguousarray(genrec, np.float64)
+        self.n_markers, self.n_chrom = len(markerpos), len(chromstarts) - 1
+        self.chromstarts = chromstarts.copy()
+        self._check(self.lib.cnf2_set_map(self.h, _ptr(markerpos), ctypes.c_int32(self.n_markers), _ptr(chromstarts),
+                                          ctypes.c_int32(self.n_chrom), _ptr(genrec)))
+
+    def set_shared_rows(self, ids):
+        ids = np.ascontiguousarray(ids, np.int32)
+        self._check(self.lib.cnf2_set_shared_rows(self.h, _ptr(ids), ctypes.c_int32(len(ids))))
+
+    def set_allreduce(self, fn):
+        """fn(device_ptr:int, count:int, cuda_stream:int) -> None; must enqueue an in-place fp64 sum all-reduce."""
+        def tramp(ctx, buf, count, stream):
+            try:
+                fn(int(buf), int(count), int(stream or 0))
+                return 0
+            except Exception as ex:  # surfaced as CNF2_ERR_CUDA by the engine
+                print("cnf2 all-reduce hook failed:", ex)
+                return 1
+        cb = ALLREDUCE_FN(tramp)
+        self._keep.append(cb)
+        self._check(self.lib.cnf2_set_allreduce(self.h, cb, None))
+
+    def set_pedigree(self, parents, empty, founder, gen, descendants, dous, all_dous=None):
+        parents = np.ascontiguousarray(parents, np.int32)
+        empty = np.ascontiguousarray(empty, np.uint8)
+        founder = np.ascontiguousarray(founder, np.uint8)
+        gen = np.ascontiguousarray(gen, np.int32)
+        descendants = np.ascontiguousarray(descendants, np.int32)
+        dous = np.ascontiguousarray(dous, np.int32)
+        all_dous = dous if all_dous is None else np.ascontiguousarray(all_dous, np.int32)
+        self.n_ind, self.n_dous = parents.shape[0], len(dous)
+        self._check(self.lib.cnf2_set_pedigree(
+            self.h, ctypes.c_int32(self.n_ind), _ptr(parents), _ptr(empty), _ptr(founder), _ptr(gen), _ptr(descendants),
+            _ptr(dous), ctypes.c_int32(len(dous)), _ptr(all_dous), ctypes.c_int32(len(all_dous))))
+
+    def set_params(self, chrom, alleles, sure, haploweight):
+        """alleles u8 [n_ind][M][2], sure f64 [n_ind][M][2], haploweight f64 [n_ind][M] (numpy, C-contiguous)."""
+        for a, dt, n in ((alleles, np.uint8, 2), (sure, np.float64, 2), (haploweight, np.float64, 1)):
+            if a.dtype != dt or not a.flags.c_contiguous or a.size != self.n_ind * self.n_markers * n:
+                raise EngineError("set_params: arrays must be C-contiguous [n_ind][n_markers](x2) of the documented dtype")
+        self._check(self.lib.cnf2_set_params(self.h, ctypes.c_int32(chrom), _ptr(alleles), _ptr(sure), _ptr(haploweight)))
+
+    def estep(self, chrom):
+        self._check(self.lib.cnf2_estep(self.h, ctypes.c_int32(chrom)))
+
+    def get_stats(self, chrom, haplobase=None, haplocount=None, infprobs=None, homozyg=None, loglik=None):
+        self._check(self.lib.cnf2_get_stats(self.h, ctypes.c_int32(chrom), _ptr(haplobase), _ptr(haplocount),
+                                            _ptr(infprobs), _ptr(homozyg), _ptr(loglik)))
+
+    def sync(self):
+        self._check(self.lib.cnf2_sync(self.h))
+
+    def last_estep_ms(self):
+        ms = ctypes.c_float()
+        self._check(self.lib.cnf2_last_estep_ms(self.h, ctypes.byref(ms)))
+        return float(ms.value)
+
+    def last_estep_launches(self):
+        n = ctypes.c_int32()
+        self._check(self.lib.cnf2_last_estep_launches(self.h, ctypes.byref(n)))
+        return int(n.value)
+
+    def stream(self):
+        return int(self.lib.cnf2_stream(self.h) or 0)
+
+    def mark(self, slot):
+        self._check(self.lib.cnf2_mark(self.h, ctypes.c_int32(slot)))
+
+    def elapsed_ms(self, a, b):
+        ms = ctypes.c_float()
+        self._check(self.lib.cnf2_elapsed_ms(self.h, ctypes.c_int32(a), ctypes.c_int32(b), ctypes.byref(ms)))
+        return float(ms.value)
+
+    def measure_peaks(self):
+        a, b = ctypes.c_double(), ctypes.c_double()
+        self._check(self.lib.cnf2_measure_peaks(self.h, ctypes.byref(a), ctypes.byref(b)))
+        return float(a.value), float(b.value)
+
+    # -- convenience: a whole E-step over all chromosomes, shaped like the oracle's outputs ------------
+    def estep_all(self, alleles, sure, haploweight, out=None):
+        K, M, C = self.n_ind, self.n_markers, self.n_chrom
+        if out is None:
+            out = dict(haplobase=np.zeros((K, M)), haplocount=np.zeros((K, M)), infprobs=np.zeros((K, M, 2, 2)),
+                       homozyg=np.zeros((K, M, 2)), loglik=np.zeros((self.n_dous, C, 2)))
+        for c in range(C):
+            self.set_params(c, alleles, sure, haploweight)
+            self.estep(c)
+            self.get_stats(c, out["haplobase"], out["haplocount"], out["infprobs"], out["homozyg"], out["loglik"])
+        return out

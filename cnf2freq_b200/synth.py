@@ -88,3 +88,61 @@ def write_alpha_files(prefix, sim):
     with open(prefix + ".gen", "w") as f:
         for name, row in zip(sim["names"], sim["tokens"]):
             f.write(name + " " + " ".join(str(int(t)) for t in row) + "\n")
+
+
+def f2_flat(n_f2, n_chrom, markers_per_chrom, spacing_cM=0.1, missing=0.2, seed=3, pinned=None):
+    """cfg3 as the flat arrays the engine's C ABI takes, in the state the reference holds them during its EM
+    iterations (see tests/golden/f2small_iter2.npz): founders A (2,2) and B (1,1) with markersure 0.02; two
+    implicit, `empty` F1 parents per F2 (readalphaped, cnF2freq.cpp:6515-6527) inferred as (2,1) with
+    markersure 0.5 and their phase locked (haploweight 0) at the first marker of each chromosome
+    (lockhaplos, :3045-3079); F2 genotypes with markersure 0.02, missing ones unknown.
+    Individual ids: 0 none, 1 A, 2 B, then per F2: itself, F1 father, F1 mother.
+    pinned: optional callable (shape, dtype) -> ndarray allocating page-locked host memory."""
+    rng = np.random.default_rng(seed)
+    alloc = pinned or (lambda shape, dtype: np.zeros(shape, dtype))
+    pos, cs = make_map(n_chrom, markers_per_chrom, spacing_cM)
+    M = pos.shape[0]
+    K = 3 + 3 * n_f2
+    f1 = np.stack([np.full(M, 2, np.uint8), np.full(M, 1, np.uint8)])
+    g0 = _gametes(rng, f1, pos, cs, n_f2)
+    g1 = _gametes(rng, f1, pos, cs, n_f2)
+    miss = rng.random((n_f2, M)) < missing
+    alleles = alloc((K, M, 2), np.uint8)
+    sure = alloc((K, M, 2), np.float64)
+    hw = alloc((K, M), np.float64)
+    alleles[...] = 0
+    sure[...] = 0
+    hw[...] = 0.5
+    alleles[1] = 2
+    alleles[2] = 1
+    sure[1:3] = 0.02
+    f2 = 3 + 3 * np.arange(n_f2)
+    a = np.stack([g0, g1], axis=2)
+    a[miss] = 0
+    alleles[f2] = a
+    sure[f2] = np.where(miss[:, :, None], 0.0, 0.02)
+    for off in (1, 2):
+        alleles[f2 + off, :, 0] = 2
+        alleles[f2 + off, :, 1] = 1
+        sure[f2 + off] = 0.5
+        hw[(f2 + off)[:, None], np.asarray(cs[:-1], np.int64)[None, :]] = 0.0
+    par = np.zeros((K, 2), np.int32)
+    par[f2, 0] = f2 + 1
+    par[f2, 1] = f2 + 2
+    par[f2 + 1] = (1, 2)
+    par[f2 + 2] = (1, 2)
+    empty = np.zeros(K, np.uint8)
+    empty[0] = 1
+    empty[f2 + 1] = 1
+    empty[f2 + 2] = 1
+    gen = np.zeros(K, np.int32)
+    gen[f2] = 2
+    gen[f2 + 1] = 1
+    gen[f2 + 2] = 1
+    desc = np.zeros(K, np.int32)
+    desc[f2] = 1
+    founder = np.zeros(K, np.uint8)
+    founder[1:3] = 1
+    return dict(par=par, empty=empty, founder=founder, gen=gen, descendants=desc, dous=f2.astype(np.int32), markerpos=pos,
+                chromstarts=cs, genrec=np.full(3, -1.0 / 50), alleles=alleles, sure=sure, haploweight=hw,
+                shared=np.array([1, 2], np.int32))

@@ -1,0 +1,138 @@
+/*
+ * cnf2_engine.h -- C ABI of the B200 (sm_100a) engine for the hot path of cnettel/cnF2freq.
+ *
+ * The reference has no plugin/FFI seam (one translation unit); the boundary is cut
+ * inside doit(): the body of the OpenMP loop over analysed individuals for one chromosome,
+ * cnF2freq.cpp:5294-5907.  What the reference computes there -- the 8 shift-mode forward/backward sweeps
+ * (initfwbw :2074-2120, realanalyze :2145-2418, adjustprobs :1579-1670, trackpossible :1075-1359), the
+ * marker x state x shift x orientation posterior enumeration (:5406-5583, ignoreflag2 :3462-3496) and the
+ * transfer into the per-individual EM sufficient statistics (moveinfprobs/movehaplos :3577-3616,
+ * :5875-5904) -- is what cnf2_estep() computes on the GPU.  Everything is fp64, like the reference.
+ *
+ * Conventions
+ *   - individual ids are 1..n_ind-1, id 0 means "no individual" (individ::n / individer[], :2447-2450);
+ *   - all [n_ind][n_markers] arrays are row-major over ALL markers of ALL chromosomes (the reference's
+ *     per-individual vectors, :853-902), caller-owned; the engine copies what it needs on set_* and
+ *     fills caller buffers on get_*;
+ *   - every call returns 0 on success or a negative cnf2_status; cnf2_last_error() has the text;
+ *   - one host thread per engine; several engines (one per GPU / rank) may coexist;
+ *   - there is NO CPU fallback: without a CUDA device cnf2_create() fails with CNF2_ERR_NO_DEVICE.
+ *
+ * Reference-side binding: see INTEGRATION.md (the replacement for the loop at cnF2freq.cpp:5294).
+ */
+#ifndef CNF2_ENGINE_H
+#define CNF2_ENGINE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct cnf2_engine cnf2_engine; /* opaque; owns all device memory */
+
+typedef enum cnf2_status
+{
+	CNF2_OK = 0,
+	CNF2_ERR_NO_DEVICE = -1,  /* no CUDA device / driver: the engine never falls back to the CPU */
+	CNF2_ERR_BAD_ARG = -2,
+	CNF2_ERR_CUDA = -3,       /* a CUDA runtime call or kernel failed; see cnf2_last_error() */
+	CNF2_ERR_STATE = -4,      /* calls out of order (e.g. estep before set_params) */
+	CNF2_ERR_UNSUPPORTED = -5 /* a settings.h combination the kernels are not built for */
+} cnf2_status;
+
+/* settings.h knobs that shape the state space (settings.h:3-47).  The kernels are instantiated for the
+ * HEAD configuration: NUMGEN 3 (64 states, 128 orientations, 8 shift modes), SELFING false,
+ * RELSKEWSTATES false, HAPLOTYPING true, DOINFPROBS true.  Anything else -> CNF2_ERR_UNSUPPORTED. */
+typedef struct cnf2_settings
+{
+	int32_t numgen;        /* settings.h:19  NUMGEN */
+	int32_t selfing;       /* settings.h:14  SELFING */
+	int32_t relskewstates; /* settings.h:16  RELSKEWSTATES */
+	int32_t haplotyping;   /* settings.h:36  HAPLOTYPING */
+	int32_t doinfprobs;    /* settings.h:12  DOINFPROBS */
+	int32_t device;        /* CUDA device ordinal of this engine (one engine per GPU / rank) */
+	int32_t ctas_per_sm;   /* 0 = let the engine choose from the occupancy query */
+	int32_t reserved;
+} cnf2_settings;
+
+/* Fills *s with the reference's HEAD settings (settings.h:3-47) and device 0. */
+void cnf2_default_settings(cnf2_settings* s);
+
+int cnf2_create(cnf2_engine** out, const cnf2_settings* settings);
+void cnf2_destroy(cnf2_engine* e);
+const char* cnf2_last_error(const cnf2_engine* e); /* e may be NULL: error of the last failed cnf2_create */
+
+/* Map: marker positions in cM, chromosome boundaries, recombination rates.
+ * Replaces the globals markerposes / chromstarts / genrec (cnF2freq.cpp:233-239, set at :7927-7943 and by
+ * readalphamap :6669-6685).  chromstarts has n_chrom+1 entries; genrec[gen] is the Haldane exponent
+ * (-1/50 at HEAD) used as r = 0.5*(1-exp(genrec[gen]*d)) (:2286, getactrec :777-780). */
+int cnf2_set_map(cnf2_engine* e, const double* markerpos_cM, int32_t n_markers, const uint32_t* chromstarts,
+                 int32_t n_chrom, const double genrec[3]);
+
+/* Pedigree: replaces individer[] / dous (cnF2freq.cpp:2447-2450) and the individ fields pars, empty,
+ * founder, gen, descendants (:853-872).  parents is [n_ind][2] (0 = none).  dous lists the analysed
+ * individuals THIS engine works on (a rank's shard of the reference's dous); loglik rows follow its order.
+ * The focus-tree tables of fixtrees (:3099-3187) are built here.  fixtrees' sticky side effect
+ * (ind->founder = true for analysed individuals without any non-empty ancestor, :3170-3177) is applied
+ * for every entry of all_dous (the union over all ranks; pass dous again when not sharded) before any
+ * tree is used, i.e. the state the reference is in from its second EM iteration on. */
+int cnf2_set_pedigree(cnf2_engine* e, int32_t n_ind, const int32_t* parents, const uint8_t* empty,
+                      const uint8_t* founder, const int32_t* gen, const int32_t* descendants, const int32_t* dous,
+                      int32_t n_dous, const int32_t* all_dous, int32_t n_all_dous);
+
+/* Parameters of one chromosome for the coming E-step: markerdata (allele pair, values 0 = unknown, 1, 2,
+ * 9 = sex/doubled-haploid sentinel, cnF2freq.cpp:225-226, :876), markersure (:878) and haploweight (:887).
+ * Arrays are [n_ind][n_markers] (x2 for the pairs); only the columns of `chrom` and the rows of the
+ * individuals this engine's focus trees touch are copied (host -> device, asynchronously when the
+ * buffers are pinned).  When the parameters of all chromosomes fit in a small part of HBM they stay resident
+ * (cnf2_estep may then be called for any chromosome set so far); otherwise only the last chromosome is kept. */
+int cnf2_set_params(cnf2_engine* e, int32_t chrom, const uint8_t* alleles, const double* sure,
+                    const double* haploweight);
+
+/* The E-step of one chromosome for all of this engine's analysed individuals: cnF2freq.cpp:5294-5907
+ * without the turn scoring (:5668-5871, row f2 of SURVEY.md section 8).  Asynchronous on the engine's
+ * stream; cnf2_get_stats / cnf2_sync wait for it. */
+int cnf2_estep(cnf2_engine* e, int32_t chrom);
+
+/* Optional exchange step between ranks (the stale MPI reduce at cnF2freq.cpp:6241-6256): called by
+ * cnf2_estep after the kernels are enqueued, with the device buffer holding the statistics rows of the
+ * individuals listed in cnf2_set_shared_rows (8 doubles per (row, marker): haplobase, haplocount,
+ * infprobs[0][1], [0][2], [1][1], [1][2], homozyg[0], homozyg[1]).  The hook must enqueue a sum-all-reduce
+ * over `count` doubles in place on `cuda_stream` (e.g. ncclAllReduce / torch.distributed.all_reduce). */
+typedef int (*cnf2_allreduce_fn)(void* ctx, double* device_buf, size_t count, void* cuda_stream);
+int cnf2_set_allreduce(cnf2_engine* e, cnf2_allreduce_fn fn, void* ctx);
+/* Individuals whose statistics rows receive contributions from more than one rank (e.g. the founders of
+ * an F2 cross).  Must be the same list, in the same order, on every rank.  Call before cnf2_set_pedigree. */
+int cnf2_set_shared_rows(cnf2_engine* e, const int32_t* ids, int32_t n_ids);
+
+/* Statistics of the chromosome last passed to cnf2_estep, copied (assigned, device -> host) into caller
+ * arrays shaped like the reference's per-individual vectors: haplobase/haplocount [n_ind][n_markers] (:901-902),
+ * infprobs [n_ind][n_markers][2 sides][2 alleles {1,2}] (:895), homozyg [n_ind][n_markers][2] (:897);
+ * loglik [n_dous][n_chrom][2] = (max_s L_s, logsumexp_s L_s), the pair printed at :5399-5401.  Only the columns of that chromosome and the rows this engine touched are written.
+ * Any pointer may be NULL to skip that output. */
+int cnf2_get_stats(cnf2_engine* e, int32_t chrom, double* haplobase, double* haplocount, double* infprobs,
+                   double* homozyg, double* loglik);
+
+/* Block until everything enqueued by this engine has finished; returns the first asynchronous error. */
+int cnf2_sync(cnf2_engine* e);
+
+/* Measurement hooks (bench.py): device time of the last cnf2_estep's kernels in milliseconds (CUDA events
+ * on the engine's stream), number of kernel launches it made, and the engine's stream handle. */
+int cnf2_last_estep_ms(cnf2_engine* e, float* ms);
+int cnf2_last_estep_launches(cnf2_engine* e, int32_t* n);
+void* cnf2_stream(cnf2_engine* e);
+/* CUDA events on the engine's stream: cnf2_mark records event `slot` (0..3); cnf2_elapsed_ms waits for
+ * event `to` and returns the device time between two recorded events. */
+int cnf2_mark(cnf2_engine* e, int32_t slot);
+int cnf2_elapsed_ms(cnf2_engine* e, int32_t from, int32_t to, float* ms);
+
+/* Microbenchmarks that define the roofline denominators on this box:
+ * register-resident DFMA throughput in TFLOP/s and device-to-device copy bandwidth in GB/s. */
+int cnf2_measure_peaks(cnf2_engine* e, double* dfma_tflops, double* copy_gbs);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
