@@ -45,6 +45,13 @@ struct Unit
 	uint8_t shiftend;            // NUMSHIFTS, or 2 when gen < 2 (:5359)
 	int32_t out;                 // row of the loglik output
 	double descendants;
+	// dense enumeration of the surviving (g, flag2) pairs through x = flag2 ^ (g << 1) (see cnf2_fast_kernel.cuh)
+	uint8_t gfixmask;            // state bits pinned by x: bit j set when orientation bit j+1 is in flag2ignore
+	uint8_t nfree;               // number of free state bits
+	uint8_t vismask;             // slots trackpossible visits from a non-founder root (pointer chain + founder flags)
+	uint8_t pad0;
+	uint8_t expand[NUMTYPES];    // j -> j deposited into the free state bits
+	uint8_t pad1[4];
 };
 
 // Shared-memory view handed to the emission routine.
@@ -193,5 +200,78 @@ __device__ double track(const Ctx& c, int slot, int inval, double second, int t,
 		}
 	}
 	return ok;
+}
+}  // namespace cnf2
+
+namespace cnf2
+{
+// The root-level part of trackpossible<UPD, 0> (cnF2freq.cpp:1166-1320) for a root that is not "at the top"
+// (genwidth 4, not a founder): everything up to, but not including, the two recursive calls.  base already
+// holds the factor of the other allele (:1298-1320); (val, main2) is what recursetrackpossible hands to
+// parent `firstpar`, (secmark, sec2) what it hands to the other parent.  incoming second is 0 at the root.
+struct RootLocal
+{
+	double base, main2, sec2;
+	int val, secmark;
+};
+
+template <int UPD>
+__device__ __forceinline__ RootLocal root_local(uchar2 a, double2 s, double hw, int inval, int firstpar, int f2,
+                                                int localshift)
+{
+	RootLocal r;
+	const int Af = f2 ? a.y : a.x, Ao = f2 ? a.x : a.y;
+	const double Sf = f2 ? s.y : s.x, So = f2 ? s.x : s.y;
+	int val = inval;
+	bool miss;
+	if (val == UNKNOWN)
+	{
+		val = Af;
+		miss = false;
+	}
+	else if (Af == UNKNOWN && val != SEXMARKER) miss = false;
+	else miss = val != Af;
+	double base, main2 = 0;
+	if (miss) base = Sf;  // incoming second is 0: no main2 (:1200-1201)
+	else
+	{
+		const double eff2 = (inval == UNKNOWN && val != UNKNOWN) ? 1.0 : 0.0;
+		base = 1.0 - Sf;
+		main2 = (Af == UNKNOWN ? 1.0 : Sf) * eff2;
+	}
+	if (UPD & 1)
+	{
+		base += main2;
+		main2 = 0;
+	}
+	else if (main2 != 0) main2 /= base;
+	const int f2n = (f2 ^ firstpar ^ localshift) & 1;
+	if (a.x == a.y && s.x == s.y) base *= f2n ? 1.0 : 0.0;
+	else base *= fabs((f2n ? 1.0 : 0.0) - hw);
+	double sec2 = 0;
+	int secmark = Ao;
+	if (!(UPD & U_GENOS))
+	{
+		if (!(UPD & U_HOMOZYGOUS))
+		{
+			if (So != 0)
+			{
+				base *= 1.0 - So;
+				sec2 = So / (1.0 - So);
+			}
+		}
+		else if (val != secmark)
+		{
+			if (secmark != UNKNOWN) base *= So;
+			secmark = val;
+		}
+		else base *= 1.0 - So;
+	}
+	r.base = base;
+	r.main2 = main2;
+	r.sec2 = sec2;
+	r.val = val;
+	r.secmark = secmark;
+	return r;
 }
 }  // namespace cnf2

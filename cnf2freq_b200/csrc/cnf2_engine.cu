@@ -2,11 +2,12 @@
 // cnF2freq.cpp:3099-3187, leaves behind), device memory, launches.  No CPU compute path exists here:
 // every entry point that would compute needs the CUDA device.
 #include "../../include/cnf2_engine.h"
-#include "cnf2_estep_kernel.cuh"
+#include "cnf2_fast_kernel.cuh"
 
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <string>
@@ -74,7 +75,10 @@ struct cnf2_engine
 	// device
 	DevBuf<uchar2> d_alleles;
 	DevBuf<double2> d_sure;
-	DevBuf<double> d_hw, d_rec, d_alpha, d_alphafac, d_stats, d_loglik;
+	DevBuf<double> d_hw, d_rec, d_alpha, d_alphafac, d_q, d_stats, d_loglik;
+	DevBuf<int32_t> d_literal;
+	int n_ctas_literal = 0;
+	bool literal_only = false;  // debugging / A-B switch: CNF2_LITERAL=1 runs every unit through the literal kernel
 	DevBuf<Unit> d_units;
 	DevBuf<unsigned int> d_counter;
 	std::vector<double> h_loglik;
@@ -175,7 +179,16 @@ extern "C" int cnf2_create(cnf2_engine** out, const cnf2_settings* settings)
 		return bail(ce, "occupancy query");
 	if (per_sm < 1) per_sm = 1;
 	if (settings->ctas_per_sm > 0) per_sm = std::min(per_sm, settings->ctas_per_sm);
+	e->n_ctas_literal = per_sm * e->n_sm;
+	if ((ce = cudaFuncSetAttribute(fast_estep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FastSmem))) != cudaSuccess)
+		return bail(ce, "cudaFuncSetAttribute(fast_estep_kernel)");
+	if ((ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fast_estep_kernel, NTHREADS, sizeof(FastSmem))) != cudaSuccess)
+		return bail(ce, "occupancy query");
+	if (per_sm < 1) per_sm = 1;
+	if (settings->ctas_per_sm > 0) per_sm = std::min(per_sm, settings->ctas_per_sm);
 	e->n_ctas = per_sm * e->n_sm;
+	const char* lit = getenv("CNF2_LITERAL");
+	e->literal_only = lit && lit[0] == '1';
 	*out = e;
 	return CNF2_OK;
 }
@@ -191,6 +204,8 @@ extern "C" void cnf2_destroy(cnf2_engine* e)
 	e->d_rec.release();
 	e->d_alpha.release();
 	e->d_alphafac.release();
+	e->d_q.release();
+	e->d_literal.release();
 	e->d_stats.release();
 	e->d_loglik.release();
 	e->d_units.release();
@@ -377,6 +392,33 @@ extern "C" int cnf2_set_pedigree(cnf2_engine* e, int32_t n_ind, const int32_t* p
 		u.shiftend = (uint8_t)(gen[ind] < 2 ? 2 : NUMSHIFTS);  // :5359
 		u.out = j;
 		u.descendants = (double)descendants[ind];
+		{
+			const int ign = u.flag2ignore;
+			u.gfixmask = (uint8_t)((ign >> 1) & (NUMTYPES - 1));
+			const int freemask = ~u.gfixmask & (NUMTYPES - 1);
+			int nfree = 0;
+			for (int b = 0; b < 6; b++) nfree += (freemask >> b) & 1;
+			u.nfree = (uint8_t)nfree;
+			for (int jx = 0; jx < NUMTYPES; jx++)
+			{
+				int g = 0, k = 0;
+				for (int b = 0; b < 6; b++)
+					if ((freemask >> b) & 1) g |= ((jx >> k++) & 1) << b;
+				u.expand[jx] = (uint8_t)g;
+			}
+			// slots visited from a non-founder root: a parent when its pointer is set, its parents when it is not a founder
+			int vis = 1;
+			for (int p = 0; p < 2; p++)
+			{
+				const int sp = 1 + 3 * p;
+				if (!ids[sp]) continue;
+				vis |= 1 << sp;
+				if (founder[ids[sp]]) continue;
+				for (int q = 0; q < 2; q++)
+					if (ids[sp + 1 + q]) vis |= 1 << (sp + 1 + q);
+			}
+			u.vismask = (uint8_t)vis;
+		}
 		std::vector<int32_t> rel;  // reltree: distinct members, empty ones included, sorted (:3179-3181)
 		for (int k = 0; k < NSLOTS; k++)
 			if (ids[k]) rel.push_back(ids[k]);
@@ -407,7 +449,8 @@ extern "C" int cnf2_set_pedigree(cnf2_engine* e, int32_t n_ind, const int32_t* p
 		CU(cudaMemcpyAsync(e->d_units.p, e->units.data(), e->units.size() * sizeof(Unit), cudaMemcpyHostToDevice, e->stream));
 	CU(e->d_loglik.ensure(e->units.size() * 2));
 	e->h_loglik.assign(e->units.size() * 2, 0.0);
-	CU(e->d_counter.ensure(1));
+	CU(e->d_counter.ensure(4));
+	CU(e->d_literal.ensure(e->units.size()));
 	CU(cudaStreamSynchronize(e->stream));
 	std::fill(e->have_params.begin(), e->have_params.end(), 0);
 	e->estep_chrom = -1;
@@ -467,17 +510,19 @@ extern "C" int cnf2_estep(cnf2_engine* e, int32_t chrom)
 	cudaSetDevice(e->settings.device);
 	const int Mc = e->mc(chrom);
 	const int n_units = (int)e->units.size();
-	const int n_ctas = std::max(1, std::min(e->n_ctas, n_units));
+	const int n_ctas = std::max(1, std::min(std::max(e->n_ctas, e->n_ctas_literal), n_units));
 	CU(e->d_alpha.ensure((size_t)n_ctas * e->max_mc * NUMSHIFTS * NUMTYPES));
 	CU(e->d_alphafac.ensure((size_t)n_ctas * e->max_mc * NUMSHIFTS));
+	CU(e->d_q.ensure((size_t)n_ctas * e->max_mc * NUMSHIFTS * 32));
 	CU(e->d_stats.ensure((size_t)e->n_rows * e->max_mc * STATS_PER_CELL));
 	CU(cudaEventRecord(e->ev0, e->stream));
 	CU(cudaMemsetAsync(e->d_stats.p, 0, (size_t)e->n_rows * Mc * STATS_PER_CELL * sizeof(double), e->stream));
-	CU(cudaMemsetAsync(e->d_counter.p, 0, sizeof(unsigned int), e->stream));
+	CU(cudaMemsetAsync(e->d_counter.p, 0, 4 * sizeof(unsigned int), e->stream));
 	e->last_launches = 0;
 	if (n_units > 0)
 	{
-		EstepArgs a{};
+		FastArgs fa{};
+		EstepArgs& a = fa.e;
 		const size_t col0 = e->resident ? e->chromstarts[chrom] : 0;
 		a.alleles = e->d_alleles.p + col0;
 		a.sure = e->d_sure.p + col0;
@@ -496,9 +541,24 @@ extern "C" int cnf2_estep(cnf2_engine* e, int32_t chrom)
 		a.n_shared = e->n_shared;
 		a.n_local = e->n_rows - e->n_shared;
 		a.loglik = e->d_loglik.p;
-		estep_kernel<<<n_ctas, NTHREADS, sizeof(Smem), e->stream>>>(a);
+		a.unit_list = nullptr;
+		a.list_count = nullptr;
+		fa.qscratch = e->d_q.p;
+		fa.literal_units = e->d_literal.p;
+		fa.literal_count = e->d_counter.p + 1;
+		if (!e->literal_only)
+		{
+			// table-driven kernel; units it cannot take (founder roots, out-of-range parameters) are listed for the literal one
+			fast_estep_kernel<<<std::max(1, std::min(e->n_ctas, n_units)), NTHREADS, sizeof(FastSmem), e->stream>>>(fa);
+			CU(cudaGetLastError());
+			e->last_launches++;
+			a.unit_list = e->d_literal.p;
+			a.list_count = e->d_counter.p + 1;
+			a.counter = e->d_counter.p + 2;
+		}
+		estep_kernel<<<std::max(1, std::min(e->n_ctas_literal, n_units)), NTHREADS, sizeof(Smem), e->stream>>>(a);
 		CU(cudaGetLastError());
-		e->last_launches = 1;
+		e->last_launches++;
 	}
 	CU(cudaEventRecord(e->ev1, e->stream));
 	if (e->allreduce && e->n_shared > 0)

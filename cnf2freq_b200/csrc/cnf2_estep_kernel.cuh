@@ -26,6 +26,8 @@ struct EstepArgs
 	int32_t n_shared;        // rows [0, n_shared) live in stats_shared
 	int32_t n_local;
 	double* loglik;          // [n_units][2]
+	const int32_t* unit_list;      // optional indirection: work item i is unit unit_list[i] ...
+	const unsigned int* list_count;  // ... for i < *list_count (device-side count written by the fast kernel)
 };
 
 // Statistics of nr rows x Mc markers, one array per statistic so that each can be copied straight into
@@ -48,6 +50,8 @@ struct __align__(16) Smem
 	double HW[NSLOTS * TILE];
 	double tot[NACC];
 	double Ls[NUMSHIFTS];
+	double beta[NUMSHIFTS * NUMTYPES];
+	unsigned short queue[NUMSHIFTS * 64];
 	uchar2 A[NSLOTS * TILE];
 	Unit unit;
 	int32_t unit_index;
@@ -138,6 +142,107 @@ __device__ __forceinline__ bool ignored(const Unit& u, int hom, int flag2, int g
 	return false;
 }
 
+// Transfer of one marker's reduced accumulators into the EM sufficient statistics, for relative r of the
+// unit (cnF2freq.cpp:5875-5904, moveinfprobs :3577-3597, movehaplos :3599-3616).
+__device__ __forceinline__ void transfer_stats(const EstepArgs& a, const Unit& u, const double* tot, const double* HW,
+                                               int r, int t, int m)
+{
+	const int Mc = a.Mc;
+	const int rootrel = u.slotrel[0];
+	double rootsum = 0, h0 = 0, h1 = 0, ip[4] = { 0, 0, 0, 0 };
+	for (int slot = 0; slot < NSLOTS; slot++)
+	{
+		if (u.row[slot] < 0) continue;
+		const int rel = u.slotrel[slot];
+		if (rel == rootrel) rootsum += tot[ACC_INF + slot * 4 + 0] + tot[ACC_INF + slot * 4 + 1];
+		if (rel == r)
+		{
+			h0 += tot[ACC_HAPLOS + slot * 2 + 0];
+			h1 += tot[ACC_HAPLOS + slot * 2 + 1];
+			for (int q = 0; q < 4; q++) ip[q] += tot[ACC_INF + slot * 4 + q];
+		}
+	}
+	const double sum = 1.0 / rootsum;
+	const int srow = u.relrow[r];
+	const StatsCell cell = srow < a.n_shared ? stats_cell(a.stats_shared, a.n_shared, Mc, srow, m)
+	                                         : stats_cell(a.stats_local, a.n_local, Mc, srow - a.n_shared, m);
+	double norm = sum * 2;
+	for (int k = 0; k < u.relhalvings[r]; k++) norm /= 2;
+	norm *= u.descendants;
+	for (int q = 0; q < 4; q++)
+		if (ip[q] != 0) atomicAdd(cell.infprobs + q, ip[q] * norm);
+	if (h0 != 0 || h1 != 0)
+	{
+		// the relative's own haploweight at this marker; any of its slots holds it
+		int slot = 0;
+		while (u.slotrel[slot] != r || u.row[slot] < 0) slot++;
+		const double w = HW[slot * TILE + t];
+		if (fabs(w - 0.5) < 0.5 - 1e-12)
+		{
+			const double eps = exp(-400.0) * (double)(0.000005f) * (double)(0.000005f) * 0.5;  // maxdiff, :228
+			const double x1 = h0 + eps, x2 = h1 + eps;
+			atomicAdd(cell.haplobase, x1 / (x1 + x2) * u.descendants);
+			atomicAdd(cell.haplocount, u.descendants);
+		}
+	}
+	if (r == rootrel)
+	{
+		atomicAdd(cell.homozyg + 0, tot[ACC_HZ + 0] * sum);
+		atomicAdd(cell.homozyg + 1, tot[ACC_HZ + 1] * sum);
+	}
+}
+
+// One surviving (state g, shift, orientation flag2) term of the posterior loop, cnF2freq.cpp:5464-5577:
+// its weight val = exp(doanalyze(classicstop(marker, g), flag2) - factor) and the scatter of val into the
+// accumulator columns (haplos via updatehaplo, infprobs via the four GENOS calls, homozyg).
+__device__ __forceinline__ void posterior_term(const Ctx& c, int t, int g, int flag2, int shift, double am, double bm,
+                                               double Fm, double B, double factor, float minfactor)
+{
+	// doanalyze with classicstop(marker, g) and orientation flag2 (:1963-2018, 2229-2266)
+	double lp = Fm;
+	double e = 0;
+	if (!(lp < minfactor))
+	{
+		double v = 0;
+		if (!(am < 1e-300))
+		{
+			e = track<0, 4>(c, 0, UNKNOWN, 0.0, t, (unsigned)(g * 2), flag2, shift, 0.0);
+			v = am * e;
+		}
+		lp += (v <= 0) ? MINFACTOR_D : log(v);
+		if (!(lp < minfactor))
+		{
+			lp += B;
+			if (bm <= 0) lp = MINFACTOR_D;
+			else lp -= log(1.0 / bm);
+		}
+	}
+	double val = lp - factor;
+	if (!(isfinite(val) && val > -200.0)) return;  // unusualstate, :5414, 5502
+	val = exp(val);
+	double sv[2][2], svs[2], hz[2];
+#pragma unroll
+	for (int side = 0; side < 2; side++)  // :5519-5529
+	{
+		sv[side][0] = track<U_GENOSPROBE, 4>(c, 0, 1, 0.0, t, (unsigned)(g * 2 + side), flag2 ^ side, shift, 0.0);
+		sv[side][1] = track<U_GENOSPROBE, 4>(c, 0, 2, 0.0, t, (unsigned)(g * 2 + side), flag2 ^ side, shift, 0.0);
+		svs[side] = sv[side][0] + sv[side][1];
+	}
+#pragma unroll
+	for (int al = 0; al < 2; al++)  // :5532-5537
+		hz[al] = track<U_HOMOZYGOUS, 4>(c, 0, al + 1, 0.0, t, (unsigned)(g * 2), flag2, shift, 0.0);
+	// updatehaplo, :1561-1575 (its first, update-free call is the emission above)
+	if (e != 0) track<U_HAPLOS, 4>(c, 0, UNKNOWN, 0.0, t, (unsigned)(g * 2), flag2, shift, val);
+#pragma unroll
+	for (int side = 0; side < 2; side++)  // :5560-5568
+#pragma unroll
+		for (int al = 0; al < 2; al++)
+			track<U_GENOS, 4>(c, 0, al + 1, 0.0, t, (unsigned)(g * 2 + side), flag2 ^ side, shift, val * sv[side][al] / svs[side]);
+#pragma unroll
+	for (int al = 0; al < 2; al++)  // :5571-5575
+		c.acc[(ACC_HZ + al) * NTHREADS] += val * hz[al] / svs[0];
+}
+
 __global__ void __launch_bounds__(NTHREADS, 1) estep_kernel(EstepArgs a)
 {
 	extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -156,8 +261,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) estep_kernel(EstepArgs a)
 		__syncthreads();
 		if (tid == 0) sm.unit_index = (int)atomicAdd(a.counter, 1u);
 		__syncthreads();
-		const int ui = sm.unit_index;
-		if (ui >= a.n_units) break;
+		int ui = sm.unit_index;
+		if (ui >= (a.unit_list ? (int)*a.list_count : a.n_units)) break;
+		if (a.unit_list) ui = a.unit_list[ui];
 		{
 			const int* src = reinterpret_cast<const int*>(a.units + ui);
 			int* dst = reinterpret_cast<int*>(&sm.unit);
@@ -247,66 +353,43 @@ __global__ void __launch_bounds__(NTHREADS, 1) estep_kernel(EstepArgs a)
 					}
 					const double* src = alpha + ((size_t)m * NUMSHIFTS + shift) * NUMTYPES;
 					const double Fm = alphafac[(size_t)m * NUMSHIFTS + shift];
-					for (int gi = 0; gi < 2; gi++)
+					// beta of this shift mode, readable by every lane of the warp
+					sm.beta[shift * NUMTYPES + lane] = b0;
+					sm.beta[shift * NUMTYPES + lane + 32] = b1;
+					__syncwarp();
+					// The surviving (g, flag2) pairs are sparse and differ from lane to lane, so they are first
+					// compacted into a per-warp queue (ballot + prefix count) and then handed out one per lane.
+					unsigned short* q = sm.queue + shift * 64;
+					int cnt = 0;
+					for (int flag2 = allowed;; flag2 = (flag2 - 1) & allowed)
 					{
-						const int g = lane + 32 * gi;
-						const double am = src[g];
-						const double bm = gi ? b1 : b0;
-						for (int flag2 = allowed;; flag2 = (flag2 - 1) & allowed)
+#pragma unroll
+						for (int gi = 0; gi < 2; gi++)
 						{
-							if (!ignored(u, hom, flag2, g, shift))
+							const int g = lane + 32 * gi;
+							const bool ok = !ignored(u, hom, flag2, g, shift);
+							const unsigned mask = __ballot_sync(0xffffffffu, ok);
+							if (ok) q[cnt + __popc(mask & ((1u << lane) - 1u))] = (unsigned short)((flag2 << 6) | g);
+							cnt += __popc(mask);
+							__syncwarp();
+							if (cnt >= 32)
 							{
-								// doanalyze with classicstop(marker, g) and orientation flag2 (:1963-2018, 2229-2266)
-								double lp = Fm;
-								double e = 0;
-								if (!(lp < minfactor))
-								{
-									double v = 0;
-									if (!(am < 1e-300))
-									{
-										e = track<0, 4>(c, 0, UNKNOWN, 0.0, t, (unsigned)(g * 2), flag2, shift, 0.0);
-										v = am * e;
-									}
-									double inner = (v <= 0) ? MINFACTOR_D : log(v);
-									lp += inner;
-									if (!(lp < minfactor))
-									{
-										lp += B;
-										if (bm <= 0) lp = MINFACTOR_D;
-										else lp -= log(1.0 / bm);
-									}
-								}
-								double val = lp - factor;
-								if (isfinite(val) && val > -200.0)
-								{
-									val = exp(val);
-									double sv[2][2], svs[2], hz[2];
-#pragma unroll
-									for (int side = 0; side < 2; side++)  // :5519-5529
-									{
-										sv[side][0] = track<U_GENOSPROBE, 4>(c, 0, 1, 0.0, t, (unsigned)(g * 2 + side), flag2 ^ side, shift, 0.0);
-										sv[side][1] = track<U_GENOSPROBE, 4>(c, 0, 2, 0.0, t, (unsigned)(g * 2 + side), flag2 ^ side, shift, 0.0);
-										svs[side] = sv[side][0] + sv[side][1];
-									}
-#pragma unroll
-									for (int al = 0; al < 2; al++)  // :5532-5537
-										hz[al] = track<U_HOMOZYGOUS, 4>(c, 0, al + 1, 0.0, t, (unsigned)(g * 2), flag2, shift, 0.0);
-									// updatehaplo, :1561-1575 (its first, update-free call is the emission above)
-									if (e != 0) track<U_HAPLOS, 4>(c, 0, UNKNOWN, 0.0, t, (unsigned)(g * 2), flag2, shift, val);
-#pragma unroll
-									for (int side = 0; side < 2; side++)  // :5560-5568
-#pragma unroll
-										for (int al = 0; al < 2; al++)
-											track<U_GENOS, 4>(c, 0, al + 1, 0.0, t, (unsigned)(g * 2 + side), flag2 ^ side, shift,
-											                  val * sv[side][al] / svs[side]);
-#pragma unroll
-									for (int al = 0; al < 2; al++)  // :5571-5575
-										c.acc[(ACC_HZ + al) * NTHREADS] += val * hz[al] / svs[0];
-								}
+								cnt -= 32;
+								const int entry = q[cnt + lane];
+								__syncwarp();
+								posterior_term(c, t, entry & 63, entry >> 6, shift, src[entry & 63], sm.beta[shift * NUMTYPES + (entry & 63)],
+								               Fm, B, factor, minfactor);
 							}
-							if (flag2 == 0) break;
 						}
+						if (flag2 == 0) break;
 					}
+					if (lane < cnt)
+					{
+						const int entry = q[lane];
+						posterior_term(c, t, entry & 63, entry >> 6, shift, src[entry & 63], sm.beta[shift * NUMTYPES + (entry & 63)], Fm,
+						               B, factor, minfactor);
+					}
+					__syncwarp();
 				}
 				__syncthreads();
 				// block-level reduction of the accumulator columns; the reader clears what it read
@@ -325,52 +408,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) estep_kernel(EstepArgs a)
 				}
 				__syncthreads();
 				// transfer into the EM sufficient statistics (:5875-5904, moveinfprobs :3577-3597, movehaplos :3599-3616)
-				if (tid < u.nrel)
-				{
-					const int r = tid;
-					const int rootrel = u.slotrel[0];
-					double rootsum = 0, h0 = 0, h1 = 0, ip[4] = { 0, 0, 0, 0 };
-					for (int slot = 0; slot < NSLOTS; slot++)
-					{
-						if (u.row[slot] < 0) continue;
-						const int rel = u.slotrel[slot];
-						if (rel == rootrel) rootsum += sm.tot[ACC_INF + slot * 4 + 0] + sm.tot[ACC_INF + slot * 4 + 1];
-						if (rel == r)
-						{
-							h0 += sm.tot[ACC_HAPLOS + slot * 2 + 0];
-							h1 += sm.tot[ACC_HAPLOS + slot * 2 + 1];
-							for (int q = 0; q < 4; q++) ip[q] += sm.tot[ACC_INF + slot * 4 + q];
-						}
-					}
-					const double sum = 1.0 / rootsum;
-					const int srow = u.relrow[r];
-					const StatsCell cell = srow < a.n_shared ? stats_cell(a.stats_shared, a.n_shared, Mc, srow, m)
-					                                         : stats_cell(a.stats_local, a.n_local, Mc, srow - a.n_shared, m);
-					double norm = sum * 2;
-					for (int k = 0; k < u.relhalvings[r]; k++) norm /= 2;
-					norm *= u.descendants;
-					for (int q = 0; q < 4; q++)
-						if (ip[q] != 0) atomicAdd(cell.infprobs + q, ip[q] * norm);
-					if (h0 != 0 || h1 != 0)
-					{
-						// the relative's own haploweight at this marker; any of its slots holds it
-						int slot = 0;
-						while (u.slotrel[slot] != r || u.row[slot] < 0) slot++;
-						const double w = sm.HW[slot * TILE + t];
-						if (fabs(w - 0.5) < 0.5 - 1e-12)
-						{
-							const double eps = exp(-400.0) * (double)(0.000005f) * (double)(0.000005f) * 0.5;  // maxdiff, :228
-							const double x1 = h0 + eps, x2 = h1 + eps;
-							atomicAdd(cell.haplobase, x1 / (x1 + x2) * u.descendants);
-							atomicAdd(cell.haplocount, u.descendants);
-						}
-					}
-					if (r == rootrel)
-					{
-						atomicAdd(cell.homozyg + 0, sm.tot[ACC_HZ + 0] * sum);
-						atomicAdd(cell.homozyg + 1, sm.tot[ACC_HZ + 1] * sum);
-					}
-				}
+				if (tid < u.nrel) transfer_stats(a, u, sm.tot, sm.HW, tid, t, m);
 				// beta for the previous marker: adjustprobs at m, then the transition (:2390-2396)
 				if (active && m > 0)
 				{
