@@ -131,16 +131,23 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+            self.rows.append((time.perf_counter(), [x.strip() for x in line.split(",")]))
 
-    def stop(self):
+    def wait_ready(self, timeout=20.0):
+        """nvidia-smi's start-up can stall the driver for seconds: wait for its first sample before timing."""
+        t0 = time.perf_counter()
+        while self.proc and not self.rows and time.perf_counter() - t0 < timeout:
+            time.sleep(0.05)
+
+    def stop(self, t_from=None, t_to=None):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
         self.thread.join(timeout=2)
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        inside = [r for ts, r in self.rows if (t_from is None or ts >= t_from) and (t_to is None or ts <= t_to + 0.25)]
+        for r in (inside or [r for _, r in self.rows]):
             if len(r) < 7:
                 continue
             try:
@@ -239,10 +246,13 @@ def ours(a, rank, world, local_rank):
     d2h = n_rows * M * 64 + len(d["dous"]) * C * 16
 
     # ---- value: inputs resident in HBM, CUDA events on the launching stream ----
+    sampler = ClockSampler(local_rank) if rank == 0 else None
     for _ in range(a.warmup):
         resident_step()
+    if sampler:
+        sampler.wait_ready()
     barrier()
-    sampler = ClockSampler(local_rank) if rank == 0 else None
+    t_from = time.perf_counter()
     eng.mark(0)
     kernel_ms = []
     for _ in range(a.steps):
@@ -250,7 +260,7 @@ def ours(a, rank, world, local_rank):
     eng.mark(1)
     barrier()
     step_ms = maxranks(eng.elapsed_ms(0, 1)) / a.steps
-    clocks = sampler.stop() if sampler else None
+    clocks = sampler.stop(t_from, time.perf_counter()) if sampler else None
     # per-launch duration of the dominant kernel (CUDA events around each launch, engine stream)
     for c in range(C):
         eng.estep(c)

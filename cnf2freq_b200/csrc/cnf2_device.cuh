@@ -275,3 +275,153 @@ __device__ __forceinline__ RootLocal root_local(uchar2 a, double2 s, double hw, 
 	return r;
 }
 }  // namespace cnf2
+
+namespace cnf2
+{
+// Per (slot, marker) constants of the emission routine, computed once when a tile is staged so that the
+// per-call path of the table-driven kernel has no division: for allele position j of the individual
+//   S    markersure                                  (cnF2freq.cpp:878)
+//   RM   (1 - S) / S      : main2 / base after a mismatch, per unit of incoming `second`   (:1200-1201, 1220)
+//   RN   effS / (1 - S)   : main2 / base after a match, effS = 1 for an unknown allele     (:1205-1209, 1220)
+//   SEC  S / (1 - S) or 0 : `secondval` handed up with the other allele                    (:1298-1302)
+//   W    phase weight for effective phase bit j: j ? 1 : 0 when homozygous with equal sureness (:1235-1238),
+//        |j - haploweight| otherwise (:1245)
+struct NodeTab
+{
+	double S[2], RM[2], RN[2], SEC[2], W[2];
+};
+
+__device__ __forceinline__ NodeTab make_nodetab(uchar2 a, double2 s, double hw)
+{
+	NodeTab n;
+	n.S[0] = s.x;
+	n.S[1] = s.y;
+	n.RM[0] = s.x != 0 ? (1.0 - s.x) / s.x : 0.0;
+	n.RM[1] = s.y != 0 ? (1.0 - s.y) / s.y : 0.0;
+	n.RN[0] = (a.x == UNKNOWN ? 1.0 : s.x) / (1.0 - s.x);
+	n.RN[1] = (a.y == UNKNOWN ? 1.0 : s.y) / (1.0 - s.y);
+	n.SEC[0] = s.x != 0 ? s.x / (1.0 - s.x) : 0.0;
+	n.SEC[1] = s.y != 0 ? s.y / (1.0 - s.y) : 0.0;
+	const bool hom = a.x == a.y && s.x == s.y;
+	n.W[0] = hom ? 0.0 : fabs(0.0 - hw);
+	n.W[1] = hom ? 1.0 : fabs(1.0 - hw);
+	return n;
+}
+
+// Shared-memory view of the table-driven kernel.
+struct FCtx
+{
+	const uchar2* A;       // [NSLOTS][TILE]
+	const NodeTab* N;      // [NSLOTS][TILE]
+	const int32_t* row;    // [NSLOTS]
+	const uint8_t* founder;
+};
+
+// trackpossible<0, 0> (cnF2freq.cpp:1075-1359) below the root, on the node constants: the value
+// recursetrackpossible returns for the subtree rooted at `slot` (genwidth GW = 2 parents, 1 grandparents).
+template <int GW>
+__device__ __forceinline__ double ftrack(const FCtx& c, int slot, int inval, double second, int t, int flag, int flag99,
+                                         int localshift)
+{
+	const bool attop = GW == 1 || c.founder[slot];
+	const uchar2 a = c.A[slot * TILE + t];
+	const NodeTab& n = c.N[slot * TILE + t];
+	const int firstpar = flag & 1;
+	int f2s = 0, f2end = 2;
+	if (flag99 != -1)
+	{
+		f2s = flag99 & 1;
+		f2end = f2s + 1;
+	}
+	double ok = 0;
+	for (int f2 = f2s; f2 < f2end; f2++)
+	{
+		const int Af = f2 ? a.y : a.x;
+		const double Sf = n.S[f2];
+		int val = inval;
+		bool miss;
+		if (val == UNKNOWN)
+		{
+			val = Af;
+			miss = false;
+		}
+		else if (Af == UNKNOWN && val != SEXMARKER) miss = false;
+		else miss = val != Af;
+		double base, up2;  // up2: the `second` handed to parent firstpar (main2 / base)
+		if (miss)
+		{
+			const bool on = Sf != 0 && second != 0;
+			base = attop ? (on ? Sf + (1.0 - Sf) * second : Sf) : Sf;
+			up2 = on ? n.RM[f2] * second : 0.0;
+		}
+		else
+		{
+			const double eff2 = (inval == UNKNOWN && val != UNKNOWN) ? 1.0 : second;
+			base = 1.0 - Sf;
+			if (attop) base += (Af == UNKNOWN ? 1.0 : Sf) * eff2;
+			up2 = n.RN[f2] * eff2;
+		}
+		base *= n.W[(f2 ^ firstpar ^ localshift) & 1];
+		if constexpr (GW > 1)
+		{
+			if (!attop && base != 0)
+			{
+				const int o = f2 ^ 1;
+				const int c0 = slot + 1, upflag = flag >> 1, upflag2 = flag99 < 0 ? -1 : flag99 >> 1;
+				if (n.S[o] != 0) base *= 1.0 - n.S[o];
+				// other allele to parent !firstpar, matched allele to parent firstpar (:1322-1340)
+				const int po = firstpar ^ 1;
+				const int cho = c0 + po, chf = c0 + firstpar;
+				base *= c.row[cho] < 0 ? 1.0 + n.SEC[o]
+				                       : ftrack<1>(c, cho, o ? a.y : a.x, n.SEC[o], t, (upflag >> po) & 1,
+				                                   upflag2 < 0 ? -1 : (upflag2 >> po) & 1, 0);
+				if (base != 0)
+					base *= c.row[chf] < 0 ? 1.0 + up2
+					                       : ftrack<1>(c, chf, val, up2, t, (upflag >> firstpar) & 1,
+					                                   upflag2 < 0 ? -1 : (upflag2 >> firstpar) & 1, 0);
+			}
+		}
+		ok += base;
+	}
+	return ok;
+}
+
+// Root-level factor and messages (see RootLocal) from the node constants; kind: 0 plain emission,
+// 1 GENOSPROBE (inval = allele), 2 HOMOZYGOUS (inval = allele).  The incoming `second` is 0 at the root, so
+// only the plain emission hands a non-zero `second` (RN) to parent firstpar.
+__device__ __forceinline__ RootLocal froot(uchar2 a, const NodeTab& n, int kind, int inval, int firstpar, int f2,
+                                           int localshift)
+{
+	RootLocal r;
+	const int Af = f2 ? a.y : a.x, Ao = f2 ? a.x : a.y;
+	const double Sf = n.S[f2], So = n.S[f2 ^ 1];
+	int val = inval;
+	bool miss;
+	if (val == UNKNOWN)
+	{
+		val = Af;
+		miss = false;
+	}
+	else if (Af == UNKNOWN && val != SEXMARKER) miss = false;
+	else miss = val != Af;
+	double base = miss ? Sf : 1.0 - Sf;
+	r.main2 = (!miss && inval == UNKNOWN && val != UNKNOWN) ? n.RN[f2] : 0.0;
+	base *= n.W[(f2 ^ firstpar ^ localshift) & 1];
+	r.sec2 = 0;
+	r.secmark = Ao;
+	if (kind != 2)
+	{
+		if (So != 0) base *= 1.0 - So;
+		r.sec2 = n.SEC[f2 ^ 1];
+	}
+	else if (val != Ao)
+	{
+		if (Ao != UNKNOWN) base *= So;
+		r.secmark = val;
+	}
+	else base *= 1.0 - So;
+	r.base = base;
+	r.val = val;
+	return r;
+}
+}  // namespace cnf2

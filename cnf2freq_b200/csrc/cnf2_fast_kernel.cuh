@@ -47,6 +47,7 @@ struct __align__(16) FastSmem
 {
 	double acc[NACC * NTHREADS];
 	FastWarp w[NUMSHIFTS];
+	NodeTab N[NSLOTS * TILE];
 	double2 S[NSLOTS * TILE];
 	double HW[NSLOTS * TILE];
 	double tot[NACC];
@@ -65,11 +66,11 @@ struct FastArgs
 };
 
 // value recursetrackpossible returns for parent p's subtree (cnF2freq.cpp:955-1058)
-__device__ __forceinline__ double subtree(const Ctx& c, int p, int inval, double second, int t, int fp3, int f23, int shift)
+__device__ __forceinline__ double subtree(const FCtx& c, int p, int inval, double second, int t, int fp3, int f23, int shift)
 {
 	const int sp = 1 + 3 * p;
 	if (c.row[sp] < 0) return 1.0 + second;
-	return track<0, 2>(c, sp, inval, second, t, (unsigned)fp3, f23, (shift >> (1 + p)) & 1, 0.0);
+	return ftrack<2>(c, sp, inval, second, t, fp3, f23, (shift >> (1 + p)) & 1);
 }
 
 // emission with all orientations summed for the two states of this lane, from the 32 subtree values
@@ -86,10 +87,10 @@ __device__ __forceinline__ void combine_q(double q, double rb, int lane, double&
 }
 
 // the lane's item of the sweep emission: root factor of its root orientation and one subtree value
-__device__ __forceinline__ void sweep_item(const Ctx& c, int t, int lane, int shift, double& q, double& rb)
+__device__ __forceinline__ void sweep_item(const FCtx& c, int t, int lane, int shift, double& q, double& rb)
 {
 	const int f = lane >> 4, p = (lane >> 3) & 1, fp3 = lane & 7;
-	const RootLocal r = root_local<0>(c.A[t], c.S[t], c.HW[t], UNKNOWN, 0, f, shift & 1);
+	const RootLocal r = froot(c.A[t], c.N[t], 0, UNKNOWN, 0, f, shift & 1);
 	rb = r.base;
 	q = p ? subtree(c, 1, r.secmark, r.sec2, t, fp3, -1, shift) : subtree(c, 0, r.val, r.main2, t, fp3, -1, shift);
 }
@@ -132,13 +133,14 @@ __device__ __forceinline__ bool load_tile_checked(FastSmem& sm, const EstepArgs&
 		sm.A[i] = al;
 		sm.S[i] = su;
 		sm.HW[i] = h;
+		sm.N[i] = make_nodetab(al, su, h);
 	}
 	return __syncthreads_or(bad) != 0;
 }
 
 // Posterior of one (marker, shift): tables, dense term enumeration, scatter into the accumulator columns.
-__device__ __forceinline__ void fast_posterior(FastSmem& sm, FastWarp& w, const Ctx& c, const Unit& u, int t, int lane,
-                                               int shift, const double* __restrict__ alpha_m, double scale)
+__device__ __forceinline__ void fast_posterior(FastSmem& sm, FastWarp& w, const FCtx& c, double* acc, const Unit& u, int t,
+                                               int lane, int shift, const double* __restrict__ alpha_m, double scale)
 {
 	const unsigned FULL = 0xffffffffu;
 	// ---- per-marker masks: relatives / slots that are homozygous with equal sureness (:1235, :3488) ----
@@ -159,14 +161,13 @@ __device__ __forceinline__ void fast_posterior(FastSmem& sm, FastWarp& w, const 
 	{
 		const int f = lane / NKIND, kind = lane % NKIND;
 		const uchar2 a0 = sm.A[t];
-		const double2 s0 = sm.S[t];
-		const double h0 = sm.HW[t];
+		const NodeTab& n0 = sm.N[t];
 		const int al = 1 + ((kind - 1) & 1);  // kinds 1,3,5 probe allele 1; kinds 2,4,6 allele 2
 		RootLocal r;
-		if (kind == 0) r = root_local<0>(a0, s0, h0, UNKNOWN, 0, f, shift & 1);
-		else if (kind <= 2) r = root_local<U_GENOSPROBE>(a0, s0, h0, al, 0, f, shift & 1);
-		else if (kind <= 4) r = root_local<U_GENOSPROBE>(a0, s0, h0, al, 1, f ^ 1, shift & 1);
-		else r = root_local<U_HOMOZYGOUS>(a0, s0, h0, al, 0, f, shift & 1);
+		if (kind == 0) r = froot(a0, n0, 0, UNKNOWN, 0, f, shift & 1);
+		else if (kind <= 2) r = froot(a0, n0, 1, al, 0, f, shift & 1);
+		else if (kind <= 4) r = froot(a0, n0, 1, al, 1, f ^ 1, shift & 1);
+		else r = froot(a0, n0, 2, al, 0, f, shift & 1);
 		w.rbase[lane] = r.base;
 		if (kind == 0)
 		{
@@ -246,7 +247,6 @@ __device__ __forceinline__ void fast_posterior(FastSmem& sm, FastWarp& w, const 
 	// ---- terms ----
 	const int smask = (shift & 1) | ((shift & 2) ? 2 : 0) | ((shift & 4) ? 16 : 0);  // shift bit of slots 0, 1, 4
 	const int vis = u.vismask, hmask = vis & ~homslot;
-	double* const acc = c.acc;
 	for (int i = lane; i < T; i += 32)
 	{
 		const int x = w.xlist[i >> nfree];
@@ -312,7 +312,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) fast_estep_kernel(FastArgs fa)
 	double* const alpha = a.alpha + (size_t)blockIdx.x * Mc * (NUMSHIFTS * NUMTYPES);
 	double* const alphafac = a.alphafac + (size_t)blockIdx.x * Mc * NUMSHIFTS;
 	double* const qs = fa.qscratch + (size_t)blockIdx.x * Mc * (NUMSHIFTS * 32);
-	Ctx c{ sm.A, sm.S, sm.HW, sm.unit.row, sm.unit.founder, sm.acc + tid };
+	FCtx c{ sm.A, sm.N, sm.unit.row, sm.unit.founder };
+	double* const acc = sm.acc + tid;
 	FastWarp& w = sm.w[shift];
 
 	for (int i = tid; i < NACC * NTHREADS; i += NTHREADS) sm.acc[i] = 0;
@@ -409,7 +410,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) fast_estep_kernel(FastArgs fa)
 						w.beta[lane] = b0;
 						w.beta[lane + 32] = b1;
 						__syncwarp();
-						fast_posterior(sm, w, c, u, t, lane, shift, alpha + ((size_t)m * NUMSHIFTS + shift) * NUMTYPES, exp(lscale));
+						fast_posterior(sm, w, c, acc, u, t, lane, shift, alpha + ((size_t)m * NUMSHIFTS + shift) * NUMTYPES, exp(lscale));
 					}
 				}
 				__syncthreads();
@@ -431,7 +432,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) fast_estep_kernel(FastArgs fa)
 				if (active && m > 0)
 				{
 					const double q = qs[((size_t)m * NUMSHIFTS + shift) * 32 + lane];
-					const RootLocal r = root_local<0>(sm.A[t], sm.S[t], sm.HW[t], UNKNOWN, 0, lane >> 4, shift & 1);
+					const RootLocal r = froot(sm.A[t], sm.N[t], 0, UNKNOWN, 0, lane >> 4, shift & 1);
 					double e0, e1;
 					combine_q(q, r.base, lane, e0, e1);
 					apply_emission(e0, e1, b0, b1, B);
