@@ -52,6 +52,11 @@ struct Unit
 	uint8_t pad0;
 	uint8_t expand[NUMTYPES];    // j -> j deposited into the free state bits
 	uint8_t pad1[4];
+	// batched kernel (cnf2_batch_kernel.cuh): x = flag2 ^ (g << 1) values passing rule 2 of ignoreflag2
+	// (bit x of xmask2), and the local configurations (3 meiosis bits | 3 orientation bits << 3) of the two
+	// parents' subtrees that some surviving (x, g) pair uses (bit cfg of cfgmask[p])
+	uint32_t xmask2[4];
+	unsigned long long cfgmask[2];
 };
 
 // Shared-memory view handed to the emission routine.

@@ -3,6 +3,7 @@
 // every entry point that would compute needs the CUDA device.
 #include "../../include/cnf2_engine.h"
 #include "cnf2_fast_kernel.cuh"
+#include "cnf2_batch_kernel.cuh"
 
 #include <algorithm>
 #include <cmath>
@@ -76,7 +77,10 @@ struct cnf2_engine
 	DevBuf<uchar2> d_alleles;
 	DevBuf<double2> d_sure;
 	DevBuf<double> d_hw, d_rec, d_alpha, d_alphafac, d_q, d_stats, d_loglik;
-	DevBuf<int32_t> d_literal;
+	DevBuf<int32_t> d_literal, d_kexp;
+	DevBuf<double> d_qstash;
+	int n_ctas_batch = 0;
+	bool use_fast = false;  // A-B switch: CNF2_KERNEL=fast runs the older table-driven kernel instead of the batched one
 	int n_ctas_literal = 0;
 	bool literal_only = false;  // debugging / A-B switch: CNF2_LITERAL=1 runs every unit through the literal kernel
 	DevBuf<Unit> d_units;
@@ -187,6 +191,11 @@ extern "C" int cnf2_create(cnf2_engine** out, const cnf2_settings* settings)
 	if (per_sm < 1) per_sm = 1;
 	if (settings->ctas_per_sm > 0) per_sm = std::min(per_sm, settings->ctas_per_sm);
 	e->n_ctas = per_sm * e->n_sm;
+	if ((ce = cudaFuncSetAttribute(batch_estep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BatchSmem))) != cudaSuccess)
+		return bail(ce, "cudaFuncSetAttribute(batch_estep_kernel)");
+	e->n_ctas_batch = e->n_sm;  // one CTA per SM: the batched kernel uses nearly all of the SM's shared memory
+	const char* kn = getenv("CNF2_KERNEL");
+	e->use_fast = kn && std::string(kn) == "fast";
 	const char* lit = getenv("CNF2_LITERAL");
 	e->literal_only = lit && lit[0] == '1';
 	*out = e;
@@ -205,6 +214,8 @@ extern "C" void cnf2_destroy(cnf2_engine* e)
 	e->d_alpha.release();
 	e->d_alphafac.release();
 	e->d_q.release();
+	e->d_kexp.release();
+	e->d_qstash.release();
 	e->d_literal.release();
 	e->d_stats.release();
 	e->d_loglik.release();
@@ -443,6 +454,25 @@ extern "C" int cnf2_set_pedigree(cnf2_engine* e, int32_t n_ind, const int32_t* p
 				if (ordered[k] == rel[r]) halvings++;
 			u.relhalvings[r] = (uint8_t)halvings;
 		}
+		// batched kernel: x values passing rule 2 of ignoreflag2 (:3483-3486) and the subtree configurations in use
+		for (int x = 0; x < NUMPATHS; x++)
+		{
+			bool ok = true;
+			for (int r = 0; r < u.nrel; r++)
+			{
+				const int filt = u.relfilter[r], filtered = x & filt;
+				if (filt && filtered && filtered != filt) ok = false;
+			}
+			if (!ok) continue;
+			u.xmask2[x >> 5] |= 1u << (x & 31);
+			for (int jx = 0; jx < (1 << u.nfree); jx++)
+			{
+				const int g = ((x >> 1) & u.gfixmask) | u.expand[jx];
+				const int flag2 = x ^ (g << 1);
+				u.cfgmask[0] |= 1ull << ((g & 7) | (((flag2 >> 1) & 7) << 3));
+				u.cfgmask[1] |= 1ull << (((g >> 3) & 7) | (((flag2 >> 4) & 7) << 3));
+			}
+		}
 	}
 	CU(e->d_units.ensure(e->units.size()));
 	if (!e->units.empty())
@@ -510,10 +540,12 @@ extern "C" int cnf2_estep(cnf2_engine* e, int32_t chrom)
 	cudaSetDevice(e->settings.device);
 	const int Mc = e->mc(chrom);
 	const int n_units = (int)e->units.size();
-	const int n_ctas = std::max(1, std::min(std::max(e->n_ctas, e->n_ctas_literal), n_units));
+	const int n_ctas = std::max(1, std::min(std::max(std::max(e->n_ctas, e->n_ctas_batch), e->n_ctas_literal), n_units));
 	CU(e->d_alpha.ensure((size_t)n_ctas * e->max_mc * NUMSHIFTS * NUMTYPES));
 	CU(e->d_alphafac.ensure((size_t)n_ctas * e->max_mc * NUMSHIFTS));
-	CU(e->d_q.ensure((size_t)n_ctas * e->max_mc * NUMSHIFTS * 32));
+	if (e->use_fast) CU(e->d_q.ensure((size_t)n_ctas * e->max_mc * NUMSHIFTS * 32));
+	CU(e->d_kexp.ensure((size_t)n_ctas * e->max_mc * NUMSHIFTS));
+	CU(e->d_qstash.ensure((size_t)n_ctas * e->max_mc * QS));
 	CU(e->d_stats.ensure((size_t)e->n_rows * e->max_mc * STATS_PER_CELL));
 	CU(cudaEventRecord(e->ev0, e->stream));
 	CU(cudaMemsetAsync(e->d_stats.p, 0, (size_t)e->n_rows * Mc * STATS_PER_CELL * sizeof(double), e->stream));
@@ -546,7 +578,23 @@ extern "C" int cnf2_estep(cnf2_engine* e, int32_t chrom)
 		fa.qscratch = e->d_q.p;
 		fa.literal_units = e->d_literal.p;
 		fa.literal_count = e->d_counter.p + 1;
-		if (!e->literal_only)
+		if (!e->literal_only && !e->use_fast)
+		{
+			// batched kernel; units it cannot take (founder roots, out-of-range parameters) are listed for the literal one
+			BatchArgs bargs{};
+			bargs.e = a;
+			bargs.kexp = e->d_kexp.p;
+			bargs.qstash = e->d_qstash.p;
+			bargs.literal_units = e->d_literal.p;
+			bargs.literal_count = e->d_counter.p + 1;
+			batch_estep_kernel<<<std::max(1, std::min(e->n_ctas_batch, n_units)), NTHREADS, sizeof(BatchSmem), e->stream>>>(bargs);
+			CU(cudaGetLastError());
+			e->last_launches++;
+			a.unit_list = e->d_literal.p;
+			a.list_count = e->d_counter.p + 1;
+			a.counter = e->d_counter.p + 2;
+		}
+		else if (!e->literal_only)
 		{
 			// table-driven kernel; units it cannot take (founder roots, out-of-range parameters) are listed for the literal one
 			fast_estep_kernel<<<std::max(1, std::min(e->n_ctas, n_units)), NTHREADS, sizeof(FastSmem), e->stream>>>(fa);

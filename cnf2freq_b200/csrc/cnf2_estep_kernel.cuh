@@ -145,7 +145,7 @@ __device__ __forceinline__ bool ignored(const Unit& u, int hom, int flag2, int g
 // Transfer of one marker's reduced accumulators into the EM sufficient statistics, for relative r of the
 // unit (cnF2freq.cpp:5875-5904, moveinfprobs :3577-3597, movehaplos :3599-3616).
 __device__ __forceinline__ void transfer_stats(const EstepArgs& a, const Unit& u, const double* tot, const double* HW,
-                                               int r, int t, int m)
+                                               int r, int t, int m, int hwstride = TILE)
 {
 	const int Mc = a.Mc;
 	const int rootrel = u.slotrel[0];
@@ -176,7 +176,7 @@ __device__ __forceinline__ void transfer_stats(const EstepArgs& a, const Unit& u
 		// the relative's own haploweight at this marker; any of its slots holds it
 		int slot = 0;
 		while (u.slotrel[slot] != r || u.row[slot] < 0) slot++;
-		const double w = HW[slot * TILE + t];
+		const double w = HW[slot * hwstride + t];
 		if (fabs(w - 0.5) < 0.5 - 1e-12)
 		{
 			const double eps = exp(-400.0) * (double)(0.000005f) * (double)(0.000005f) * 0.5;  // maxdiff, :228
