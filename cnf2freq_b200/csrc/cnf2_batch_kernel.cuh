@@ -27,7 +27,8 @@
 
 namespace cnf2
 {
-constexpr int TB = 8;    // markers per backward batch (one warp each in the posterior phase)
+constexpr int TB = 4;    // markers per backward batch (one warp each in the posterior phase)
+constexpr int ACCS = TB * 32;  // accumulator columns: one per lane of the posterior warps
 constexpr int TF = 32;   // markers per forward tile
 constexpr int QS = 68;   // sweep-emission table per marker: Q[p][s_p][g_p][f] (64) + R[s0][f] (4)
 constexpr int RC = 16;   // root constants per marker
@@ -37,13 +38,13 @@ constexpr double EXP_M200_B = 1.3838965267367376e-87;  // exp(-200): unusualstat
 
 struct BwdSmem
 {
-	double acc[NACC * NTHREADS];
+	double acc[NACC * ACCS];
 	double Wt[TB * NUMSHIFTS * NUMTYPES];
 	double tab[TB * 2 * 2 * 64 * TABW];  // [marker][parent][f][cfg][TABW]
 	double qh[TB * QS];
 	NodeTab nt[NSLOTS * TB];
 	double HW[NSLOTS * TB];
-	double tot[NUMSHIFTS * NACC];
+	double tot[TB * NACC];
 	double rootc[TB * RC];
 	uchar2 A[NSLOTS * TB];
 	unsigned char xl[TB * NUMPATHS];
@@ -126,7 +127,7 @@ __device__ __forceinline__ PMsg pmsg(uchar2 a, const NodeTab& n, int o, int v, d
 // Scale (p0, p1) of the whole warp by the power of two that brings the largest entry into [1, 2).
 __device__ __forceinline__ void rescale(double& p0, double& p1, int& k)
 {
-	const int e = (__double2hiint(fmax(p0, p1)) >> 20) & 0x7ff;
+	const int e = max(__double2hiint(p0), __double2hiint(p1)) >> 20;  // non-negative doubles order like their high words
 	const int w = __reduce_max_sync(0xffffffffu, e);
 	if (w == 0) return;  // all zero
 	const double sc = __hiloint2double((2046 - w) << 20, 0);
@@ -402,22 +403,22 @@ __device__ __forceinline__ void batch_posterior(BwdSmem& b, const Unit& u, int t
 		// updatehaplo (:1561-1575): visited, non-homozygous slots at their effective phase bit x_k ^ s_k
 		if (hmask & 1)
 		{
-			acc[(ACC_HAPLOS + f) * NTHREADS] += (ts[0] + ts[2]) + (ts[4] + ts[6]);        // s0 = 0: bit f
-			acc[(ACC_HAPLOS + (f ^ 1)) * NTHREADS] += (ts[1] + ts[3]) + (ts[5] + ts[7]);  // s0 = 1
+			acc[(ACC_HAPLOS + f) * ACCS] += (ts[0] + ts[2]) + (ts[4] + ts[6]);        // s0 = 0: bit f
+			acc[(ACC_HAPLOS + (f ^ 1)) * ACCS] += (ts[1] + ts[3]) + (ts[5] + ts[7]);  // s0 = 1
 		}
 		if (hmask & 2)
 		{
-			acc[(ACC_HAPLOS + 2 + x1) * NTHREADS] += p01 + p45;
-			acc[(ACC_HAPLOS + 2 + (x1 ^ 1)) * NTHREADS] += p23 + p67;
+			acc[(ACC_HAPLOS + 2 + x1) * ACCS] += p01 + p45;
+			acc[(ACC_HAPLOS + 2 + (x1 ^ 1)) * ACCS] += p23 + p67;
 		}
 		if (hmask & 16)
 		{
-			acc[(ACC_HAPLOS + 8 + x4) * NTHREADS] += p01 + p23;
-			acc[(ACC_HAPLOS + 8 + (x4 ^ 1)) * NTHREADS] += p45 + p67;
+			acc[(ACC_HAPLOS + 8 + x4) * ACCS] += p01 + p23;
+			acc[(ACC_HAPLOS + 8 + (x4 ^ 1)) * ACCS] += p45 + p67;
 		}
 #pragma unroll
 		for (int k = 2; k < NSLOTS; k++)
-			if (k != 4 && ((hmask >> k) & 1)) acc[(ACC_HAPLOS + k * 2 + ((x >> k) & 1)) * NTHREADS] += V;
+			if (k != 4 && ((hmask >> k) & 1)) acc[(ACC_HAPLOS + k * 2 + ((x >> k) & 1)) * ACCS] += V;
 		// the four GENOS calls (:5560-5568): root, parent `side`, that parent's parent picked by its meiosis bit
 #pragma unroll
 		for (int side = 0; side < 2; side++)
@@ -425,24 +426,24 @@ __device__ __forceinline__ void batch_posterior(BwdSmem& b, const Unit& u, int t
 			const double* Ts = side ? T1 : T0;
 			const double u0 = V * Ts[1], u1 = V * Ts[2];
 			const int sp = 1 + 3 * side, gs = sp + 1 + ((g >> (3 * side)) & 1);
-			double* a0 = acc + (ACC_INF + (f ^ side) * 2) * NTHREADS;
+			double* a0 = acc + (ACC_INF + (f ^ side) * 2) * ACCS;
 			a0[0] += u0;
-			a0[NTHREADS] += u1;
+			a0[ACCS] += u1;
 			if ((vis >> sp) & 1)
 			{
-				double* ap = acc + (ACC_INF + (sp * 2 + ((flag2 >> sp) & 1)) * 2) * NTHREADS;
+				double* ap = acc + (ACC_INF + (sp * 2 + ((flag2 >> sp) & 1)) * 2) * ACCS;
 				ap[0] += u0;
-				ap[NTHREADS] += u1;
+				ap[ACCS] += u1;
 				if ((vis >> gs) & 1)
 				{
-					double* ag = acc + (ACC_INF + (gs * 2 + ((flag2 >> gs) & 1)) * 2) * NTHREADS;
+					double* ag = acc + (ACC_INF + (gs * 2 + ((flag2 >> gs) & 1)) * 2) * ACCS;
 					ag[0] += u0;
-					ag[NTHREADS] += u1;
+					ag[ACCS] += u1;
 				}
 			}
 		}
-		acc[(ACC_HZ + 0) * NTHREADS] += V * T0[3] * T1[3];  // :5571-5575
-		acc[(ACC_HZ + 1) * NTHREADS] += V * T0[4] * T1[4];
+		acc[(ACC_HZ + 0) * ACCS] += V * T0[3] * T1[3];  // :5571-5575
+		acc[(ACC_HZ + 1) * ACCS] += V * T0[4] * T1[4];
 	}
 }
 
@@ -502,7 +503,7 @@ __device__ __forceinline__ void batch_prepare(BwdSmem& b, const Unit& u, int t, 
 	__syncwarp();
 }
 
-__global__ void __launch_bounds__(NTHREADS, 1) batch_estep_kernel(BatchArgs ba)
+__global__ void __launch_bounds__(NTHREADS, 2) batch_estep_kernel(BatchArgs ba)
 {
 	extern __shared__ __align__(16) unsigned char smem_raw[];
 	BatchSmem& sm = *reinterpret_cast<BatchSmem*>(smem_raw);
@@ -515,7 +516,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) batch_estep_kernel(BatchArgs ba)
 	double* const qs = ba.qstash + (size_t)blockIdx.x * Mc * QS;
 	constexpr int FWD_DOUBLES = (int)((sizeof(FwdSmem) + 7) / 8);
 
-	for (int i = tid; i < NACC * NTHREADS; i += NTHREADS) b.acc[i] = 0;
+	for (int i = tid; i < NACC * ACCS; i += NTHREADS) b.acc[i] = 0;
 
 	for (;;)
 	{
@@ -567,7 +568,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) batch_estep_kernel(BatchArgs ba)
 			}
 		}
 		__syncthreads();
-		for (int i = tid; i < FWD_DOUBLES; i += NTHREADS) b.acc[i] = 0;  // the forward tile aliases the accumulators
+		for (int i = tid; i < min(FWD_DOUBLES, NACC * ACCS); i += NTHREADS) b.acc[i] = 0;  // the forward tile aliases the accumulators
 		if (literal)
 		{
 			if (tid == 0) ba.literal_units[atomicAdd(ba.literal_count, 1u)] = ui;
@@ -596,6 +597,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) batch_estep_kernel(BatchArgs ba)
 		if (isnan(factor) || factor < MINFACTOR_D) continue;  // :5403
 		const bool contributing = active && !(factor - L > 40);  // :5421
 		const double minfactor = (double)(float)(-200.0 + factor);  // unusualstate + factor as a float, :1936
+		// exp(k ln 2 - factor) = 2^(k + kf) * exp(frem) with -factor = kf ln 2 + frem: one exp per unit
+		const int kf = (int)rint(-factor / LN2);
+		const double efrem = exp(-factor - (double)kf * LN2);
 
 		// ---- backward sweep (:2109-2116) in batches of TB markers, each followed by its posterior phase ----
 		double b0 = 1.0, b1 = 1.0;  // :2111-2114
@@ -632,10 +636,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) batch_estep_kernel(BatchArgs ba)
 				if (contributing)
 				{
 					// val = exp(F- + log(alpha e) + B + log beta - factor) (:1963-2018, :5499-5508); the factors are k ln 2 here
-					const double lscale = (double)(kar[t] + kb) * LN2 - factor;
-					if (!((double)kar[t] * LN2 + 5.0 < minfactor) && lscale > -600.0 && lscale < 600.0)
+					const int ke = kar[t] + kb + kf;
+					if (!((double)kar[t] * LN2 + 5.0 < minfactor) && ke > -860 && ke < 860)  // |F + B - factor| < 600 in the literal kernel
 					{
-						const double sc = exp(lscale);
+						const double sc = __hiloint2double((1023 + ke) << 20, 0) * efrem;
 						w0 = a0r[t] * b0 * sc;
 						w1 = a1r[t] * b1 * sc;
 					}
@@ -661,7 +665,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) batch_estep_kernel(BatchArgs ba)
 				// the warp reduces its own 32 accumulator columns; the reader clears what it read
 				for (int k = lane; k < NACC; k += 32)
 				{
-					double* col = b.acc + k * NTHREADS + warp * 32;
+					double* col = b.acc + k * ACCS + warp * 32;
 					double v = 0;
 #pragma unroll 8
 					for (int j = 0; j < 32; j++)

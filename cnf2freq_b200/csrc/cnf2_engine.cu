@@ -193,7 +193,11 @@ extern "C" int cnf2_create(cnf2_engine** out, const cnf2_settings* settings)
 	e->n_ctas = per_sm * e->n_sm;
 	if ((ce = cudaFuncSetAttribute(batch_estep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BatchSmem))) != cudaSuccess)
 		return bail(ce, "cudaFuncSetAttribute(batch_estep_kernel)");
-	e->n_ctas_batch = e->n_sm;  // one CTA per SM: the batched kernel uses nearly all of the SM's shared memory
+	if ((ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, batch_estep_kernel, NTHREADS, sizeof(BatchSmem))) != cudaSuccess)
+		return bail(ce, "occupancy query");
+	if (per_sm < 1) per_sm = 1;
+	if (settings->ctas_per_sm > 0) per_sm = std::min(per_sm, settings->ctas_per_sm);
+	e->n_ctas_batch = per_sm * e->n_sm;
 	const char* kn = getenv("CNF2_KERNEL");
 	e->use_fast = kn && std::string(kn) == "fast";
 	const char* lit = getenv("CNF2_LITERAL");
