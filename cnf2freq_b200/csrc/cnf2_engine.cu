@@ -4,6 +4,7 @@
 #include "../../include/cnf2_engine.h"
 #include "cnf2_fast_kernel.cuh"
 #include "cnf2_batch_kernel.cuh"
+#include "cnf2_warp_kernel.cuh"
 
 #include <algorithm>
 #include <cmath>
@@ -79,7 +80,8 @@ struct cnf2_engine
 	DevBuf<double> d_hw, d_rec, d_alpha, d_alphafac, d_q, d_stats, d_loglik;
 	DevBuf<int32_t> d_literal, d_kexp;
 	DevBuf<double> d_qstash;
-	int n_ctas_batch = 0;
+	int n_ctas_batch = 0, n_ctas_warp = 0;
+	bool use_batch = false;  // A-B switch: CNF2_KERNEL=batch runs the CTA-per-unit batched kernel
 	bool use_fast = false;  // A-B switch: CNF2_KERNEL=fast runs the older table-driven kernel instead of the batched one
 	int n_ctas_literal = 0;
 	bool literal_only = false;  // debugging / A-B switch: CNF2_LITERAL=1 runs every unit through the literal kernel
@@ -198,8 +200,18 @@ extern "C" int cnf2_create(cnf2_engine** out, const cnf2_settings* settings)
 	if (per_sm < 1) per_sm = 1;
 	if (settings->ctas_per_sm > 0) per_sm = std::min(per_sm, settings->ctas_per_sm);
 	e->n_ctas_batch = per_sm * e->n_sm;
+	if ((ce = cudaFuncSetAttribute(warp_estep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(WarpSmem))) != cudaSuccess)
+		return bail(ce, "cudaFuncSetAttribute(warp_estep_kernel)");
+	if ((ce = cudaFuncSetAttribute(warp_estep_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100)) != cudaSuccess)
+		return bail(ce, "cudaFuncSetAttribute(warp_estep_kernel carveout)");
+	if ((ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, warp_estep_kernel, 32, sizeof(WarpSmem))) != cudaSuccess)
+		return bail(ce, "occupancy query");
+	if (per_sm < 1) per_sm = 1;
+	if (settings->ctas_per_sm > 0) per_sm = std::min(per_sm, settings->ctas_per_sm);
+	e->n_ctas_warp = per_sm * e->n_sm;
 	const char* kn = getenv("CNF2_KERNEL");
 	e->use_fast = kn && std::string(kn) == "fast";
+	e->use_batch = kn && std::string(kn) == "batch";
 	const char* lit = getenv("CNF2_LITERAL");
 	e->literal_only = lit && lit[0] == '1';
 	*out = e;
@@ -544,7 +556,7 @@ extern "C" int cnf2_estep(cnf2_engine* e, int32_t chrom)
 	cudaSetDevice(e->settings.device);
 	const int Mc = e->mc(chrom);
 	const int n_units = (int)e->units.size();
-	const int n_ctas = std::max(1, std::min(std::max(std::max(e->n_ctas, e->n_ctas_batch), e->n_ctas_literal), n_units));
+	const int n_ctas = std::max(1, std::min(std::max(std::max(std::max(e->n_ctas, e->n_ctas_batch), e->n_ctas_warp), e->n_ctas_literal), n_units));
 	CU(e->d_alpha.ensure((size_t)n_ctas * e->max_mc * NUMSHIFTS * NUMTYPES));
 	CU(e->d_alphafac.ensure((size_t)n_ctas * e->max_mc * NUMSHIFTS));
 	if (e->use_fast) CU(e->d_q.ensure((size_t)n_ctas * e->max_mc * NUMSHIFTS * 32));
@@ -591,7 +603,10 @@ extern "C" int cnf2_estep(cnf2_engine* e, int32_t chrom)
 			bargs.qstash = e->d_qstash.p;
 			bargs.literal_units = e->d_literal.p;
 			bargs.literal_count = e->d_counter.p + 1;
-			batch_estep_kernel<<<std::max(1, std::min(e->n_ctas_batch, n_units)), NTHREADS, sizeof(BatchSmem), e->stream>>>(bargs);
+			if (e->use_batch)
+				batch_estep_kernel<<<std::max(1, std::min(e->n_ctas_batch, n_units)), NTHREADS, sizeof(BatchSmem), e->stream>>>(bargs);
+			else  // one warp per unit
+				warp_estep_kernel<<<std::max(1, std::min(e->n_ctas_warp, n_units)), 32, sizeof(WarpSmem), e->stream>>>(bargs);
 			CU(cudaGetLastError());
 			e->last_launches++;
 			a.unit_list = e->d_literal.p;

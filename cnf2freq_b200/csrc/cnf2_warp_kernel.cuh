@@ -1,0 +1,552 @@
+// The warp-per-unit E-step kernel (the product path).
+//
+// One warp = one (analysed individual, chromosome) unit from start to end; CTAs are single warps, several per
+// SM, fed from an atomic queue.  No block-wide barrier exists anywhere: the warp runs its forward sweep, its
+// backward sweep and the posterior of every marker on its own.
+//
+//   * sweeps (cnF2freq.cpp:2145-2418): ALL 8 shift modes live in one warp: lane = shift * 4 + (state bits 4-5),
+//     16 states (bits 0-3) per lane in registers.  The transition R(r)^{(x)6} is four in-register butterfly
+//     stages and two shfl.xor stages on 16 independent values per lane; the emission comes from the marker's
+//     shift-independent table (see cnf2_batch_kernel.cuh); the vectors are scaled by exact powers of two per
+//     shift mode instead of being renormalised.
+//   * posterior (:5406-5583): W_s[g] = alpha_s[g] beta_s[g] exp(F + B - factor) is transposed through shared
+//     memory, then each lane takes one surviving (x, g) pair for all 8 shift modes (batch_posterior's scheme),
+//     scatters into its private accumulator column, the warp reduces its 32 columns and transfers them into
+//     the EM sufficient statistics (:5875-5904).
+//   * the orientation-fixed subtree tables are direct-indexed by local configuration; one lane builds one
+//     (entry, root orientation) pair.
+#pragma once
+#include "cnf2_batch_kernel.cuh"
+
+namespace cnf2
+{
+constexpr int WB = TB;        // markers staged at a time (the stride gfix / root_constants expect)
+constexpr int WTS = 17;       // row stride of the transposed W (doubles): conflict-free 64-bit stores
+constexpr int T0W = 3, T1W = 5;
+
+struct __align__(16) WarpSmem
+{
+	double acc[NACC * 32];
+	double Wt[32 * WTS];           // [shift * 4 + (g >> 4)][g & 15]
+	double tab0[2 * 64 * T0W];     // [f][cfg]: Q(plain), rho0[1], rho0[2]
+	double tab1[2 * 64 * T1W];     // [f][cfg]: Q(plain), rho1[1], rho1[2], Q(1,0)/Q(plain), Q(2,0)/Q(plain)
+	double qh[WB * QS];
+	NodeTab nt[NSLOTS * WB];
+	double HW[NSLOTS * WB];
+	double tot[NACC];
+	double rootc[RC];
+	uchar2 A[NSLOTS * WB];
+	unsigned char xl[NUMPATHS];
+	unsigned char el[128];
+	int nX, nE, listtag;
+	int homslot[WB], gpmust[WB];
+	Unit unit;
+};
+
+// One (entry, root orientation) pair of the posterior tables of marker t (see post_entry in cnf2_batch_kernel.cuh).
+__device__ __forceinline__ void post_entry1(const Unit& u, const uchar2* A, const NodeTab* N, const double* __restrict__ rc, int t, int p,
+                                            int cfg, int f, double* __restrict__ tab0, double* __restrict__ tab1)
+{
+	const int m = cfg & 1, ma = (cfg >> 1) & 1, mb = (cfg >> 2) & 1, o = (cfg >> 3) & 1, oa = (cfg >> 4) & 1, ob = (cfg >> 5) & 1;
+	const int sp = 1 + 3 * p;
+	const uchar2 a0 = A[t];
+	const NodeTab& n0 = N[t];
+	const bool absent = u.row[sp] < 0, attop = !absent && u.founder[sp];
+	const uchar2 ap = A[sp * WB + t];
+	const NodeTab& np = N[sp * WB + t];
+	const int kf = sp + 1 + m, of = m ? ob : oa, wf = of ^ (m ? mb : ma);
+	double pre = 1.0;
+	if (!absent && !attop)
+	{
+		const int ko = sp + 1 + (m ^ 1), oo = m ? oa : ob, wo = oo ^ (m ? ma : mb);
+		if (np.S[o ^ 1] != 0) pre = 1.0 - np.S[o ^ 1];
+		pre *= gfix(u, A, N, ko, t, o ? ap.x : ap.y, np.SEC[o ^ 1], oo, wo);
+	}
+	auto Q = [&](int v, double sec) -> double {
+		if (absent) return 1.0 + sec;
+		if (attop) return gval(ap, np, o, v, sec);
+		const PMsg pm = pmsg(ap, np, o, v, sec);
+		return pm.nb * pre * gfix(u, A, N, kf, t, pm.v2, pm.up2, of, wf);
+	};
+	const double P1 = Q(1, 0.0), P2 = Q(2, 0.0);
+	if (p == 0)
+	{
+		double* e = tab0 + (f * 64 + cfg) * T0W;
+		const int v = f ? a0.y : a0.x;
+		e[0] = Q(v, v != UNKNOWN ? n0.RN[f] : 0.0);
+		const double A1 = rc[4 + f] * P1, A2 = rc[6 + f] * P2;
+		const double sum = A1 + A2, inv = sum > 0 ? 1.0 / sum : 0.0;
+		e[1] = A1 * inv;
+		e[2] = A2 * inv;
+	}
+	else
+	{
+		double* e = tab1 + (f * 64 + cfg) * T1W;
+		const int v = f ? a0.x : a0.y;
+		const double E = Q(v, n0.SEC[f ^ 1]);
+		e[0] = E;
+		const double A1 = rc[4 + (f ^ 1)] * P1, A2 = rc[6 + (f ^ 1)] * P2;  // side 1 probes the root at orientation f ^ 1
+		const double sum = A1 + A2, inv = sum > 0 ? 1.0 / sum : 0.0, invE = E > 0 ? 1.0 / E : 0.0;
+		e[1] = A1 * inv;
+		e[2] = A2 * inv;
+		e[3] = P1 * invE;
+		e[4] = P2 * invE;
+	}
+}
+
+// Posterior of the current marker: dense enumeration of the (x, g) pairs, 8 shift modes per pair
+// (batch_posterior's scheme on this kernel's layouts).  rootc[12..15] = phase weights of parent 0 / parent 1.
+__device__ __forceinline__ void warp_posterior(WarpSmem& w, const Unit& u, int homslot, int lane)
+{
+	const double* rc = w.rootc;
+	double* const acc = w.acc + lane;
+	const int nfree = u.nfree, gfix_ = u.gfixmask;
+	const int T = w.nX << nfree;
+	const int vis = u.vismask, hmask = vis & ~homslot;
+	const double wp00 = rc[12], wp01 = rc[13], wp10 = rc[14], wp11 = rc[15];
+	const double hf10 = rc[8], hf11 = rc[9], hf20 = rc[10], hf21 = rc[11];
+	for (int i = lane; i < T; i += 32)
+	{
+		const int x = w.xl[i >> nfree];
+		const int g = ((x >> 1) & gfix_) | u.expand[i & ((1 << nfree) - 1)];
+		const int flag2 = x ^ (g << 1);
+		const int f = x & 1, x1 = (x >> 1) & 1, x4 = (x >> 4) & 1;
+		const int cfg0 = (g & 7) | (((flag2 >> 1) & 7) << 3), cfg1 = ((g >> 3) & 7) | (((flag2 >> 4) & 7) << 3);
+		const double* T0 = w.tab0 + (f * 64 + cfg0) * T0W;
+		const double* T1 = w.tab1 + (f * 64 + cfg1) * T1W;
+		const double ep = rc[f] * T0[0] * T1[0];
+		if (!(ep > 0)) continue;
+		// the 8 shift modes: s = s0 | s1 << 1 | s2 << 2 flips the phase-weight index of root / parent 0 / parent 1
+		const double r0 = ep * rc[2 + f], r1 = ep * rc[2 + (f ^ 1)];
+		const double a0 = x1 ? wp01 : wp00, a1 = x1 ? wp00 : wp01;  // parent 0 at s1 = 0, 1
+		const double b0 = x4 ? wp11 : wp10, b1 = x4 ? wp10 : wp11;  // parent 1 at s2 = 0, 1
+		const double c00 = a0 * b0, c10 = a1 * b0, c01 = a0 * b1, c11 = a1 * b1;  // [s1][s2]
+		const double* W = w.Wt + (g >> 4) * WTS + (g & 15);
+		double ts[8];
+		ts[0] = r0 * c00 * W[0 * 4 * WTS];
+		ts[1] = r1 * c00 * W[1 * 4 * WTS];
+		ts[2] = r0 * c10 * W[2 * 4 * WTS];
+		ts[3] = r1 * c10 * W[3 * 4 * WTS];
+		ts[4] = r0 * c01 * W[4 * 4 * WTS];
+		ts[5] = r1 * c01 * W[5 * 4 * WTS];
+		ts[6] = r0 * c11 * W[6 * 4 * WTS];
+		ts[7] = r1 * c11 * W[7 * 4 * WTS];
+#pragma unroll
+		for (int s = 0; s < 8; s++) ts[s] = ts[s] > EXP_M200_B ? ts[s] : 0.0;  // unusualstate, :5414, 5502
+		const double p01 = ts[0] + ts[1], p23 = ts[2] + ts[3], p45 = ts[4] + ts[5], p67 = ts[6] + ts[7];
+		const double V = (p01 + p23) + (p45 + p67);
+		if (!(V > 0)) continue;
+		// updatehaplo (:1561-1575): visited, non-homozygous slots at their effective phase bit x_k ^ s_k
+		if (hmask & 1)
+		{
+			acc[(ACC_HAPLOS + f) * 32] += (ts[0] + ts[2]) + (ts[4] + ts[6]);        // s0 = 0: bit f
+			acc[(ACC_HAPLOS + (f ^ 1)) * 32] += (ts[1] + ts[3]) + (ts[5] + ts[7]);  // s0 = 1
+		}
+		if (hmask & 2)
+		{
+			acc[(ACC_HAPLOS + 2 + x1) * 32] += p01 + p45;
+			acc[(ACC_HAPLOS + 2 + (x1 ^ 1)) * 32] += p23 + p67;
+		}
+		if (hmask & 16)
+		{
+			acc[(ACC_HAPLOS + 8 + x4) * 32] += p01 + p23;
+			acc[(ACC_HAPLOS + 8 + (x4 ^ 1)) * 32] += p45 + p67;
+		}
+#pragma unroll
+		for (int k = 2; k < NSLOTS; k++)
+			if (k != 4 && ((hmask >> k) & 1)) acc[(ACC_HAPLOS + k * 2 + ((x >> k) & 1)) * 32] += V;
+		// the four GENOS calls (:5560-5568): root, parent `side`, that parent's parent picked by its meiosis bit
+#pragma unroll
+		for (int side = 0; side < 2; side++)
+		{
+			const double* Ts = side ? T1 : T0;
+			const double u0 = V * Ts[1], u1 = V * Ts[2];
+			const int sp = 1 + 3 * side, gs = sp + 1 + ((g >> (3 * side)) & 1);
+			double* q0 = acc + (ACC_INF + (f ^ side) * 2) * 32;
+			q0[0] += u0;
+			q0[32] += u1;
+			if ((vis >> sp) & 1)
+			{
+				double* qp = acc + (ACC_INF + (sp * 2 + ((flag2 >> sp) & 1)) * 2) * 32;
+				qp[0] += u0;
+				qp[32] += u1;
+				if ((vis >> gs) & 1)
+				{
+					double* qg = acc + (ACC_INF + (gs * 2 + ((flag2 >> gs) & 1)) * 2) * 32;
+					qg[0] += u0;
+					qg[32] += u1;
+				}
+			}
+		}
+		// homozyg (:5571-5575): rho0[al] * hfd[al][f] * Q1(al, 0) / Q1(plain)
+		acc[(ACC_HZ + 0) * 32] += V * T0[1] * (f ? hf11 : hf10) * T1[3];
+		acc[(ACC_HZ + 1) * 32] += V * T0[2] * (f ? hf21 : hf20) * T1[4];
+	}
+}
+
+// ---- sweeps: lane = shift * 4 + gh, state g = r | gh << 4, r = 0..15 in registers ----
+
+// Transition (cnF2freq.cpp:2270-2367): bits 0-3 inside the lane, bits 4-5 across lanes 1 and 2 apart.
+// TYPEGENS = {1,0,0,1,0,0} (settings.h:23): genrec[1] (r1) for the child meioses, bits 0 and 3.
+__device__ __forceinline__ void transition16(double (&p)[16], double r0, double r1)
+{
+	if (!(r0 > 0) && !(r1 > 0)) return;  // same position: identity (:2273)
+#pragma unroll
+	for (int b = 0; b < 4; b++)
+	{
+		const double r = (b == 0 || b == 3) ? r1 : r0;
+#pragma unroll
+		for (int i = 0; i < 16; i++)
+			if (!(i & (1 << b)))
+			{
+				const double d = r * (p[i | (1 << b)] - p[i]);
+				p[i] += d;
+				p[i | (1 << b)] -= d;
+			}
+	}
+#pragma unroll
+	for (int b = 1; b <= 2; b <<= 1)
+#pragma unroll
+		for (int i = 0; i < 16; i++)
+		{
+			const double q = __shfl_xor_sync(0xffffffffu, p[i], b);
+			p[i] += r0 * (q - p[i]);
+		}
+}
+
+// p *= emission (all orientations summed) from the marker's sweep table q (layout: sweep_family)
+__device__ __forceinline__ void emit16(double (&p)[16], const double* __restrict__ q, int lane)
+{
+	const int s = lane >> 2, gh = lane & 3;
+	const int s0 = s & 1, s1 = (s >> 1) & 1, s2 = s >> 2;
+	const double2 R = *reinterpret_cast<const double2*>(q + 64 + s0 * 2);
+	const double2* Q1 = reinterpret_cast<const double2*>(q + (((2 + s2) * 8) + gh * 2) * 2);
+	const double2* Q0 = reinterpret_cast<const double2*>(q + (s1 * 8) * 2);
+	const double2 qa = Q1[0], qb = Q1[1];
+	const double c0a = R.x * qa.x, c1a = R.y * qa.y, c0b = R.x * qb.x, c1b = R.y * qb.y;
+#pragma unroll
+	for (int j = 0; j < 8; j++)
+	{
+		const double2 q0 = Q0[j];
+		p[j] *= c0a * q0.x + c1a * q0.y;
+		p[j + 8] *= c0b * q0.x + c1b * q0.y;
+	}
+}
+
+// Scale the 64 entries of each shift mode (4 lanes x 16) by the power of two that brings the largest into [1, 2).
+__device__ __forceinline__ void rescale16(double (&p)[16], int& k)
+{
+	int e = 0;
+#pragma unroll
+	for (int i = 0; i < 16; i++) e = max(e, __double2hiint(p[i]));  // non-negative doubles order like their high words
+	e = max(e, __shfl_xor_sync(0xffffffffu, e, 1));
+	e = max(e, __shfl_xor_sync(0xffffffffu, e, 2));
+	const int w = e >> 20;
+	if (w == 0) return;  // all zero
+	const double sc = __hiloint2double((2046 - w) << 20, 0);
+#pragma unroll
+	for (int i = 0; i < 16; i++) p[i] *= sc;
+	k += w - 1023;
+}
+
+// scratch layout of one marker's alpha: chunk j (two consecutive states) of lane l at double2 index j * 32 + l
+__device__ __forceinline__ void store_alpha(double2* __restrict__ dst, const double (&p)[16], int lane)
+{
+#pragma unroll
+	for (int j = 0; j < 8; j++) dst[j * 32 + lane] = make_double2(p[2 * j], p[2 * j + 1]);
+}
+__device__ __forceinline__ void load_alpha(const double2* __restrict__ src, double (&p)[16], int lane)
+{
+#pragma unroll
+	for (int j = 0; j < 8; j++)
+	{
+		const double2 v = src[j * 32 + lane];
+		p[2 * j] = v.x;
+		p[2 * j + 1] = v.y;
+	}
+}
+
+// Raw marker data of one (slot, marker) pair, held in registers between its load and its use.
+struct RawItem
+{
+	uchar2 al;
+	double2 su;
+	double h;
+};
+// lane i < 28 loads (slot = i >> 2, t = i & 3) of markers [m0, m0 + n)
+__device__ __forceinline__ RawItem raw_load(const Unit& u, const EstepArgs& a, int m0, int n, int lane)
+{
+	RawItem r;
+	r.al = make_uchar2(0, 0);
+	r.su = make_double2(0, 0);
+	r.h = 0;
+	const int slot = lane >> 2, t = lane & 3;
+	if (slot < NSLOTS && t < n && m0 >= 0)
+	{
+		const int row = u.row[slot];
+		if (row >= 0)
+		{
+			const size_t o = (size_t)row * a.ld + m0 + t;
+			r.al = a.alleles[o];
+			r.su = a.sure[o];
+			r.h = a.hw[o];
+		}
+	}
+	return r;
+}
+// writes the staged item; returns whether it is outside the regular range (markersure in [0,1), haploweight in [0,1])
+__device__ __forceinline__ bool raw_commit(WarpSmem& w, const RawItem& r, int lane)
+{
+	const int slot = lane >> 2, t = lane & 3;
+	if (slot >= NSLOTS) return false;
+	const int i = slot * WB + t;
+	w.A[i] = r.al;
+	w.nt[i] = make_nodetab(r.al, r.su, r.h);
+	w.HW[i] = r.h;
+	return !(r.su.x >= 0 && r.su.x < 1 && r.su.y >= 0 && r.su.y < 1 && r.h >= 0 && r.h <= 1);
+}
+
+// Lists of the posterior phase for a marker whose shift-independent rule-3 mask is gpmust (see batch_prepare).
+__device__ __forceinline__ void warp_lists(WarpSmem& w, const Unit& u, int gpmust, int lane)
+{
+	const unsigned FULL = 0xffffffffu;
+	int nX = 0, nE = 0;
+#pragma unroll
+	for (int r4 = 0; r4 < 4; r4++)
+	{
+		const int x = r4 * 32 + lane;
+		const bool ok = ((u.xmask2[r4] >> lane) & 1) && (x & gpmust) == gpmust;
+		const unsigned mask = __ballot_sync(FULL, ok);
+		if (ok) w.xl[nX + __popc(mask & ((1u << lane) - 1u))] = (unsigned char)x;
+		nX += __popc(mask);
+	}
+#pragma unroll
+	for (int r4 = 0; r4 < 4; r4++)
+	{
+		const int c = r4 * 32 + lane, p = c >> 6, cfg = c & 63;
+		const int sub = (gpmust >> (1 + 3 * p)) & 7, xc = (cfg & 7) ^ (cfg >> 3);
+		const bool ok = ((u.cfgmask[p] >> cfg) & 1ull) && (xc & sub) == sub;
+		const unsigned mask = __ballot_sync(FULL, ok);
+		if (ok) w.el[nE + __popc(mask & ((1u << lane) - 1u))] = (unsigned char)c;
+		nE += __popc(mask);
+	}
+	if (lane == 0)
+	{
+		w.nX = nX;
+		w.nE = nE;
+		w.listtag = gpmust;
+	}
+	__syncwarp();
+}
+
+typedef BatchArgs WarpArgs;  // alpha scratch: [n_warps][Mc][512] doubles in store_alpha's layout
+
+__global__ void __launch_bounds__(32) warp_estep_kernel(WarpArgs wa)
+{
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	WarpSmem& w = *reinterpret_cast<WarpSmem*>(smem_raw);
+	const EstepArgs& a = wa.e;
+	const unsigned FULL = 0xffffffffu;
+	const int lane = threadIdx.x, s = lane >> 2;
+	const int Mc = a.Mc, E = Mc - 1;
+	double2* const alpha = reinterpret_cast<double2*>(a.alpha) + (size_t)blockIdx.x * Mc * (NUMSHIFTS * NUMTYPES / 2);
+	int32_t* const kexp = wa.kexp + (size_t)blockIdx.x * Mc * NUMSHIFTS;
+	double* const qs = wa.qstash + (size_t)blockIdx.x * Mc * QS;
+
+	for (int i = lane; i < NACC * 32; i += 32) w.acc[i] = 0;
+
+	for (;;)
+	{
+		int ui = 0;
+		if (lane == 0) ui = (int)atomicAdd(a.counter, 1u);
+		ui = __shfl_sync(FULL, ui, 0);
+		if (ui >= a.n_units) break;
+		__syncwarp();
+		{
+			const int* src = reinterpret_cast<const int*>(a.units + ui);
+			int* dst = reinterpret_cast<int*>(&w.unit);
+			for (int i = lane; i < (int)(sizeof(Unit) / 4); i += 32) dst[i] = src[i];
+			if (lane == 0) w.listtag = -1;
+		}
+		__syncwarp();
+		const Unit& u = w.unit;
+		bool literal = u.founder[0] != 0;  // a root "at the top" never recurses (:1120): literal kernel
+		const bool active = s < u.shiftend && !(s & u.shiftignore);
+
+		// ---- forward sweep (initfwbw + realanalyze<STORE|FORWARD>, cnF2freq.cpp:2086-2107) ----
+		double p[16];
+#pragma unroll
+		for (int i = 0; i < 16; i++) p[i] = active ? 1.0 / NUMTYPES : 0.0;  // EVENGEN, :2100-2104
+		int ka = 0;
+		if (!literal)
+		{
+			RawItem raw = raw_load(u, a, 0, min(WB, Mc), lane);
+			for (int m0 = 0; m0 < Mc; m0 += WB)
+			{
+				const int n = min(WB, Mc - m0);
+				__syncwarp();
+				const bool bad = raw_commit(w, raw, lane);
+				if (m0 + WB < Mc) raw = raw_load(u, a, m0 + WB, min(WB, Mc - m0 - WB), lane);
+				if (__any_sync(FULL, bad))
+				{
+					literal = true;
+					break;
+				}
+				__syncwarp();
+				if ((lane >> 3) < n) sweep_family<WB>(u, w.A, w.nt, lane >> 3, lane & 7, w.qh + (lane >> 3) * QS);
+				__syncwarp();
+				for (int i = lane; i < n * QS; i += 32) qs[(size_t)m0 * QS + i] = w.qh[i];
+				for (int t = 0; t < n; t++)
+				{
+					const int m = m0 + t;
+					store_alpha(alpha + (size_t)m * (NUMSHIFTS * NUMTYPES / 2), p, lane);
+					if ((lane & 3) == 0) kexp[(size_t)m * NUMSHIFTS + s] = ka;
+					emit16(p, w.qh + t * QS, lane);
+					rescale16(p, ka);
+					if (m < E) transition16(p, a.rec0[m], a.rec1[m]);
+				}
+			}
+		}
+		if (literal)
+		{
+			if (lane == 0) wa.literal_units[atomicAdd(wa.literal_count, 1u)] = ui;
+			continue;
+		}
+		// doanalyze / quickanalyze with NONESTOP (:1984-2018): log-factor of alpha+ at the last marker, per shift mode
+		double L;
+		{
+			double sum = 0;
+#pragma unroll
+			for (int i = 0; i < 16; i++) sum += p[i];
+			sum += __shfl_xor_sync(FULL, sum, 1);
+			sum += __shfl_xor_sync(FULL, sum, 2);
+			L = sum > 0 ? (double)ka * LN2 + log(sum) : MINFACTOR_D;
+		}
+		double factor = -1e15, realfactor = 0;  // :5373-5403
+		double Ls[NUMSHIFTS];
+#pragma unroll
+		for (int j = 0; j < NUMSHIFTS; j++)
+		{
+			Ls[j] = __shfl_sync(FULL, L, j * 4);
+			if (j < u.shiftend && !(j & u.shiftignore)) factor = fmax(factor, Ls[j]);
+		}
+#pragma unroll
+		for (int j = 0; j < NUMSHIFTS; j++)
+			if (j < u.shiftend && !(j & u.shiftignore)) realfactor += exp(Ls[j] - factor);
+		const double maxfactor = factor;
+		factor += log(realfactor);
+		if (lane == 0)
+		{
+			a.loglik[(size_t)u.out * 2 + 0] = maxfactor;
+			a.loglik[(size_t)u.out * 2 + 1] = factor;
+		}
+		if (isnan(factor) || factor < MINFACTOR_D) continue;  // :5403
+		const bool contributing = active && !(factor - L > 40);  // :5421
+		const double minfactor = (double)(float)(-200.0 + factor);  // unusualstate + factor as a float, :1936
+		// exp(k ln 2 - factor) = 2^(k + kf) * exp(frem) with -factor = kf ln 2 + frem: one exp per unit
+		const int kf = (int)rint(-factor / LN2);
+		const double efrem = exp(-factor - (double)kf * LN2);
+
+		// ---- backward sweep (:2109-2116), the posterior of each marker right behind it ----
+		double b[16];
+#pragma unroll
+		for (int i = 0; i < 16; i++) b[i] = 1.0;  // :2111-2114
+		int kb = 0;
+		const int mlast = ((Mc - 1) / WB) * WB;
+		RawItem raw = raw_load(u, a, mlast, Mc - mlast, lane);
+		double an[16];
+		load_alpha(alpha + (size_t)(Mc - 1) * (NUMSHIFTS * NUMTYPES / 2), an, lane);
+		int kan = kexp[(size_t)(Mc - 1) * NUMSHIFTS + s];
+		for (int m0 = mlast; m0 >= 0; m0 -= WB)
+		{
+			const int n = min(WB, Mc - m0);
+			__syncwarp();
+			raw_commit(w, raw, lane);
+			for (int i = lane; i < n * QS; i += 32) w.qh[i] = qs[(size_t)m0 * QS + i];
+			// homozygous with equal sureness (:1235, :3488), per (slot, marker) of the batch
+			const bool homi = (lane >> 2) < NSLOTS && u.row[(lane >> 2) % NSLOTS] >= 0 && raw.al.x == raw.al.y && raw.su.x == raw.su.y;
+			const unsigned homb = __ballot_sync(FULL, homi);
+			if (m0 >= WB) raw = raw_load(u, a, m0 - WB, WB, lane);
+			if (lane < WB)
+			{
+				int hs = 0, hom = 0, gp = 0;
+				for (int k = 0; k < NSLOTS; k++)
+					if ((homb >> (k * 4 + lane)) & 1)
+					{
+						hs |= 1 << k;
+						hom |= 1 << u.slotrel[k];
+					}
+				for (int i = 0; i < u.nrel; i++)  // rule 3 (:3488-3493) of the relatives whose rule does not involve the shift mode
+					if (((hom >> i) & 1) && u.relshift[i] == 0) gp |= u.relfilter[i];
+				w.homslot[lane] = hs;
+				w.gpmust[lane] = gp;
+			}
+			__syncwarp();
+			for (int t = n - 1; t >= 0; t--)
+			{
+				const int m = m0 + t;
+				// W = alpha beta exp(F- + B - factor) (:1963-2018, :5499-5508); the factors are k ln 2 here
+				double W[16];
+				{
+					double sc = 0;
+					const int ke = kan + kb + kf;
+					if (contributing && !((double)kan * LN2 + 5.0 < minfactor) && ke > -860 && ke < 860)
+						sc = __hiloint2double((1023 + ke) << 20, 0) * efrem;
+#pragma unroll
+					for (int i = 0; i < 16; i++) W[i] = an[i] * (b[i] * sc);
+				}
+				if (m > 0)
+				{
+					load_alpha(alpha + (size_t)(m - 1) * (NUMSHIFTS * NUMTYPES / 2), an, lane);
+					kan = kexp[(size_t)(m - 1) * NUMSHIFTS + s];
+				}
+				const int gp = w.gpmust[t];
+				if (gp != w.listtag) warp_lists(w, u, gp, lane);
+				if (lane < 2) root_constants(w.A[t], w.nt[t], lane, w.rootc);
+				else if (lane < 4)
+				{
+					const int sp = lane == 2 ? 1 : 4;
+					const bool there = u.row[sp] >= 0;
+					w.rootc[12 + (lane - 2) * 2 + 0] = there ? w.nt[sp * WB + t].W[0] : 1.0;
+					w.rootc[12 + (lane - 2) * 2 + 1] = there ? w.nt[sp * WB + t].W[1] : 1.0;
+				}
+#pragma unroll
+				for (int i = 0; i < 16; i++) w.Wt[lane * WTS + i] = W[i];
+				__syncwarp();
+				for (int i = lane; i < 2 * w.nE; i += 32)
+				{
+					const int c = w.el[i >> 1];
+					post_entry1(u, w.A, w.nt, w.rootc, t, c >> 6, c & 63, i & 1, w.tab0, w.tab1);
+				}
+				__syncwarp();
+				warp_posterior(w, u, w.homslot[t], lane);
+				__syncwarp();
+				// the warp reduces its 32 accumulator columns; the reader clears what it read
+				for (int k = lane; k < NACC; k += 32)
+				{
+					double* col = w.acc + k * 32;
+					double v = 0;
+#pragma unroll 8
+					for (int j = 0; j < 32; j++)
+					{
+						double* q = col + ((j + lane) & 31);
+						v += *q;
+						*q = 0;
+					}
+					w.tot[k] = v;
+				}
+				__syncwarp();
+				// transfer into the EM sufficient statistics (:5875-5904, moveinfprobs :3577-3597, movehaplos :3599-3616)
+				if (lane < u.nrel) transfer_stats(a, u, w.tot, w.HW, lane, t, m, WB);
+				if (m > 0)
+				{
+					emit16(b, w.qh + t * QS, lane);
+					rescale16(b, kb);
+					transition16(b, a.rec0[m - 1], a.rec1[m - 1]);
+				}
+				__syncwarp();
+			}
+		}
+	}
+}
+}  // namespace cnf2
