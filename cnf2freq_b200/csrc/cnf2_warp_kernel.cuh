@@ -136,51 +136,47 @@ __device__ __forceinline__ void warp_posterior(WarpSmem& w, const Unit& u, int h
 		const double p01 = ts[0] + ts[1], p23 = ts[2] + ts[3], p45 = ts[4] + ts[5], p67 = ts[6] + ts[7];
 		const double V = (p01 + p23) + (p45 + p67);
 		if (!(V > 0)) continue;
-		// updatehaplo (:1561-1575): visited, non-homozygous slots at their effective phase bit x_k ^ s_k
-		if (hmask & 1)
-		{
-			acc[(ACC_HAPLOS + f) * 32] += (ts[0] + ts[2]) + (ts[4] + ts[6]);        // s0 = 0: bit f
-			acc[(ACC_HAPLOS + (f ^ 1)) * 32] += (ts[1] + ts[3]) + (ts[5] + ts[7]);  // s0 = 1
-		}
-		if (hmask & 2)
-		{
-			acc[(ACC_HAPLOS + 2 + x1) * 32] += p01 + p45;
-			acc[(ACC_HAPLOS + 2 + (x1 ^ 1)) * 32] += p23 + p67;
-		}
-		if (hmask & 16)
-		{
-			acc[(ACC_HAPLOS + 8 + x4) * 32] += p01 + p23;
-			acc[(ACC_HAPLOS + 8 + (x4 ^ 1)) * 32] += p45 + p67;
-		}
-#pragma unroll
-		for (int k = 2; k < NSLOTS; k++)
-			if (k != 4 && ((hmask >> k) & 1)) acc[(ACC_HAPLOS + k * 2 + ((x >> k) & 1)) * 32] += V;
-		// the four GENOS calls (:5560-5568): root, parent `side`, that parent's parent picked by its meiosis bit
+		// Scatter: updatehaplo (:1561-1575) adds to every visited, non-homozygous slot at its effective phase bit
+		// x_k ^ s_k; the four GENOS calls (:5560-5568) add to the root, parent `side` and that parent's parent picked
+		// by its meiosis bit; homozyg (:5571-5575).  The 24 targets of one pair are distinct columns entries, so all
+		// are read before any is written (the loads overlap instead of forming one chain).
+		int idx[24];
+		double add[24];
+		bool en[24];
+		idx[0] = ACC_HAPLOS + f, add[0] = (ts[0] + ts[2]) + (ts[4] + ts[6]), en[0] = hmask & 1;            // s0 = 0: bit f
+		idx[1] = ACC_HAPLOS + (f ^ 1), add[1] = (ts[1] + ts[3]) + (ts[5] + ts[7]), en[1] = hmask & 1;      // s0 = 1
+		idx[2] = ACC_HAPLOS + 2 + x1, add[2] = p01 + p45, en[2] = hmask & 2;
+		idx[3] = ACC_HAPLOS + 2 + (x1 ^ 1), add[3] = p23 + p67, en[3] = hmask & 2;
+		idx[4] = ACC_HAPLOS + 8 + x4, add[4] = p01 + p23, en[4] = hmask & 16;
+		idx[5] = ACC_HAPLOS + 8 + (x4 ^ 1), add[5] = p45 + p67, en[5] = hmask & 16;
+		idx[6] = ACC_HAPLOS + 4 + ((x >> 2) & 1), add[6] = V, en[6] = hmask & 4;
+		idx[7] = ACC_HAPLOS + 6 + ((x >> 3) & 1), add[7] = V, en[7] = hmask & 8;
+		idx[8] = ACC_HAPLOS + 10 + ((x >> 5) & 1), add[8] = V, en[8] = hmask & 32;
+		idx[9] = ACC_HAPLOS + 12 + ((x >> 6) & 1), add[9] = V, en[9] = hmask & 64;
 #pragma unroll
 		for (int side = 0; side < 2; side++)
 		{
 			const double* Ts = side ? T1 : T0;
 			const double u0 = V * Ts[1], u1 = V * Ts[2];
 			const int sp = 1 + 3 * side, gs = sp + 1 + ((g >> (3 * side)) & 1);
-			double* q0 = acc + (ACC_INF + (f ^ side) * 2) * 32;
-			q0[0] += u0;
-			q0[32] += u1;
-			if ((vis >> sp) & 1)
-			{
-				double* qp = acc + (ACC_INF + (sp * 2 + ((flag2 >> sp) & 1)) * 2) * 32;
-				qp[0] += u0;
-				qp[32] += u1;
-				if ((vis >> gs) & 1)
-				{
-					double* qg = acc + (ACC_INF + (gs * 2 + ((flag2 >> gs) & 1)) * 2) * 32;
-					qg[0] += u0;
-					qg[32] += u1;
-				}
-			}
+			const int j = 10 + side * 6;
+			idx[j] = ACC_INF + (f ^ side) * 2, add[j] = u0, en[j] = true;
+			idx[j + 1] = idx[j] + 1, add[j + 1] = u1, en[j + 1] = true;
+			idx[j + 2] = ACC_INF + (sp * 2 + ((flag2 >> sp) & 1)) * 2, add[j + 2] = u0, en[j + 2] = (vis >> sp) & 1;
+			idx[j + 3] = idx[j + 2] + 1, add[j + 3] = u1, en[j + 3] = en[j + 2];
+			idx[j + 4] = ACC_INF + (gs * 2 + ((flag2 >> gs) & 1)) * 2, add[j + 4] = u0, en[j + 4] = en[j + 2] && ((vis >> gs) & 1);
+			idx[j + 5] = idx[j + 4] + 1, add[j + 5] = u1, en[j + 5] = en[j + 4];
 		}
-		// homozyg (:5571-5575): rho0[al] * hfd[al][f] * Q1(al, 0) / Q1(plain)
-		acc[(ACC_HZ + 0) * 32] += V * T0[1] * (f ? hf11 : hf10) * T1[3];
-		acc[(ACC_HZ + 1) * 32] += V * T0[2] * (f ? hf21 : hf20) * T1[4];
+		// homozyg: rho0[al] * hfd[al][f] * Q1(al, 0) / Q1(plain)
+		idx[22] = ACC_HZ + 0, add[22] = V * T0[1] * (f ? hf11 : hf10) * T1[3], en[22] = true;
+		idx[23] = ACC_HZ + 1, add[23] = V * T0[2] * (f ? hf21 : hf20) * T1[4], en[23] = true;
+		double cur[24];
+#pragma unroll
+		for (int j = 0; j < 24; j++)
+			if (en[j]) cur[j] = acc[idx[j] * 32];
+#pragma unroll
+		for (int j = 0; j < 24; j++)
+			if (en[j]) acc[idx[j] * 32] = cur[j] + add[j];
 	}
 }
 
@@ -525,15 +521,16 @@ __global__ void __launch_bounds__(32) warp_estep_kernel(WarpArgs wa)
 				for (int k = lane; k < NACC; k += 32)
 				{
 					double* col = w.acc + k * 32;
-					double v = 0;
-#pragma unroll 8
-					for (int j = 0; j < 32; j++)
+					double v0 = 0, v1 = 0, v2 = 0, v3 = 0;
+#pragma unroll
+					for (int j = 0; j < 32; j += 4)
 					{
-						double* q = col + ((j + lane) & 31);
-						v += *q;
-						*q = 0;
+						double *q0 = col + ((j + lane) & 31), *q1 = col + ((j + 1 + lane) & 31), *q2 = col + ((j + 2 + lane) & 31),
+						       *q3 = col + ((j + 3 + lane) & 31);
+						v0 += *q0, v1 += *q1, v2 += *q2, v3 += *q3;
+						*q0 = 0, *q1 = 0, *q2 = 0, *q3 = 0;
 					}
-					w.tot[k] = v;
+					w.tot[k] = (v0 + v1) + (v2 + v3);
 				}
 				__syncwarp();
 				// transfer into the EM sufficient statistics (:5875-5904, moveinfprobs :3577-3597, movehaplos :3599-3616)
