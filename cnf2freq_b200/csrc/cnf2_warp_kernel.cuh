@@ -180,6 +180,56 @@ __device__ __forceinline__ void warp_posterior(WarpSmem& w, const Unit& u, int h
 	}
 }
 
+// Transfer of one marker's reduced accumulators into the EM sufficient statistics (cnF2freq.cpp:5875-5904,
+// moveinfprobs :3577-3597, movehaplos :3599-3616; same arithmetic as transfer_stats), one lane per output:
+// relative r, q = 0 haplobase, 1 haplocount, 2..5 infprobs, 6..7 homozyg (root only).
+__device__ __forceinline__ void transfer_lane(const EstepArgs& a, const Unit& u, const double* __restrict__ tot, const double* __restrict__ HW,
+                                              int r, int q, int t, int m)
+{
+	const int rootrel = u.slotrel[0];
+	if (q >= 6 && r != rootrel) return;
+	double rootsum = 0, h0 = 0, h1 = 0, ip = 0, w = 0;
+#pragma unroll
+	for (int slot = 0; slot < NSLOTS; slot++)
+	{
+		if (u.row[slot] < 0) continue;
+		const int rel = u.slotrel[slot];
+		if (rel == rootrel) rootsum += tot[ACC_INF + slot * 4 + 0] + tot[ACC_INF + slot * 4 + 1];
+		if (rel == r)
+		{
+			h0 += tot[ACC_HAPLOS + slot * 2 + 0];
+			h1 += tot[ACC_HAPLOS + slot * 2 + 1];
+			ip += tot[ACC_INF + slot * 4 + ((q - 2) & 3)];
+			w = HW[slot * WB + t];  // the relative's own haploweight; any of its slots holds it
+		}
+	}
+	const size_t Mc = a.Mc;
+	const int srow = u.relrow[r];
+	const bool sh = srow < a.n_shared;
+	double* base = sh ? a.stats_shared : a.stats_local;
+	const size_t nr = sh ? a.n_shared : a.n_local, cell = (size_t)(sh ? srow : srow - a.n_shared) * Mc + m, plane = nr * Mc;
+	if (q < 2)
+	{
+		if ((h0 != 0 || h1 != 0) && fabs(w - 0.5) < 0.5 - 1e-12)
+		{
+			const double eps = 1.9151695967140057e-174 * (double)(0.000005f) * (double)(0.000005f) * 0.5;  // exp(-400) * maxdiff^2 / 2, :228
+			const double x1 = h0 + eps, x2 = h1 + eps;
+			atomicAdd(base + q * plane + cell, q ? u.descendants : x1 / (x1 + x2) * u.descendants);
+		}
+	}
+	else if (q < 6)
+	{
+		if (ip != 0)
+		{
+			double norm = 1.0 / rootsum * 2;
+			for (int k = 0; k < u.relhalvings[r]; k++) norm /= 2;
+			norm *= u.descendants;
+			atomicAdd(base + 2 * plane + cell * 4 + (q - 2), ip * norm);
+		}
+	}
+	else atomicAdd(base + 6 * plane + cell * 2 + (q - 6), tot[ACC_HZ + q - 6] * (1.0 / rootsum));
+}
+
 // ---- sweeps: lane = shift * 4 + gh, state g = r | gh << 4, r = 0..15 in registers ----
 
 // Transition (cnF2freq.cpp:2270-2367): bits 0-3 inside the lane, bits 4-5 across lanes 1 and 2 apart.
@@ -534,7 +584,12 @@ __global__ void __launch_bounds__(32) warp_estep_kernel(WarpArgs wa)
 				}
 				__syncwarp();
 				// transfer into the EM sufficient statistics (:5875-5904, moveinfprobs :3577-3597, movehaplos :3599-3616)
-				if (lane < u.nrel) transfer_stats(a, u, w.tot, w.HW, lane, t, m, WB);
+				for (int i = lane; i < u.nrel * 6 + 2; i += 32)
+				{
+					const int n6 = u.nrel * 6;
+					if (i < n6) transfer_lane(a, u, w.tot, w.HW, i / 6, i % 6, t, m);
+					else transfer_lane(a, u, w.tot, w.HW, u.slotrel[0], 6 + i - n6, t, m);
+				}
 				if (m > 0)
 				{
 					emit16(b, w.qh + t * QS, lane);
