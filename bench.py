@@ -162,6 +162,16 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def traffic_from_profile(per_launch_im):
+    """dram__bytes_read.sum + dram__bytes_write.sum of warp_estep_kernel from the committed ncu --set full capture
+    (profiles/r1_warp_kernel_traffic.json: bytes per individual-marker of that capture), scaled to this launch."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "r1_warp_kernel_traffic.json")))
+        return t["dram_bytes_per_individual_marker"] * per_launch_im
+    except (OSError, ValueError, KeyError):
+        return None
+
+
 def measured_peaks():
     try:
         return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -278,10 +288,10 @@ def ours(a, rank, world, local_rank):
         by = per_launch_im * BYTES_PER_INDMARKER / (launch_ms * 1e-3) * 1e-9
         t_fp64 = per_launch_im * FLOP_PER_INDMARKER / (dfma_tflops * 1e12)
         t_hbm = per_launch_im * BYTES_PER_INDMARKER / (hbm_peak * 1e9)
-        roof = {"bound": "fp64" if t_fp64 >= t_hbm else "hbm", "kernel": "cnf2::fast_estep_kernel (+ the literal cnf2::estep_kernel for the units it hands over; none in this workload)",
+        roof = {"bound": "fp64" if t_fp64 >= t_hbm else "hbm", "kernel": "cnf2::warp_estep_kernel (+ the literal cnf2::estep_kernel for the units it hands over; none in this workload)",
                 "achieved": fl if t_fp64 >= t_hbm else by, "peak": dfma_tflops if t_fp64 >= t_hbm else hbm_peak,
                 "unit": "TFLOP/s" if t_fp64 >= t_hbm else "GB/s",
-                "frac": (fl / dfma_tflops) if t_fp64 >= t_hbm else by / hbm_peak, "traffic": None,
+                "frac": (fl / dfma_tflops) if t_fp64 >= t_hbm else by / hbm_peak, "traffic": traffic_from_profile(per_launch_im),
                 "launch_ms": launch_ms,
                 "peak_source": "fp64: register-resident DFMA kernel measured in this run (MEASURED_PEAKS.json has no fp64 "
                                "figure); hbm: MEASURED_PEAKS.json" + ("" if peaks else " absent -> fallback 6650 GB/s"),
