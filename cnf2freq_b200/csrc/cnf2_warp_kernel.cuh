@@ -38,7 +38,7 @@ struct __align__(16) WarpSmem
 	uchar2 A[NSLOTS * WB];
 	unsigned char xl[NUMPATHS];
 	unsigned char el[128];
-	int nX, nE, listtag;
+	int nX, nE, nE0, listtag;
 	int homslot[WB], gpmust[WB];
 	Unit unit;
 };
@@ -176,6 +176,104 @@ __device__ __forceinline__ void warp_posterior(WarpSmem& w, const Unit& u, int h
 			if (en[j]) cur[j] = acc[idx[j] * 32];
 #pragma unroll
 		for (int j = 0; j < 24; j++)
+			if (en[j]) acc[idx[j] * 32] = cur[j] + add[j];
+	}
+}
+
+// Posterior of the current marker, pairwise form.  A surviving term factorises as
+//   val = rbase[f] * E0[f][cfg0] * E1[f][cfg1] * sum_s Wr[f ^ s0] Wp0[x1 ^ s1] Wp1[x4 ^ s2] W_s[g0 | g1 << 3]
+// and every scatter target of :5556-5575 depends on the term only through (f, cfg0) [root as side 0, parent 0's
+// subtree] or (f, cfg1) [root as side 1, parent 1's subtree]; homozyg is a product of one factor of each side.
+// One lane owns one (side, local configuration, root orientation) entry, runs over the compatible entries of
+// the OTHER side (rule 2 of ignoreflag2 couples the sides through Unit::xmask2) summing in registers, and
+// scatters its sums once.  Every (x, g) pair is visited twice, once from each side, with no memory traffic but
+// the W and table reads.  The unusualstate cut of single terms (val > e^-200, :5414) is not applied here (it
+// removes at most e^-200 of the posterior mass); whole shift modes below it are cut where W is formed.
+__device__ __forceinline__ void warp_posterior_pairs(WarpSmem& w, const Unit& u, int homslot, int lane)
+{
+	const double* rc = w.rootc;
+	double* const acc = w.acc + lane;
+	const int vis = u.vismask, hmask = vis & ~homslot;
+	const int nE = w.nE, nE0 = w.nE0;
+	for (int i = lane; i < 2 * nE; i += 32)
+	{
+		const int c = w.el[i >> 1], f = i & 1;
+		const int p = c >> 6, cfg = c & 63;
+		const int gown = cfg & 7, xown = gown ^ (cfg >> 3);
+		// phase weights: own parent at its shift bit 0 / 1, and the table of the other parent
+		const double own0 = rc[12 + p * 2 + (xown & 1)], own1 = rc[12 + p * 2 + ((xown & 1) ^ 1)];
+		const double* wo = rc + 12 + (p ^ 1) * 2;
+		const double rA = rc[2 + f], rB = rc[2 + (f ^ 1)];  // root at s0 = 0, 1
+		// W_s[g] at s = s0 + 2 s1 + 4 s2: stride of the own / the other parent's shift bit
+		const int strOwn = (p ? 4 : 2) * 4 * WTS, strOth = (p ? 2 : 4) * 4 * WTS;
+		const int gshift = p ? 0 : 3;
+		const double* Wbase = w.Wt + (p ? ((gown << 3) >> 4) * WTS + ((gown << 3) & 15) : gown);
+		const double* Tp = p ? w.tab0 + f * 64 * T0W : w.tab1 + f * 64 * T1W;
+		const int tw = p ? T0W : T1W;
+		const int jlo = p ? 0 : nE0, jhi = p ? nE0 : nE;
+		double Sz0 = 0, Sz1 = 0, So0 = 0, So1 = 0, Sx1 = 0, Sx2 = 0;
+		for (int j = jlo; j < jhi; j++)
+		{
+			const int co = w.el[j] & 63, goth = co & 7, xoth = goth ^ (co >> 3);
+			const int x = f | ((p ? xoth : xown) << 1) | ((p ? xown : xoth) << 4);
+			if (!((u.xmask2[x >> 5] >> (x & 31)) & 1)) continue;  // rule 2 (:3483-3486)
+			const int go = goth << gshift;
+			const double* W = Wbase + (go >> 4) * WTS + (go & 15);
+			const double* T = Tp + co * tw;
+			const double E = T[0];
+			const double q0 = wo[xoth & 1], q1 = wo[(xoth & 1) ^ 1];  // other parent at its shift bit 0 / 1
+			const double A00 = rA * W[0], B00 = rB * W[4 * WTS];
+			const double A01 = rA * W[strOth], B01 = rB * W[4 * WTS + strOth];
+			const double A10 = rA * W[strOwn], B10 = rB * W[4 * WTS + strOwn];
+			const double A11 = rA * W[strOwn + strOth], B11 = rB * W[4 * WTS + strOwn + strOth];
+			const double z0 = own0 * (q0 * A00 + q1 * A01) + own1 * (q0 * A10 + q1 * A11);  // s0 = 0
+			const double z1 = own0 * (q0 * B00 + q1 * B01) + own1 * (q0 * B10 + q1 * B11);  // s0 = 1
+			const double o0 = own0 * (q0 * (A00 + B00) + q1 * (A01 + B01));                // own shift bit 0
+			const double o1 = own1 * (q0 * (A10 + B10) + q1 * (A11 + B11));                // own shift bit 1
+			Sz0 += E * z0;
+			Sz1 += E * z1;
+			So0 += E * o0;
+			So1 += E * o1;
+			if (!p)
+			{
+				const double tot = E * (o0 + o1);
+				Sx1 += tot * T[3];
+				Sx2 += tot * T[4];
+			}
+		}
+		const double* To = p ? w.tab1 + (f * 64 + cfg) * T1W : w.tab0 + (f * 64 + cfg) * T0W;
+		const double F = rc[f] * To[0];
+		Sz0 *= F, Sz1 *= F, So0 *= F, So1 *= F;
+		const double S = So0 + So1;
+		if (!(S > 0)) continue;
+		const int sp = 1 + 3 * p, o_ = cfg >> 3;
+		const int gs = sp + 1 + (gown & 1);
+		const double u0 = S * To[1], u1 = S * To[2];
+		int idx[14];
+		double add[14];
+		bool en[14];
+		idx[0] = ACC_HAPLOS + f, add[0] = Sz0, en[0] = !p && (hmask & 1);            // root: s0 = 0 -> bit f
+		idx[1] = ACC_HAPLOS + (f ^ 1), add[1] = Sz1, en[1] = en[0];
+		idx[2] = ACC_HAPLOS + sp * 2 + (xown & 1), add[2] = So0, en[2] = (hmask >> sp) & 1;
+		idx[3] = ACC_HAPLOS + sp * 2 + ((xown & 1) ^ 1), add[3] = So1, en[3] = en[2];
+		idx[4] = ACC_HAPLOS + (sp + 1) * 2 + ((xown >> 1) & 1), add[4] = S, en[4] = (hmask >> (sp + 1)) & 1;
+		idx[5] = ACC_HAPLOS + (sp + 2) * 2 + ((xown >> 2) & 1), add[5] = S, en[5] = (hmask >> (sp + 2)) & 1;
+		// the GENOS calls of side p (:5560-5568): root at orientation f ^ side, the parent, its parent picked by the meiosis bit
+		idx[6] = ACC_INF + (f ^ p) * 2, add[6] = u0, en[6] = true;
+		idx[7] = idx[6] + 1, add[7] = u1, en[7] = true;
+		idx[8] = ACC_INF + (sp * 2 + (o_ & 1)) * 2, add[8] = u0, en[8] = (vis >> sp) & 1;
+		idx[9] = idx[8] + 1, add[9] = u1, en[9] = en[8];
+		idx[10] = ACC_INF + (gs * 2 + ((o_ >> (gs - sp)) & 1)) * 2, add[10] = u0, en[10] = en[8] && ((vis >> gs) & 1);
+		idx[11] = idx[10] + 1, add[11] = u1, en[11] = en[10];
+		// homozyg (:5571-5575): rho0[al] * hfd[al][f] * sum over the other side of val * Q1(al, 0) / Q1(plain)
+		idx[12] = ACC_HZ + 0, add[12] = F * Sx1 * To[1] * rc[8 + f], en[12] = !p;
+		idx[13] = ACC_HZ + 1, add[13] = F * Sx2 * To[2] * rc[10 + f], en[13] = !p;
+		double cur[14];
+#pragma unroll
+		for (int j = 0; j < 14; j++)
+			if (en[j]) cur[j] = acc[idx[j] * 32];
+#pragma unroll
+		for (int j = 0; j < 14; j++)
 			if (en[j]) acc[idx[j] * 32] = cur[j] + add[j];
 	}
 }
@@ -356,7 +454,7 @@ __device__ __forceinline__ bool raw_commit(WarpSmem& w, const RawItem& r, int la
 __device__ __forceinline__ void warp_lists(WarpSmem& w, const Unit& u, int gpmust, int lane)
 {
 	const unsigned FULL = 0xffffffffu;
-	int nX = 0, nE = 0;
+	int nX = 0, nE = 0, nE0 = 0;
 #pragma unroll
 	for (int r4 = 0; r4 < 4; r4++)
 	{
@@ -375,11 +473,13 @@ __device__ __forceinline__ void warp_lists(WarpSmem& w, const Unit& u, int gpmus
 		const unsigned mask = __ballot_sync(FULL, ok);
 		if (ok) w.el[nE + __popc(mask & ((1u << lane) - 1u))] = (unsigned char)c;
 		nE += __popc(mask);
+		if (r4 == 1) nE0 = nE;  // entries of parent 0 come first
 	}
 	if (lane == 0)
 	{
 		w.nX = nX;
 		w.nE = nE;
+		w.nE0 = nE0;
 		w.listtag = gpmust;
 	}
 	__syncwarp();
@@ -565,7 +665,7 @@ __global__ void __launch_bounds__(32) warp_estep_kernel(WarpArgs wa)
 					post_entry1(u, w.A, w.nt, w.rootc, t, c >> 6, c & 63, i & 1, w.tab0, w.tab1);
 				}
 				__syncwarp();
-				warp_posterior(w, u, w.homslot[t], lane);
+				warp_posterior_pairs(w, u, w.homslot[t], lane);
 				__syncwarp();
 				// the warp reduces its 32 accumulator columns; the reader clears what it read
 				for (int k = lane; k < NACC; k += 32)
