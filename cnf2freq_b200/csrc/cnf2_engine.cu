@@ -81,6 +81,7 @@ struct cnf2_engine
 	DevBuf<int32_t> d_literal, d_kexp;
 	DevBuf<double> d_qstash;
 	int n_ctas_batch = 0, n_ctas_warp = 0;
+	int cap0 = 64, cap1 = 64;  // posterior table capacities of the warp kernel for this pedigree
 	bool use_batch = false;  // A-B switch: CNF2_KERNEL=batch runs the CTA-per-unit batched kernel
 	bool use_fast = false;  // A-B switch: CNF2_KERNEL=fast runs the older table-driven kernel instead of the batched one
 	int n_ctas_literal = 0;
@@ -200,15 +201,10 @@ extern "C" int cnf2_create(cnf2_engine** out, const cnf2_settings* settings)
 	if (per_sm < 1) per_sm = 1;
 	if (settings->ctas_per_sm > 0) per_sm = std::min(per_sm, settings->ctas_per_sm);
 	e->n_ctas_batch = per_sm * e->n_sm;
-	if ((ce = cudaFuncSetAttribute(warp_estep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(WarpSmem))) != cudaSuccess)
+	if ((ce = cudaFuncSetAttribute(warp_estep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)warp_smem_bytes(64, 64))) != cudaSuccess)
 		return bail(ce, "cudaFuncSetAttribute(warp_estep_kernel)");
 	if ((ce = cudaFuncSetAttribute(warp_estep_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100)) != cudaSuccess)
 		return bail(ce, "cudaFuncSetAttribute(warp_estep_kernel carveout)");
-	if ((ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, warp_estep_kernel, 32, sizeof(WarpSmem))) != cudaSuccess)
-		return bail(ce, "occupancy query");
-	if (per_sm < 1) per_sm = 1;
-	if (settings->ctas_per_sm > 0) per_sm = std::min(per_sm, settings->ctas_per_sm);
-	e->n_ctas_warp = per_sm * e->n_sm;
 	const char* kn = getenv("CNF2_KERNEL");
 	e->use_fast = kn && std::string(kn) == "fast";
 	e->use_batch = kn && std::string(kn) == "batch";
@@ -490,6 +486,20 @@ extern "C" int cnf2_set_pedigree(cnf2_engine* e, int32_t n_ind, const int32_t* p
 			}
 		}
 	}
+	// warp kernel: posterior table capacities = the largest number of subtree configurations any unit uses
+	e->cap0 = e->cap1 = 1;
+	for (const Unit& u : e->units)
+	{
+		e->cap0 = std::max(e->cap0, __builtin_popcountll(u.cfgmask[0]));
+		e->cap1 = std::max(e->cap1, __builtin_popcountll(u.cfgmask[1]));
+	}
+	{
+		int per_sm = 0;
+		CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, warp_estep_kernel, 32, warp_smem_bytes(e->cap0, e->cap1)));
+		if (per_sm < 1) per_sm = 1;
+		if (e->settings.ctas_per_sm > 0) per_sm = std::min(per_sm, e->settings.ctas_per_sm);
+		e->n_ctas_warp = per_sm * e->n_sm;
+	}
 	CU(e->d_units.ensure(e->units.size()));
 	if (!e->units.empty())
 		CU(cudaMemcpyAsync(e->d_units.p, e->units.data(), e->units.size() * sizeof(Unit), cudaMemcpyHostToDevice, e->stream));
@@ -606,7 +616,10 @@ extern "C" int cnf2_estep(cnf2_engine* e, int32_t chrom)
 			if (e->use_batch)
 				batch_estep_kernel<<<std::max(1, std::min(e->n_ctas_batch, n_units)), NTHREADS, sizeof(BatchSmem), e->stream>>>(bargs);
 			else  // one warp per unit
-				warp_estep_kernel<<<std::max(1, std::min(e->n_ctas_warp, n_units)), 32, sizeof(WarpSmem), e->stream>>>(bargs);
+			{
+				WarpArgs wargs{ bargs, e->cap0, e->cap1 };
+				warp_estep_kernel<<<std::max(1, std::min(e->n_ctas_warp, n_units)), 32, warp_smem_bytes(e->cap0, e->cap1), e->stream>>>(wargs);
+			}
 			CU(cudaGetLastError());
 			e->last_launches++;
 			a.unit_list = e->d_literal.p;

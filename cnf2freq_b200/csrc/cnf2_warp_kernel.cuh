@@ -23,29 +23,31 @@ namespace cnf2
 constexpr int WB = TB;        // markers staged at a time (the stride gfix / root_constants expect)
 constexpr int WTS = 17;       // row stride of the transposed W (doubles): conflict-free 64-bit stores
 constexpr int T0W = 3, T1W = 5;
+constexpr int NCOL = 8;       // accumulator columns; lanes scatter in 32 / NCOL passes
+constexpr int ACS = NCOL + 1; // row stride of the accumulators (doubles)
 
 struct __align__(16) WarpSmem
 {
-	double acc[NACC * 32];
+	double acc[NACC * ACS];
 	double Wt[32 * WTS];           // [shift * 4 + (g >> 4)][g & 15]
-	double tab0[2 * 64 * T0W];     // [f][cfg]: Q(plain), rho0[1], rho0[2]
-	double tab1[2 * 64 * T1W];     // [f][cfg]: Q(plain), rho1[1], rho1[2], Q(1,0)/Q(plain), Q(2,0)/Q(plain)
 	double qh[WB * QS];
 	NodeTab nt[NSLOTS * WB];
 	double HW[NSLOTS * WB];
 	double tot[NACC];
 	double rootc[RC];
 	uchar2 A[NSLOTS * WB];
-	unsigned char xl[NUMPATHS];
 	unsigned char el[128];
-	int nX, nE, nE0, listtag;
+	int nE, nE0, listtag;
 	int homslot[WB], gpmust[WB];
 	Unit unit;
+	// followed by the posterior tables of the current marker, sized by the host for the pedigree (WarpArgs::cap0/cap1):
+	//   tab0[cap0][f][T0W]: Q(plain), rho0[1], rho0[2];  tab1[cap1][f][T1W]: Q(plain), rho1[1], rho1[2], Q(al,0)/Q(plain)
+	// entry k of a table is the k-th needed configuration of that parent at this marker (its position in el)
 };
 
 // One (entry, root orientation) pair of the posterior tables of marker t (see post_entry in cnf2_batch_kernel.cuh).
 __device__ __forceinline__ void post_entry1(const Unit& u, const uchar2* A, const NodeTab* N, const double* __restrict__ rc, int t, int p,
-                                            int cfg, int f, double* __restrict__ tab0, double* __restrict__ tab1)
+                                            int cfg, int f, double* __restrict__ e)
 {
 	const int m = cfg & 1, ma = (cfg >> 1) & 1, mb = (cfg >> 2) & 1, o = (cfg >> 3) & 1, oa = (cfg >> 4) & 1, ob = (cfg >> 5) & 1;
 	const int sp = 1 + 3 * p;
@@ -71,7 +73,6 @@ __device__ __forceinline__ void post_entry1(const Unit& u, const uchar2* A, cons
 	const double P1 = Q(1, 0.0), P2 = Q(2, 0.0);
 	if (p == 0)
 	{
-		double* e = tab0 + (f * 64 + cfg) * T0W;
 		const int v = f ? a0.y : a0.x;
 		e[0] = Q(v, v != UNKNOWN ? n0.RN[f] : 0.0);
 		const double A1 = rc[4 + f] * P1, A2 = rc[6 + f] * P2;
@@ -81,7 +82,6 @@ __device__ __forceinline__ void post_entry1(const Unit& u, const uchar2* A, cons
 	}
 	else
 	{
-		double* e = tab1 + (f * 64 + cfg) * T1W;
 		const int v = f ? a0.x : a0.y;
 		const double E = Q(v, n0.SEC[f ^ 1]);
 		e[0] = E;
@@ -94,92 +94,6 @@ __device__ __forceinline__ void post_entry1(const Unit& u, const uchar2* A, cons
 	}
 }
 
-// Posterior of the current marker: dense enumeration of the (x, g) pairs, 8 shift modes per pair
-// (batch_posterior's scheme on this kernel's layouts).  rootc[12..15] = phase weights of parent 0 / parent 1.
-__device__ __forceinline__ void warp_posterior(WarpSmem& w, const Unit& u, int homslot, int lane)
-{
-	const double* rc = w.rootc;
-	double* const acc = w.acc + lane;
-	const int nfree = u.nfree, gfix_ = u.gfixmask;
-	const int T = w.nX << nfree;
-	const int vis = u.vismask, hmask = vis & ~homslot;
-	const double wp00 = rc[12], wp01 = rc[13], wp10 = rc[14], wp11 = rc[15];
-	const double hf10 = rc[8], hf11 = rc[9], hf20 = rc[10], hf21 = rc[11];
-	for (int i = lane; i < T; i += 32)
-	{
-		const int x = w.xl[i >> nfree];
-		const int g = ((x >> 1) & gfix_) | u.expand[i & ((1 << nfree) - 1)];
-		const int flag2 = x ^ (g << 1);
-		const int f = x & 1, x1 = (x >> 1) & 1, x4 = (x >> 4) & 1;
-		const int cfg0 = (g & 7) | (((flag2 >> 1) & 7) << 3), cfg1 = ((g >> 3) & 7) | (((flag2 >> 4) & 7) << 3);
-		const double* T0 = w.tab0 + (f * 64 + cfg0) * T0W;
-		const double* T1 = w.tab1 + (f * 64 + cfg1) * T1W;
-		const double ep = rc[f] * T0[0] * T1[0];
-		if (!(ep > 0)) continue;
-		// the 8 shift modes: s = s0 | s1 << 1 | s2 << 2 flips the phase-weight index of root / parent 0 / parent 1
-		const double r0 = ep * rc[2 + f], r1 = ep * rc[2 + (f ^ 1)];
-		const double a0 = x1 ? wp01 : wp00, a1 = x1 ? wp00 : wp01;  // parent 0 at s1 = 0, 1
-		const double b0 = x4 ? wp11 : wp10, b1 = x4 ? wp10 : wp11;  // parent 1 at s2 = 0, 1
-		const double c00 = a0 * b0, c10 = a1 * b0, c01 = a0 * b1, c11 = a1 * b1;  // [s1][s2]
-		const double* W = w.Wt + (g >> 4) * WTS + (g & 15);
-		double ts[8];
-		ts[0] = r0 * c00 * W[0 * 4 * WTS];
-		ts[1] = r1 * c00 * W[1 * 4 * WTS];
-		ts[2] = r0 * c10 * W[2 * 4 * WTS];
-		ts[3] = r1 * c10 * W[3 * 4 * WTS];
-		ts[4] = r0 * c01 * W[4 * 4 * WTS];
-		ts[5] = r1 * c01 * W[5 * 4 * WTS];
-		ts[6] = r0 * c11 * W[6 * 4 * WTS];
-		ts[7] = r1 * c11 * W[7 * 4 * WTS];
-#pragma unroll
-		for (int s = 0; s < 8; s++) ts[s] = ts[s] > EXP_M200_B ? ts[s] : 0.0;  // unusualstate, :5414, 5502
-		const double p01 = ts[0] + ts[1], p23 = ts[2] + ts[3], p45 = ts[4] + ts[5], p67 = ts[6] + ts[7];
-		const double V = (p01 + p23) + (p45 + p67);
-		if (!(V > 0)) continue;
-		// Scatter: updatehaplo (:1561-1575) adds to every visited, non-homozygous slot at its effective phase bit
-		// x_k ^ s_k; the four GENOS calls (:5560-5568) add to the root, parent `side` and that parent's parent picked
-		// by its meiosis bit; homozyg (:5571-5575).  The 24 targets of one pair are distinct columns entries, so all
-		// are read before any is written (the loads overlap instead of forming one chain).
-		int idx[24];
-		double add[24];
-		bool en[24];
-		idx[0] = ACC_HAPLOS + f, add[0] = (ts[0] + ts[2]) + (ts[4] + ts[6]), en[0] = hmask & 1;            // s0 = 0: bit f
-		idx[1] = ACC_HAPLOS + (f ^ 1), add[1] = (ts[1] + ts[3]) + (ts[5] + ts[7]), en[1] = hmask & 1;      // s0 = 1
-		idx[2] = ACC_HAPLOS + 2 + x1, add[2] = p01 + p45, en[2] = hmask & 2;
-		idx[3] = ACC_HAPLOS + 2 + (x1 ^ 1), add[3] = p23 + p67, en[3] = hmask & 2;
-		idx[4] = ACC_HAPLOS + 8 + x4, add[4] = p01 + p23, en[4] = hmask & 16;
-		idx[5] = ACC_HAPLOS + 8 + (x4 ^ 1), add[5] = p45 + p67, en[5] = hmask & 16;
-		idx[6] = ACC_HAPLOS + 4 + ((x >> 2) & 1), add[6] = V, en[6] = hmask & 4;
-		idx[7] = ACC_HAPLOS + 6 + ((x >> 3) & 1), add[7] = V, en[7] = hmask & 8;
-		idx[8] = ACC_HAPLOS + 10 + ((x >> 5) & 1), add[8] = V, en[8] = hmask & 32;
-		idx[9] = ACC_HAPLOS + 12 + ((x >> 6) & 1), add[9] = V, en[9] = hmask & 64;
-#pragma unroll
-		for (int side = 0; side < 2; side++)
-		{
-			const double* Ts = side ? T1 : T0;
-			const double u0 = V * Ts[1], u1 = V * Ts[2];
-			const int sp = 1 + 3 * side, gs = sp + 1 + ((g >> (3 * side)) & 1);
-			const int j = 10 + side * 6;
-			idx[j] = ACC_INF + (f ^ side) * 2, add[j] = u0, en[j] = true;
-			idx[j + 1] = idx[j] + 1, add[j + 1] = u1, en[j + 1] = true;
-			idx[j + 2] = ACC_INF + (sp * 2 + ((flag2 >> sp) & 1)) * 2, add[j + 2] = u0, en[j + 2] = (vis >> sp) & 1;
-			idx[j + 3] = idx[j + 2] + 1, add[j + 3] = u1, en[j + 3] = en[j + 2];
-			idx[j + 4] = ACC_INF + (gs * 2 + ((flag2 >> gs) & 1)) * 2, add[j + 4] = u0, en[j + 4] = en[j + 2] && ((vis >> gs) & 1);
-			idx[j + 5] = idx[j + 4] + 1, add[j + 5] = u1, en[j + 5] = en[j + 4];
-		}
-		// homozyg: rho0[al] * hfd[al][f] * Q1(al, 0) / Q1(plain)
-		idx[22] = ACC_HZ + 0, add[22] = V * T0[1] * (f ? hf11 : hf10) * T1[3], en[22] = true;
-		idx[23] = ACC_HZ + 1, add[23] = V * T0[2] * (f ? hf21 : hf20) * T1[4], en[23] = true;
-		double cur[24];
-#pragma unroll
-		for (int j = 0; j < 24; j++)
-			if (en[j]) cur[j] = acc[idx[j] * 32];
-#pragma unroll
-		for (int j = 0; j < 24; j++)
-			if (en[j]) acc[idx[j] * 32] = cur[j] + add[j];
-	}
-}
-
 // Posterior of the current marker, pairwise form.  A surviving term factorises as
 //   val = rbase[f] * E0[f][cfg0] * E1[f][cfg1] * sum_s Wr[f ^ s0] Wp0[x1 ^ s1] Wp1[x4 ^ s2] W_s[g0 | g1 << 3]
 // and every scatter target of :5556-5575 depends on the term only through (f, cfg0) [root as side 0, parent 0's
@@ -189,15 +103,18 @@ __device__ __forceinline__ void warp_posterior(WarpSmem& w, const Unit& u, int h
 // scatters its sums once.  Every (x, g) pair is visited twice, once from each side, with no memory traffic but
 // the W and table reads.  The unusualstate cut of single terms (val > e^-200, :5414) is not applied here (it
 // removes at most e^-200 of the posterior mass); whole shift modes below it are cut where W is formed.
-__device__ __forceinline__ void warp_posterior_pairs(WarpSmem& w, const Unit& u, int homslot, int lane)
+__device__ __forceinline__ void warp_posterior_pairs(WarpSmem& w, const Unit& u, int homslot, int lane, const double* __restrict__ tab0,
+                                                     const double* __restrict__ tab1)
 {
 	const double* rc = w.rootc;
-	double* const acc = w.acc + lane;
+	double* const acc = w.acc + (lane & (NCOL - 1));
 	const int vis = u.vismask, hmask = vis & ~homslot;
 	const int nE = w.nE, nE0 = w.nE0;
-	for (int i = lane; i < 2 * nE; i += 32)
+	for (int ibase = 0; ibase < 2 * nE; ibase += 32)
 	{
-		const int c = w.el[i >> 1], f = i & 1;
+		const int i = ibase + lane;
+		const bool valid = i < 2 * nE;
+		const int c = w.el[valid ? i >> 1 : 0], f = i & 1;
 		const int p = c >> 6, cfg = c & 63;
 		const int gown = cfg & 7, xown = gown ^ (cfg >> 3);
 		// phase weights: own parent at its shift bit 0 / 1, and the table of the other parent
@@ -208,9 +125,9 @@ __device__ __forceinline__ void warp_posterior_pairs(WarpSmem& w, const Unit& u,
 		const int strOwn = (p ? 4 : 2) * 4 * WTS, strOth = (p ? 2 : 4) * 4 * WTS;
 		const int gshift = p ? 0 : 3;
 		const double* Wbase = w.Wt + (p ? ((gown << 3) >> 4) * WTS + ((gown << 3) & 15) : gown);
-		const double* Tp = p ? w.tab0 + f * 64 * T0W : w.tab1 + f * 64 * T1W;
-		const int tw = p ? T0W : T1W;
-		const int jlo = p ? 0 : nE0, jhi = p ? nE0 : nE;
+		const double* Tp = p ? tab0 + f * T0W : tab1 + f * T1W;  // the other parent's table, this root orientation
+		const int tw = 2 * (p ? T0W : T1W);
+		const int jlo = p ? 0 : nE0, jhi = valid ? (p ? nE0 : nE) : jlo;
 		double Sz0 = 0, Sz1 = 0, So0 = 0, So1 = 0, Sx1 = 0, Sx2 = 0;
 		for (int j = jlo; j < jhi; j++)
 		{
@@ -219,7 +136,7 @@ __device__ __forceinline__ void warp_posterior_pairs(WarpSmem& w, const Unit& u,
 			if (!((u.xmask2[x >> 5] >> (x & 31)) & 1)) continue;  // rule 2 (:3483-3486)
 			const int go = goth << gshift;
 			const double* W = Wbase + (go >> 4) * WTS + (go & 15);
-			const double* T = Tp + co * tw;
+			const double* T = Tp + (j - jlo) * tw;
 			const double E = T[0];
 			const double q0 = wo[xoth & 1], q1 = wo[(xoth & 1) ^ 1];  // other parent at its shift bit 0 / 1
 			const double A00 = rA * W[0], B00 = rB * W[4 * WTS];
@@ -241,11 +158,12 @@ __device__ __forceinline__ void warp_posterior_pairs(WarpSmem& w, const Unit& u,
 				Sx2 += tot * T[4];
 			}
 		}
-		const double* To = p ? w.tab1 + (f * 64 + cfg) * T1W : w.tab0 + (f * 64 + cfg) * T0W;
+		const int slot = (valid ? i >> 1 : 0) - (p ? nE0 : 0);
+		const double* To = p ? tab1 + (slot * 2 + f) * T1W : tab0 + (slot * 2 + f) * T0W;
 		const double F = rc[f] * To[0];
 		Sz0 *= F, Sz1 *= F, So0 *= F, So1 *= F;
 		const double S = So0 + So1;
-		if (!(S > 0)) continue;
+		const bool live = valid && S > 0;
 		const int sp = 1 + 3 * p, o_ = cfg >> 3;
 		const int gs = sp + 1 + (gown & 1);
 		const double u0 = S * To[1], u1 = S * To[2];
@@ -268,13 +186,23 @@ __device__ __forceinline__ void warp_posterior_pairs(WarpSmem& w, const Unit& u,
 		// homozyg (:5571-5575): rho0[al] * hfd[al][f] * sum over the other side of val * Q1(al, 0) / Q1(plain)
 		idx[12] = ACC_HZ + 0, add[12] = F * Sx1 * To[1] * rc[8 + f], en[12] = !p;
 		idx[13] = ACC_HZ + 1, add[13] = F * Sx2 * To[2] * rc[10 + f], en[13] = !p;
-		double cur[14];
+		// NCOL lanes at a time add into their own accumulator column; the targets of one entry are distinct, so
+		// all are read before any is written
+#pragma unroll 1
+		for (int pass = 0; pass < 32 / NCOL; pass++)
+		{
+			if (live && (lane / NCOL) == pass)
+			{
+				double cur[14];
 #pragma unroll
-		for (int j = 0; j < 14; j++)
-			if (en[j]) cur[j] = acc[idx[j] * 32];
+				for (int j = 0; j < 14; j++)
+					if (en[j]) cur[j] = acc[idx[j] * ACS];
 #pragma unroll
-		for (int j = 0; j < 14; j++)
-			if (en[j]) acc[idx[j] * 32] = cur[j] + add[j];
+				for (int j = 0; j < 14; j++)
+					if (en[j]) acc[idx[j] * ACS] = cur[j] + add[j];
+			}
+			__syncwarp();
+		}
 	}
 }
 
@@ -454,16 +382,7 @@ __device__ __forceinline__ bool raw_commit(WarpSmem& w, const RawItem& r, int la
 __device__ __forceinline__ void warp_lists(WarpSmem& w, const Unit& u, int gpmust, int lane)
 {
 	const unsigned FULL = 0xffffffffu;
-	int nX = 0, nE = 0, nE0 = 0;
-#pragma unroll
-	for (int r4 = 0; r4 < 4; r4++)
-	{
-		const int x = r4 * 32 + lane;
-		const bool ok = ((u.xmask2[r4] >> lane) & 1) && (x & gpmust) == gpmust;
-		const unsigned mask = __ballot_sync(FULL, ok);
-		if (ok) w.xl[nX + __popc(mask & ((1u << lane) - 1u))] = (unsigned char)x;
-		nX += __popc(mask);
-	}
+	int nE = 0, nE0 = 0;
 #pragma unroll
 	for (int r4 = 0; r4 < 4; r4++)
 	{
@@ -477,7 +396,6 @@ __device__ __forceinline__ void warp_lists(WarpSmem& w, const Unit& u, int gpmus
 	}
 	if (lane == 0)
 	{
-		w.nX = nX;
 		w.nE = nE;
 		w.nE0 = nE0;
 		w.listtag = gpmust;
@@ -485,12 +403,23 @@ __device__ __forceinline__ void warp_lists(WarpSmem& w, const Unit& u, int gpmus
 	__syncwarp();
 }
 
-typedef BatchArgs WarpArgs;  // alpha scratch: [n_warps][Mc][512] doubles in store_alpha's layout
-
-__global__ void __launch_bounds__(32) warp_estep_kernel(WarpArgs wa)
+struct WarpArgs
 {
+	BatchArgs b;          // alpha scratch: [n_warps][Mc][512] doubles in store_alpha's layout
+	int32_t cap0, cap1;   // capacity (entries) of the posterior tables of parent 0 / parent 1
+};
+__host__ __device__ inline size_t warp_smem_bytes(int cap0, int cap1)
+{
+	return sizeof(WarpSmem) + ((size_t)cap0 * 2 * T0W + (size_t)cap1 * 2 * T1W) * sizeof(double);
+}
+
+__global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wargs)
+{
+	const BatchArgs& wa = wargs.b;
 	extern __shared__ __align__(16) unsigned char smem_raw[];
 	WarpSmem& w = *reinterpret_cast<WarpSmem*>(smem_raw);
+	double* const tab0 = reinterpret_cast<double*>(smem_raw + sizeof(WarpSmem));
+	double* const tab1 = tab0 + (size_t)wargs.cap0 * 2 * T0W;
 	const EstepArgs& a = wa.e;
 	const unsigned FULL = 0xffffffffu;
 	const int lane = threadIdx.x, s = lane >> 2;
@@ -499,7 +428,7 @@ __global__ void __launch_bounds__(32) warp_estep_kernel(WarpArgs wa)
 	int32_t* const kexp = wa.kexp + (size_t)blockIdx.x * Mc * NUMSHIFTS;
 	double* const qs = wa.qstash + (size_t)blockIdx.x * Mc * QS;
 
-	for (int i = lane; i < NACC * 32; i += 32) w.acc[i] = 0;
+	for (int i = lane; i < NACC * ACS; i += 32) w.acc[i] = 0;
 
 	for (;;)
 	{
@@ -662,25 +591,24 @@ __global__ void __launch_bounds__(32) warp_estep_kernel(WarpArgs wa)
 				for (int i = lane; i < 2 * w.nE; i += 32)
 				{
 					const int c = w.el[i >> 1];
-					post_entry1(u, w.A, w.nt, w.rootc, t, c >> 6, c & 63, i & 1, w.tab0, w.tab1);
+					const int pp = c >> 6, slot = (i >> 1) - (pp ? w.nE0 : 0);
+					post_entry1(u, w.A, w.nt, w.rootc, t, pp, c & 63, i & 1, pp ? tab1 + (slot * 2 + (i & 1)) * T1W : tab0 + (slot * 2 + (i & 1)) * T0W);
 				}
 				__syncwarp();
-				warp_posterior_pairs(w, u, w.homslot[t], lane);
+				warp_posterior_pairs(w, u, w.homslot[t], lane, tab0, tab1);
 				__syncwarp();
-				// the warp reduces its 32 accumulator columns; the reader clears what it read
+				// the warp reduces its accumulator columns; the reader clears what it read
 				for (int k = lane; k < NACC; k += 32)
 				{
-					double* col = w.acc + k * 32;
-					double v0 = 0, v1 = 0, v2 = 0, v3 = 0;
+					double* col = w.acc + k * ACS;
+					double v0 = 0, v1 = 0;
 #pragma unroll
-					for (int j = 0; j < 32; j += 4)
+					for (int j = 0; j < NCOL; j += 2)
 					{
-						double *q0 = col + ((j + lane) & 31), *q1 = col + ((j + 1 + lane) & 31), *q2 = col + ((j + 2 + lane) & 31),
-						       *q3 = col + ((j + 3 + lane) & 31);
-						v0 += *q0, v1 += *q1, v2 += *q2, v3 += *q3;
-						*q0 = 0, *q1 = 0, *q2 = 0, *q3 = 0;
+						v0 += col[j], v1 += col[j + 1];
+						col[j] = 0, col[j + 1] = 0;
 					}
-					w.tot[k] = (v0 + v1) + (v2 + v3);
+					w.tot[k] = v0 + v1;
 				}
 				__syncwarp();
 				// transfer into the EM sufficient statistics (:5875-5904, moveinfprobs :3577-3597, movehaplos :3599-3616)
