@@ -2,8 +2,6 @@
 // cnF2freq.cpp:3099-3187, leaves behind), device memory, launches.  No CPU compute path exists here:
 // every entry point that would compute needs the CUDA device.
 #include "../../include/cnf2_engine.h"
-#include "cnf2_fast_kernel.cuh"
-#include "cnf2_batch_kernel.cuh"
 #include "cnf2_warp_kernel.cuh"
 
 #include <algorithm>
@@ -25,6 +23,8 @@ struct Run  // consecutive rows holding consecutive individual ids: one 2-D copy
 {
 	int32_t row0, id0, n;
 };
+
+constexpr int NSLOT = 2;  // E-steps of consecutive chromosomes in flight (the tail of one launch overlaps the next)
 
 template <typename T>
 struct DevBuf
@@ -48,16 +48,30 @@ struct DevBuf
 		n = 0;
 	}
 };
+// Everything one in-flight E-step owns: its stream, scratch, statistics and the events around it.
+struct Slot
+{
+	cudaStream_t stream = nullptr;
+	cudaEvent_t ev0 = nullptr, ev1 = nullptr, done = nullptr, tail = nullptr;  // kernels start / end, all-reduce done, mark join
+	DevBuf<double> alpha, alphafac, qstash, stats, loglik;
+	DevBuf<int32_t> kexp, literal;
+	DevBuf<unsigned int> counter;
+	int chrom = -1;
+	int n_shared = 0;
+	double* stats_shared() { return stats.p; }
+	double* stats_local(int Mc) { return stats.p + (size_t)n_shared * Mc * STATS_PER_CELL; }
+};
 }  // namespace
 
 struct cnf2_engine
 {
 	cnf2_settings settings{};
 	std::string error;
-	cudaStream_t stream = nullptr;
-	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+	cudaStream_t stream = nullptr;  // copies of parameters, marks, microbenchmarks
+	cudaStream_t comm = nullptr;    // the all-reduce hook runs here, in call order
+	Slot slots[NSLOT];
+	int next_slot = 0, last_slot = -1;
 	int n_sm = 0;
-	int n_ctas = 0;
 
 	// map
 	std::vector<double> markerpos;
@@ -77,24 +91,18 @@ struct cnf2_engine
 	// device
 	DevBuf<uchar2> d_alleles;
 	DevBuf<double2> d_sure;
-	DevBuf<double> d_hw, d_rec, d_alpha, d_alphafac, d_q, d_stats, d_loglik;
-	DevBuf<int32_t> d_literal, d_kexp;
-	DevBuf<double> d_qstash;
-	int n_ctas_batch = 0, n_ctas_warp = 0;
+	DevBuf<double> d_hw, d_rec;
+	int n_ctas_warp = 0;
 	int cap0 = 64, cap1 = 64;  // posterior table capacities of the warp kernel for this pedigree
-	bool use_batch = false;  // A-B switch: CNF2_KERNEL=batch runs the CTA-per-unit batched kernel
-	bool use_fast = false;  // A-B switch: CNF2_KERNEL=fast runs the older table-driven kernel instead of the batched one
 	int n_ctas_literal = 0;
 	bool literal_only = false;  // debugging / A-B switch: CNF2_LITERAL=1 runs every unit through the literal kernel
 	DevBuf<Unit> d_units;
-	DevBuf<unsigned int> d_counter;
 	std::vector<double> h_loglik;
 
 	// parameters stay resident for every chromosome when they fit (resident), else one chromosome at a time
 	bool resident = false;
 	size_t ld = 0;
 	std::vector<uint8_t> have_params;
-	int estep_chrom = -1;
 	cudaEvent_t marks[4] = { nullptr, nullptr, nullptr, nullptr };
 	int last_launches = 0;
 	cnf2_allreduce_fn allreduce = nullptr;
@@ -111,8 +119,6 @@ struct cnf2_engine
 		return fail(CNF2_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
 	}
 	int mc(int chrom) const { return (int)(chromstarts[chrom + 1] - chromstarts[chrom]); }
-	double* stats_shared() { return d_stats.p; }
-	double* stats_local(int Mc) { return d_stats.p + (size_t)n_shared * Mc * STATS_PER_CELL; }
 };
 
 #define CU(call)                                      \
@@ -177,8 +183,15 @@ extern "C" int cnf2_create(cnf2_engine** out, const cnf2_settings* settings)
 	if ((ce = cudaGetDeviceProperties(&prop, settings->device)) != cudaSuccess) return bail(ce, "cudaGetDeviceProperties");
 	e->n_sm = prop.multiProcessorCount;
 	if ((ce = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(ce, "cudaStreamCreate");
-	if ((ce = cudaEventCreate(&e->ev0)) != cudaSuccess) return bail(ce, "cudaEventCreate");
-	if ((ce = cudaEventCreate(&e->ev1)) != cudaSuccess) return bail(ce, "cudaEventCreate");
+	if ((ce = cudaStreamCreateWithFlags(&e->comm, cudaStreamNonBlocking)) != cudaSuccess) return bail(ce, "cudaStreamCreate");
+	for (Slot& sl : e->slots)
+	{
+		if ((ce = cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(ce, "cudaStreamCreate");
+		if ((ce = cudaEventCreate(&sl.ev0)) != cudaSuccess) return bail(ce, "cudaEventCreate");
+		if ((ce = cudaEventCreate(&sl.ev1)) != cudaSuccess) return bail(ce, "cudaEventCreate");
+		if ((ce = cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming)) != cudaSuccess) return bail(ce, "cudaEventCreate");
+		if ((ce = cudaEventCreateWithFlags(&sl.tail, cudaEventDisableTiming)) != cudaSuccess) return bail(ce, "cudaEventCreate");
+	}
 	if ((ce = cudaFuncSetAttribute(estep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem))) != cudaSuccess)
 		return bail(ce, "cudaFuncSetAttribute(estep_kernel)");
 	int per_sm = 0;
@@ -187,27 +200,10 @@ extern "C" int cnf2_create(cnf2_engine** out, const cnf2_settings* settings)
 	if (per_sm < 1) per_sm = 1;
 	if (settings->ctas_per_sm > 0) per_sm = std::min(per_sm, settings->ctas_per_sm);
 	e->n_ctas_literal = per_sm * e->n_sm;
-	if ((ce = cudaFuncSetAttribute(fast_estep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FastSmem))) != cudaSuccess)
-		return bail(ce, "cudaFuncSetAttribute(fast_estep_kernel)");
-	if ((ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fast_estep_kernel, NTHREADS, sizeof(FastSmem))) != cudaSuccess)
-		return bail(ce, "occupancy query");
-	if (per_sm < 1) per_sm = 1;
-	if (settings->ctas_per_sm > 0) per_sm = std::min(per_sm, settings->ctas_per_sm);
-	e->n_ctas = per_sm * e->n_sm;
-	if ((ce = cudaFuncSetAttribute(batch_estep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BatchSmem))) != cudaSuccess)
-		return bail(ce, "cudaFuncSetAttribute(batch_estep_kernel)");
-	if ((ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, batch_estep_kernel, NTHREADS, sizeof(BatchSmem))) != cudaSuccess)
-		return bail(ce, "occupancy query");
-	if (per_sm < 1) per_sm = 1;
-	if (settings->ctas_per_sm > 0) per_sm = std::min(per_sm, settings->ctas_per_sm);
-	e->n_ctas_batch = per_sm * e->n_sm;
 	if ((ce = cudaFuncSetAttribute(warp_estep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)warp_smem_bytes(64, 64))) != cudaSuccess)
 		return bail(ce, "cudaFuncSetAttribute(warp_estep_kernel)");
 	if ((ce = cudaFuncSetAttribute(warp_estep_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100)) != cudaSuccess)
 		return bail(ce, "cudaFuncSetAttribute(warp_estep_kernel carveout)");
-	const char* kn = getenv("CNF2_KERNEL");
-	e->use_fast = kn && std::string(kn) == "fast";
-	e->use_batch = kn && std::string(kn) == "batch";
 	const char* lit = getenv("CNF2_LITERAL");
 	e->literal_only = lit && lit[0] == '1';
 	*out = e;
@@ -223,20 +219,21 @@ extern "C" void cnf2_destroy(cnf2_engine* e)
 	e->d_sure.release();
 	e->d_hw.release();
 	e->d_rec.release();
-	e->d_alpha.release();
-	e->d_alphafac.release();
-	e->d_q.release();
-	e->d_kexp.release();
-	e->d_qstash.release();
-	e->d_literal.release();
-	e->d_stats.release();
-	e->d_loglik.release();
+	for (Slot& sl : e->slots)
+	{
+		if (sl.stream) cudaStreamSynchronize(sl.stream);
+		sl.alpha.release(), sl.alphafac.release(), sl.qstash.release(), sl.stats.release(), sl.loglik.release();
+		sl.kexp.release(), sl.literal.release(), sl.counter.release();
+		if (sl.ev0) cudaEventDestroy(sl.ev0);
+		if (sl.ev1) cudaEventDestroy(sl.ev1);
+		if (sl.done) cudaEventDestroy(sl.done);
+		if (sl.tail) cudaEventDestroy(sl.tail);
+		if (sl.stream) cudaStreamDestroy(sl.stream);
+	}
+	if (e->comm) cudaStreamSynchronize(e->comm), cudaStreamDestroy(e->comm);
 	e->d_units.release();
-	e->d_counter.release();
 	for (cudaEvent_t m : e->marks)
 		if (m) cudaEventDestroy(m);
-	if (e->ev0) cudaEventDestroy(e->ev0);
-	if (e->ev1) cudaEventDestroy(e->ev1);
 	if (e->stream) cudaStreamDestroy(e->stream);
 	delete e;
 }
@@ -257,7 +254,8 @@ extern "C" int cnf2_set_map(cnf2_engine* e, const double* markerpos, int32_t n_m
 	e->max_mc = 0;
 	for (int c = 0; c < n_chrom; c++) e->max_mc = std::max(e->max_mc, e->mc(c));
 	e->have_params.assign(n_chrom, 0);
-	e->estep_chrom = -1;
+	for (Slot& sl : e->slots) sl.chrom = -1;
+	e->last_slot = -1;
 	return CNF2_OK;
 }
 
@@ -503,13 +501,18 @@ extern "C" int cnf2_set_pedigree(cnf2_engine* e, int32_t n_ind, const int32_t* p
 	CU(e->d_units.ensure(e->units.size()));
 	if (!e->units.empty())
 		CU(cudaMemcpyAsync(e->d_units.p, e->units.data(), e->units.size() * sizeof(Unit), cudaMemcpyHostToDevice, e->stream));
-	CU(e->d_loglik.ensure(e->units.size() * 2));
+	for (Slot& sl : e->slots)
+	{
+		CU(cudaStreamSynchronize(sl.stream));
+		CU(sl.loglik.ensure(e->units.size() * 2));
+		CU(sl.counter.ensure(4));
+		CU(sl.literal.ensure(e->units.size()));
+	}
 	e->h_loglik.assign(e->units.size() * 2, 0.0);
-	CU(e->d_counter.ensure(4));
-	CU(e->d_literal.ensure(e->units.size()));
 	CU(cudaStreamSynchronize(e->stream));
 	std::fill(e->have_params.begin(), e->have_params.end(), 0);
-	e->estep_chrom = -1;
+	for (Slot& sl : e->slots) sl.chrom = -1;
+	e->last_slot = -1;
 	// 26 bytes of parameters per (row, marker): keep all chromosomes on the device when that is a small part of HBM
 	size_t free_b = 0, total_b = 0;
 	CU(cudaMemGetInfo(&free_b, &total_b));
@@ -527,6 +530,8 @@ extern "C" int cnf2_set_params(cnf2_engine* e, int32_t chrom, const uint8_t* all
 	if (chrom < 0 || chrom + 1 >= (int)e->chromstarts.size() || !alleles || !sure || !haploweight)
 		return e->fail(CNF2_ERR_BAD_ARG, "cnf2_set_params: bad argument");
 	cudaSetDevice(e->settings.device);
+	if (!e->resident)  // the buffers hold one chromosome: kernels still reading the previous one finish first
+		for (Slot& sl : e->slots) CU(cudaStreamSynchronize(sl.stream));
 	const size_t M = e->markerpos.size();
 	const size_t c0 = e->chromstarts[chrom];
 	const size_t Mc = e->mc(chrom), ld = e->ld;
@@ -566,21 +571,28 @@ extern "C" int cnf2_estep(cnf2_engine* e, int32_t chrom)
 	cudaSetDevice(e->settings.device);
 	const int Mc = e->mc(chrom);
 	const int n_units = (int)e->units.size();
-	const int n_ctas = std::max(1, std::min(std::max(std::max(std::max(e->n_ctas, e->n_ctas_batch), e->n_ctas_warp), e->n_ctas_literal), n_units));
-	CU(e->d_alpha.ensure((size_t)n_ctas * e->max_mc * NUMSHIFTS * NUMTYPES));
-	CU(e->d_alphafac.ensure((size_t)n_ctas * e->max_mc * NUMSHIFTS));
-	if (e->use_fast) CU(e->d_q.ensure((size_t)n_ctas * e->max_mc * NUMSHIFTS * 32));
-	CU(e->d_kexp.ensure((size_t)n_ctas * e->max_mc * NUMSHIFTS));
-	CU(e->d_qstash.ensure((size_t)n_ctas * e->max_mc * QS));
-	CU(e->d_stats.ensure((size_t)e->n_rows * e->max_mc * STATS_PER_CELL));
-	CU(cudaEventRecord(e->ev0, e->stream));
-	CU(cudaMemsetAsync(e->d_stats.p, 0, (size_t)e->n_rows * Mc * STATS_PER_CELL * sizeof(double), e->stream));
-	CU(cudaMemsetAsync(e->d_counter.p, 0, 4 * sizeof(unsigned int), e->stream));
+	// the next slot; what it held (the E-step before the previous one) is overwritten
+	Slot& sl = e->slots[e->next_slot];
+	e->last_slot = e->next_slot;
+	e->next_slot = (e->next_slot + 1) % NSLOT;
+	for (Slot& o : e->slots)
+		if (o.chrom == chrom) o.chrom = -1;
+	const int n_ctas = std::max(1, std::min(std::max(e->n_ctas_warp, e->n_ctas_literal), n_units));
+	CU(sl.alpha.ensure((size_t)n_ctas * e->max_mc * NUMSHIFTS * NUMTYPES));
+	CU(sl.alphafac.ensure((size_t)std::max(1, std::min(e->n_ctas_literal, n_units)) * e->max_mc * NUMSHIFTS));
+	CU(sl.kexp.ensure((size_t)n_ctas * e->max_mc * NUMSHIFTS));
+	CU(sl.qstash.ensure((size_t)n_ctas * e->max_mc * QS));
+	CU(sl.stats.ensure((size_t)e->n_rows * e->max_mc * STATS_PER_CELL));
+	sl.n_shared = e->n_shared;
+	sl.chrom = chrom;
+	CU(cudaEventRecord(sl.ev0, sl.stream));
+	CU(cudaMemsetAsync(sl.stats.p, 0, (size_t)e->n_rows * Mc * STATS_PER_CELL * sizeof(double), sl.stream));
+	CU(cudaMemsetAsync(sl.counter.p, 0, 4 * sizeof(unsigned int), sl.stream));
 	e->last_launches = 0;
 	if (n_units > 0)
 	{
-		FastArgs fa{};
-		EstepArgs& a = fa.e;
+		WarpArgs wa{};
+		EstepArgs& a = wa.e;
 		const size_t col0 = e->resident ? e->chromstarts[chrom] : 0;
 		a.alleles = e->d_alleles.p + col0;
 		a.sure = e->d_sure.p + col0;
@@ -591,62 +603,46 @@ extern "C" int cnf2_estep(cnf2_engine* e, int32_t chrom)
 		a.n_units = n_units;
 		a.Mc = Mc;
 		a.ld = (int32_t)e->ld;
-		a.counter = e->d_counter.p;
-		a.alpha = e->d_alpha.p;
-		a.alphafac = e->d_alphafac.p;
-		a.stats_shared = e->stats_shared();
-		a.stats_local = e->stats_local(Mc);
+		a.counter = sl.counter.p;
+		a.alpha = sl.alpha.p;
+		a.alphafac = sl.alphafac.p;
+		a.stats_shared = sl.stats_shared();
+		a.stats_local = sl.stats_local(Mc);
 		a.n_shared = e->n_shared;
 		a.n_local = e->n_rows - e->n_shared;
-		a.loglik = e->d_loglik.p;
+		a.loglik = sl.loglik.p;
 		a.unit_list = nullptr;
 		a.list_count = nullptr;
-		fa.qscratch = e->d_q.p;
-		fa.literal_units = e->d_literal.p;
-		fa.literal_count = e->d_counter.p + 1;
-		if (!e->literal_only && !e->use_fast)
+		if (!e->literal_only)
 		{
-			// batched kernel; units it cannot take (founder roots, out-of-range parameters) are listed for the literal one
-			BatchArgs bargs{};
-			bargs.e = a;
-			bargs.kexp = e->d_kexp.p;
-			bargs.qstash = e->d_qstash.p;
-			bargs.literal_units = e->d_literal.p;
-			bargs.literal_count = e->d_counter.p + 1;
-			if (e->use_batch)
-				batch_estep_kernel<<<std::max(1, std::min(e->n_ctas_batch, n_units)), NTHREADS, sizeof(BatchSmem), e->stream>>>(bargs);
-			else  // one warp per unit
-			{
-				WarpArgs wargs{ bargs, e->cap0, e->cap1 };
-				warp_estep_kernel<<<std::max(1, std::min(e->n_ctas_warp, n_units)), 32, warp_smem_bytes(e->cap0, e->cap1), e->stream>>>(wargs);
-			}
+			// one warp per unit; units it cannot take (founder roots, out-of-range parameters) are listed for the literal kernel
+			wa.kexp = sl.kexp.p;
+			wa.qstash = sl.qstash.p;
+			wa.literal_units = sl.literal.p;
+			wa.literal_count = sl.counter.p + 1;
+			wa.cap0 = e->cap0;
+			wa.cap1 = e->cap1;
+			warp_estep_kernel<<<std::max(1, std::min(e->n_ctas_warp, n_units)), 32, warp_smem_bytes(e->cap0, e->cap1), sl.stream>>>(wa);
 			CU(cudaGetLastError());
 			e->last_launches++;
-			a.unit_list = e->d_literal.p;
-			a.list_count = e->d_counter.p + 1;
-			a.counter = e->d_counter.p + 2;
+			a.unit_list = sl.literal.p;
+			a.list_count = sl.counter.p + 1;
+			a.counter = sl.counter.p + 2;
 		}
-		else if (!e->literal_only)
-		{
-			// table-driven kernel; units it cannot take (founder roots, out-of-range parameters) are listed for the literal one
-			fast_estep_kernel<<<std::max(1, std::min(e->n_ctas, n_units)), NTHREADS, sizeof(FastSmem), e->stream>>>(fa);
-			CU(cudaGetLastError());
-			e->last_launches++;
-			a.unit_list = e->d_literal.p;
-			a.list_count = e->d_counter.p + 1;
-			a.counter = e->d_counter.p + 2;
-		}
-		estep_kernel<<<std::max(1, std::min(e->n_ctas_literal, n_units)), NTHREADS, sizeof(Smem), e->stream>>>(a);
+		estep_kernel<<<std::max(1, std::min(e->n_ctas_literal, n_units)), NTHREADS, sizeof(Smem), sl.stream>>>(a);
 		CU(cudaGetLastError());
 		e->last_launches++;
 	}
-	CU(cudaEventRecord(e->ev1, e->stream));
+	CU(cudaEventRecord(sl.ev1, sl.stream));
 	if (e->allreduce && e->n_shared > 0)
 	{
-		const int rc = e->allreduce(e->allreduce_ctx, e->stats_shared(), (size_t)e->n_shared * Mc * STATS_PER_CELL, (void*)e->stream);
+		// the hook runs on one stream for all slots, so every rank issues its collectives in the order of its cnf2_estep calls
+		CU(cudaStreamWaitEvent(e->comm, sl.ev1, 0));
+		const int rc = e->allreduce(e->allreduce_ctx, sl.stats_shared(), (size_t)e->n_shared * Mc * STATS_PER_CELL, (void*)e->comm);
 		if (rc) return e->fail(CNF2_ERR_CUDA, "cnf2_estep: all-reduce hook failed");
+		CU(cudaEventRecord(sl.done, e->comm));
+		CU(cudaStreamWaitEvent(sl.stream, sl.done, 0));
 	}
-	e->estep_chrom = chrom;
 	return CNF2_OK;
 }
 
@@ -654,6 +650,8 @@ extern "C" int cnf2_sync(cnf2_engine* e)
 {
 	if (!e) return CNF2_ERR_BAD_ARG;
 	cudaSetDevice(e->settings.device);
+	for (Slot& sl : e->slots) CU(cudaStreamSynchronize(sl.stream));
+	CU(cudaStreamSynchronize(e->comm));
 	CU(cudaStreamSynchronize(e->stream));
 	CU(cudaGetLastError());
 	return CNF2_OK;
@@ -663,27 +661,31 @@ extern "C" int cnf2_get_stats(cnf2_engine* e, int32_t chrom, double* haplobase, 
                               double* homozyg, double* loglik)
 {
 	if (!e) return CNF2_ERR_BAD_ARG;
-	if (e->estep_chrom != chrom || chrom < 0) return e->fail(CNF2_ERR_STATE, "cnf2_get_stats: cnf2_estep for this chromosome first");
+	Slot* slp = nullptr;
+	for (Slot& o : e->slots)
+		if (chrom >= 0 && o.chrom == chrom) slp = &o;
+	if (!slp) return e->fail(CNF2_ERR_STATE, "cnf2_get_stats: cnf2_estep for this chromosome first (only the last two E-steps are kept)");
+	Slot& sl = *slp;
 	cudaSetDevice(e->settings.device);
 	const size_t M = e->markerpos.size(), c0 = e->chromstarts[chrom], Mc = e->mc(chrom);
 	for (const Run& r : e->runs)
 	{
 		const bool sh = r.row0 < e->n_shared;
-		const StatsCell src = sh ? stats_cell(e->stats_shared(), e->n_shared, Mc, r.row0, 0)
-		                         : stats_cell(e->stats_local((int)Mc), e->n_rows - e->n_shared, Mc, r.row0 - e->n_shared, 0);
+		const StatsCell src = sh ? stats_cell(sl.stats_shared(), e->n_shared, Mc, r.row0, 0)
+		                         : stats_cell(sl.stats_local((int)Mc), e->n_rows - e->n_shared, Mc, r.row0 - e->n_shared, 0);
 		const size_t dst = (size_t)r.id0 * M + c0;
 		if (haplobase)
-			CU(cudaMemcpy2DAsync(haplobase + dst, M * 8, src.haplobase, Mc * 8, Mc * 8, r.n, cudaMemcpyDeviceToHost, e->stream));
+			CU(cudaMemcpy2DAsync(haplobase + dst, M * 8, src.haplobase, Mc * 8, Mc * 8, r.n, cudaMemcpyDeviceToHost, sl.stream));
 		if (haplocount)
-			CU(cudaMemcpy2DAsync(haplocount + dst, M * 8, src.haplocount, Mc * 8, Mc * 8, r.n, cudaMemcpyDeviceToHost, e->stream));
+			CU(cudaMemcpy2DAsync(haplocount + dst, M * 8, src.haplocount, Mc * 8, Mc * 8, r.n, cudaMemcpyDeviceToHost, sl.stream));
 		if (infprobs)
-			CU(cudaMemcpy2DAsync(infprobs + dst * 4, M * 32, src.infprobs, Mc * 32, Mc * 32, r.n, cudaMemcpyDeviceToHost, e->stream));
+			CU(cudaMemcpy2DAsync(infprobs + dst * 4, M * 32, src.infprobs, Mc * 32, Mc * 32, r.n, cudaMemcpyDeviceToHost, sl.stream));
 		if (homozyg)
-			CU(cudaMemcpy2DAsync(homozyg + dst * 2, M * 16, src.homozyg, Mc * 16, Mc * 16, r.n, cudaMemcpyDeviceToHost, e->stream));
+			CU(cudaMemcpy2DAsync(homozyg + dst * 2, M * 16, src.homozyg, Mc * 16, Mc * 16, r.n, cudaMemcpyDeviceToHost, sl.stream));
 	}
 	if (loglik && !e->units.empty())
-		CU(cudaMemcpyAsync(e->h_loglik.data(), e->d_loglik.p, e->units.size() * 2 * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
-	CU(cudaStreamSynchronize(e->stream));
+		CU(cudaMemcpyAsync(e->h_loglik.data(), sl.loglik.p, e->units.size() * 2 * sizeof(double), cudaMemcpyDeviceToHost, sl.stream));
+	CU(cudaStreamSynchronize(sl.stream));
 	CU(cudaGetLastError());
 	if (loglik)
 	{
@@ -699,10 +701,11 @@ extern "C" int cnf2_get_stats(cnf2_engine* e, int32_t chrom, double* haplobase, 
 
 extern "C" int cnf2_last_estep_ms(cnf2_engine* e, float* ms)
 {
-	if (!e || !ms) return CNF2_ERR_BAD_ARG;
+	if (!e || !ms || e->last_slot < 0) return CNF2_ERR_BAD_ARG;
 	cudaSetDevice(e->settings.device);
-	CU(cudaEventSynchronize(e->ev1));
-	CU(cudaEventElapsedTime(ms, e->ev0, e->ev1));
+	Slot& sl = e->slots[e->last_slot];
+	CU(cudaEventSynchronize(sl.ev1));
+	CU(cudaEventElapsedTime(ms, sl.ev0, sl.ev1));
 	return CNF2_OK;
 }
 
@@ -718,7 +721,14 @@ extern "C" int cnf2_mark(cnf2_engine* e, int32_t slot)
 	if (!e || slot < 0 || slot >= 4) return CNF2_ERR_BAD_ARG;
 	cudaSetDevice(e->settings.device);
 	if (!e->marks[slot]) CU(cudaEventCreate(&e->marks[slot]));
+	// the mark comes after everything enqueued so far and before everything enqueued later, on every stream
+	for (Slot& sl : e->slots)
+	{
+		CU(cudaEventRecord(sl.tail, sl.stream));
+		CU(cudaStreamWaitEvent(e->stream, sl.tail, 0));
+	}
 	CU(cudaEventRecord(e->marks[slot], e->stream));
+	for (Slot& sl : e->slots) CU(cudaStreamWaitEvent(sl.stream, e->marks[slot], 0));
 	return CNF2_OK;
 }
 

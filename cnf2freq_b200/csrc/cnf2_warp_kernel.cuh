@@ -7,20 +7,21 @@
 //   * sweeps (cnF2freq.cpp:2145-2418): ALL 8 shift modes live in one warp: lane = shift * 4 + (state bits 4-5),
 //     16 states (bits 0-3) per lane in registers.  The transition R(r)^{(x)6} is four in-register butterfly
 //     stages and two shfl.xor stages on 16 independent values per lane; the emission comes from the marker's
-//     shift-independent table (see cnf2_batch_kernel.cuh); the vectors are scaled by exact powers of two per
+//     shift-independent table (see cnf2_tables.cuh); the vectors are scaled by exact powers of two per
 //     shift mode instead of being renormalised.
 //   * posterior (:5406-5583): W_s[g] = alpha_s[g] beta_s[g] exp(F + B - factor) is transposed through shared
-//     memory, then each lane takes one surviving (x, g) pair for all 8 shift modes (batch_posterior's scheme),
-//     scatters into its private accumulator column, the warp reduces its 32 columns and transfers them into
-//     the EM sufficient statistics (:5875-5904).
+//     memory; one lane owns one (parent subtree configuration, root orientation) entry and sums over the
+//     compatible entries of the other parent's side for all 8 shift modes (warp_posterior_pairs), scatters once into
+//     an accumulator column, the warp reduces the columns and transfers them into the EM sufficient statistics
+//     (:5875-5904).
 //   * the orientation-fixed subtree tables are direct-indexed by local configuration; one lane builds one
 //     (entry, root orientation) pair.
 #pragma once
-#include "cnf2_batch_kernel.cuh"
+#include "cnf2_tables.cuh"
 
 namespace cnf2
 {
-constexpr int WB = TB;        // markers staged at a time (the stride gfix / root_constants expect)
+constexpr int WB = 4;         // markers staged at a time
 constexpr int WTS = 17;       // row stride of the transposed W (doubles): conflict-free 64-bit stores
 constexpr int T0W = 3, T1W = 5;
 constexpr int NCOL = 8;       // accumulator columns; lanes scatter in 32 / NCOL passes
@@ -45,7 +46,7 @@ struct __align__(16) WarpSmem
 	// entry k of a table is the k-th needed configuration of that parent at this marker (its position in el)
 };
 
-// One (entry, root orientation) pair of the posterior tables of marker t (see post_entry in cnf2_batch_kernel.cuh).
+// One (entry, root orientation) pair of the posterior tables of marker t .
 __device__ __forceinline__ void post_entry1(const Unit& u, const uchar2* A, const NodeTab* N, const double* __restrict__ rc, int t, int p,
                                             int cfg, int f, double* __restrict__ e)
 {
@@ -62,13 +63,13 @@ __device__ __forceinline__ void post_entry1(const Unit& u, const uchar2* A, cons
 	{
 		const int ko = sp + 1 + (m ^ 1), oo = m ? oa : ob, wo = oo ^ (m ? ma : mb);
 		if (np.S[o ^ 1] != 0) pre = 1.0 - np.S[o ^ 1];
-		pre *= gfix(u, A, N, ko, t, o ? ap.x : ap.y, np.SEC[o ^ 1], oo, wo);
+		pre *= gfix<WB>(u, A, N, ko, t, o ? ap.x : ap.y, np.SEC[o ^ 1], oo, wo);
 	}
 	auto Q = [&](int v, double sec) -> double {
 		if (absent) return 1.0 + sec;
 		if (attop) return gval(ap, np, o, v, sec);
 		const PMsg pm = pmsg(ap, np, o, v, sec);
-		return pm.nb * pre * gfix(u, A, N, kf, t, pm.v2, pm.up2, of, wf);
+		return pm.nb * pre * gfix<WB>(u, A, N, kf, t, pm.v2, pm.up2, of, wf);
 	};
 	const double P1 = Q(1, 0.0), P2 = Q(2, 0.0);
 	if (p == 0)
@@ -345,14 +346,14 @@ struct RawItem
 	double2 su;
 	double h;
 };
-// lane i < 28 loads (slot = i >> 2, t = i & 3) of markers [m0, m0 + n)
+// lane i < NSLOTS * WB loads (slot = i / WB, t = i % WB) of markers [m0, m0 + n)
 __device__ __forceinline__ RawItem raw_load(const Unit& u, const EstepArgs& a, int m0, int n, int lane)
 {
 	RawItem r;
 	r.al = make_uchar2(0, 0);
 	r.su = make_double2(0, 0);
 	r.h = 0;
-	const int slot = lane >> 2, t = lane & 3;
+	const int slot = lane / WB, t = lane % WB;
 	if (slot < NSLOTS && t < n && m0 >= 0)
 	{
 		const int row = u.row[slot];
@@ -369,7 +370,7 @@ __device__ __forceinline__ RawItem raw_load(const Unit& u, const EstepArgs& a, i
 // writes the staged item; returns whether it is outside the regular range (markersure in [0,1), haploweight in [0,1])
 __device__ __forceinline__ bool raw_commit(WarpSmem& w, const RawItem& r, int lane)
 {
-	const int slot = lane >> 2, t = lane & 3;
+	const int slot = lane / WB, t = lane % WB;
 	if (slot >= NSLOTS) return false;
 	const int i = slot * WB + t;
 	w.A[i] = r.al;
@@ -405,21 +406,24 @@ __device__ __forceinline__ void warp_lists(WarpSmem& w, const Unit& u, int gpmus
 
 struct WarpArgs
 {
-	BatchArgs b;          // alpha scratch: [n_warps][Mc][512] doubles in store_alpha's layout
-	int32_t cap0, cap1;   // capacity (entries) of the posterior tables of parent 0 / parent 1
+	EstepArgs e;             // alpha scratch: [n_warps][Mc][512] doubles in store_alpha's layout
+	int32_t* kexp;           // [n_warps][Mc][NUMSHIFTS] power-of-two exponent of the stored alpha
+	double* qstash;          // [n_warps][Mc][QS] sweep-emission tables (forward pass -> backward pass)
+	int32_t* literal_units;  // units the literal kernel has to do
+	unsigned int* literal_count;
+	int32_t cap0, cap1;      // capacity (entries) of the posterior tables of parent 0 / parent 1
 };
 __host__ __device__ inline size_t warp_smem_bytes(int cap0, int cap1)
 {
 	return sizeof(WarpSmem) + ((size_t)cap0 * 2 * T0W + (size_t)cap1 * 2 * T1W) * sizeof(double);
 }
 
-__global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wargs)
+__global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wa)
 {
-	const BatchArgs& wa = wargs.b;
 	extern __shared__ __align__(16) unsigned char smem_raw[];
 	WarpSmem& w = *reinterpret_cast<WarpSmem*>(smem_raw);
 	double* const tab0 = reinterpret_cast<double*>(smem_raw + sizeof(WarpSmem));
-	double* const tab1 = tab0 + (size_t)wargs.cap0 * 2 * T0W;
+	double* const tab1 = tab0 + (size_t)wa.cap0 * 2 * T0W;
 	const EstepArgs& a = wa.e;
 	const unsigned FULL = 0xffffffffu;
 	const int lane = threadIdx.x, s = lane >> 2;
@@ -539,14 +543,14 @@ __global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wargs)
 			raw_commit(w, raw, lane);
 			for (int i = lane; i < n * QS; i += 32) w.qh[i] = qs[(size_t)m0 * QS + i];
 			// homozygous with equal sureness (:1235, :3488), per (slot, marker) of the batch
-			const bool homi = (lane >> 2) < NSLOTS && u.row[(lane >> 2) % NSLOTS] >= 0 && raw.al.x == raw.al.y && raw.su.x == raw.su.y;
+			const bool homi = (lane / WB) < NSLOTS && u.row[(lane / WB) % NSLOTS] >= 0 && raw.al.x == raw.al.y && raw.su.x == raw.su.y;
 			const unsigned homb = __ballot_sync(FULL, homi);
 			if (m0 >= WB) raw = raw_load(u, a, m0 - WB, WB, lane);
 			if (lane < WB)
 			{
 				int hs = 0, hom = 0, gp = 0;
 				for (int k = 0; k < NSLOTS; k++)
-					if ((homb >> (k * 4 + lane)) & 1)
+					if ((homb >> (k * WB + lane)) & 1)
 					{
 						hs |= 1 << k;
 						hom |= 1 << u.slotrel[k];

@@ -92,22 +92,25 @@ int cnf2_set_params(cnf2_engine* e, int32_t chrom, const uint8_t* alleles, const
                     const double* haploweight);
 
 /* The E-step of one chromosome for all of this engine's analysed individuals: cnF2freq.cpp:5294-5907
- * without the turn scoring (:5668-5871, row f2 of SURVEY.md section 8).  Asynchronous on the engine's
- * stream; cnf2_get_stats / cnf2_sync wait for it. */
+ * without the turn scoring (:5668-5871, row f2 of SURVEY.md section 8).  Asynchronous; cnf2_get_stats /
+ * cnf2_sync wait for it.  Two E-steps are kept in flight (each with its own stream, scratch and statistics
+ * block), so the tail of one chromosome's launch overlaps the next chromosome's: call cnf2_estep for chromosome
+ * c + 1 before cnf2_get_stats for chromosome c to use that. */
 int cnf2_estep(cnf2_engine* e, int32_t chrom);
 
 /* Optional exchange step between ranks (the stale MPI reduce at cnF2freq.cpp:6241-6256): called by
  * cnf2_estep after the kernels are enqueued, with the device buffer holding the statistics rows of the
  * individuals listed in cnf2_set_shared_rows (8 doubles per (row, marker): haplobase, haplocount,
  * infprobs[0][1], [0][2], [1][1], [1][2], homozyg[0], homozyg[1]).  The hook must enqueue a sum-all-reduce
- * over `count` doubles in place on `cuda_stream` (e.g. ncclAllReduce / torch.distributed.all_reduce). */
+ * over `count` doubles in place on `cuda_stream` (e.g. ncclAllReduce / torch.distributed.all_reduce).  The
+ * engine passes one and the same stream for every call, so collectives are issued in cnf2_estep call order. */
 typedef int (*cnf2_allreduce_fn)(void* ctx, double* device_buf, size_t count, void* cuda_stream);
 int cnf2_set_allreduce(cnf2_engine* e, cnf2_allreduce_fn fn, void* ctx);
 /* Individuals whose statistics rows receive contributions from more than one rank (e.g. the founders of
  * an F2 cross).  Must be the same list, in the same order, on every rank.  Call before cnf2_set_pedigree. */
 int cnf2_set_shared_rows(cnf2_engine* e, const int32_t* ids, int32_t n_ids);
 
-/* Statistics of the chromosome last passed to cnf2_estep, copied (assigned, device -> host) into caller
+/* Statistics of a chromosome among the last two passed to cnf2_estep, copied (assigned, device -> host) into caller
  * arrays shaped like the reference's per-individual vectors: haplobase/haplocount [n_ind][n_markers] (:901-902),
  * infprobs [n_ind][n_markers][2 sides][2 alleles {1,2}] (:895), homozyg [n_ind][n_markers][2] (:897);
  * loglik [n_dous][n_chrom][2] = (max_s L_s, logsumexp_s L_s), the pair printed at :5399-5401.  Only the columns of that chromosome and the rows this engine touched are written.
