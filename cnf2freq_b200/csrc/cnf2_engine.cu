@@ -24,7 +24,7 @@ struct Run  // consecutive rows holding consecutive individual ids: one 2-D copy
 	int32_t row0, id0, n;
 };
 
-constexpr int NSLOT = 2;  // E-steps of consecutive chromosomes in flight (the tail of one launch overlaps the next)
+constexpr int NSLOT = 4;  // most E-steps of consecutive chromosomes in flight (the tail of one launch overlaps the next ones)
 
 template <typename T>
 struct DevBuf
@@ -71,6 +71,7 @@ struct cnf2_engine
 	cudaStream_t comm = nullptr;    // the all-reduce hook runs here, in call order
 	Slot slots[NSLOT];
 	int next_slot = 0, last_slot = -1;
+	int n_slots = 2;  // E-steps in flight (CNF2_SLOTS, 1..NSLOT)
 	int n_sm = 0;
 
 	// map
@@ -206,6 +207,8 @@ extern "C" int cnf2_create(cnf2_engine** out, const cnf2_settings* settings)
 		return bail(ce, "cudaFuncSetAttribute(warp_estep_kernel carveout)");
 	const char* lit = getenv("CNF2_LITERAL");
 	e->literal_only = lit && lit[0] == '1';
+	if (const char* cp = getenv("CNF2_CTAS_PER_SM")) e->settings.ctas_per_sm = atoi(cp);
+	if (const char* ns = getenv("CNF2_SLOTS")) e->n_slots = std::max(1, std::min(NSLOT, atoi(ns)));
 	*out = e;
 	return CNF2_OK;
 }
@@ -497,6 +500,9 @@ extern "C" int cnf2_set_pedigree(cnf2_engine* e, int32_t n_ind, const int32_t* p
 		if (per_sm < 1) per_sm = 1;
 		if (e->settings.ctas_per_sm > 0) per_sm = std::min(per_sm, e->settings.ctas_per_sm);
 		e->n_ctas_warp = per_sm * e->n_sm;
+		if (getenv("CNF2_DEBUG"))
+			fprintf(stderr, "cnf2: warp kernel %d warps per SM, %zu B shared memory per warp (tables %d + %d entries)\n", per_sm,
+			        warp_smem_bytes(e->cap0, e->cap1), e->cap0, e->cap1);
 	}
 	CU(e->d_units.ensure(e->units.size()));
 	if (!e->units.empty())
@@ -574,7 +580,7 @@ extern "C" int cnf2_estep(cnf2_engine* e, int32_t chrom)
 	// the next slot; what it held (the E-step before the previous one) is overwritten
 	Slot& sl = e->slots[e->next_slot];
 	e->last_slot = e->next_slot;
-	e->next_slot = (e->next_slot + 1) % NSLOT;
+	e->next_slot = (e->next_slot + 1) % e->n_slots;
 	for (Slot& o : e->slots)
 		if (o.chrom == chrom) o.chrom = -1;
 	const int n_ctas = std::max(1, std::min(std::max(e->n_ctas_warp, e->n_ctas_literal), n_units));

@@ -27,8 +27,23 @@ constexpr int T0W = 3, T1W = 5;
 constexpr int NCOL = 8;       // accumulator columns; lanes scatter in 32 / NCOL passes
 constexpr int ACS = NCOL + 1; // row stride of the accumulators (doubles)
 
+// One output of the transfer step (relative r, quantity q: 0 haplobase, 1 haplocount, 2..5 infprobs, 6..7 homozyg),
+// fixed for a (unit, chromosome): where it goes and what it sums.
+struct TrMeta
+{
+	double* ptr0;   // address of the output at marker 0 of the chromosome; marker m is `stride` doubles further per marker
+	double scale;   // q < 2: descendants; q 2..5: 2 / 2^halvings * descendants (moveinfprobs, :3584-3594); else 1
+	uint8_t mask;   // tree slots the relative occupies (non-null ones)
+	uint8_t first;  // lowest of them: its haploweight is the relative's
+	uint8_t q;
+	uint8_t stride;
+	uint8_t pad[4];
+};
+constexpr int NTR = NSLOTS * 6 + 2;
+
 struct __align__(16) WarpSmem
 {
+	TrMeta tr[NTR];
 	double acc[NACC * ACS];
 	double Wt[32 * WTS];           // [shift * 4 + (g >> 4)][g & 15]
 	double qh[WB * QS];
@@ -39,6 +54,7 @@ struct __align__(16) WarpSmem
 	uchar2 A[NSLOTS * WB];
 	unsigned char el[128];
 	int nE, nE0, listtag;
+	int ntr, rootmask;
 	int homslot[WB], gpmust[WB];
 	Unit unit;
 	// followed by the posterior tables of the current marker, sized by the host for the pedigree (WarpArgs::cap0/cap1):
@@ -208,53 +224,100 @@ __device__ __forceinline__ void warp_posterior_pairs(WarpSmem& w, const Unit& u,
 }
 
 // Transfer of one marker's reduced accumulators into the EM sufficient statistics (cnF2freq.cpp:5875-5904,
-// moveinfprobs :3577-3597, movehaplos :3599-3616; same arithmetic as transfer_stats), one lane per output:
-// relative r, q = 0 haplobase, 1 haplocount, 2..5 infprobs, 6..7 homozyg (root only).
-__device__ __forceinline__ void transfer_lane(const EstepArgs& a, const Unit& u, const double* __restrict__ tot, const double* __restrict__ HW,
-                                              int r, int q, int t, int m)
+// moveinfprobs :3577-3597, movehaplos :3599-3616; same arithmetic as transfer_stats), one lane per output.
+// transfer_setup fills the per-(unit, chromosome) description of every output once; transfer_out is the
+// per-marker part.
+__device__ __forceinline__ void transfer_setup(WarpSmem& w, const EstepArgs& a, const Unit& u, int lane)
 {
-	const int rootrel = u.slotrel[0];
-	if (q >= 6 && r != rootrel) return;
-	double rootsum = 0, h0 = 0, h1 = 0, ip = 0, w = 0;
-#pragma unroll
-	for (int slot = 0; slot < NSLOTS; slot++)
+	const int rootrel = u.slotrel[0], nout = u.nrel * 6 + 2;
+	for (int i = lane; i < nout; i += 32)
 	{
-		if (u.row[slot] < 0) continue;
-		const int rel = u.slotrel[slot];
-		if (rel == rootrel) rootsum += tot[ACC_INF + slot * 4 + 0] + tot[ACC_INF + slot * 4 + 1];
-		if (rel == r)
+		const int n6 = u.nrel * 6;
+		const int r = i < n6 ? i / 6 : rootrel, q = i < n6 ? i % 6 : 6 + i - n6;
+		int mask = 0;
+		for (int slot = NSLOTS - 1; slot >= 0; slot--)
+			if (u.row[slot] >= 0 && u.slotrel[slot] == r) mask |= 1 << slot;
+		const size_t Mc = a.Mc;
+		const int srow = u.relrow[r];
+		const bool sh = srow < a.n_shared;
+		double* base = sh ? a.stats_shared : a.stats_local;
+		const size_t nr = sh ? a.n_shared : a.n_local, cell = (size_t)(sh ? srow : srow - a.n_shared) * Mc, plane = nr * Mc;
+		TrMeta t;
+		t.mask = (uint8_t)mask;
+		t.first = (uint8_t)(mask ? __ffs(mask) - 1 : 0);
+		t.q = (uint8_t)q;
+		if (q < 2)
 		{
+			t.ptr0 = base + q * plane + cell;
+			t.stride = 1;
+			t.scale = u.descendants;
+		}
+		else if (q < 6)
+		{
+			t.ptr0 = base + 2 * plane + cell * 4 + (q - 2);
+			t.stride = 4;
+			double sc = 2;
+			for (int k = 0; k < u.relhalvings[r]; k++) sc /= 2;
+			t.scale = sc * u.descendants;
+		}
+		else
+		{
+			t.ptr0 = base + 6 * plane + cell * 2 + (q - 6);
+			t.stride = 2;
+			t.scale = 1.0;
+		}
+		w.tr[i] = t;
+	}
+	if (lane == 0)
+	{
+		int rm = 0;
+		for (int slot = 0; slot < NSLOTS; slot++)
+			if (u.row[slot] >= 0 && u.slotrel[slot] == rootrel) rm |= 1 << slot;
+		w.rootmask = rm;
+		w.ntr = nout;
+	}
+}
+__device__ __forceinline__ void transfer_out(const WarpSmem& w, const double* __restrict__ tot, int t, int m, int lane)
+{
+	double rootsum = 0;
+	for (int rm = w.rootmask; rm; rm &= rm - 1)
+	{
+		const int slot = __ffs(rm) - 1;
+		rootsum += tot[ACC_INF + slot * 4 + 0] + tot[ACC_INF + slot * 4 + 1];
+	}
+	const double inv = 1.0 / rootsum;
+	for (int i = lane; i < w.ntr; i += 32)
+	{
+		const TrMeta mt = w.tr[i];
+		const int q = mt.q;
+		double* const dst = mt.ptr0 + (size_t)m * mt.stride;
+		if (q >= 6)
+		{
+			atomicAdd(dst, tot[ACC_HZ + q - 6] * inv);
+			continue;
+		}
+		if (q >= 2)
+		{
+			double ip = 0;
+			for (int sm = mt.mask; sm; sm &= sm - 1) ip += tot[ACC_INF + (__ffs(sm) - 1) * 4 + (q - 2)];
+			if (ip != 0) atomicAdd(dst, ip * (inv * mt.scale));
+			continue;
+		}
+		double h0 = 0, h1 = 0;
+		for (int sm = mt.mask; sm; sm &= sm - 1)
+		{
+			const int slot = __ffs(sm) - 1;
 			h0 += tot[ACC_HAPLOS + slot * 2 + 0];
 			h1 += tot[ACC_HAPLOS + slot * 2 + 1];
-			ip += tot[ACC_INF + slot * 4 + ((q - 2) & 3)];
-			w = HW[slot * WB + t];  // the relative's own haploweight; any of its slots holds it
 		}
-	}
-	const size_t Mc = a.Mc;
-	const int srow = u.relrow[r];
-	const bool sh = srow < a.n_shared;
-	double* base = sh ? a.stats_shared : a.stats_local;
-	const size_t nr = sh ? a.n_shared : a.n_local, cell = (size_t)(sh ? srow : srow - a.n_shared) * Mc + m, plane = nr * Mc;
-	if (q < 2)
-	{
-		if ((h0 != 0 || h1 != 0) && fabs(w - 0.5) < 0.5 - 1e-12)
+		const double hw = w.HW[mt.first * WB + t];  // the relative's own haploweight; any of its slots holds it
+		if ((h0 != 0 || h1 != 0) && fabs(hw - 0.5) < 0.5 - 1e-12)
 		{
 			const double eps = 1.9151695967140057e-174 * (double)(0.000005f) * (double)(0.000005f) * 0.5;  // exp(-400) * maxdiff^2 / 2, :228
 			const double x1 = h0 + eps, x2 = h1 + eps;
-			atomicAdd(base + q * plane + cell, q ? u.descendants : x1 / (x1 + x2) * u.descendants);
+			atomicAdd(dst, q ? mt.scale : x1 / (x1 + x2) * mt.scale);
 		}
 	}
-	else if (q < 6)
-	{
-		if (ip != 0)
-		{
-			double norm = 1.0 / rootsum * 2;
-			for (int k = 0; k < u.relhalvings[r]; k++) norm /= 2;
-			norm *= u.descendants;
-			atomicAdd(base + 2 * plane + cell * 4 + (q - 2), ip * norm);
-		}
-	}
-	else atomicAdd(base + 6 * plane + cell * 2 + (q - 6), tot[ACC_HZ + q - 6] * (1.0 / rootsum));
 }
 
 // ---- sweeps: lane = shift * 4 + gh, state g = r | gh << 4, r = 0..15 in registers ----
@@ -449,6 +512,7 @@ __global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wa)
 		}
 		__syncwarp();
 		const Unit& u = w.unit;
+		transfer_setup(w, a, u, lane);
 		bool literal = u.founder[0] != 0;  // a root "at the top" never recurses (:1120): literal kernel
 		const bool active = s < u.shiftend && !(s & u.shiftignore);
 
@@ -592,15 +656,20 @@ __global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wa)
 #pragma unroll
 				for (int i = 0; i < 16; i++) w.Wt[lane * WTS + i] = W[i];
 				__syncwarp();
+#ifndef CNF2_X_NOTAB
 				for (int i = lane; i < 2 * w.nE; i += 32)
 				{
 					const int c = w.el[i >> 1];
 					const int pp = c >> 6, slot = (i >> 1) - (pp ? w.nE0 : 0);
 					post_entry1(u, w.A, w.nt, w.rootc, t, pp, c & 63, i & 1, pp ? tab1 + (slot * 2 + (i & 1)) * T1W : tab0 + (slot * 2 + (i & 1)) * T0W);
 				}
+#endif
 				__syncwarp();
+#ifndef CNF2_X_NOPAIRS
 				warp_posterior_pairs(w, u, w.homslot[t], lane, tab0, tab1);
+#endif
 				__syncwarp();
+#ifndef CNF2_X_NOREDUCE
 				// the warp reduces its accumulator columns; the reader clears what it read
 				for (int k = lane; k < NACC; k += 32)
 				{
@@ -614,14 +683,12 @@ __global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wa)
 					}
 					w.tot[k] = v0 + v1;
 				}
+#endif
 				__syncwarp();
+#ifndef CNF2_X_NOTRANSFER
 				// transfer into the EM sufficient statistics (:5875-5904, moveinfprobs :3577-3597, movehaplos :3599-3616)
-				for (int i = lane; i < u.nrel * 6 + 2; i += 32)
-				{
-					const int n6 = u.nrel * 6;
-					if (i < n6) transfer_lane(a, u, w.tot, w.HW, i / 6, i % 6, t, m);
-					else transfer_lane(a, u, w.tot, w.HW, u.slotrel[0], 6 + i - n6, t, m);
-				}
+				transfer_out(w, w.tot, t, m, lane);
+#endif
 				if (m > 0)
 				{
 					emit16(b, w.qh + t * QS, lane);
