@@ -577,6 +577,13 @@ __global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wa)
 		for (int j = 0; j < NUMSHIFTS; j++)
 			if (j < u.shiftend && !(j & u.shiftignore)) realfactor += exp(Ls[j] - factor);
 		const double maxfactor = factor;
+		if (!(maxfactor > MINFACTOR_D))
+		{
+			// impossible under every shift mode: the reference goes on with factor = MINFACTOR + log(n) and scatters the
+			// NaNs of its 0/0 terms (:5403 compares against a float constant); the literal kernel reproduces that
+			if (lane == 0) wa.literal_units[atomicAdd(wa.literal_count, 1u)] = ui;
+			continue;
+		}
 		factor += log(realfactor);
 		if (lane == 0)
 		{

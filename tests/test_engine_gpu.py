@@ -56,6 +56,9 @@ def test_engine_matches_oracle_on_golden_inputs(eng, name):
     (randomped.fullsib, dict(n_fam=1, n_off=2, n_chrom=1, mpc=9, seed=14)),
     (randomped.tangled, dict(n_chrom=2, mpc=21, seed=15)),
     (randomped.tangled, dict(n_chrom=1, mpc=70, seed=16, missing=0.5)),
+    # two of the six units are impossible under every shift mode (zero likelihood): the reference carries on with
+    # factor = MINFACTOR + log 8 and scatters NaNs into the relatives' statistics; so do we
+    (randomped.fullsib, dict(n_fam=2, n_off=3, n_chrom=1, mpc=17, seed=42)),
 ])
 def test_engine_matches_oracle_on_random_pedigrees(eng, maker, kw):
     pb = maker(**kw)
