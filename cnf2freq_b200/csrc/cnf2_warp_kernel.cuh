@@ -22,10 +22,19 @@
 namespace cnf2
 {
 constexpr int WB = 4;         // markers staged at a time
-constexpr int WTS = 17;       // row stride of the transposed W (doubles): conflict-free 64-bit stores
 constexpr int T0W = 3, T1W = 5;
 constexpr int NCOL = 8;       // accumulator columns; lanes scatter in 32 / NCOL passes
-constexpr int ACS = NCOL + 1; // row stride of the accumulators (doubles)
+constexpr int NACCP = NACC + 2; // column stride of the accumulators (doubles): 16-byte aligned pairs, columns on distinct banks
+
+// Swizzled layout of W_s[g] (8 shift modes x 64 states) in shared memory: the 8 shift modes of a state are one
+// 64-byte row (four 16-byte chunks (s1, s2), each holding s0 = 0, 1); rows and chunks are permuted by XORs of the
+// state's bits so that the sweep lanes' 64-bit stores and the posterior lanes' 128-bit loads are conflict-free.
+// The address is GF(2)-linear in g:  ws_addr(g, s) = ws_base(g) ^ s,  ws_base(g0 ^ g1) = ws_base(g0) ^ ws_base(g1).
+__host__ __device__ constexpr int ws_base(int g)
+{
+	const int b3 = (g >> 3) & 1, b4 = (g >> 4) & 1, b5 = (g >> 5) & 1;
+	return ((g ^ b3 ^ b5) << 3) | ((((g >> 1) & 3) ^ (2 * b4 + b5)) << 1);
+}
 
 // One output of the transfer step (relative r, quantity q: 0 haplobase, 1 haplocount, 2..5 infprobs, 6..7 homozyg),
 // fixed for a (unit, chromosome): where it goes and what it sums.
@@ -44,16 +53,18 @@ constexpr int NTR = NSLOTS * 6 + 2;
 struct __align__(16) WarpSmem
 {
 	TrMeta tr[NTR];
-	double acc[NACC * ACS];
-	double Wt[32 * WTS];           // [shift * 4 + (g >> 4)][g & 15]
+	double acc[NCOL * NACCP];      // [column][accumulator]
+	double Ws[NUMSHIFTS * NUMTYPES]; // ws_base(g) ^ s
 	double qh[WB * QS];
 	NodeTab nt[NSLOTS * WB];
 	double HW[NSLOTS * WB];
 	double tot[NACC];
 	double rootc[RC];
 	uchar2 A[NSLOTS * WB];
-	unsigned char el[128];
-	int nE, nE0, listtag;
+	unsigned char el[128];         // list of the needed configurations: parent << 6 | cfg; parent 0 first, phase bit 0 first
+	unsigned char vmk[256];        // per (entry, root orientation): bit xo = rule 2 admits the other parent's x = xo
+	unsigned short ainfo[128];     // per entry: ws_base of its meiosis bits at the parent's place | x << 10
+	int nE, nE0, nX0, nX1, listtag; // nX0 / nX1: entries of parent 0 / 1 with phase bit x & 1 = 0
 	int ntr, rootmask;
 	int homslot[WB], gpmust[WB];
 	Unit unit;
@@ -116,93 +127,89 @@ __device__ __forceinline__ void post_entry1(const Unit& u, const uchar2* A, cons
 // and every scatter target of :5556-5575 depends on the term only through (f, cfg0) [root as side 0, parent 0's
 // subtree] or (f, cfg1) [root as side 1, parent 1's subtree]; homozyg is a product of one factor of each side.
 // One lane owns one (side, local configuration, root orientation) entry, runs over the compatible entries of
-// the OTHER side (rule 2 of ignoreflag2 couples the sides through Unit::xmask2) summing in registers, and
-// scatters its sums once.  Every (x, g) pair is visited twice, once from each side, with no memory traffic but
-// the W and table reads.  The unusualstate cut of single terms (val > e^-200, :5414) is not applied here (it
-// removes at most e^-200 of the posterior mass); whole shift modes below it are cut where W is formed.
+// the OTHER side (rule 2 of ignoreflag2 couples the sides through Unit::xmask2, precomputed as vmk) summing in
+// registers, and scatters its sums once.  The sums are kept raw -- per (own shift bit, root shift bit), weighted
+// only by the other side's emission and phase weight -- and combined with the lane's own weights after the loop.
+// The unusualstate cut of single terms (val > e^-200, :5414) is not applied here (it removes at most e^-200 of
+// the posterior mass); whole shift modes below it are cut where W is formed.
 __device__ __forceinline__ void warp_posterior_pairs(WarpSmem& w, const Unit& u, int homslot, int lane, const double* __restrict__ tab0,
                                                      const double* __restrict__ tab1)
 {
 	const double* rc = w.rootc;
-	double* const acc = w.acc + (lane & (NCOL - 1));
+	double* const acc = w.acc + (lane & (NCOL - 1)) * NACCP;
 	const int vis = u.vismask, hmask = vis & ~homslot;
 	const int nE = w.nE, nE0 = w.nE0;
+	const double2* const Ws2 = reinterpret_cast<const double2*>(w.Ws);
 	for (int ibase = 0; ibase < 2 * nE; ibase += 32)
 	{
 		const int i = ibase + lane;
 		const bool valid = i < 2 * nE;
-		const int c = w.el[valid ? i >> 1 : 0], f = i & 1;
+		const int ie = valid ? i >> 1 : 0;
+		const int c = w.el[ie], f = i & 1;
 		const int p = c >> 6, cfg = c & 63;
 		const int gown = cfg & 7, xown = gown ^ (cfg >> 3);
 		// phase weights: own parent at its shift bit 0 / 1, and the table of the other parent
 		const double own0 = rc[12 + p * 2 + (xown & 1)], own1 = rc[12 + p * 2 + ((xown & 1) ^ 1)];
-		const double* wo = rc + 12 + (p ^ 1) * 2;
+		const double wo0 = rc[12 + (p ^ 1) * 2], wo1 = rc[12 + (p ^ 1) * 2 + 1];
 		const double rA = rc[2 + f], rB = rc[2 + (f ^ 1)];  // root at s0 = 0, 1
-		// W_s[g] at s = s0 + 2 s1 + 4 s2: stride of the own / the other parent's shift bit
-		const int strOwn = (p ? 4 : 2) * 4 * WTS, strOth = (p ? 2 : 4) * 4 * WTS;
-		const int gshift = p ? 0 : 3;
-		const double* Wbase = w.Wt + (p ? ((gown << 3) >> 4) * WTS + ((gown << 3) & 15) : gown);
+		const int aown = w.ainfo[ie] & 1023;
+		const int vm = w.vmk[valid ? i : 0];
+		// chunk (s1, s2) of a row is at ^ (s1 + 2 s2) << 1; the own parent's shift bit is s1 for parent 0, s2 for parent 1
+		const int kown = p ? 4 : 2, koth = p ? 2 : 4;
 		const double* Tp = p ? tab0 + f * T0W : tab1 + f * T1W;  // the other parent's table, this root orientation
 		const int tw = 2 * (p ? T0W : T1W);
 		const int jlo = p ? 0 : nE0, jhi = valid ? (p ? nE0 : nE) : jlo;
-		double Sz0 = 0, Sz1 = 0, So0 = 0, So1 = 0, Sx1 = 0, Sx2 = 0;
-		for (int j = jlo; j < jhi; j++)
-		{
-			const int co = w.el[j] & 63, goth = co & 7, xoth = goth ^ (co >> 3);
-			const int x = f | ((p ? xoth : xown) << 1) | ((p ? xown : xoth) << 4);
-			if (!((u.xmask2[x >> 5] >> (x & 31)) & 1)) continue;  // rule 2 (:3483-3486)
-			const int go = goth << gshift;
-			const double* W = Wbase + (go >> 4) * WTS + (go & 15);
-			const double* T = Tp + (j - jlo) * tw;
-			const double E = T[0];
-			const double q0 = wo[xoth & 1], q1 = wo[(xoth & 1) ^ 1];  // other parent at its shift bit 0 / 1
-			const double A00 = rA * W[0], B00 = rB * W[4 * WTS];
-			const double A01 = rA * W[strOth], B01 = rB * W[4 * WTS + strOth];
-			const double A10 = rA * W[strOwn], B10 = rB * W[4 * WTS + strOwn];
-			const double A11 = rA * W[strOwn + strOth], B11 = rB * W[4 * WTS + strOwn + strOth];
-			const double z0 = own0 * (q0 * A00 + q1 * A01) + own1 * (q0 * A10 + q1 * A11);  // s0 = 0
-			const double z1 = own0 * (q0 * B00 + q1 * B01) + own1 * (q0 * B10 + q1 * B11);  // s0 = 1
-			const double o0 = own0 * (q0 * (A00 + B00) + q1 * (A01 + B01));                // own shift bit 0
-			const double o1 = own1 * (q0 * (A10 + B10) + q1 * (A11 + B11));                // own shift bit 1
-			Sz0 += E * z0;
-			Sz1 += E * z1;
-			So0 += E * o0;
-			So1 += E * o1;
-			if (!p)
+		const int jmid = min(jhi, jlo + (p ? w.nX0 : w.nX1));  // the other parent's entries with phase bit 0 come first
+		const double k00 = own0 * rA, k01 = own0 * rB, k10 = own1 * rA, k11 = own1 * rB;
+		double Rx0 = 0, Ry0 = 0, Rx1 = 0, Ry1 = 0, Sx1 = 0, Sx2 = 0;
+		auto run = [&](int ja, int jb, double qa, double qb) {  // qa / qb: the other parent's weight at its shift bit 0 / 1
+			const double* T = Tp + (ja - jlo) * tw;
+#pragma unroll 2
+			for (int j = ja; j < jb; j++, T += tw)
 			{
-				const double tot = E * (o0 + o1);
-				Sx1 += tot * T[3];
-				Sx2 += tot * T[4];
+				const int info = w.ainfo[j];
+				const int a0 = aown ^ (info & 1023);
+				const double E = ((vm >> (info >> 10)) & 1) ? T[0] : 0.0;  // rule 2 (:3483-3486)
+				const double Ea = E * qa, Eb = E * qb;
+				const double2 c00 = Ws2[a0 >> 1], cT = Ws2[(a0 ^ koth) >> 1], cO = Ws2[(a0 ^ kown) >> 1], c11 = Ws2[(a0 ^ 6) >> 1];
+				const double tx0 = Ea * c00.x + Eb * cT.x, ty0 = Ea * c00.y + Eb * cT.y;  // own shift bit 0; root shift bit 0 / 1
+				const double tx1 = Ea * cO.x + Eb * c11.x, ty1 = Ea * cO.y + Eb * c11.y;  // own shift bit 1
+				Rx0 += tx0, Ry0 += ty0, Rx1 += tx1, Ry1 += ty1;
+				if (!p)
+				{
+					const double tot = k00 * tx0 + k01 * ty0 + k10 * tx1 + k11 * ty1;
+					Sx1 += tot * T[3];
+					Sx2 += tot * T[4];
+				}
 			}
-		}
-		const int slot = (valid ? i >> 1 : 0) - (p ? nE0 : 0);
+		};
+		run(jlo, jmid, wo0, wo1);
+		run(jmid, jhi, wo1, wo0);
+		const int slot = ie - (p ? nE0 : 0);
 		const double* To = p ? tab1 + (slot * 2 + f) * T1W : tab0 + (slot * 2 + f) * T0W;
 		const double F = rc[f] * To[0];
-		Sz0 *= F, Sz1 *= F, So0 *= F, So1 *= F;
+		const double Sz0 = F * rA * (own0 * Rx0 + own1 * Rx1), Sz1 = F * rB * (own0 * Ry0 + own1 * Ry1);  // root shift bit 0 / 1
+		const double So0 = F * own0 * (rA * Rx0 + rB * Ry0), So1 = F * own1 * (rA * Rx1 + rB * Ry1);    // own shift bit 0 / 1
 		const double S = So0 + So1;
 		const bool live = valid && S > 0;
-		const int sp = 1 + 3 * p, o_ = cfg >> 3;
+		const int sp = 1 + 3 * p, o_ = cfg >> 3, xb = xown & 1;
 		const int gs = sp + 1 + (gown & 1);
 		const double u0 = S * To[1], u1 = S * To[2];
-		int idx[14];
-		double add[14];
-		bool en[14];
-		idx[0] = ACC_HAPLOS + f, add[0] = Sz0, en[0] = !p && (hmask & 1);            // root: s0 = 0 -> bit f
-		idx[1] = ACC_HAPLOS + (f ^ 1), add[1] = Sz1, en[1] = en[0];
-		idx[2] = ACC_HAPLOS + sp * 2 + (xown & 1), add[2] = So0, en[2] = (hmask >> sp) & 1;
-		idx[3] = ACC_HAPLOS + sp * 2 + ((xown & 1) ^ 1), add[3] = So1, en[3] = en[2];
-		idx[4] = ACC_HAPLOS + (sp + 1) * 2 + ((xown >> 1) & 1), add[4] = S, en[4] = (hmask >> (sp + 1)) & 1;
-		idx[5] = ACC_HAPLOS + (sp + 2) * 2 + ((xown >> 2) & 1), add[5] = S, en[5] = (hmask >> (sp + 2)) & 1;
+		// scatter targets: pairs of adjacent accumulators (128-bit read-modify-write) and two single ones
+		int pk[6], sk[2];
+		double2 pv[6];
+		bool pe[6], se[2];
+		pk[0] = ACC_HAPLOS, pv[0] = f ? make_double2(Sz1, Sz0) : make_double2(Sz0, Sz1), pe[0] = !p && (hmask & 1);  // root: s0 = 0 -> bit f
+		pk[1] = ACC_HAPLOS + sp * 2, pv[1] = xb ? make_double2(So1, So0) : make_double2(So0, So1), pe[1] = (hmask >> sp) & 1;
+		sk[0] = ACC_HAPLOS + (sp + 1) * 2 + ((xown >> 1) & 1), se[0] = (hmask >> (sp + 1)) & 1;
+		sk[1] = ACC_HAPLOS + (sp + 2) * 2 + ((xown >> 2) & 1), se[1] = (hmask >> (sp + 2)) & 1;
 		// the GENOS calls of side p (:5560-5568): root at orientation f ^ side, the parent, its parent picked by the meiosis bit
-		idx[6] = ACC_INF + (f ^ p) * 2, add[6] = u0, en[6] = true;
-		idx[7] = idx[6] + 1, add[7] = u1, en[7] = true;
-		idx[8] = ACC_INF + (sp * 2 + (o_ & 1)) * 2, add[8] = u0, en[8] = (vis >> sp) & 1;
-		idx[9] = idx[8] + 1, add[9] = u1, en[9] = en[8];
-		idx[10] = ACC_INF + (gs * 2 + ((o_ >> (gs - sp)) & 1)) * 2, add[10] = u0, en[10] = en[8] && ((vis >> gs) & 1);
-		idx[11] = idx[10] + 1, add[11] = u1, en[11] = en[10];
+		const double2 uu = make_double2(u0, u1);
+		pk[2] = ACC_INF + (f ^ p) * 2, pv[2] = uu, pe[2] = true;
+		pk[3] = ACC_INF + (sp * 2 + (o_ & 1)) * 2, pv[3] = uu, pe[3] = (vis >> sp) & 1;
+		pk[4] = ACC_INF + (gs * 2 + ((o_ >> (gs - sp)) & 1)) * 2, pv[4] = uu, pe[4] = pe[3] && ((vis >> gs) & 1);
 		// homozyg (:5571-5575): rho0[al] * hfd[al][f] * sum over the other side of val * Q1(al, 0) / Q1(plain)
-		idx[12] = ACC_HZ + 0, add[12] = F * Sx1 * To[1] * rc[8 + f], en[12] = !p;
-		idx[13] = ACC_HZ + 1, add[13] = F * Sx2 * To[2] * rc[10 + f], en[13] = !p;
+		pk[5] = ACC_HZ, pv[5] = make_double2(F * Sx1 * To[1] * rc[8 + f], F * Sx2 * To[2] * rc[10 + f]), pe[5] = !p;
 		// NCOL lanes at a time add into their own accumulator column; the targets of one entry are distinct, so
 		// all are read before any is written
 #pragma unroll 1
@@ -210,13 +217,20 @@ __device__ __forceinline__ void warp_posterior_pairs(WarpSmem& w, const Unit& u,
 		{
 			if (live && (lane / NCOL) == pass)
 			{
-				double cur[14];
+				double2 cur[6];
+				double cs[2];
 #pragma unroll
-				for (int j = 0; j < 14; j++)
-					if (en[j]) cur[j] = acc[idx[j] * ACS];
+				for (int j = 0; j < 6; j++)
+					if (pe[j]) cur[j] = *reinterpret_cast<const double2*>(acc + pk[j]);
 #pragma unroll
-				for (int j = 0; j < 14; j++)
-					if (en[j]) acc[idx[j] * ACS] = cur[j] + add[j];
+				for (int j = 0; j < 2; j++)
+					if (se[j]) cs[j] = acc[sk[j]];
+#pragma unroll
+				for (int j = 0; j < 6; j++)
+					if (pe[j]) *reinterpret_cast<double2*>(acc + pk[j]) = make_double2(cur[j].x + pv[j].x, cur[j].y + pv[j].y);
+#pragma unroll
+				for (int j = 0; j < 2; j++)
+					if (se[j]) acc[sk[j]] = cs[j] + S;
 			}
 			__syncwarp();
 		}
@@ -442,26 +456,49 @@ __device__ __forceinline__ bool raw_commit(WarpSmem& w, const RawItem& r, int la
 	return !(r.su.x >= 0 && r.su.x < 1 && r.su.y >= 0 && r.su.y < 1 && r.h >= 0 && r.h <= 1);
 }
 
-// Lists of the posterior phase for a marker whose shift-independent rule-3 mask is gpmust (see batch_prepare).
+// Lists of the posterior phase for a marker whose shift-independent rule-3 mask is gpmust (see batch_prepare):
+// the needed configurations of parent 0, then of parent 1, each with the phase bit x & 1 = 0 ones first; per entry
+// the W row offset of its meiosis bits and its x; per (entry, root orientation) the rule-2 mask over the other side's x.
 __device__ __forceinline__ void warp_lists(WarpSmem& w, const Unit& u, int gpmust, int lane)
 {
 	const unsigned FULL = 0xffffffffu;
-	int nE = 0, nE0 = 0;
+	int nE = 0, nE0 = 0, nX[2] = { 0, 0 };
 #pragma unroll
-	for (int r4 = 0; r4 < 4; r4++)
+	for (int r8 = 0; r8 < 8; r8++)
 	{
-		const int c = r4 * 32 + lane, p = c >> 6, cfg = c & 63;
+		const int p = r8 >> 2, xb = (r8 >> 1) & 1, cfg = (r8 & 1) * 32 + lane;
 		const int sub = (gpmust >> (1 + 3 * p)) & 7, xc = (cfg & 7) ^ (cfg >> 3);
-		const bool ok = ((u.cfgmask[p] >> cfg) & 1ull) && (xc & sub) == sub;
+		const bool ok = ((u.cfgmask[p] >> cfg) & 1ull) && (xc & sub) == sub && (xc & 1) == xb;
 		const unsigned mask = __ballot_sync(FULL, ok);
-		if (ok) w.el[nE + __popc(mask & ((1u << lane) - 1u))] = (unsigned char)c;
+		if (ok)
+		{
+			const int pos = nE + __popc(mask & ((1u << lane) - 1u));
+			w.el[pos] = (unsigned char)(p << 6 | cfg);
+			w.ainfo[pos] = (unsigned short)(ws_base((cfg & 7) << (p ? 3 : 0)) | xc << 10);
+		}
 		nE += __popc(mask);
-		if (r4 == 1) nE0 = nE;  // entries of parent 0 come first
+		if (!xb) nX[p] += __popc(mask);
+		if (r8 == 3) nE0 = nE;  // entries of parent 0 come first
+	}
+	__syncwarp();
+	for (int i = lane; i < 2 * nE; i += 32)
+	{
+		const int c = w.el[i >> 1], f = i & 1, p = c >> 6, xown = (c & 7) ^ ((c & 63) >> 3);
+		int vm = 0;
+#pragma unroll
+		for (int xo = 0; xo < 8; xo++)
+		{
+			const int x = f | ((p ? xo : xown) << 1) | ((p ? xown : xo) << 4);
+			vm |= ((u.xmask2[x >> 5] >> (x & 31)) & 1) << xo;
+		}
+		w.vmk[i] = (unsigned char)vm;
 	}
 	if (lane == 0)
 	{
 		w.nE = nE;
 		w.nE0 = nE0;
+		w.nX0 = nX[0];
+		w.nX1 = nX[1];
 		w.listtag = gpmust;
 	}
 	__syncwarp();
@@ -495,7 +532,7 @@ __global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wa)
 	int32_t* const kexp = wa.kexp + (size_t)blockIdx.x * Mc * NUMSHIFTS;
 	double* const qs = wa.qstash + (size_t)blockIdx.x * Mc * QS;
 
-	for (int i = lane; i < NACC * ACS; i += 32) w.acc[i] = 0;
+	for (int i = lane; i < NCOL * NACCP; i += 32) w.acc[i] = 0;
 
 	for (;;)
 	{
@@ -661,7 +698,7 @@ __global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wa)
 					w.rootc[12 + (lane - 2) * 2 + 1] = there ? w.nt[sp * WB + t].W[1] : 1.0;
 				}
 #pragma unroll
-				for (int i = 0; i < 16; i++) w.Wt[lane * WTS + i] = W[i];
+				for (int i = 0; i < 16; i++) w.Ws[(ws_base((lane & 3) << 4) ^ s) ^ ws_base(i)] = W[i];
 				__syncwarp();
 #ifndef CNF2_X_NOTAB
 				for (int i = lane; i < 2 * w.nE; i += 32)
@@ -680,13 +717,13 @@ __global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wa)
 				// the warp reduces its accumulator columns; the reader clears what it read
 				for (int k = lane; k < NACC; k += 32)
 				{
-					double* col = w.acc + k * ACS;
+					double* col = w.acc + k;
 					double v0 = 0, v1 = 0;
 #pragma unroll
 					for (int j = 0; j < NCOL; j += 2)
 					{
-						v0 += col[j], v1 += col[j + 1];
-						col[j] = 0, col[j + 1] = 0;
+						v0 += col[j * NACCP], v1 += col[(j + 1) * NACCP];
+						col[j * NACCP] = 0, col[(j + 1) * NACCP] = 0;
 					}
 					w.tot[k] = v0 + v1;
 				}
