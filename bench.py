@@ -50,7 +50,9 @@ def parse():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--individuals", type=int, default=2000, help="analysed F2 individuals per GPU")
+    ap.add_argument("--workload", default="f2", choices=["f2", "fullsib"],
+                    help="f2: BASELINE.json configs[2] (the bench workload); fullsib: configs[3]'s pedigree shape (families of 20 offspring)")
+    ap.add_argument("--individuals", type=int, default=2000, help="analysed individuals per GPU")
     ap.add_argument("--chroms", type=int, default=10)
     ap.add_argument("--markers-per-chrom", type=int, default=1000)
     ap.add_argument("--cpu-sample-individuals", type=int, default=64)
@@ -60,6 +62,9 @@ def parse():
 
 
 def workload_name(a):
+    if a.workload == "fullsib":
+        return (f"synthetic outbred full-sib families (3 generations, 20 offspring each), {a.individuals} individuals x "
+                f"{a.chroms * a.markers_per_chrom} markers ({a.chroms} chromosomes x {a.markers_per_chrom}) per GPU, 5% missing")
     return (f"synthetic F2 intercross, {a.individuals} individuals x {a.chroms * a.markers_per_chrom} markers "
             f"({a.chroms} chromosomes x {a.markers_per_chrom}) per GPU, 20% missing")
 
@@ -195,7 +200,11 @@ def ours(a, rank, world, local_rank):
         t = torch.zeros(tuple(shape), dtype={np.uint8: torch.uint8, np.float64: torch.float64}[dtype], pin_memory=True)
         return t.numpy()
 
-    d = synth.f2_flat(a.individuals, a.chroms, a.markers_per_chrom, spacing_cM=0.1, missing=0.2, seed=3 + rank, pinned=pinned)
+    if a.workload == "fullsib":
+        d = synth.fullsib_flat(max(1, a.individuals // 20), 20, a.chroms, a.markers_per_chrom, spacing_cM=0.02, missing=0.05,
+                               seed=4 + rank, pinned=pinned)
+    else:
+        d = synth.f2_flat(a.individuals, a.chroms, a.markers_per_chrom, spacing_cM=0.1, missing=0.2, seed=3 + rank, pinned=pinned)
     K, M, C = d["par"].shape[0], d["markerpos"].shape[0], a.chroms
     eng = Engine(device=local_rank)
     eng.set_map(d["markerpos"], d["chromstarts"], d["genrec"])
@@ -254,7 +263,8 @@ def ours(a, rank, world, local_rank):
         e2e_step()
     barrier()
     e2e_s = maxranks(time.perf_counter() - t0) / a.steps
-    n_rows = int((np.unique(np.concatenate([d["dous"], d["par"][d["dous"]].ravel(), [1, 2]])) > 0).sum())
+    pars = d["par"][d["dous"]].ravel()
+    n_rows = int((np.unique(np.concatenate([d["dous"], pars, d["par"][pars].ravel(), d["shared"]])) > 0).sum())
     h2d = n_rows * M * 26 + 2 * M * 8
     d2h = n_rows * M * 64 + len(d["dous"]) * C * 16
 

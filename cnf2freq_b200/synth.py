@@ -146,3 +146,61 @@ def f2_flat(n_f2, n_chrom, markers_per_chrom, spacing_cM=0.1, missing=0.2, seed=
     return dict(par=par, empty=empty, founder=founder, gen=gen, descendants=desc, dous=f2.astype(np.int32), markerpos=pos,
                 chromstarts=cs, genrec=np.full(3, -1.0 / 50), alleles=alleles, sure=sure, haploweight=hw,
                 shared=np.array([1, 2], np.int32))
+
+
+def fullsib_flat(n_fam, n_off, n_chrom, markers_per_chrom, spacing_cM=0.02, missing=0.05, seed=4, pinned=None):
+    """cfg4 (outbred full-sib families, three generations, no inbreeding: 7 distinct tree members, all 128
+    orientations and 8 shift modes in play) as the flat arrays of the C ABI.  Per family: 4 founders (gen 0,
+    i.i.d. alleles at frequency 0.5), 2 parents (gen 1), n_off analysed offspring (gen 2); genotypes Mendelian,
+    `missing` of them unknown in every generation, known ones with markersure 0.02 (readalphadata,
+    cnF2freq.cpp:6584-6587); haploweight 0.5.  Ids: 0 none, then per family 4 founders, 2 parents, the offspring.
+    Families are independent, so sharding whole families over ranks needs no shared rows."""
+    rng = np.random.default_rng(seed)
+    alloc = pinned or (lambda shape, dtype: np.zeros(shape, dtype))
+    pos, cs = make_map(n_chrom, markers_per_chrom, spacing_cM)
+    M = pos.shape[0]
+    per = 6 + n_off
+    K = 1 + n_fam * per
+    alleles = alloc((K, M, 2), np.uint8)
+    sure = alloc((K, M, 2), np.float64)
+    hw = alloc((K, M), np.float64)
+    alleles[...] = 0
+    sure[...] = 0
+    hw[...] = 0.5
+    par = np.zeros((K, 2), np.int32)
+    gen = np.zeros(K, np.int32)
+    desc = np.zeros(K, np.int32)
+    dous = []
+    for f in range(n_fam):
+        b = 1 + f * per
+        founders = rng.integers(1, 3, size=(4, 2, M)).astype(np.uint8)
+        pars = []
+        for p in range(2):
+            x = _gametes(rng, founders[2 * p], pos, cs, 1)[0]
+            y = _gametes(rng, founders[2 * p + 1], pos, cs, 1)[0]
+            pars.append(np.stack([x, y]))
+        o0 = _gametes(rng, pars[0], pos, cs, n_off)
+        o1 = _gametes(rng, pars[1], pos, cs, n_off)
+        for q in range(4):
+            alleles[b + q] = founders[q].T
+        for p in range(2):
+            alleles[b + 4 + p] = pars[p].T
+            par[b + 4 + p] = (b + 2 * p, b + 2 * p + 1)
+            gen[b + 4 + p] = 1
+        ids = b + 6 + np.arange(n_off)
+        alleles[ids] = np.stack([o0, o1], axis=2)
+        par[ids] = (b + 4, b + 5)
+        gen[ids] = 2
+        desc[ids] = 1
+        dous.extend(ids.tolist())
+    miss = rng.random((K, M)) < missing
+    alleles[miss] = 0
+    known = alleles[:, :, 0] != 0
+    sure[known] = 0.02
+    empty = np.zeros(K, np.uint8)
+    empty[0] = 1
+    founder = np.zeros(K, np.uint8)
+    founder[(gen == 0) & (np.arange(K) > 0)] = 1
+    return dict(par=par, empty=empty, founder=founder, gen=gen, descendants=desc, dous=np.asarray(dous, np.int32),
+                markerpos=pos, chromstarts=cs, genrec=np.full(3, -1.0 / 50), alleles=alleles, sure=sure, haploweight=hw,
+                shared=np.zeros(0, np.int32))

@@ -102,3 +102,15 @@ def test_one_kernel_launch_per_estep(eng):
     eng.sync()
     assert eng.last_estep_launches() >= 1
     assert eng.last_estep_ms() > 0
+
+
+@pytest.mark.parametrize("maker,kw", [
+    ("f2_flat", dict(n_f2=6, n_chrom=2, markers_per_chrom=30, seed=3)),            # bench workload (configs[2]) in small
+    ("fullsib_flat", dict(n_fam=2, n_off=3, n_chrom=1, markers_per_chrom=25, seed=4)),  # configs[3]'s pedigree shape
+])
+def test_engine_matches_oracle_on_bench_workloads(eng, maker, kw):
+    from cnf2freq_b200 import synth
+    d = getattr(synth, maker)(**kw)
+    pb = ol.Problem(d["par"], d["empty"], d["founder"], d["gen"], d["descendants"], d["dous"], d["markerpos"],
+                    d["chromstarts"], d["genrec"], d["alleles"], d["sure"], d["haploweight"])
+    compare(run_engine(eng, pb), ol.oracle_estep(pb), maker)
