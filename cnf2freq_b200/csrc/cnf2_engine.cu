@@ -95,6 +95,7 @@ struct cnf2_engine
 	DevBuf<double> d_hw, d_rec;
 	int n_ctas_warp = 0;
 	int cap0 = 64, cap1 = 64;  // posterior table capacities of the warp kernel for this pedigree
+	int cls = 0;               // CLS when some unit's rule-2 mask is all ones (class sums in use)
 	int n_ctas_literal = 0;
 	bool literal_only = false;  // debugging / A-B switch: CNF2_LITERAL=1 runs every unit through the literal kernel
 	DevBuf<Unit> d_units;
@@ -201,10 +202,13 @@ extern "C" int cnf2_create(cnf2_engine** out, const cnf2_settings* settings)
 	if (per_sm < 1) per_sm = 1;
 	if (settings->ctas_per_sm > 0) per_sm = std::min(per_sm, settings->ctas_per_sm);
 	e->n_ctas_literal = per_sm * e->n_sm;
-	if ((ce = cudaFuncSetAttribute(warp_estep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)warp_smem_bytes(64, 64))) != cudaSuccess)
-		return bail(ce, "cudaFuncSetAttribute(warp_estep_kernel)");
-	if ((ce = cudaFuncSetAttribute(warp_estep_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100)) != cudaSuccess)
-		return bail(ce, "cudaFuncSetAttribute(warp_estep_kernel carveout)");
+	for (auto kern : { warp_estep_kernel<false>, warp_estep_kernel<true> })
+	{
+		if ((ce = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)warp_smem_bytes(64, 64, CLS))) != cudaSuccess)
+			return bail(ce, "cudaFuncSetAttribute(warp_estep_kernel)");
+		if ((ce = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100)) != cudaSuccess)
+			return bail(ce, "cudaFuncSetAttribute(warp_estep_kernel carveout)");
+	}
 	const char* lit = getenv("CNF2_LITERAL");
 	e->literal_only = lit && lit[0] == '1';
 	if (const char* cp = getenv("CNF2_CTAS_PER_SM")) e->settings.ctas_per_sm = atoi(cp);
@@ -489,20 +493,23 @@ extern "C" int cnf2_set_pedigree(cnf2_engine* e, int32_t n_ind, const int32_t* p
 	}
 	// warp kernel: posterior table capacities = the largest number of subtree configurations any unit uses
 	e->cap0 = e->cap1 = 1;
+	e->cls = 0;
 	for (const Unit& u : e->units)
 	{
 		e->cap0 = std::max(e->cap0, __builtin_popcountll(u.cfgmask[0]));
 		e->cap1 = std::max(e->cap1, __builtin_popcountll(u.cfgmask[1]));
+		if ((u.xmask2[0] & u.xmask2[1] & u.xmask2[2] & u.xmask2[3]) == 0xffffffffu) e->cls = CLS;
 	}
 	{
 		int per_sm = 0;
-		CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, warp_estep_kernel, 32, warp_smem_bytes(e->cap0, e->cap1)));
+		CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, e->cls ? warp_estep_kernel<true> : warp_estep_kernel<false>, 32,
+		                                                 warp_smem_bytes(e->cap0, e->cap1, e->cls)));
 		if (per_sm < 1) per_sm = 1;
 		if (e->settings.ctas_per_sm > 0) per_sm = std::min(per_sm, e->settings.ctas_per_sm);
 		e->n_ctas_warp = per_sm * e->n_sm;
 		if (getenv("CNF2_DEBUG"))
 			fprintf(stderr, "cnf2: warp kernel %d warps per SM, %zu B shared memory per warp (tables %d + %d entries)\n", per_sm,
-			        warp_smem_bytes(e->cap0, e->cap1), e->cap0, e->cap1);
+			        warp_smem_bytes(e->cap0, e->cap1, e->cls), e->cap0, e->cap1);
 	}
 	CU(e->d_units.ensure(e->units.size()));
 	if (!e->units.empty())
@@ -628,7 +635,11 @@ extern "C" int cnf2_estep(cnf2_engine* e, int32_t chrom)
 			wa.literal_count = sl.counter.p + 1;
 			wa.cap0 = e->cap0;
 			wa.cap1 = e->cap1;
-			warp_estep_kernel<<<std::max(1, std::min(e->n_ctas_warp, n_units)), 32, warp_smem_bytes(e->cap0, e->cap1), sl.stream>>>(wa);
+			wa.cls = e->cls;
+			const int grid = std::max(1, std::min(e->n_ctas_warp, n_units));
+			const size_t smem = warp_smem_bytes(e->cap0, e->cap1, e->cls);
+			if (e->cls) warp_estep_kernel<true><<<grid, 32, smem, sl.stream>>>(wa);
+			else warp_estep_kernel<false><<<grid, 32, smem, sl.stream>>>(wa);
 			CU(cudaGetLastError());
 			e->last_launches++;
 			a.unit_list = sl.literal.p;
