@@ -114,3 +114,54 @@ def test_engine_matches_oracle_on_bench_workloads(eng, maker, kw):
     pb = ol.Problem(d["par"], d["empty"], d["founder"], d["gen"], d["descendants"], d["dous"], d["markerpos"],
                     d["chromstarts"], d["genrec"], d["alleles"], d["sure"], d["haploweight"])
     compare(run_engine(eng, pb), ol.oracle_estep(pb), maker)
+
+
+def test_full_size_chromosome_properties(eng):
+    """BASELINE.json configs[2] at full size for one chromosome (2,000 F2 x 1,000 markers; the oracle would need
+    hours): size-independent properties of the statistics.
+      * moveinfprobs normalises by the root's side-0 sum (cnF2freq.cpp:5879-5885, :3577-3597): an analysed individual
+        that occurs once in its own tree gets infprobs[m][0][1] + infprobs[m][0][2] == descendants at every marker;
+      * movehaplos (:3599-3616) adds `descendants` to haplocount exactly where the individual's phase matters
+        (not homozygous-with-equal-sureness, :1235-1239, which includes unknown genotypes) and is not locked;
+      * linearity: the statistics of two disjoint shards of the analysed individuals add up to the whole
+        (what the all-reduce relies on);
+      * the two likelihood columns differ by at most log 8 (8 shift modes)."""
+    from cnf2freq_b200 import synth
+    d = synth.f2_flat(2000, 1, 1000, spacing_cM=0.1, missing=0.2, seed=3)
+    pb = ol.Problem(d["par"], d["empty"], d["founder"], d["gen"], d["descendants"], d["dous"], d["markerpos"],
+                    d["chromstarts"], d["genrec"], d["alleles"], d["sure"], d["haploweight"])
+    whole = run_engine(eng, pb, shared=[1, 2])
+    f2 = d["dous"]
+    side0 = whole["infprobs"][f2][:, :, 0, :].sum(axis=2)
+    assert_close(side0, np.ones_like(side0), "root side-0 infprobs sum", rtol=1e-9)
+    side1 = whole["infprobs"][f2][:, :, 1, :].sum(axis=2)
+    assert_close(side1, np.ones_like(side1), "root side-1 infprobs sum", rtol=1e-9)
+    al, su = d["alleles"][f2], d["sure"][f2]
+    phased = (al[:, :, 0] != al[:, :, 1]) | (su[:, :, 0] != su[:, :, 1])
+    assert_close(whole["haplocount"][f2], phased.astype(np.float64), "root haplocount", rtol=0, atol=0)
+    assert np.all(whole["haplobase"][f2] >= 0) and np.all(whole["haplobase"][f2] <= 1)
+    # the founders are homozygous everywhere: no phase statistics; every F2 adds to their genotype statistics
+    assert_close(whole["haplocount"][1:3], np.zeros((2, 1000)), "founder haplocount", rtol=0, atol=0)
+    assert np.all(whole["infprobs"][1:3].sum(axis=(2, 3)) > 0)
+    ll = whole["loglik"][:, 0, :]
+    assert np.all(np.isfinite(ll)) and np.all(ll[:, 1] >= ll[:, 0]) and np.all(ll[:, 1] - ll[:, 0] <= np.log(8) + 1e-12)
+    acc = {k: np.zeros_like(whole[k]) for k in STATS}
+    for r in range(2):
+        part = run_engine(eng, pb, dous=f2[r::2], all_dous=f2, shared=[1, 2])
+        for k in STATS:
+            acc[k] += part[k]
+    for k in STATS:
+        assert_close(acc[k], whole[k], f"linearity:{k}", rtol=1e-9, atol=1e-12)
+
+
+def test_no_analysed_individuals(eng):
+    """An empty shard (a rank with nothing to do) is legal: the E-step launches nothing and touches nothing."""
+    pb = randomped.f2_cross(n_f2=2, n_chrom=1, mpc=5, seed=3)
+    engine_problem(eng, pb, dous=np.zeros(0, np.int32), all_dous=pb.dous, shared=np.zeros(0, np.int32))
+    eng.set_params(0, pb.alleles, pb.sure, pb.haploweight)
+    eng.estep(0)
+    out = dict(haplobase=np.full((len(pb.par), 5), 7.0), haplocount=np.full((len(pb.par), 5), 7.0))
+    eng.get_stats(0, out["haplobase"], out["haplocount"])
+    eng.sync()
+    assert eng.last_estep_launches() == 0
+    assert np.all(out["haplobase"] == 7.0) and np.all(out["haplocount"] == 7.0)
