@@ -19,6 +19,38 @@ namespace cnf2
 constexpr int QS = 68;   // sweep-emission table per marker: Q[p][s_p][g_p][f] (64) + R[s0][f] (4)
 constexpr int RC = 16;   // root constants per marker
 constexpr double LN2 = 0.693147180559945309417232121458;
+// Reciprocal for the per-marker tables: rcp.approx (>= 20 bits) + two Newton steps, ~1 ulp for normal x > 0.
+// x = 0 gives NaN instead of inf; every caller either guards x != 0 or only multiplies a value that is then NaN in
+// the reference too (0 * inf).  The parity tolerance is 1e-9 relative; an IEEE division costs ~4x the instructions
+// on the dependent chain of a latency-bound warp.
+__device__ __forceinline__ double frcp(double x)
+{
+	double r;
+	asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+	r = fma(fma(-x, r, 1.0), r, r);
+	r = fma(fma(-x, r, 1.0), r, r);
+	return r;
+}
+// NodeTab (cnf2_device.cuh) with two reciprocals per allele position instead of three divisions
+__device__ __forceinline__ NodeTab make_nodetab_fast(uchar2 a, double2 s, double hw)
+{
+	NodeTab n;
+	n.S[0] = s.x;
+	n.S[1] = s.y;
+	const double ix = s.x != 0 ? frcp(s.x) : 0.0, iy = s.y != 0 ? frcp(s.y) : 0.0;
+	const double jx = frcp(1.0 - s.x), jy = frcp(1.0 - s.y);
+	n.RM[0] = (1.0 - s.x) * ix;
+	n.RM[1] = (1.0 - s.y) * iy;
+	n.RN[0] = (a.x == UNKNOWN ? 1.0 : s.x) * jx;
+	n.RN[1] = (a.y == UNKNOWN ? 1.0 : s.y) * jy;
+	n.SEC[0] = s.x * jx;
+	n.SEC[1] = s.y * jy;
+	const bool hom = a.x == a.y && s.x == s.y;
+	n.W[0] = hom ? 0.0 : fabs(0.0 - hw);
+	n.W[1] = hom ? 1.0 : fabs(1.0 - hw);
+	return n;
+}
+
 // markermiss<0> (cnF2freq.cpp:303-316) for an incoming value v against the individual's allele A
 __device__ __forceinline__ bool bmiss(int v, int A)
 {
@@ -172,6 +204,7 @@ __device__ __forceinline__ void root_constants(const uchar2 a0, const NodeTab& n
 	const int Af = f ? a0.y : a0.x, Ao = f ? a0.x : a0.y;
 	const double Sf = n0.S[f], So = n0.S[f ^ 1];
 	const double d = So != 0 ? 1.0 - So : 1.0;  // :1298-1302
+	const double invd = frcp(d);
 	rc[f] = (1.0 - Sf) * d;                      // plain emission, root level, without the phase weight
 	rc[2 + f] = n0.W[f];
 #pragma unroll
@@ -180,7 +213,7 @@ __device__ __forceinline__ void root_constants(const uchar2 a0, const NodeTab& n
 		const int v = al + 1;
 		rc[4 + al * 2 + f] = bmiss(v, Af) ? Sf : 1.0 - Sf;                                  // GENOSPROBE root factor (:1198-1217)
 		const double hf = (v != Ao) ? (Ao != UNKNOWN ? So : 1.0) : 1.0 - So;                // HOMOZYGOUS, :1306-1319
-		rc[8 + al * 2 + f] = hf / d;
+		rc[8 + al * 2 + f] = hf * invd;
 	}
 }
 }  // namespace cnf2

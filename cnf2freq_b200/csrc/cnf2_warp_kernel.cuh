@@ -107,7 +107,7 @@ __device__ __forceinline__ void post_entry1(const Unit& u, const uchar2* A, cons
 		const int v = f ? a0.y : a0.x;
 		e[0] = Q(v, v != UNKNOWN ? n0.RN[f] : 0.0);
 		const double A1 = rc[4 + f] * P1, A2 = rc[6 + f] * P2;
-		const double sum = A1 + A2, inv = sum > 0 ? 1.0 / sum : 0.0;
+		const double sum = A1 + A2, inv = sum > 0 ? frcp(sum) : 0.0;
 		e[1] = A1 * inv;
 		e[2] = A2 * inv;
 	}
@@ -117,7 +117,7 @@ __device__ __forceinline__ void post_entry1(const Unit& u, const uchar2* A, cons
 		const double E = Q(v, n0.SEC[f ^ 1]);
 		e[0] = E;
 		const double A1 = rc[4 + (f ^ 1)] * P1, A2 = rc[6 + (f ^ 1)] * P2;  // side 1 probes the root at orientation f ^ 1
-		const double sum = A1 + A2, inv = sum > 0 ? 1.0 / sum : 0.0, invE = E > 0 ? 1.0 / E : 0.0;
+		const double sum = A1 + A2, inv = sum > 0 ? frcp(sum) : 0.0, invE = E > 0 ? frcp(E) : 0.0;
 		e[1] = A1 * inv;
 		e[2] = A2 * inv;
 		e[3] = P1 * invE;
@@ -390,7 +390,7 @@ __device__ __forceinline__ void transfer_out(const WarpSmem& w, const double* __
 		const int slot = __ffs(rm) - 1;
 		rootsum += tot[ACC_INF + slot * 4 + 0] + tot[ACC_INF + slot * 4 + 1];
 	}
-	const double inv = 1.0 / rootsum;
+	const double inv = frcp(rootsum);
 	for (int i = lane; i < w.ntr; i += 32)
 	{
 		const TrMeta mt = w.tr[i];
@@ -420,7 +420,7 @@ __device__ __forceinline__ void transfer_out(const WarpSmem& w, const double* __
 		{
 			const double eps = 1.9151695967140057e-174 * (double)(0.000005f) * (double)(0.000005f) * 0.5;  // exp(-400) * maxdiff^2 / 2, :228
 			const double x1 = h0 + eps, x2 = h1 + eps;
-			atomicAdd(dst, q ? mt.scale : x1 / (x1 + x2) * mt.scale);
+			atomicAdd(dst, q ? mt.scale : x1 * frcp(x1 + x2) * mt.scale);
 		}
 	}
 }
@@ -542,7 +542,7 @@ __device__ __forceinline__ bool raw_commit(WarpSmem& w, const RawItem& r, int la
 	if (slot >= NSLOTS) return false;
 	const int i = slot * WB + t;
 	w.A[i] = r.al;
-	w.nt[i] = make_nodetab(r.al, r.su, r.h);
+	w.nt[i] = make_nodetab_fast(r.al, r.su, r.h);
 	w.HW[i] = r.h;
 	return !(r.su.x >= 0 && r.su.x < 1 && r.su.y >= 0 && r.su.y < 1 && r.h >= 0 && r.h <= 1);
 }
