@@ -13,7 +13,8 @@ all-reduced over NCCL once per chromosome).
 
 value      inputs resident in HBM; CUDA events on the engine's stream around the K steps; max over ranks.
 e2e        through the C ABI with pinned HOST buffers: every step copies the parameters host->device
-           (cnf2_set_params) and the statistics device->host (cnf2_get_stats).
+           (cnf2_set_params_packed) and the statistics device->host (cnf2_get_stats_packed), row-ordered
+           contiguous blocks per chromosome; three E-steps in flight.
 roofline   fp64-pipe and HBM bounds from the algorithmic work of SURVEY.md 8(d): 67,584 flop and
            694 B per individual-marker; peaks: fp64 measured in this run (register-resident DFMA kernel,
            MEASURED_PEAKS.json has no fp64 figure), HBM from MEASURED_PEAKS.json.
@@ -206,7 +207,8 @@ def ours(a, rank, world, local_rank):
     else:
         d = synth.f2_flat(a.individuals, a.chroms, a.markers_per_chrom, spacing_cM=0.1, missing=0.2, seed=3 + rank, pinned=pinned)
     K, M, C = d["par"].shape[0], d["markerpos"].shape[0], a.chroms
-    eng = Engine(device=local_rank)
+    # three E-steps in flight; the page-locked parameter arrays are not touched while a step runs
+    eng = Engine(device=local_rank, async_params=True, in_flight=3)
     eng.set_map(d["markerpos"], d["chromstarts"], d["genrec"])
     eng.set_shared_rows(d["shared"])
     if world > 1:
@@ -220,9 +222,12 @@ def ours(a, rank, world, local_rank):
                 dist.all_reduce(t, op=dist.ReduceOp.SUM)
         eng.set_allreduce(allreduce)
     eng.set_pedigree(d["par"], d["empty"], d["founder"], d["gen"], d["descendants"], d["dous"])
-    out = dict(haplobase=pinned((K, M), np.float64), haplocount=pinned((K, M), np.float64),
-               infprobs=pinned((K, M, 2, 2), np.float64), homozyg=pinned((K, M, 2), np.float64),
-               loglik=np.zeros((len(d["dous"]), C, 2)))
+    # statistics come back in the engine's row order, one contiguous block per quantity and chromosome
+    # (cnf2_get_stats_packed): unstrided device -> host copies into page-locked memory; two buffers, alternating
+    R, mc, LAG = len(eng.row_ids()), a.markers_per_chrom, 2
+    out = [dict(haplobase=pinned((R, mc), np.float64), haplocount=pinned((R, mc), np.float64),
+                infprobs=pinned((R, mc, 2, 2), np.float64), homozyg=pinned((R, mc, 2), np.float64),
+                loglik=pinned((len(d["dous"]), 2), np.float64)) for _ in range(3)]
 
     def barrier():
         eng.sync()
@@ -237,14 +242,42 @@ def ours(a, rank, world, local_rank):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    # parameters per chromosome in the engine's row order (cnf2_set_params_packed): unstrided host -> device copies
+    ids = eng.row_ids()
+    P = []
+    for c in range(C):
+        cols = slice(int(d["chromstarts"][c]), int(d["chromstarts"][c + 1]))
+        blk = (pinned((R, mc, 2), np.uint8), pinned((R, mc, 2), np.float64), pinned((R, mc), np.float64))
+        blk[0][...] = d["alleles"][ids][:, cols]
+        blk[1][...] = d["sure"][ids][:, cols]
+        blk[2][...] = d["haploweight"][ids][:, cols]
+        P.append(blk)
+
     def e2e_step():
-        # two E-steps in flight: chromosome c + 1 is handed over and started before chromosome c's statistics are read
-        for c in range(C):
-            eng.set_params(c, d["alleles"], d["sure"], d["haploweight"])
-            eng.estep(c)
-            if c > 0:
-                eng.get_stats(c - 1, out["haplobase"], out["haplocount"], out["infprobs"], out["homozyg"], out["loglik"])
-        eng.get_stats(C - 1, out["haplobase"], out["haplocount"], out["infprobs"], out["homozyg"], out["loglik"])
+        # E-steps in flight: chromosome c is handed over and started before chromosome c - LAG's statistics are read
+        for c in range(C + LAG):
+            if c < C:
+                eng.set_params_packed(c, *P[c])
+                eng.estep(c)
+            if c >= LAG:
+                eng.get_stats_packed(c - LAG, **out[(c - LAG) % 3])
+
+    def e2e_trace():
+        # CNF2_DEBUG: host time spent inside each call of one e2e step (ms per chromosome)
+        tt = {"set_params": [], "estep": [], "get_stats": []}
+        for c in range(C + LAG):
+            t = time.perf_counter()
+            if c < C:
+                eng.set_params_packed(c, *P[c])
+            t1 = time.perf_counter()
+            if c < C:
+                eng.estep(c)
+            t2 = time.perf_counter()
+            if c >= LAG:
+                eng.get_stats_packed(c - LAG, **out[(c - LAG) % 3])
+            t3 = time.perf_counter()
+            tt["set_params"].append(1e3 * (t1 - t)), tt["estep"].append(1e3 * (t2 - t1)), tt["get_stats"].append(1e3 * (t3 - t2))
+        print("cnf2: e2e host ms per call: " + "; ".join(k + " " + " ".join("%.1f" % x for x in v) for k, v in tt.items()), file=sys.stderr)
 
     def resident_step():
         for c in range(C):
@@ -254,6 +287,9 @@ def ours(a, rank, world, local_rank):
     for _ in range(max(1, a.warmup)):
         e2e_step()
     barrier()
+    if os.environ.get("CNF2_DEBUG") and rank == 0:
+        e2e_trace()
+        barrier()
     ind_markers = len(d["dous"]) * M
     states_per_step = ind_markers * NUMTYPES * world
 
@@ -308,7 +344,7 @@ def ours(a, rank, world, local_rank):
                 "unit": "TFLOP/s" if t_fp64 >= t_hbm else "GB/s",
                 "frac": (fl / dfma_tflops) if t_fp64 >= t_hbm else by / hbm_peak, "traffic": traffic_from_profile(per_launch_im),
                 "launch_ms": launch_ms, "launch_ms_isolated": launch_ms_isolated,
-                "launch_ms_note": "launch_ms = timed region / launches (two launches in flight, the tail of one overlaps the next); isolated = one launch alone, CUDA events around it",
+                "launch_ms_note": "launch_ms = timed region / launches (launches in flight, the tail of one overlaps the next); isolated = one launch alone, CUDA events around it",
                 "peak_source": "fp64: register-resident DFMA kernel measured in this run (MEASURED_PEAKS.json has no fp64 "
                                "figure); hbm: MEASURED_PEAKS.json" + ("" if peaks else " absent -> fallback 6650 GB/s"),
                 "hbm": {"achieved": by, "peak": hbm_peak, "unit": "GB/s", "frac": by / hbm_peak, "copy_gbs_this_run": copy_gbs},

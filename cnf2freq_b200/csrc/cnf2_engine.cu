@@ -106,6 +106,7 @@ struct cnf2_engine
 	size_t ld = 0;
 	std::vector<uint8_t> have_params;
 	cudaEvent_t marks[4] = { nullptr, nullptr, nullptr, nullptr };
+	cudaEvent_t params_ready = nullptr;  // behind the last cnf2_set_params copies on `stream`
 	int last_launches = 0;
 	cnf2_allreduce_fn allreduce = nullptr;
 	void* allreduce_ctx = nullptr;
@@ -186,6 +187,7 @@ extern "C" int cnf2_create(cnf2_engine** out, const cnf2_settings* settings)
 	e->n_sm = prop.multiProcessorCount;
 	if ((ce = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(ce, "cudaStreamCreate");
 	if ((ce = cudaStreamCreateWithFlags(&e->comm, cudaStreamNonBlocking)) != cudaSuccess) return bail(ce, "cudaStreamCreate");
+	if ((ce = cudaEventCreateWithFlags(&e->params_ready, cudaEventDisableTiming)) != cudaSuccess) return bail(ce, "cudaEventCreate");
 	for (Slot& sl : e->slots)
 	{
 		if ((ce = cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(ce, "cudaStreamCreate");
@@ -212,6 +214,7 @@ extern "C" int cnf2_create(cnf2_engine** out, const cnf2_settings* settings)
 	const char* lit = getenv("CNF2_LITERAL");
 	e->literal_only = lit && lit[0] == '1';
 	if (const char* cp = getenv("CNF2_CTAS_PER_SM")) e->settings.ctas_per_sm = atoi(cp);
+	if (settings->in_flight > 0) e->n_slots = std::min(NSLOT, (int)settings->in_flight);
 	if (const char* ns = getenv("CNF2_SLOTS")) e->n_slots = std::max(1, std::min(NSLOT, atoi(ns)));
 	*out = e;
 	return CNF2_OK;
@@ -241,6 +244,7 @@ extern "C" void cnf2_destroy(cnf2_engine* e)
 	e->d_units.release();
 	for (cudaEvent_t m : e->marks)
 		if (m) cudaEventDestroy(m);
+	if (e->params_ready) cudaEventDestroy(e->params_ready);
 	if (e->stream) cudaStreamDestroy(e->stream);
 	delete e;
 }
@@ -531,12 +535,12 @@ extern "C" int cnf2_set_pedigree(cnf2_engine* e, int32_t n_ind, const int32_t* p
 	CU(cudaMemGetInfo(&free_b, &total_b));
 	const size_t M = e->markerpos.size();
 	e->resident = !e->markerpos.empty() && (double)e->n_rows * M * 26.0 < 0.4 * (double)free_b;
-	e->ld = e->resident ? M : (size_t)e->max_mc;
+	e->ld = 0;  // parameters are stored per chromosome: [n_rows][Mc] blocks, chromosome c at n_rows * chromstarts[c] when resident
 	return CNF2_OK;
 }
 
-extern "C" int cnf2_set_params(cnf2_engine* e, int32_t chrom, const uint8_t* alleles, const double* sure,
-                               const double* haploweight)
+static int set_params_impl(cnf2_engine* e, int32_t chrom, const uint8_t* alleles, const double* sure, const double* haploweight,
+                           bool packed)
 {
 	if (!e) return CNF2_ERR_BAD_ARG;
 	if (e->chromstarts.empty() || e->rowof.empty()) return e->fail(CNF2_ERR_STATE, "cnf2_set_params: set_map and set_pedigree first");
@@ -547,18 +551,27 @@ extern "C" int cnf2_set_params(cnf2_engine* e, int32_t chrom, const uint8_t* all
 		for (Slot& sl : e->slots) CU(cudaStreamSynchronize(sl.stream));
 	const size_t M = e->markerpos.size();
 	const size_t c0 = e->chromstarts[chrom];
-	const size_t Mc = e->mc(chrom), ld = e->ld;
+	const size_t Mc = e->mc(chrom), ld = Mc;
 	const size_t col0 = e->resident ? c0 : 0;
-	CU(e->d_alleles.ensure((size_t)e->n_rows * ld));
-	CU(e->d_sure.ensure((size_t)e->n_rows * ld));
-	CU(e->d_hw.ensure((size_t)e->n_rows * ld));
-	for (const Run& r : e->runs)
+	const size_t total = (size_t)e->n_rows * (e->resident ? M : (size_t)e->max_mc), blk = (size_t)e->n_rows * col0;
+	CU(e->d_alleles.ensure(total));
+	CU(e->d_sure.ensure(total));
+	CU(e->d_hw.ensure(total));
+	if (packed)
 	{
-		const size_t src = (size_t)r.id0 * M + c0, dst = (size_t)r.row0 * ld + col0;
-		CU(cudaMemcpy2DAsync(e->d_alleles.p + dst, ld * 2, alleles + src * 2, M * 2, Mc * 2, r.n, cudaMemcpyHostToDevice, e->stream));
-		CU(cudaMemcpy2DAsync(e->d_sure.p + dst, ld * 16, sure + src * 2, M * 16, Mc * 16, r.n, cudaMemcpyHostToDevice, e->stream));
-		CU(cudaMemcpy2DAsync(e->d_hw.p + dst, ld * 8, haploweight + src, M * 8, Mc * 8, r.n, cudaMemcpyHostToDevice, e->stream));
+		// row-ordered contiguous blocks [n_rows][Mc]: one unstrided copy per array
+		CU(cudaMemcpyAsync(e->d_alleles.p + blk, alleles, (size_t)e->n_rows * Mc * 2, cudaMemcpyHostToDevice, e->stream));
+		CU(cudaMemcpyAsync(e->d_sure.p + blk, sure, (size_t)e->n_rows * Mc * 16, cudaMemcpyHostToDevice, e->stream));
+		CU(cudaMemcpyAsync(e->d_hw.p + blk, haploweight, (size_t)e->n_rows * Mc * 8, cudaMemcpyHostToDevice, e->stream));
 	}
+	else
+		for (const Run& r : e->runs)
+		{
+			const size_t src = (size_t)r.id0 * M + c0, dst = blk + (size_t)r.row0 * ld;
+			CU(cudaMemcpy2DAsync(e->d_alleles.p + dst, ld * 2, alleles + src * 2, M * 2, Mc * 2, r.n, cudaMemcpyHostToDevice, e->stream));
+			CU(cudaMemcpy2DAsync(e->d_sure.p + dst, ld * 16, sure + src * 2, M * 16, Mc * 16, r.n, cudaMemcpyHostToDevice, e->stream));
+			CU(cudaMemcpy2DAsync(e->d_hw.p + dst, ld * 8, haploweight + src, M * 8, Mc * 8, r.n, cudaMemcpyHostToDevice, e->stream));
+		}
 	// recombination fractions towards the next marker (:2286; getactrec :777-780 ignores sex and marker)
 	std::vector<double> rec(2 * Mc, 0.0);
 	for (size_t m = 0; m + 1 < Mc; m++)
@@ -570,10 +583,25 @@ extern "C" int cnf2_set_params(cnf2_engine* e, int32_t chrom, const uint8_t* all
 	}
 	CU(e->d_rec.ensure(2 * (e->resident ? M : (size_t)e->max_mc)));
 	CU(cudaMemcpyAsync(e->d_rec.p + 2 * col0, rec.data(), rec.size() * sizeof(double), cudaMemcpyHostToDevice, e->stream));
-	CU(cudaStreamSynchronize(e->stream));  // rec is a stack-lifetime buffer; caller buffers may be reused after return
+	CU(cudaEventRecord(e->params_ready, e->stream));
+	// async_params: the copies from page-locked caller buffers are left in flight (the E-step waits for them on the
+	// device); otherwise caller buffers may be reused after return.  rec is pageable: staged before the call returns.
+	if (!e->settings.async_params) CU(cudaStreamSynchronize(e->stream));
 	if (!e->resident) std::fill(e->have_params.begin(), e->have_params.end(), 0);
 	e->have_params[chrom] = 1;
 	return CNF2_OK;
+}
+
+extern "C" int cnf2_set_params(cnf2_engine* e, int32_t chrom, const uint8_t* alleles, const double* sure,
+                               const double* haploweight)
+{
+	return set_params_impl(e, chrom, alleles, sure, haploweight, false);
+}
+
+extern "C" int cnf2_set_params_packed(cnf2_engine* e, int32_t chrom, const uint8_t* alleles, const double* sure,
+                                      const double* haploweight)
+{
+	return set_params_impl(e, chrom, alleles, sure, haploweight, true);
 }
 
 extern "C" int cnf2_estep(cnf2_engine* e, int32_t chrom)
@@ -598,6 +626,7 @@ extern "C" int cnf2_estep(cnf2_engine* e, int32_t chrom)
 	CU(sl.stats.ensure((size_t)e->n_rows * e->max_mc * STATS_PER_CELL));
 	sl.n_shared = e->n_shared;
 	sl.chrom = chrom;
+	CU(cudaStreamWaitEvent(sl.stream, e->params_ready, 0));
 	CU(cudaEventRecord(sl.ev0, sl.stream));
 	CU(cudaMemsetAsync(sl.stats.p, 0, (size_t)e->n_rows * Mc * STATS_PER_CELL * sizeof(double), sl.stream));
 	CU(cudaMemsetAsync(sl.counter.p, 0, 4 * sizeof(unsigned int), sl.stream));
@@ -607,15 +636,15 @@ extern "C" int cnf2_estep(cnf2_engine* e, int32_t chrom)
 		WarpArgs wa{};
 		EstepArgs& a = wa.e;
 		const size_t col0 = e->resident ? e->chromstarts[chrom] : 0;
-		a.alleles = e->d_alleles.p + col0;
-		a.sure = e->d_sure.p + col0;
-		a.hw = e->d_hw.p + col0;
+		a.alleles = e->d_alleles.p + (size_t)e->n_rows * col0;
+		a.sure = e->d_sure.p + (size_t)e->n_rows * col0;
+		a.hw = e->d_hw.p + (size_t)e->n_rows * col0;
 		a.rec0 = e->d_rec.p + 2 * col0;
 		a.rec1 = e->d_rec.p + 2 * col0 + Mc;
 		a.units = e->d_units.p;
 		a.n_units = n_units;
 		a.Mc = Mc;
-		a.ld = (int32_t)e->ld;
+		a.ld = Mc;
 		a.counter = sl.counter.p;
 		a.alpha = sl.alpha.p;
 		a.alphafac = sl.alphafac.p;
@@ -713,6 +742,50 @@ extern "C" int cnf2_get_stats(cnf2_engine* e, int32_t chrom, double* haplobase, 
 			loglik[(j * C + chrom) * 2 + 1] = e->h_loglik[j * 2 + 1];
 		}
 	}
+	return CNF2_OK;
+}
+
+extern "C" int cnf2_row_count(cnf2_engine* e, int32_t* n_rows)
+{
+	if (!e || !n_rows) return CNF2_ERR_BAD_ARG;
+	*n_rows = e->n_rows;
+	return CNF2_OK;
+}
+
+extern "C" int cnf2_row_ids(cnf2_engine* e, int32_t* ids)
+{
+	if (!e || !ids) return CNF2_ERR_BAD_ARG;
+	for (int32_t r = 0; r < e->n_rows; r++) ids[r] = e->rowid[r];
+	return CNF2_OK;
+}
+
+extern "C" int cnf2_get_stats_packed(cnf2_engine* e, int32_t chrom, double* haplobase, double* haplocount, double* infprobs,
+                                     double* homozyg, double* loglik)
+{
+	if (!e) return CNF2_ERR_BAD_ARG;
+	Slot* slp = nullptr;
+	for (Slot& o : e->slots)
+		if (chrom >= 0 && o.chrom == chrom) slp = &o;
+	if (!slp) return e->fail(CNF2_ERR_STATE, "cnf2_get_stats_packed: cnf2_estep for this chromosome first (only the last E-steps in flight are kept)");
+	Slot& sl = *slp;
+	cudaSetDevice(e->settings.device);
+	const size_t Mc = e->mc(chrom);
+	// the device holds a shared block and a local block, each as planes haplobase | haplocount | infprobs | homozyg
+	for (int blk = 0; blk < 2; blk++)
+	{
+		const size_t nr = blk ? (size_t)(e->n_rows - e->n_shared) : (size_t)e->n_shared, row0 = blk ? (size_t)e->n_shared : 0;
+		if (!nr) continue;
+		const double* base = blk ? sl.stats_local((int)Mc) : sl.stats_shared();
+		const size_t plane = nr * Mc, off = row0 * Mc;
+		if (haplobase) CU(cudaMemcpyAsync(haplobase + off, base, plane * 8, cudaMemcpyDeviceToHost, sl.stream));
+		if (haplocount) CU(cudaMemcpyAsync(haplocount + off, base + plane, plane * 8, cudaMemcpyDeviceToHost, sl.stream));
+		if (infprobs) CU(cudaMemcpyAsync(infprobs + off * 4, base + 2 * plane, plane * 32, cudaMemcpyDeviceToHost, sl.stream));
+		if (homozyg) CU(cudaMemcpyAsync(homozyg + off * 2, base + 6 * plane, plane * 16, cudaMemcpyDeviceToHost, sl.stream));
+	}
+	if (loglik && !e->units.empty())
+		CU(cudaMemcpyAsync(loglik, sl.loglik.p, e->units.size() * 2 * sizeof(double), cudaMemcpyDeviceToHost, sl.stream));
+	CU(cudaStreamSynchronize(sl.stream));
+	CU(cudaGetLastError());
 	return CNF2_OK;
 }
 

@@ -17,13 +17,13 @@ SYMBOLS = [
     "cnf2_default_settings", "cnf2_create", "cnf2_destroy", "cnf2_last_error", "cnf2_set_map", "cnf2_set_pedigree",
     "cnf2_set_params", "cnf2_estep", "cnf2_set_allreduce", "cnf2_set_shared_rows", "cnf2_get_stats", "cnf2_sync",
     "cnf2_last_estep_ms", "cnf2_last_estep_launches", "cnf2_stream", "cnf2_measure_peaks", "cnf2_mark",
-    "cnf2_elapsed_ms",
+    "cnf2_elapsed_ms", "cnf2_row_count", "cnf2_row_ids", "cnf2_get_stats_packed", "cnf2_set_params_packed",
 ]
 
 
 class Settings(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int32) for n in
-                ("numgen", "selfing", "relskewstates", "haplotyping", "doinfprobs", "device", "ctas_per_sm", "reserved")]
+                ("numgen", "selfing", "relskewstates", "haplotyping", "doinfprobs", "device", "ctas_per_sm", "async_params", "in_flight", "reserved")]
 
 
 ALLREDUCE_FN = ctypes.CFUNCTYPE(ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p)
@@ -62,12 +62,14 @@ def _ptr(a):
 class Engine:
     """One engine = one GPU (one rank).  Method names follow the C ABI."""
 
-    def __init__(self, device=0, ctas_per_sm=0):
+    def __init__(self, device=0, ctas_per_sm=0, async_params=False, in_flight=0):
         self.lib = load_library()
         s = Settings()
         self.lib.cnf2_default_settings(ctypes.byref(s))
         s.device = device
         s.ctas_per_sm = ctas_per_sm
+        s.async_params = 1 if async_params else 0
+        s.in_flight = in_flight
         self.h = ctypes.c_void_p()
         rc = self.lib.cnf2_create(ctypes.byref(self.h), ctypes.byref(s))
         if rc != 0:
@@ -137,12 +139,34 @@ class Engine:
                 raise EngineError("set_params: arrays must be C-contiguous [n_ind][n_markers](x2) of the documented dtype")
         self._check(self.lib.cnf2_set_params(self.h, ctypes.c_int32(chrom), _ptr(alleles), _ptr(sure), _ptr(haploweight)))
 
+    def set_params_packed(self, chrom, alleles, sure, haploweight):
+        """Row-ordered (row_ids()) arrays of this chromosome only: alleles u8 [n_rows][Mc][2], sure f64 [n_rows][Mc][2],
+        haploweight f64 [n_rows][Mc]."""
+        for a, dt in ((alleles, np.uint8), (sure, np.float64), (haploweight, np.float64)):
+            if a.dtype != dt or not a.flags.c_contiguous:
+                raise EngineError("set_params_packed: arrays must be C-contiguous of the documented dtype")
+        self._check(self.lib.cnf2_set_params_packed(self.h, ctypes.c_int32(chrom), _ptr(alleles), _ptr(sure), _ptr(haploweight)))
+
     def estep(self, chrom):
         self._check(self.lib.cnf2_estep(self.h, ctypes.c_int32(chrom)))
 
     def get_stats(self, chrom, haplobase=None, haplocount=None, infprobs=None, homozyg=None, loglik=None):
         self._check(self.lib.cnf2_get_stats(self.h, ctypes.c_int32(chrom), _ptr(haplobase), _ptr(haplocount),
                                             _ptr(infprobs), _ptr(homozyg), _ptr(loglik)))
+
+    def row_ids(self):
+        """Individual id of every statistics row of this engine (shared rows first)."""
+        n = ctypes.c_int32()
+        self._check(self.lib.cnf2_row_count(self.h, ctypes.byref(n)))
+        ids = np.zeros(n.value, np.int32)
+        if n.value:
+            self._check(self.lib.cnf2_row_ids(self.h, _ptr(ids)))
+        return ids
+
+    def get_stats_packed(self, chrom, haplobase=None, haplocount=None, infprobs=None, homozyg=None, loglik=None):
+        """Row-ordered contiguous blocks ([n_rows][Mc]...; see include/cnf2_engine.h): unstrided device -> host copies."""
+        self._check(self.lib.cnf2_get_stats_packed(self.h, ctypes.c_int32(chrom), _ptr(haplobase), _ptr(haplocount),
+                                                   _ptr(infprobs), _ptr(homozyg), _ptr(loglik)))
 
     def sync(self):
         self._check(self.lib.cnf2_sync(self.h))

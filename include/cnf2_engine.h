@@ -54,6 +54,10 @@ typedef struct cnf2_settings
 	int32_t doinfprobs;    /* settings.h:12  DOINFPROBS */
 	int32_t device;        /* CUDA device ordinal of this engine (one engine per GPU / rank) */
 	int32_t ctas_per_sm;   /* 0 = let the engine choose from the occupancy query */
+	int32_t async_params;  /* 0: cnf2_set_params returns when its copies are done (caller buffers reusable at once);
+	                          1: copies from page-locked buffers stay in flight -- keep the arrays unchanged until the
+	                          chromosome's cnf2_get_stats* or cnf2_sync returns */
+	int32_t in_flight;     /* E-steps kept in flight (their statistics stay readable): 0 = default (2), up to 4 */
 	int32_t reserved;
 } cnf2_settings;
 
@@ -91,9 +95,15 @@ int cnf2_set_pedigree(cnf2_engine* e, int32_t n_ind, const int32_t* parents, con
 int cnf2_set_params(cnf2_engine* e, int32_t chrom, const uint8_t* alleles, const double* sure,
                     const double* haploweight);
 
+/* The same for arrays already in the engine's row order (cnf2_row_ids) and holding only this chromosome:
+ * alleles [n_rows][Mc][2], sure [n_rows][Mc][2], haploweight [n_rows][Mc] -- three unstrided host -> device
+ * copies.  The reference keeps these per individual (:876-887), so a binding gathers them either way. */
+int cnf2_set_params_packed(cnf2_engine* e, int32_t chrom, const uint8_t* alleles, const double* sure,
+                           const double* haploweight);
+
 /* The E-step of one chromosome for all of this engine's analysed individuals: cnF2freq.cpp:5294-5907
  * without the turn scoring (:5668-5871, row f2 of SURVEY.md section 8).  Asynchronous; cnf2_get_stats /
- * cnf2_sync wait for it.  Two E-steps are kept in flight (each with its own stream, scratch and statistics
+ * cnf2_sync wait for it.  Two E-steps (cnf2_settings.in_flight) are kept in flight (each with its own stream, scratch and statistics
  * block), so the tail of one chromosome's launch overlaps the next chromosome's: call cnf2_estep for chromosome
  * c + 1 before cnf2_get_stats for chromosome c to use that. */
 int cnf2_estep(cnf2_engine* e, int32_t chrom);
@@ -117,6 +127,18 @@ int cnf2_set_shared_rows(cnf2_engine* e, const int32_t* ids, int32_t n_ids);
  * Any pointer may be NULL to skip that output. */
 int cnf2_get_stats(cnf2_engine* e, int32_t chrom, double* haplobase, double* haplocount, double* infprobs,
                    double* homozyg, double* loglik);
+
+/* The same statistics in the engine's own row order, one contiguous block per quantity (device -> host copies
+ * without a stride: the form for page-locked buffers on a hot loop).  The reference keeps these statistics in
+ * per-individual vectors (cnF2freq.cpp:895-902), so a binding scatters rows into individuals either way:
+ * cnf2_row_ids gives the individual id of every row (cnf2_row_count of them: the individuals this engine's focus
+ * trees touch, shared rows first).  haplobase/haplocount [n_rows][Mc], infprobs [n_rows][Mc][2][2],
+ * homozyg [n_rows][Mc][2] with Mc = markers of `chrom`; loglik [n_dous][2] for this chromosome.  Any pointer may
+ * be NULL. */
+int cnf2_row_count(cnf2_engine* e, int32_t* n_rows);
+int cnf2_row_ids(cnf2_engine* e, int32_t* ids);
+int cnf2_get_stats_packed(cnf2_engine* e, int32_t chrom, double* haplobase, double* haplocount, double* infprobs,
+                          double* homozyg, double* loglik);
 
 /* Block until everything enqueued by this engine has finished; returns the first asynchronous error. */
 int cnf2_sync(cnf2_engine* e);

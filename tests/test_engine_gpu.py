@@ -165,3 +165,33 @@ def test_no_analysed_individuals(eng):
     eng.sync()
     assert eng.last_estep_launches() == 0
     assert np.all(out["haplobase"] == 7.0) and np.all(out["haplocount"] == 7.0)
+
+
+def test_packed_statistics_equal_the_scattered_ones(eng):
+    pb = randomped.tangled(n_chrom=2, mpc=13, seed=51)
+    engine_problem(eng, pb, shared=np.array([1, 4], np.int32))
+    ids = eng.row_ids()
+    assert len(set(ids.tolist())) == len(ids) and ids[0] == 1 and ids[1] == 4
+    K, M = len(pb.par), len(pb.markerpos)
+    for c in range(2):
+        eng.set_params(c, pb.alleles, pb.sure, pb.haploweight)
+        eng.estep(c)
+        full = dict(haplobase=np.zeros((K, M)), haplocount=np.zeros((K, M)), infprobs=np.zeros((K, M, 2, 2)),
+                    homozyg=np.zeros((K, M, 2)), loglik=np.zeros((len(pb.dous), 2, 2)))
+        eng.get_stats(c, **full)
+        Mc = 13
+        pk = dict(haplobase=np.zeros((len(ids), Mc)), haplocount=np.zeros((len(ids), Mc)), infprobs=np.zeros((len(ids), Mc, 2, 2)),
+                  homozyg=np.zeros((len(ids), Mc, 2)), loglik=np.zeros((len(pb.dous), 2)))
+        eng.get_stats_packed(c, **pk)
+        for k in STATS:
+            assert np.array_equal(pk[k], full[k][ids, c * Mc:(c + 1) * Mc], equal_nan=True), k
+        assert np.array_equal(pk["loglik"], full["loglik"][:, c, :])
+        # the same E-step from row-ordered parameter blocks of this chromosome
+        cols = slice(c * Mc, (c + 1) * Mc)
+        eng.set_params_packed(c, np.ascontiguousarray(pb.alleles[ids][:, cols]), np.ascontiguousarray(pb.sure[ids][:, cols]),
+                              np.ascontiguousarray(pb.haploweight[ids][:, cols]))
+        eng.estep(c)
+        pk2 = {k: np.zeros_like(v) for k, v in pk.items()}
+        eng.get_stats_packed(c, **pk2)
+        for k in pk:
+            assert_close(pk2[k], pk[k], "packed parameters:" + k, rtol=1e-12, atol=1e-15)  # atomics: order of summation
