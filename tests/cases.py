@@ -7,7 +7,8 @@ import numpy as np
 import oracle_lib as ol
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-GOLDEN_CASES = sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN, "*.npz")))
+GOLDEN_CASES = sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN, "*.npz"))
+                      if not os.path.basename(p).startswith("mstep_"))
 STATS = ("haplobase", "haplocount", "infprobs", "homozyg")
 RTOL = 1e-9  # BASELINE.json north_star: posteriors within 1e-9 relative (fp64)
 

@@ -1,0 +1,64 @@
+"""Golden fixtures of the M-step (row a6 / f1) from the REFERENCE's own code: for whole EM iterations of
+oracle/_ref/cnf2ref (single-threaded) the parameters before doit(), the EM statistics as they stood before each
+chromosome's M-step pass ("FIRST PASS" hook of oracle/ref_driver.cpp), and the parameters + step-size scalars after
+doit().  Only iterations without phase inversions are kept (negshift > -1e-10 everywhere).  Only runs where
+/root/reference exists; the fixtures are committed.
+
+usage: python tests/golden/make_mstep_golden.py
+"""
+import os
+import subprocess
+import sys
+import tempfile
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+from cnf2dump import read_dump  # noqa: E402
+from cnf2freq_b200 import synth  # noqa: E402
+
+REF = os.environ.get("CNF2_REFERENCE_DIR", "/root/reference")
+BIN = os.path.join(ROOT, "oracle", "_ref", "cnf2ref")
+
+
+def collect(prefix, iterations):
+    prob = read_dump(prefix + ".problem")
+    C = len(prob["chromstarts"]) - 1
+    out = dict(par=np.stack([prob["par0"], prob["par1"]], axis=1).astype(np.int32), exists=prob["exists"], empty=prob["empty"],
+               hasprior=prob["hasprior"], descendants=prob["descendants"], dous=prob["dous"],
+               chromstarts=prob["chromstarts"].astype(np.uint32), iterations=np.asarray(iterations))
+    for it in iterations:
+        a, b = read_dump(f"{prefix}.iter{it}.params"), read_dump(f"{prefix}.iter{it}.state")
+        assert b["negshift"].min() > -1e-10, "phase inversion in this iteration"
+        for k in ("alleles", "sure", "haploweight", "relhaplo", "prioralleles", "priorsure", "scalars"):
+            out[f"it{it}_before_{k}"] = a[k]
+        for k in ("alleles", "sure", "haploweight", "scalars", "children"):  # children is rebuilt inside doit (:5246-5259)
+            out[f"it{it}_after_{k}"] = b[k]
+        for c in range(C):
+            st = read_dump(f"{prefix}.iter{it}.chrom{c}.stats")
+            for k in ("haplobase", "haplocount", "infprobs", "homozyg"):
+                out[f"it{it}_c{c}_{k}"] = st[k]
+    return out
+
+
+def main():
+    env = dict(os.environ, OMP_NUM_THREADS="1")
+    with tempfile.TemporaryDirectory() as tmp:
+        args = ["--mapfile", f"{REF}/demoplantimpute.map", "--pedfile", f"{REF}/demoplantimpute.ped", "--genfile",
+                f"{REF}/demoplantimpute.gen"]
+        subprocess.run([BIN] + args + ["--count", "4", "--dump", tmp + "/demo"], env=env, capture_output=True, check=True)
+        np.savez_compressed(os.path.join(HERE, "mstep_demo.npz"), **collect(tmp + "/demo", [1, 2, 3]))
+        sim = synth.simulate_f2(n_f2=6, n_chrom=2, markers_per_chrom=24, spacing_cM=1.5, missing=0.2, seed=3)
+        synth.write_alpha_files(tmp + "/f2", sim)
+        args = ["--mapfile", tmp + "/f2.map", "--pedfile", tmp + "/f2.ped", "--genfile", tmp + "/f2.gen"]
+        subprocess.run([BIN] + args + ["--count", "3", "--dump", tmp + "/f2"], env=env, capture_output=True, check=True)
+        np.savez_compressed(os.path.join(HERE, "mstep_f2.npz"), **collect(tmp + "/f2", [1, 2]))
+    for n in ("mstep_demo.npz", "mstep_f2.npz"):
+        print(n, os.path.getsize(os.path.join(HERE, n)), "bytes")
+
+
+if __name__ == "__main__":
+    main()

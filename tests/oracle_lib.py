@@ -10,10 +10,10 @@ _LIB = os.path.join(ROOT, "oracle", "_build", "libcnf2oracle.so")
 
 
 def build_oracle(force=False):
-    src = os.path.join(ROOT, "oracle", "cnf2_oracle.cpp")
-    if force or not os.path.exists(_LIB) or os.path.getmtime(_LIB) < os.path.getmtime(src):
+    srcs = [os.path.join(ROOT, "oracle", f) for f in ("cnf2_oracle.cpp", "cnf2_mstep_oracle.cpp")]
+    if force or not os.path.exists(_LIB) or os.path.getmtime(_LIB) < max(os.path.getmtime(s) for s in srcs):
         os.makedirs(os.path.dirname(_LIB), exist_ok=True)
-        subprocess.check_call(["g++", "-std=c++17", "-O2", "-fopenmp", "-fPIC", "-shared", "-o", _LIB, src])
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-fopenmp", "-fPIC", "-shared", "-o", _LIB] + srcs)
     return _LIB
 
 
@@ -93,3 +93,30 @@ def oracle_estep(pb, fwbw_for=None, counters=False):
     if fwbw_for is not None:
         out.update(fwbw=fw, fwbwfactors=ff, fwbwmask=fm)
     return out
+
+
+def oracle_mstep(chromstarts, active, empty, children, descendants, alleles, sure, haploweight, relhaplo, hasprior,
+                 prioralleles, priorsure, haplobase, haplocount, infprobs, homozyg, scalefactor, entropyfactor):
+    """One pass of the reference's M-step block (cnF2freq.cpp:6356-6367) on copies of the arrays.  Returns
+    dict(alleles, sure, haploweight, haplobase, haplocount, hitnnn)."""
+    K, M = haploweight.shape
+    cs = np.ascontiguousarray(chromstarts, np.uint32)
+    c = lambda a, dt: np.array(a, dt, order="C", copy=True)
+    al, su, hw = c(alleles, np.uint8), c(sure, np.float64), c(haploweight, np.float64)
+    hb, hc, ip, hz = c(haplobase, np.float64), c(haplocount, np.float64), c(infprobs, np.float64), c(homozyg, np.float64)
+    f = lib().cnf2_oracle_mstep
+    f.restype = ctypes.c_longlong
+    hit = f(ctypes.c_int(K), ctypes.c_int(M), ctypes.c_int(len(cs) - 1), _p(cs), _p(c(active, np.uint8)), _p(c(empty, np.uint8)),
+            _p(c(children, np.int32)), _p(c(descendants, np.int32)), _p(al), _p(su), _p(hw), _p(c(relhaplo, np.float64)),
+            _p(c(hasprior, np.uint8)), _p(c(prioralleles, np.uint8)), _p(c(priorsure, np.float64)), _p(hb), _p(hc), _p(ip), _p(hz),
+            ctypes.c_double(scalefactor), ctypes.c_double(entropyfactor))
+    return dict(alleles=al, sure=su, haploweight=hw, haplobase=hb, haplocount=hc, hitnnn=int(hit))
+
+
+def oracle_scalefactor(scalefactor, hitnnn, n_dous, oldhitnnn, oldhitnnn2):
+    """The step-size control behind the pass (cnF2freq.cpp:6373-6390).  Returns (scalefactor, oldhitnnn, oldhitnnn2)."""
+    f = lib().cnf2_oracle_scalefactor
+    f.restype = ctypes.c_double
+    o1, o2 = ctypes.c_int32(int(oldhitnnn)), ctypes.c_int32(int(oldhitnnn2))
+    sf = f(ctypes.c_double(scalefactor), ctypes.c_longlong(hitnnn), ctypes.c_int(n_dous), ctypes.byref(o1), ctypes.byref(o2))
+    return float(sf), o1.value, o2.value
