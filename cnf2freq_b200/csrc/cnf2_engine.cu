@@ -3,6 +3,7 @@
 // every entry point that would compute needs the CUDA device.
 #include "../../include/cnf2_engine.h"
 #include "cnf2_warp_kernel.cuh"
+#include "cnf2_mstep_kernel.cuh"
 
 #include <algorithm>
 #include <cmath>
@@ -99,6 +100,15 @@ struct cnf2_engine
 	int n_ctas_literal = 0;
 	bool literal_only = false;  // debugging / A-B switch: CNF2_LITERAL=1 runs every unit through the literal kernel
 	DevBuf<Unit> d_units;
+	// M-step (row a6): inputs the E-step does not need, carried haplobase/haplocount, scratch
+	DevBuf<double> d_relhaplo, d_carry_base, d_carry_count, d_ratio, d_fw;
+	DevBuf<double2> d_priorsure;
+	DevBuf<uchar2> d_prioral;
+	DevBuf<MstepRow> d_msrows;
+	DevBuf<uint8_t> d_anyinfo;
+	DevBuf<unsigned long long> d_hit;
+	std::vector<uint8_t> carry_valid;
+	bool have_ms_inputs = false;
 	std::vector<double> h_loglik;
 
 	// parameters stay resident for every chromosome when they fit (resident), else one chromosome at a time
@@ -742,6 +752,142 @@ extern "C" int cnf2_get_stats(cnf2_engine* e, int32_t chrom, double* haplobase, 
 			loglik[(j * C + chrom) * 2 + 1] = e->h_loglik[j * 2 + 1];
 		}
 	}
+	return CNF2_OK;
+}
+
+extern "C" int cnf2_set_mstep_inputs(cnf2_engine* e, const double* relhaplo, const uint8_t* prioralleles, const double* priorsure,
+                                     const uint8_t* hasprior, const int32_t* children, const uint8_t* empty,
+                                     const int32_t* descendants)
+{
+	if (!e || !relhaplo || !prioralleles || !priorsure || !hasprior || !children || !empty || !descendants) return CNF2_ERR_BAD_ARG;
+	if (e->chromstarts.empty() || e->rowof.empty()) return e->fail(CNF2_ERR_STATE, "cnf2_set_mstep_inputs: set_map and set_pedigree first");
+	if (!e->resident) return e->fail(CNF2_ERR_STATE, "cnf2_set_mstep_inputs: the M-step needs the parameters of all chromosomes resident");
+	cudaSetDevice(e->settings.device);
+	const size_t M = e->markerpos.size(), total = (size_t)e->n_rows * M;
+	CU(e->d_relhaplo.ensure(total));
+	CU(e->d_prioral.ensure(total));
+	CU(e->d_priorsure.ensure(total));
+	CU(e->d_carry_base.ensure(total));
+	CU(e->d_carry_count.ensure(total));
+	CU(e->d_ratio.ensure((size_t)e->n_rows * e->max_mc));
+	CU(e->d_fw.ensure((size_t)e->n_rows * e->max_mc * 2));
+	CU(e->d_anyinfo.ensure(e->n_rows));
+	CU(e->d_hit.ensure(1));
+	CU(e->d_msrows.ensure(e->n_rows));
+	for (size_t c = 0; c + 1 < e->chromstarts.size(); c++)
+	{
+		const size_t c0 = e->chromstarts[c], Mc = e->mc((int)c), blk = (size_t)e->n_rows * c0;
+		for (const Run& r : e->runs)
+		{
+			const size_t src = (size_t)r.id0 * M + c0, dst = blk + (size_t)r.row0 * Mc;
+			CU(cudaMemcpy2DAsync(e->d_relhaplo.p + dst, Mc * 8, relhaplo + src, M * 8, Mc * 8, r.n, cudaMemcpyHostToDevice, e->stream));
+			CU(cudaMemcpy2DAsync(e->d_prioral.p + dst, Mc * 2, prioralleles + src * 2, M * 2, Mc * 2, r.n, cudaMemcpyHostToDevice, e->stream));
+			CU(cudaMemcpy2DAsync(e->d_priorsure.p + dst, Mc * 16, priorsure + src * 2, M * 16, Mc * 16, r.n, cudaMemcpyHostToDevice, e->stream));
+		}
+	}
+	std::vector<MstepRow> rows(e->n_rows);
+	for (int32_t r = 0; r < e->n_rows; r++)
+	{
+		const int32_t id = e->rowid[r];
+		rows[r] = MstepRow{ children[id], descendants[id], empty[id], hasprior[id], { 0, 0 } };
+	}
+	CU(cudaMemcpyAsync(e->d_msrows.p, rows.data(), rows.size() * sizeof(MstepRow), cudaMemcpyHostToDevice, e->stream));
+	CU(cudaStreamSynchronize(e->stream));
+	e->carry_valid.assign(e->chromstarts.size() - 1, 0);
+	e->have_ms_inputs = true;
+	return CNF2_OK;
+}
+
+extern "C" int cnf2_begin_iteration(cnf2_engine* e)
+{
+	if (!e) return CNF2_ERR_BAD_ARG;
+	std::fill(e->carry_valid.begin(), e->carry_valid.end(), 0);  // doit zeroes haplobase / haplocount, :5222-5234
+	return CNF2_OK;
+}
+
+extern "C" int cnf2_mstep(cnf2_engine* e, int32_t chrom, double scalefactor, double entropyfactor, int64_t* hitnnn)
+{
+	if (!e) return CNF2_ERR_BAD_ARG;
+	if (!e->have_ms_inputs) return e->fail(CNF2_ERR_STATE, "cnf2_mstep: cnf2_set_mstep_inputs first");
+	Slot* slp = nullptr;
+	for (Slot& o : e->slots)
+		if (chrom >= 0 && o.chrom == chrom) slp = &o;
+	if (!slp) return e->fail(CNF2_ERR_STATE, "cnf2_mstep: cnf2_estep for this chromosome first (its statistics must still be in flight)");
+	Slot& sl = *slp;
+	cudaSetDevice(e->settings.device);
+	CU(cudaMemsetAsync(e->d_hit.p, 0, sizeof(unsigned long long), sl.stream));
+	const int C = (int)e->chromstarts.size() - 1;
+	auto args = [&](int c, bool fresh) {
+		const size_t blk = (size_t)e->n_rows * e->chromstarts[c];
+		const int Mc = e->mc(c);
+		MstepArgs a{};
+		a.alleles = e->d_alleles.p + blk;
+		a.sure = e->d_sure.p + blk;
+		a.hw = e->d_hw.p + blk;
+		a.relhaplo = e->d_relhaplo.p + blk;
+		a.prioralleles = e->d_prioral.p + blk;
+		a.priorsure = e->d_priorsure.p + blk;
+		a.rows = e->d_msrows.p;
+		a.stats_shared = sl.stats_shared();
+		a.stats_local = sl.stats_local(Mc);
+		a.carry_base = e->d_carry_base.p + blk;
+		a.carry_count = e->d_carry_count.p + blk;
+		a.ratio = e->d_ratio.p;
+		a.fw = e->d_fw.p;
+		a.anyinfo = e->d_anyinfo.p;
+		a.hitnnn = e->d_hit.p;
+		a.n_rows = e->n_rows;
+		a.n_shared = e->n_shared;
+		a.Mc = Mc;
+		a.fresh = fresh ? 1 : 0;
+		a.scalefactor = scalefactor;
+		a.entropyfactor = entropyfactor;
+		return a;
+	};
+	if (e->n_rows > 0)
+	{
+		// processinfprobs only has statistics for this chromosome; updatehaploweights also walks the chromosomes whose
+		// pass came earlier in the iteration, with the haplobase / haplocount that pass left behind (:6239-6367)
+		for (int c = 0; c < C; c++)
+		{
+			const bool fresh = c == chrom;
+			if (!fresh && !e->carry_valid[c]) continue;
+			const MstepArgs a = args(c, fresh);
+			const size_t cells = (size_t)e->n_rows * a.Mc;
+			const unsigned gc = (unsigned)((cells + 127) / 128), gr = (unsigned)((e->n_rows + 127) / 128);
+			if (fresh) mstep_infprobs_kernel<<<gc, 128, 0, sl.stream>>>(a);
+			mstep_relskew_kernel<<<gr, 128, 0, sl.stream>>>(a);
+			mstep_haploweight_kernel<<<gc, 128, 0, sl.stream>>>(a);
+			CU(cudaGetLastError());
+		}
+	}
+	e->carry_valid[chrom] = 1;
+	unsigned long long hit = 0;
+	CU(cudaMemcpyAsync(&hit, e->d_hit.p, sizeof(hit), cudaMemcpyDeviceToHost, sl.stream));
+	CU(cudaStreamSynchronize(sl.stream));
+	CU(cudaGetLastError());
+	if (hitnnn) *hitnnn = (int64_t)hit;
+	return CNF2_OK;
+}
+
+extern "C" int cnf2_get_params(cnf2_engine* e, int32_t chrom, uint8_t* alleles, double* sure, double* haploweight)
+{
+	if (!e) return CNF2_ERR_BAD_ARG;
+	if (chrom < 0 || chrom >= (int)e->have_params.size() || !e->have_params[chrom])
+		return e->fail(CNF2_ERR_STATE, "cnf2_get_params: no parameters of this chromosome on the device");
+	cudaSetDevice(e->settings.device);
+	const size_t M = e->markerpos.size(), c0 = e->chromstarts[chrom], Mc = e->mc(chrom);
+	const size_t blk = (size_t)e->n_rows * (e->resident ? c0 : 0);
+	for (const Run& r : e->runs)
+	{
+		const size_t dst = (size_t)r.id0 * M + c0, src = blk + (size_t)r.row0 * Mc;
+		if (alleles)
+			CU(cudaMemcpy2DAsync(alleles + dst * 2, M * 2, e->d_alleles.p + src, Mc * 2, Mc * 2, r.n, cudaMemcpyDeviceToHost, e->stream));
+		if (sure) CU(cudaMemcpy2DAsync(sure + dst * 2, M * 16, e->d_sure.p + src, Mc * 16, Mc * 16, r.n, cudaMemcpyDeviceToHost, e->stream));
+		if (haploweight)
+			CU(cudaMemcpy2DAsync(haploweight + dst, M * 8, e->d_hw.p + src, Mc * 8, Mc * 8, r.n, cudaMemcpyDeviceToHost, e->stream));
+	}
+	CU(cudaStreamSynchronize(e->stream));
 	return CNF2_OK;
 }
 

@@ -1,0 +1,351 @@
+// The M-step on the device (row a6 / f1 of SURVEY.md section 8): one pass of the reference's block at
+// cnF2freq.cpp:6356-6367 for one chromosome's fresh statistics, plus the re-run of updatehaploweights that the
+// reference makes on the chromosomes it finished earlier in the same iteration (the block sits inside the
+// chromosome loop and walks all markers, :6239-6367).
+//
+//   mstep_infprobs_kernel     processinfprobs (:4179-4323): one thread per (row, marker), both sides
+//   mstep_relskew_kernel      relskewhmm (:4325-4467): one thread per (row, chromosome), sequential two-state sweep
+//   mstep_haploweight_kernel  updatehaploweights (:4533-4734): one thread per (row, marker)
+//
+// The step solver (cappedgd :4040-4177, caplogitchange :4006-4038, 15-point Gauss-Legendre as
+// boost::math::quadrature::gauss<double, 15>) is the same arithmetic in the same order as the reference; the only
+// difference is the device's log().  lastinved is -1 (no phase inversion in flight, :6290), so breakathalf is false.
+#pragma once
+#include "cnf2_estep_kernel.cuh"
+
+namespace cnf2
+{
+constexpr double MS_MAXDIFF = (double)0.000005f;  // const float maxdiff, :228
+
+struct MstepRow  // per statistics row
+{
+	int32_t children;     // individ::children as rebuilt by doit (:5246-5259)
+	int32_t descendants;  // :872
+	uint8_t empty, hasprior, pad[2];
+};
+
+struct MstepArgs
+{
+	// parameters of the chromosome, [n_rows][Mc] blocks (in/out)
+	uchar2* alleles;
+	double2* sure;
+	double* hw;
+	const double* relhaplo;
+	const uchar2* prioralleles;
+	const double2* priorsure;
+	const MstepRow* rows;
+	// statistics: the chromosome's E-step block (fresh) or the carried haplobase/haplocount of an earlier pass
+	double *stats_shared, *stats_local;
+	double *carry_base, *carry_count;  // [n_rows][Mc]
+	double *ratio, *fw;                // scratch [n_rows][Mc], [n_rows][Mc][2]
+	uint8_t* anyinfo;                  // [n_rows]
+	unsigned long long* hitnnn;
+	int32_t n_rows, n_shared, Mc;
+	int32_t fresh;  // 1: statistics come from the E-step block; 0: from the carry arrays
+	double scalefactor, entropyfactor;
+};
+
+__device__ __forceinline__ double ms_caplogit(double intended, double orig, double epsilon, unsigned long long& hit)
+{
+	const double nnn = 3;
+	const double limn = (nnn - 1.0) * orig * (-1 + orig);
+	const double limd1 = -1 - (nnn - 1.0) * orig;
+	const double limd2 = (nnn - 1.0) * orig - nnn;
+	intended = fmin(intended, 1.0 - epsilon);
+	intended = fmax(intended, epsilon);
+	const double diff = intended - orig;
+	if (diff > limn / limd1)
+	{
+		intended = orig + limn / limd1;
+		if (intended < 0.5) hit++;
+	}
+	if (diff < -limn / limd2)
+	{
+		intended = orig - limn / limd2;
+		if (intended > 0.5) hit++;
+	}
+	return intended;
+}
+
+template <class F>
+__device__ __forceinline__ double ms_gauss15(F f, double a, double b)
+{
+	const double x[8] = { 0.0,
+		                  0.2011940939974345223006283033946,
+		                  0.3941513470775633698972073709810,
+		                  0.5709721726085388475372267372539,
+		                  0.7244177313601700474161860546139,
+		                  0.8482065834104272162006483207742,
+		                  0.9372733924007059043077589477102,
+		                  0.9879925180204854284895657185866 };
+	const double w[8] = { 0.2025782419255612728806201999675,
+		                  0.1984314853271115764561183264438,
+		                  0.1861610000155622110268005618664,
+		                  0.1662692058169939335532008604812,
+		                  0.1395706779261543144478047945110,
+		                  0.1071592204671719350118695466859,
+		                  0.0703660474881081247092674164507,
+		                  0.0307532419961172683546283935772 };
+	const double avg = (a + b) * 0.5, scale = (b - a) * 0.5;
+	double result = f(avg) * w[0];
+#pragma unroll 1
+	for (int i = 1; i < 8; i++) result += (f(avg + scale * x[i]) + f(avg - scale * x[i])) * w[i];
+	return result * scale;
+}
+
+template <class G>
+__device__ __forceinline__ double ms_cappedgd(G gradient, double orig, double epsilon, double scalefactor, unsigned long long& hit)
+{
+	unsigned long long dump = 0;
+	auto actual = [&](double val) {
+		val = fmin(fmax(val, epsilon), 1 - epsilon);
+		return 1. / gradient(val);
+	};
+	const double lolim = ms_caplogit(epsilon, orig, epsilon, dump);
+	double lo = lolim - epsilon * 0.125;
+	const double hilim = ms_caplogit(1 - epsilon, orig, epsilon, dump);
+	double hi = hilim + epsilon * 0.125;
+	orig = ms_caplogit(orig, orig, epsilon, dump);
+	const double gradval = actual(orig);
+	if (!isfinite(gradval) || !scalefactor)
+	{
+		lo = orig;
+		hi = orig;
+	}
+	const bool lowside = gradval < 0;
+	if (lowside) hi = orig;
+	else lo = orig;
+#pragma unroll 1
+	for (int i = 0; i < 51 && scalefactor; i++)
+	{
+		if (lo > hilim || hi < lolim) break;
+		const double mid = (lo + hi) / 2;
+		double prel = 0;
+		const double g = actual(mid);
+		if (((g < 0) != lowside) || !isfinite(g)) prel = (scalefactor + 0.1) * 1.1;
+		else
+		{
+			double start = orig, end = mid;
+			if (start > end)
+			{
+				const double t = start;
+				start = end;
+				end = t;
+			}
+			if (end - start < 1e-10) break;
+			prel = ms_gauss15(actual, start, end);
+			if (end != mid) prel = -prel;
+			if (!isfinite(prel)) prel = (scalefactor + 0.1) * 1.1;
+		}
+		if (fabs(prel - scalefactor) < scalefactor * 1e-3) break;
+		if ((prel < scalefactor) != lowside) lo = mid;
+		else hi = mid;
+	}
+	if (!scalefactor)
+	{
+		lo = orig;
+		hi = orig;
+	}
+	return ms_caplogit((lo + hi) / 2, orig, epsilon, hit);
+}
+
+__device__ __forceinline__ double ms_sq(double v) { return v * v; }
+// common part of the gradients at :4275 and :4688, terms in the reference's order
+__device__ __forceinline__ double ms_gcore(double c, double h, double s, double x)
+{
+	const double lx = log(x), l1 = log(1 - x);
+	return -(-ms_sq(c * h) * lx + ms_sq(c * h) * l1 + ms_sq(c) * h * s * lx - ms_sq(c) * h * s * l1 - ms_sq(c) * h * s - ms_sq(c * s) * x +
+	         ms_sq(c * s) + c * ms_sq(h) * lx - c * ms_sq(h) * l1 + c * ms_sq(h) + 2 * c * h * s * x - c * h * s * lx + c * h * s * l1 -
+	         c * h * s - ms_sq(h) * x) /
+	       ms_sq(c * h + c * s * x - c * s - h * x);
+}
+
+__device__ __forceinline__ StatsCell ms_cell(const MstepArgs& a, int row, int m)
+{
+	return row < a.n_shared ? stats_cell(a.stats_shared, a.n_shared, a.Mc, row, m)
+	                        : stats_cell(a.stats_local, a.n_rows - a.n_shared, a.Mc, row - a.n_shared, m);
+}
+
+// processinfprobs (:4179-4323) for both sides of one (row, marker).  A statistic that is exactly 0 is an absent key
+// of the reference's small_map (the E-step never adds a zero).  infprobs/homozyg are not cleared here: the next
+// E-step of the chromosome zeroes its block.
+__global__ void __launch_bounds__(128) mstep_infprobs_kernel(MstepArgs a)
+{
+	const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (idx >= (size_t)a.n_rows * a.Mc) return;
+	const int row = (int)(idx / a.Mc), m = (int)(idx % a.Mc);
+	const MstepRow r = a.rows[row];
+	const StatsCell cell = ms_cell(a, row, m);
+	uchar2 al = a.alleles[idx];
+	double2 su = a.sure[idx];
+	const uchar2 pal = r.hasprior ? a.prioralleles[idx] : make_uchar2(0, 0);
+	const double2 psu = r.hasprior ? a.priorsure[idx] : make_double2(0, 0);
+	const double epsilon = MS_MAXDIFF / (r.children + 1), etf = 1 * a.entropyfactor;
+	unsigned long long hit = 0;
+#pragma unroll 1
+	for (int side = 0; side < 2; side++)
+	{
+		double ip[2] = { cell.infprobs[side * 2], cell.infprobs[side * 2 + 1] };
+		double sum = 0;
+		for (int k = 0; k < 2; k++)
+			if (ip[k] != 0) sum += ip[k];
+		const int priorval = side ? pal.y : pal.x;
+		const int curmarker = side ? al.y : al.x;
+		const double cursure = side ? su.y : su.x;
+#pragma unroll 1
+		for (int k = 0; k < 2; k++)
+		{
+			if (ip[k] == 0) continue;
+			const int allele = k + 1;
+			double curprob = 0.5;
+			if (curmarker != 0) curprob = fabs((curmarker == allele ? 1 : 0) - cursure);
+			const double hzygcorred = ip[k];
+			double priord = 0;
+			if (priorval != 0)
+			{
+				double priorprob = 1.0 - (side ? psu.y : psu.x);
+				if (allele != priorval) priorprob = 1.0 - priorprob;
+				if (priorprob == 0) priord -= 10000;
+				else if (priorprob == 1) priord += 10000;
+				else
+				{
+					priorprob = fmin(fmax(priorprob, 1e-14), 1 - 1e-14);
+					priord += log(priorprob) - log(1 - priorprob);
+				}
+			}
+			auto gradient = [&](double x) {
+				double g = ms_gcore(curprob, hzygcorred, sum, x);
+				g += etf * log(1 / x - 1);
+				g += etf * priord;
+				return g;
+			};
+			ip[k] = ms_cappedgd(gradient, curprob, epsilon, a.scalefactor, hit);
+		}
+		double bestprob = 0;
+		int bestmarker = 0;
+		for (int k = 0; k < 2; k++)
+		{
+			if (ip[k] == 0) continue;
+			if (ip[k] > bestprob - (side ? 1e-30 : 0))
+			{
+				bestmarker = k + 1;
+				bestprob = ip[k];
+			}
+		}
+		if (!r.empty && (bestmarker != 0 || bestprob > 0) && r.hasprior)
+		{
+			if (side) al.y = (unsigned char)bestmarker, su.y = 1.0 - bestprob;
+			else al.x = (unsigned char)bestmarker, su.x = 1.0 - bestprob;
+		}
+	}
+	a.alleles[idx] = al;
+	a.sure[idx] = su;
+	if (hit) atomicAdd(a.hitnnn, hit);
+}
+
+// relskewhmm (:4325-4467, realhmm): one thread per row walks the chromosome forward (stores the two forward values per
+// marker) and backward (ratio = P(state 1)); anyinfo = some haplocount of the chromosome is non-zero (:4560-4565).
+__global__ void __launch_bounds__(128) mstep_relskew_kernel(MstepArgs a)
+{
+	const int row = blockIdx.x * blockDim.x + threadIdx.x;
+	if (row >= a.n_rows) return;
+	const int Mc = a.Mc;
+	bool any = false;
+	for (int m = 0; m < Mc && !any; m++)
+	{
+		const double hc = a.fresh ? *ms_cell(a, row, m).haplocount : a.carry_count[(size_t)row * Mc + m];
+		if (hc) any = true;
+	}
+	a.anyinfo[row] = any;
+	if (!any) return;
+	const double* hw = a.hw + (size_t)row * Mc;
+	const double* rh = a.relhaplo + (size_t)row * Mc;
+	double2* fw = reinterpret_cast<double2*>(a.fw) + (size_t)row * Mc;
+	double* ratio = a.ratio + (size_t)row * Mc;
+	double s0 = 0.5, s1 = 0.5;
+	for (int m = 0; m < Mc; m++)
+	{
+		const double w = hw[m];
+		s0 *= fabs(1 - w);
+		s1 *= fabs(0 - w);
+		fw[m] = make_double2(s0, s1);
+		if (s0 + s1 < 1e-10) s0 *= 1e20, s1 *= 1e20;
+		const double n = rh[m], nb = 1 - n;
+		const double t0 = s0 * n + s1 * nb, t1 = s1 * n + s0 * nb;
+		s0 = t0, s1 = t1;
+	}
+	s0 = s1 = 0.5;
+	{
+		const double2 f = fw[Mc - 1];
+		ratio[Mc - 1] = f.y / (f.x + f.y);
+	}
+	for (int m = Mc - 2; m >= 0; m--)
+	{
+		const double w = hw[m + 1];
+		s0 *= fabs(1 - w);
+		s1 *= fabs(0 - w);
+		const double n = rh[m], nb = 1 - n;
+		const double t0 = s0 * n + s1 * nb, t1 = s1 * n + s0 * nb;
+		s0 = t0, s1 = t1;
+		if (s0 + s1 < 1e-10) s0 *= 1e20, s1 *= 1e20;
+		const double2 f = fw[m];
+		const double r0 = s0 * f.x, r1 = s1 * f.y;
+		ratio[m] = r1 / (r0 + r1);
+	}
+}
+
+// updatehaploweights (:4533-4734) for one (row, marker); the adjusted haplobase/haplocount are kept in the carry
+// arrays because the reference re-runs this on the chromosome after every later chromosome of the iteration.
+__global__ void __launch_bounds__(128) mstep_haploweight_kernel(MstepArgs a)
+{
+	const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (idx >= (size_t)a.n_rows * a.Mc) return;
+	const int row = (int)(idx / a.Mc), m = (int)(idx % a.Mc);
+	double hb, hc;
+	if (a.fresh)
+	{
+		const StatsCell cell = ms_cell(a, row, m);
+		hb = *cell.haplobase, hc = *cell.haplocount;
+	}
+	else hb = a.carry_base[idx], hc = a.carry_count[idx];
+	const double w = a.hw[idx];
+	if (a.anyinfo[row] && w && w != 1)
+	{
+		const MstepRow r = a.rows[row];
+		const double relskewterm = a.ratio[idx];
+		const uchar2 al = a.alleles[idx];
+		const double2 su = a.sure[idx];
+		const double scorea = 1.0 - su.x;
+		double scoreb = 1.0 - su.y;
+		if (al.x != al.y) scoreb = 1 - scoreb;
+		double similarity = scorea * scoreb + (1 - scorea) * (1 - scoreb);
+		if (!hc || similarity == 1.0)
+		{
+			hc = fmax(1.0, hc);
+			hb = w * hc;
+		}
+		else
+		{
+			if (similarity >= 1 - MS_MAXDIFF) similarity = 1 - MS_MAXDIFF;
+			double count = hc;
+			hb -= count * w;
+			count = count - similarity * count;
+			hb += count * w;
+			hb *= hc / count;
+			if (hb < 0) hb = 0;
+			if (hb >= hc) hb = hc;
+		}
+		const double ef = a.entropyfactor, desc = (double)r.descendants;
+		auto gradient = [&](double in) {
+			double out = ms_gcore(w, hb, hc, in);
+			out += ((1 - similarity) * 1 * (ef * log(1 / in - 1)) + (relskewterm - in) / (in - in * in) * desc);
+			return out;
+		};
+		unsigned long long hit = 0;
+		a.hw[idx] = ms_cappedgd(gradient, w, MS_MAXDIFF / (r.children + 1), a.scalefactor, hit);
+		if (hit) atomicAdd(a.hitnnn, hit);
+	}
+	a.carry_base[idx] = hb;
+	a.carry_count[idx] = hc;
+}
+}  // namespace cnf2

@@ -17,7 +17,8 @@ SYMBOLS = [
     "cnf2_default_settings", "cnf2_create", "cnf2_destroy", "cnf2_last_error", "cnf2_set_map", "cnf2_set_pedigree",
     "cnf2_set_params", "cnf2_estep", "cnf2_set_allreduce", "cnf2_set_shared_rows", "cnf2_get_stats", "cnf2_sync",
     "cnf2_last_estep_ms", "cnf2_last_estep_launches", "cnf2_stream", "cnf2_measure_peaks", "cnf2_mark",
-    "cnf2_elapsed_ms", "cnf2_row_count", "cnf2_row_ids", "cnf2_get_stats_packed", "cnf2_set_params_packed",
+    "cnf2_elapsed_ms", "cnf2_row_count", "cnf2_row_ids", "cnf2_get_stats_packed", "cnf2_set_params_packed", "cnf2_set_mstep_inputs",
+    "cnf2_begin_iteration", "cnf2_mstep", "cnf2_get_params",
 ]
 
 
@@ -167,6 +168,26 @@ class Engine:
         """Row-ordered contiguous blocks ([n_rows][Mc]...; see include/cnf2_engine.h): unstrided device -> host copies."""
         self._check(self.lib.cnf2_get_stats_packed(self.h, ctypes.c_int32(chrom), _ptr(haplobase), _ptr(haplocount),
                                                    _ptr(infprobs), _ptr(homozyg), _ptr(loglik)))
+
+    # -- M-step on the device (rows a6 / f1) ---------------------------------------------------------
+    def set_mstep_inputs(self, relhaplo, prioralleles, priorsure, hasprior, children, empty, descendants):
+        c = np.ascontiguousarray
+        self._check(self.lib.cnf2_set_mstep_inputs(
+            self.h, _ptr(c(relhaplo, np.float64)), _ptr(c(prioralleles, np.uint8)), _ptr(c(priorsure, np.float64)),
+            _ptr(c(hasprior, np.uint8)), _ptr(c(children, np.int32)), _ptr(c(empty, np.uint8)), _ptr(c(descendants, np.int32))))
+
+    def begin_iteration(self):
+        self._check(self.lib.cnf2_begin_iteration(self.h))
+
+    def mstep(self, chrom, scalefactor, entropyfactor):
+        """The reference's M-step pass after chromosome `chrom`'s E-step; returns hitnnn."""
+        hit = ctypes.c_int64()
+        self._check(self.lib.cnf2_mstep(self.h, ctypes.c_int32(chrom), ctypes.c_double(scalefactor),
+                                        ctypes.c_double(entropyfactor), ctypes.byref(hit)))
+        return int(hit.value)
+
+    def get_params(self, chrom, alleles, sure, haploweight):
+        self._check(self.lib.cnf2_get_params(self.h, ctypes.c_int32(chrom), _ptr(alleles), _ptr(sure), _ptr(haploweight)))
 
     def sync(self):
         self._check(self.lib.cnf2_sync(self.h))

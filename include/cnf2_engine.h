@@ -140,6 +140,28 @@ int cnf2_row_ids(cnf2_engine* e, int32_t* ids);
 int cnf2_get_stats_packed(cnf2_engine* e, int32_t chrom, double* haplobase, double* haplocount, double* infprobs,
                           double* homozyg, double* loglik);
 
+/* ---- M-step on the device ------------------------------------------------
+ * cnf2_mstep makes the pass of cnF2freq.cpp:6356-6367 that the reference runs after chromosome `chrom`'s E-step:
+ * processinfprobs (:4179-4323) on the chromosome's fresh statistics -> new markerdata / markersure, then
+ * updatehaploweights (:4533-4734, with relskewhmm :4325-4467 and the step solver cappedgd :4040-4177) -> new
+ * haploweight, for this chromosome and -- as the reference's block sits inside its chromosome loop and walks all
+ * markers -- again for the chromosomes whose pass came earlier in the iteration, on the haplobase / haplocount that
+ * pass left behind.  The parameters are updated in place on the device (the next cnf2_estep of the chromosome uses
+ * them without an upload); cnf2_get_params reads them back ([n_ind][n_markers] arrays, columns of `chrom`).
+ * scalefactor / entropyfactor are the reference's globals (:3573-3574); *hitnnn receives the pass's count of capped
+ * steps (:4022-4032), from which the caller runs the step-size control (:6373-6390).  Phase inversions (negshifter,
+ * :6336-6340) are host logic and not part of this call: lastinved is taken as -1 (:6290).
+ * cnf2_set_mstep_inputs: relhaplo (:889), prior markerdata / markersure (:880-881) as [n_ind][n_markers](x2) arrays,
+ * and per individual hasprior (priormarkerdata.size() > 0), children (:5246-5259), empty, descendants.  Needs the
+ * parameters of all chromosomes resident.  cnf2_begin_iteration forgets the carried haplobase / haplocount
+ * (doit zeroes them, :5222-5234). */
+int cnf2_set_mstep_inputs(cnf2_engine* e, const double* relhaplo, const uint8_t* prioralleles, const double* priorsure,
+                          const uint8_t* hasprior, const int32_t* children, const uint8_t* empty,
+                          const int32_t* descendants);
+int cnf2_begin_iteration(cnf2_engine* e);
+int cnf2_mstep(cnf2_engine* e, int32_t chrom, double scalefactor, double entropyfactor, int64_t* hitnnn);
+int cnf2_get_params(cnf2_engine* e, int32_t chrom, uint8_t* alleles, double* sure, double* haploweight);
+
 /* Block until everything enqueued by this engine has finished; returns the first asynchronous error. */
 int cnf2_sync(cnf2_engine* e);
 

@@ -29,11 +29,12 @@ def collect(prefix, iterations):
     C = len(prob["chromstarts"]) - 1
     out = dict(par=np.stack([prob["par0"], prob["par1"]], axis=1).astype(np.int32), exists=prob["exists"], empty=prob["empty"],
                hasprior=prob["hasprior"], descendants=prob["descendants"], dous=prob["dous"],
-               chromstarts=prob["chromstarts"].astype(np.uint32), iterations=np.asarray(iterations))
+               chromstarts=prob["chromstarts"].astype(np.uint32), iterations=np.asarray(iterations), gen=prob["gen"],
+               markerpos=prob["markerposes"], genrec=prob["genrec"])
     for it in iterations:
         a, b = read_dump(f"{prefix}.iter{it}.params"), read_dump(f"{prefix}.iter{it}.state")
         assert b["negshift"].min() > -1e-10, "phase inversion in this iteration"
-        for k in ("alleles", "sure", "haploweight", "relhaplo", "prioralleles", "priorsure", "scalars"):
+        for k in ("alleles", "sure", "haploweight", "relhaplo", "prioralleles", "priorsure", "scalars", "founder"):
             out[f"it{it}_before_{k}"] = a[k]
         for k in ("alleles", "sure", "haploweight", "scalars", "children"):  # children is rebuilt inside doit (:5246-5259)
             out[f"it{it}_after_{k}"] = b[k]
