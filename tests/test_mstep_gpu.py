@@ -61,3 +61,105 @@ def test_device_mstep_reproduces_the_reference_iteration(eng, name, its):
         assert_close(su, g[f"it{it}_after_sure"], f"{name} it{it} markersure", rtol=RTOL, atol=ATOL)
         assert_close(hw, g[f"it{it}_after_haploweight"], f"{name} it{it} haploweight", rtol=RTOL, atol=ATOL)
         assert_close(sc, g[f"it{it}_after_scalars"], f"{name} it{it} scalefactor / hitnnn", rtol=1e-12)
+
+
+def test_em_loop_stays_on_the_device(eng):
+    """Iterations 2 and 3 of the demo back to back: parameters are uploaded once, every E-step uses what the previous
+    M-step left on the device; the end state equals the reference's after its third iteration."""
+    g = dict(np.load(os.path.join(GOLDEN, "mstep_demo.npz")))
+    b = lambda k: g[f"it2_before_{k}"]
+    assert np.array_equal(g["it2_before_relhaplo"], g["it3_before_relhaplo"])
+    eng.set_map(g["markerpos"], g["chromstarts"], g["genrec"])
+    eng.set_shared_rows(np.zeros(0, np.int32))
+    eng.set_pedigree(g["par"], g["empty"], b("founder"), g["gen"], g["descendants"], g["dous"])
+    al, su, hw = b("alleles").copy(), b("sure").copy(), b("haploweight").copy()
+    eng.set_params(0, al, su, hw)
+    eng.set_mstep_inputs(b("relhaplo"), b("prioralleles"), b("priorsure"), g["hasprior"], g["it2_after_children"], g["empty"],
+                         g["descendants"])
+    sf, ent, o1, o2 = b("scalars")
+    for it in (2, 3):
+        eng.begin_iteration()
+        eng.estep(0)
+        hit = eng.mstep(0, sf, ent)
+        sf, o1, o2 = ol.oracle_scalefactor(sf, hit, len(g["dous"]), o1, o2)
+    eng.get_params(0, al, su, hw)
+    assert np.array_equal(al, g["it3_after_alleles"])
+    assert_close(su, g["it3_after_sure"], "markersure after two device iterations", rtol=RTOL, atol=ATOL)
+    assert_close(hw, g["it3_after_haploweight"], "haploweight after two device iterations", rtol=RTOL, atol=ATOL)
+    assert_close(np.array([sf, ent, o1, o2]), g["it3_after_scalars"], "scalars", rtol=1e-12)
+
+
+def stationary(alleles, sure, infprobs, prioralleles, hasprior):
+    """Cells where processinfprobs sits on a fixed point: the statistics equal the current parameter (infprobs[a] ==
+    sum * curprob, no prior), so the data term of the gradient (:4275) cancels the entropy term identically and what
+    is left is a rounding residue of ~1e-12 whose SIGN decides the direction of the reference's step (cappedgd
+    integrates 1 / gradient).  These are exact ties of the update: any other libm or FMA contraction -- the reference's
+    own -ffast-math build included -- lands elsewhere; they are left out of the comparison (both sides of the cell and
+    its haploweight, which reads the new markersure)."""
+    K, M = alleles.shape[:2]
+    tie = np.zeros((K, M), bool)
+    for side in range(2):
+        ip = infprobs[:, :, side, :]
+        tot = ip.sum(axis=2)
+        for k in range(2):
+            cur = np.where(alleles[:, :, side] != 0, np.abs((alleles[:, :, side] == k + 1).astype(float) - sure[:, :, side]), 0.5)
+            noprior = (prioralleles[:, :, side] == 0) | (hasprior[:, None] == 0)
+            tie |= (ip[:, :, k] != 0) & noprior & (np.abs(ip[:, :, k] - tot * cur) <= 1e-6 * tot)
+    return tie
+
+
+@pytest.mark.parametrize("maker,kw", [
+    ("f2_cross", dict(n_f2=9, n_chrom=2, mpc=21, seed=61)),
+    ("fullsib", dict(n_fam=2, n_off=3, n_chrom=1, mpc=15, seed=62)),
+    ("tangled", dict(n_chrom=2, mpc=17, seed=63)),
+])
+def test_device_mstep_matches_oracle_on_random_pedigrees(eng, maker, kw):
+    """Random parameters (locked phases, zero sureness, priors on some individuals): the oracle's M-step on the
+    statistics the engine's E-step produced, pass by pass, against cnf2_mstep."""
+    import randomped
+    from cases import STATS, engine_problem
+    pb = getattr(randomped, maker)(**kw)
+    rng = np.random.default_rng(kw["seed"])
+    K, M, C = pb.K, pb.M, pb.C
+    relhaplo = rng.uniform(0.6, 1.0, (K, M))
+    hasprior = (rng.random(K) < 0.7).astype(np.uint8)
+    prioral = pb.alleles.copy()
+    prioral[rng.random((K, M)) < 0.2] = 0
+    priorsure = np.where(rng.random((K, M, 2)) < 0.1, 0.0, rng.uniform(0.0, 0.3, (K, M, 2)))
+    children = rng.integers(0, 4, K).astype(np.int32)
+    engine_problem(eng, pb, shared=np.zeros(0, np.int32))
+    al, su, hw = pb.alleles.copy(), pb.sure.copy(), pb.haploweight.copy()
+    for c in range(C):
+        eng.set_params(c, al, su, hw)
+    eng.set_mstep_inputs(relhaplo, prioral, priorsure, hasprior, children, pb.empty, pb.descendants)
+    eng.begin_iteration()
+    sf, ent = 0.013, 1.0
+    active = np.ones(K, np.uint8)
+    active[0] = 0
+    hb, hc = np.zeros((K, M)), np.zeros((K, M))  # haplobase / haplocount as the reference's vectors hold them
+    ral, rsu, rhw = al.copy(), su.copy(), hw.copy()
+    tie = np.zeros((K, M), bool)
+    for c in range(C):
+        eng.estep(c)
+        st = dict(haplobase=np.zeros((K, M)), haplocount=np.zeros((K, M)), infprobs=np.zeros((K, M, 2, 2)), homozyg=np.zeros((K, M, 2)))
+        eng.get_stats(c, **st)
+        cols = slice(int(pb.chromstarts[c]), int(pb.chromstarts[c + 1]))
+        hb[:, cols], hc[:, cols] = st["haplobase"][:, cols], st["haplocount"][:, cols]
+        if np.isnan(st["infprobs"]).any() or np.isnan(hb).any():
+            pytest.skip("impossible unit in this random draw (NaN statistics)")
+        ral_in, rsu_in = ral.copy(), rsu.copy()
+        r = ol.oracle_mstep(pb.chromstarts, active, pb.empty, children, pb.descendants, ral, rsu, rhw, relhaplo, hasprior, prioral,
+                            priorsure, hb, hc, st["infprobs"], st["homozyg"], sf, ent)
+        ral, rsu, rhw, hb, hc = r["alleles"], r["sure"], r["haploweight"], r["haplobase"], r["haplocount"]
+        tie |= stationary(ral_in, rsu_in, st["infprobs"], prioral, hasprior)
+        hit = eng.mstep(c, sf, ent)
+        assert abs(hit - r["hitnnn"]) <= 2 * int(tie.sum()), (c, hit, r["hitnnn"])
+        sf, _, _ = ol.oracle_scalefactor(sf, r["hitnnn"], len(pb.dous), 0, 0)
+    for c in range(C):
+        eng.get_params(c, al, su, hw)
+    ok = ~tie
+    assert ok.sum() > 0.5 * ok.size
+    assert np.array_equal(al[ok], ral[ok])
+    assert_close(su[ok], rsu[ok], "markersure", rtol=RTOL, atol=ATOL)
+    assert_close(hw[ok], rhw[ok], "haploweight", rtol=RTOL, atol=ATOL)
+    assert not np.array_equal(hw, pb.haploweight)
