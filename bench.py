@@ -59,6 +59,7 @@ def parse():
     ap.add_argument("--cpu-sample-individuals", type=int, default=64)
     ap.add_argument("--cpu-sample-markers", type=int, default=500)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-mstep", action="store_true", help="skip the device M-step timing (em_iteration)")
     return ap.parse_args()
 
 
@@ -330,6 +331,34 @@ def ours(a, rank, world, local_rank):
     launch_ms = step_ms / C
     launches_per_estep = eng.last_estep_launches()
 
+    # ---- the M-step on the device (row a6), timed after everything else because it updates the parameters in place:
+    # one EM iteration = per chromosome E-step + the reference's M-step pass (cnF2freq.cpp:6356-6367)
+    em = None
+    if not a.no_mstep:
+        K_ind = d["par"].shape[0]
+        rel = np.full((K_ind, M), 0.9)                         # relhaplo: the reference's start value is a constant too
+        children = np.bincount(d["par"].ravel(), minlength=K_ind).astype(np.int32)
+        children[0] = 0
+        eng.set_mstep_inputs(rel, d["alleles"], d["sure"], np.ones(K_ind, np.uint8), children, d["empty"], d["descendants"])
+        barrier()
+        t_e, t_m, hits = 0.0, 0.0, 0
+        t0 = time.perf_counter()
+        eng.begin_iteration()
+        for c in range(C):
+            eng.mark(2)
+            eng.estep(c)
+            eng.mark(3)
+            t1 = time.perf_counter()
+            hits += eng.mstep(c, 0.013, 1.0)                   # blocks until the pass is done
+            t_m += time.perf_counter() - t1
+            t_e += eng.elapsed_ms(2, 3) * 1e-3
+        barrier()
+        em_s = maxranks(time.perf_counter() - t0)
+        em = {"value": states_per_step / em_s, "unit": UNIT, "ms_per_iteration": em_s * 1e3, "estep_ms": t_e * 1e3, "mstep_ms": t_m * 1e3,
+              "hitnnn": hits, "note": "one EM iteration on the device: per chromosome the E-step and the reference's M-step pass "
+              "(processinfprobs + updatehaploweights, bisection with 15-point Gauss-Legendre per cell); the M-step of chromosome c "
+              "also re-runs updatehaploweights on chromosomes < c as the reference does"}
+
     if rank == 0:
         dfma_tflops, copy_gbs = eng.measure_peaks()
         peaks = measured_peaks()
@@ -363,7 +392,7 @@ def ours(a, rank, world, local_rank):
                        "step": "E-step of all chromosomes: fwd/bwd sweeps for 8 shift modes + posterior scatter into EM statistics"},
             "e2e": {"value": states_per_step / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": e2e_s * 1e3},
-            "gpu_launches": a.steps * C * launches_per_estep, "roofline": roof, "cpu_baseline": cpu, "clocks": clocks,
+            "gpu_launches": a.steps * C * launches_per_estep, "em_iteration": em, "roofline": roof, "cpu_baseline": cpu, "clocks": clocks,
         }
         print(json.dumps(line))
     eng.close()
