@@ -150,10 +150,14 @@ __device__ __forceinline__ double ms_cappedgd(G gradient, double orig, double ep
 }
 
 __device__ __forceinline__ double ms_sq(double v) { return v * v; }
-// common part of the gradients at :4275 and :4688, terms in the reference's order
-__device__ __forceinline__ double ms_gcore(double c, double h, double s, double x)
+// Common part of the gradients at :4275 and :4688, terms in the reference's order, plus the entropy term's
+// log(1 / x - 1), returned through *et as log(1 - x) - log(x): the two logs are the data term's own (the reference
+// takes a third log of 1 / x - 1; the two forms differ by <= 2 ulp of the term).  fp64 log is what this kernel spends
+// its time on.
+__device__ __forceinline__ double ms_gcore(double c, double h, double s, double x, double* et)
 {
 	const double lx = log(x), l1 = log(1 - x);
+	*et = l1 - lx;
 	return -(-ms_sq(c * h) * lx + ms_sq(c * h) * l1 + ms_sq(c) * h * s * lx - ms_sq(c) * h * s * l1 - ms_sq(c) * h * s - ms_sq(c * s) * x +
 	         ms_sq(c * s) + c * ms_sq(h) * lx - c * ms_sq(h) * l1 + c * ms_sq(h) + 2 * c * h * s * x - c * h * s * lx + c * h * s * l1 -
 	         c * h * s - ms_sq(h) * x) /
@@ -214,8 +218,9 @@ __global__ void __launch_bounds__(128) mstep_infprobs_kernel(MstepArgs a)
 				}
 			}
 			auto gradient = [&](double x) {
-				double g = ms_gcore(curprob, hzygcorred, sum, x);
-				g += etf * log(1 / x - 1);
+				double et;
+				double g = ms_gcore(curprob, hzygcorred, sum, x, &et);
+				g += etf * et;
 				g += etf * priord;
 				return g;
 			};
@@ -337,8 +342,9 @@ __global__ void __launch_bounds__(128) mstep_haploweight_kernel(MstepArgs a)
 		}
 		const double ef = a.entropyfactor, desc = (double)r.descendants;
 		auto gradient = [&](double in) {
-			double out = ms_gcore(w, hb, hc, in);
-			out += ((1 - similarity) * 1 * (ef * log(1 / in - 1)) + (relskewterm - in) / (in - in * in) * desc);
+			double et;
+			double out = ms_gcore(w, hb, hc, in, &et);
+			out += ((1 - similarity) * 1 * (ef * et) + (relskewterm - in) / (in - in * in) * desc);
 			return out;
 		};
 		unsigned long long hit = 0;
