@@ -11,7 +11,7 @@
 // boost::math::quadrature::gauss<double, 15>) is the same arithmetic in the same order as the reference; the only
 // difference is the device's log().  lastinved is -1 (no phase inversion in flight, :6290), so breakathalf is false.
 #pragma once
-#include "cnf2_estep_kernel.cuh"
+#include "cnf2_tables.cuh"
 
 namespace cnf2
 {
@@ -67,6 +67,15 @@ __device__ __forceinline__ double ms_caplogit(double intended, double orig, doub
 	return intended;
 }
 
+// 1 / x on the solver's inner loop (two per gradient evaluation): frcp (~1 ulp) where x is an ordinary number, the IEEE
+// division where it is not, so that 1 / 0 = inf and non-finite gradients keep steering the bisection as they do in
+// the reference (:4131, :4144).
+__device__ __forceinline__ double ms_rcp(double x)
+{
+	const double ax = fabs(x);
+	return (ax > 1e-290 && ax < 1e290) ? frcp(x) : 1.0 / x;
+}
+
 template <class F>
 __device__ __forceinline__ double ms_gauss15(F f, double a, double b)
 {
@@ -99,7 +108,7 @@ __device__ __forceinline__ double ms_cappedgd(G gradient, double orig, double ep
 	unsigned long long dump = 0;
 	auto actual = [&](double val) {
 		val = fmin(fmax(val, epsilon), 1 - epsilon);
-		return 1. / gradient(val);
+		return ms_rcp(gradient(val));
 	};
 	const double lolim = ms_caplogit(epsilon, orig, epsilon, dump);
 	double lo = lolim - epsilon * 0.125;
@@ -160,8 +169,8 @@ __device__ __forceinline__ double ms_gcore(double c, double h, double s, double 
 	*et = l1 - lx;
 	return -(-ms_sq(c * h) * lx + ms_sq(c * h) * l1 + ms_sq(c) * h * s * lx - ms_sq(c) * h * s * l1 - ms_sq(c) * h * s - ms_sq(c * s) * x +
 	         ms_sq(c * s) + c * ms_sq(h) * lx - c * ms_sq(h) * l1 + c * ms_sq(h) + 2 * c * h * s * x - c * h * s * lx + c * h * s * l1 -
-	         c * h * s - ms_sq(h) * x) /
-	       ms_sq(c * h + c * s * x - c * s - h * x);
+	         c * h * s - ms_sq(h) * x) *
+	       ms_rcp(ms_sq(c * h + c * s * x - c * s - h * x));
 }
 
 __device__ __forceinline__ StatsCell ms_cell(const MstepArgs& a, int row, int m)
