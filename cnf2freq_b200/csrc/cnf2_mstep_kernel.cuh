@@ -173,6 +173,161 @@ __device__ __forceinline__ double ms_gcore(double c, double h, double s, double 
 	       ms_rcp(ms_sq(c * h + c * s * x - c * s - h * x));
 }
 
+// ---- the warp-cooperative form of cappedgd ----
+// Each lane owns one solve (or none).  A bisection step needs the gradient at the midpoint (every lane evaluates its
+// own) and, for about a third of the steps, a 15-point integral.  Lanes take their integral steps at different
+// iterations, so a lane-private solver makes the warp pay 16 evaluations on nearly every step; here the integrals
+// pending after a step are served two at a time, one per half-warp, its 15 points on 15 lanes with the owner's
+// parameters fetched by shuffle, and the owner sums the values in the reference's order.  Arithmetic per solve is
+// unchanged.
+struct MsParams
+{
+	double c, h, s;        // data term: (curprob, hzygcorred, sum) or (haploweight, haplobase, haplocount)
+	double p0, p1, p2, p3; // MODE 0: etf, etf * priord; MODE 1: (1 - similarity) * 1, ef, relskewterm, descendants
+	double eps;
+};
+template <int MODE>
+__device__ __forceinline__ double ms_actual(const MsParams& P, double val)
+{
+	val = fmin(fmax(val, P.eps), 1 - P.eps);
+	double et;
+	double g = ms_gcore(P.c, P.h, P.s, val, &et);
+	if (MODE == 0)
+	{
+		g += P.p0 * et;  // entropy term, :4288
+		g += P.p1;       // prior, :4289
+	}
+	else g += (P.p0 * (P.p1 * et) + (P.p2 - val) / (val - val * val) * P.p3);  // :4689-4692
+	return ms_rcp(g);
+}
+__device__ __forceinline__ MsParams ms_fetch(const MsParams& P, int src)
+{
+	const unsigned FULL = 0xffffffffu;
+	MsParams Q;
+	Q.c = __shfl_sync(FULL, P.c, src), Q.h = __shfl_sync(FULL, P.h, src), Q.s = __shfl_sync(FULL, P.s, src);
+	Q.p0 = __shfl_sync(FULL, P.p0, src), Q.p1 = __shfl_sync(FULL, P.p1, src), Q.p2 = __shfl_sync(FULL, P.p2, src);
+	Q.p3 = __shfl_sync(FULL, P.p3, src), Q.eps = __shfl_sync(FULL, P.eps, src);
+	return Q;
+}
+// All 32 lanes call this together; `active` lanes get their solve's result (the others get `orig` back).
+template <int MODE>
+__device__ __forceinline__ double ms_cappedgd_warp(const MsParams& P, double orig, double scalefactor, bool active, unsigned long long& hit)
+{
+	const unsigned FULL = 0xffffffffu;
+	const int lane = threadIdx.x & 31, half = lane >> 4, q = lane & 15;
+	const double GX[8] = { 0.0,
+		                   0.2011940939974345223006283033946,
+		                   0.3941513470775633698972073709810,
+		                   0.5709721726085388475372267372539,
+		                   0.7244177313601700474161860546139,
+		                   0.8482065834104272162006483207742,
+		                   0.9372733924007059043077589477102,
+		                   0.9879925180204854284895657185866 };
+	const double GW[8] = { 0.2025782419255612728806201999675,
+		                   0.1984314853271115764561183264438,
+		                   0.1861610000155622110268005618664,
+		                   0.1662692058169939335532008604812,
+		                   0.1395706779261543144478047945110,
+		                   0.1071592204671719350118695466859,
+		                   0.0703660474881081247092674164507,
+		                   0.0307532419961172683546283935772 };
+	// this lane's quadrature point: q = 0 the centre, 1..7 centre + scale x_q, 8..14 centre - scale x_(q-7), 15 idle
+	const double myx = q == 0 ? 0.0 : (q < 8 ? GX[q & 7] : (q < 15 ? -GX[(q - 7) & 7] : 0.0));
+	unsigned long long dump = 0;
+	const double epsilon = P.eps;
+	double lolim = 0, hilim = 0, lo = 0, hi = 0;
+	bool lowside = false, done = !active;
+	if (active)
+	{
+		lolim = ms_caplogit(epsilon, orig, epsilon, dump);
+		lo = lolim - epsilon * 0.125;
+		hilim = ms_caplogit(1 - epsilon, orig, epsilon, dump);
+		hi = hilim + epsilon * 0.125;
+		orig = ms_caplogit(orig, orig, epsilon, dump);
+		const double gradval = ms_actual<MODE>(P, orig);
+		if (!isfinite(gradval) || !scalefactor)
+		{
+			lo = orig;
+			hi = orig;
+		}
+		lowside = gradval < 0;
+		if (lowside) hi = orig;
+		else lo = orig;
+		if (!scalefactor) done = true;
+	}
+#pragma unroll 1
+	for (int i = 0; i < 51; i++)
+	{
+		if (!done && (lo > hilim || hi < lolim)) done = true;
+		if (__all_sync(FULL, done)) break;
+		double mid = 0, prel = 0, start = 0, end = 0;
+		bool pending = false;
+		if (!done)
+		{
+			mid = (lo + hi) / 2;
+			const double g = ms_actual<MODE>(P, mid);
+			if (((g < 0) != lowside) || !isfinite(g)) prel = (scalefactor + 0.1) * 1.1;
+			else
+			{
+				start = orig, end = mid;
+				if (start > end)
+				{
+					const double t = start;
+					start = end;
+					end = t;
+				}
+				if (end - start < 1e-10) done = true;
+				else pending = true;
+			}
+		}
+		// integrals of the lanes that need one, two per round
+		unsigned mask = __ballot_sync(FULL, pending);
+		while (mask)
+		{
+			const int o0 = __ffs(mask) - 1;
+			mask &= mask - 1;
+			const int o1 = mask ? __ffs(mask) - 1 : -1;
+			if (o1 >= 0) mask &= mask - 1;
+			const int owner = half ? o1 : o0;  // the solve this half-warp serves (-1: none)
+			const int src = owner < 0 ? lane : owner;
+			const MsParams Q = ms_fetch(P, src);
+			const double a0 = __shfl_sync(FULL, start, src), b0 = __shfl_sync(FULL, end, src);
+			const double avg = (a0 + b0) * 0.5, scale = (b0 - a0) * 0.5;
+			double f = 0;
+			if (owner >= 0 && q < 15) f = ms_actual<MODE>(Q, avg + scale * myx);
+			// the owner (any lane of the warp) gathers its half-warp's values in the reference's order
+			const bool mine = lane == o0 || lane == o1;
+			const int base = lane == o1 ? 16 : 0;
+			double result = __shfl_sync(FULL, f, base) * GW[0];
+#pragma unroll
+			for (int k = 1; k < 8; k++)
+			{
+				const double fp = __shfl_sync(FULL, f, base + k), fm = __shfl_sync(FULL, f, base + 7 + k);
+				result += (fp + fm) * GW[k];
+			}
+			if (mine)
+			{
+				prel = result * ((end - start) * 0.5);
+				if (end != mid) prel = -prel;
+				if (!isfinite(prel)) prel = (scalefactor + 0.1) * 1.1;
+			}
+		}
+		if (!done)
+		{
+			if (fabs(prel - scalefactor) < scalefactor * 1e-3) done = true;
+			else if ((prel < scalefactor) != lowside) lo = mid;
+			else hi = mid;
+		}
+	}
+	if (!active) return orig;
+	if (!scalefactor)
+	{
+		lo = orig;
+		hi = orig;
+	}
+	return ms_caplogit((lo + hi) / 2, orig, epsilon, hit);
+}
+
 __device__ __forceinline__ StatsCell ms_cell(const MstepArgs& a, int row, int m)
 {
 	return row < a.n_shared ? stats_cell(a.stats_shared, a.n_shared, a.Mc, row, m)
@@ -184,8 +339,9 @@ __device__ __forceinline__ StatsCell ms_cell(const MstepArgs& a, int row, int m)
 // E-step of the chromosome zeroes its block.
 __global__ void __launch_bounds__(128) mstep_infprobs_kernel(MstepArgs a)
 {
-	const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-	if (idx >= (size_t)a.n_rows * a.Mc) return;
+	const size_t idx0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x, cells = (size_t)a.n_rows * a.Mc;
+	const bool valid = idx0 < cells;  // every lane stays for the warp-cooperative solver
+	const size_t idx = valid ? idx0 : cells - 1;
 	const int row = (int)(idx / a.Mc), m = (int)(idx % a.Mc);
 	const MstepRow r = a.rows[row];
 	const StatsCell cell = ms_cell(a, row, m);
@@ -208,13 +364,12 @@ __global__ void __launch_bounds__(128) mstep_infprobs_kernel(MstepArgs a)
 #pragma unroll 1
 		for (int k = 0; k < 2; k++)
 		{
-			if (ip[k] == 0) continue;
+			const bool active = valid && ip[k] != 0;
 			const int allele = k + 1;
 			double curprob = 0.5;
 			if (curmarker != 0) curprob = fabs((curmarker == allele ? 1 : 0) - cursure);
-			const double hzygcorred = ip[k];
 			double priord = 0;
-			if (priorval != 0)
+			if (active && priorval != 0)
 			{
 				double priorprob = 1.0 - (side ? psu.y : psu.x);
 				if (allele != priorval) priorprob = 1.0 - priorprob;
@@ -226,14 +381,9 @@ __global__ void __launch_bounds__(128) mstep_infprobs_kernel(MstepArgs a)
 					priord += log(priorprob) - log(1 - priorprob);
 				}
 			}
-			auto gradient = [&](double x) {
-				double et;
-				double g = ms_gcore(curprob, hzygcorred, sum, x, &et);
-				g += etf * et;
-				g += etf * priord;
-				return g;
-			};
-			ip[k] = ms_cappedgd(gradient, curprob, epsilon, a.scalefactor, hit);
+			const MsParams P{ curprob, ip[k], sum, etf, etf * priord, 0.0, 0.0, epsilon };
+			const double res = ms_cappedgd_warp<0>(P, curprob, a.scalefactor, active, hit);
+			if (active) ip[k] = res;
 		}
 		double bestprob = 0;
 		int bestmarker = 0;
@@ -252,9 +402,12 @@ __global__ void __launch_bounds__(128) mstep_infprobs_kernel(MstepArgs a)
 			else al.x = (unsigned char)bestmarker, su.x = 1.0 - bestprob;
 		}
 	}
-	a.alleles[idx] = al;
-	a.sure[idx] = su;
-	if (hit) atomicAdd(a.hitnnn, hit);
+	if (valid)
+	{
+		a.alleles[idx] = al;
+		a.sure[idx] = su;
+		if (hit) atomicAdd(a.hitnnn, hit);
+	}
 }
 
 // relskewhmm (:4325-4467, realhmm): one thread per row walks the chromosome forward (stores the two forward values per
@@ -312,8 +465,9 @@ __global__ void __launch_bounds__(128) mstep_relskew_kernel(MstepArgs a)
 // arrays because the reference re-runs this on the chromosome after every later chromosome of the iteration.
 __global__ void __launch_bounds__(128) mstep_haploweight_kernel(MstepArgs a)
 {
-	const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-	if (idx >= (size_t)a.n_rows * a.Mc) return;
+	const size_t idx0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x, cells = (size_t)a.n_rows * a.Mc;
+	const bool valid = idx0 < cells;  // every lane stays for the warp-cooperative solver
+	const size_t idx = valid ? idx0 : cells - 1;
 	const int row = (int)(idx / a.Mc), m = (int)(idx % a.Mc);
 	double hb, hc;
 	if (a.fresh)
@@ -323,16 +477,17 @@ __global__ void __launch_bounds__(128) mstep_haploweight_kernel(MstepArgs a)
 	}
 	else hb = a.carry_base[idx], hc = a.carry_count[idx];
 	const double w = a.hw[idx];
-	if (a.anyinfo[row] && w && w != 1)
+	const bool active = valid && a.anyinfo[row] && w && w != 1;
+	const MstepRow r = a.rows[row];
+	double similarity = 0;
+	if (active)
 	{
-		const MstepRow r = a.rows[row];
-		const double relskewterm = a.ratio[idx];
 		const uchar2 al = a.alleles[idx];
 		const double2 su = a.sure[idx];
 		const double scorea = 1.0 - su.x;
 		double scoreb = 1.0 - su.y;
 		if (al.x != al.y) scoreb = 1 - scoreb;
-		double similarity = scorea * scoreb + (1 - scorea) * (1 - scoreb);
+		similarity = scorea * scoreb + (1 - scorea) * (1 - scoreb);
 		if (!hc || similarity == 1.0)
 		{
 			hc = fmax(1.0, hc);
@@ -349,18 +504,20 @@ __global__ void __launch_bounds__(128) mstep_haploweight_kernel(MstepArgs a)
 			if (hb < 0) hb = 0;
 			if (hb >= hc) hb = hc;
 		}
-		const double ef = a.entropyfactor, desc = (double)r.descendants;
-		auto gradient = [&](double in) {
-			double et;
-			double out = ms_gcore(w, hb, hc, in, &et);
-			out += ((1 - similarity) * 1 * (ef * et) + (relskewterm - in) / (in - in * in) * desc);
-			return out;
-		};
-		unsigned long long hit = 0;
-		a.hw[idx] = ms_cappedgd(gradient, w, MS_MAXDIFF / (r.children + 1), a.scalefactor, hit);
+	}
+	const MsParams P{ w, hb, hc, (1 - similarity) * 1, a.entropyfactor, active ? a.ratio[idx] : 0.0, (double)r.descendants,
+		              MS_MAXDIFF / (r.children + 1) };
+	unsigned long long hit = 0;
+	const double res = ms_cappedgd_warp<1>(P, w, a.scalefactor, active, hit);
+	if (active)
+	{
+		a.hw[idx] = res;
 		if (hit) atomicAdd(a.hitnnn, hit);
 	}
-	a.carry_base[idx] = hb;
-	a.carry_count[idx] = hc;
+	if (valid)
+	{
+		a.carry_base[idx] = hb;
+		a.carry_count[idx] = hc;
+	}
 }
 }  // namespace cnf2
