@@ -210,8 +210,14 @@ __device__ __forceinline__ MsParams ms_fetch(const MsParams& P, int src)
 	return Q;
 }
 // All 32 lanes call this together; `active` lanes get their solve's result (the others get `orig` back).
+// count_only: the caller throws the result away and only needs the final caplogitchange's hitnnn increment
+// (processinfprobs of an `empty` individual or one without priors, :4301-4311).  That increment needs the end point
+// beyond the cap (:4022-4032), i.e. every bisection decision towards the cap; the first decision away from it (or a
+// stop at the first midpoint, which lies halfway to the cap) rules it out, so such a solve ends there.  Exact: the
+// count is what the full solve would give.
 template <int MODE>
-__device__ __forceinline__ double ms_cappedgd_warp(const MsParams& P, double orig, double scalefactor, bool active, unsigned long long& hit)
+__device__ __forceinline__ double ms_cappedgd_warp(const MsParams& P, double orig, double scalefactor, bool active, unsigned long long& hit,
+                                                   bool count_only = false)
 {
 	const unsigned FULL = 0xffffffffu;
 	const int lane = threadIdx.x & 31, half = lane >> 4, q = lane & 15;
@@ -315,8 +321,16 @@ __device__ __forceinline__ double ms_cappedgd_warp(const MsParams& P, double ori
 		if (!done)
 		{
 			if (fabs(prel - scalefactor) < scalefactor * 1e-3) done = true;
-			else if ((prel < scalefactor) != lowside) lo = mid;
-			else hi = mid;
+			else if ((prel < scalefactor) != lowside)
+			{
+				lo = mid;
+				if (count_only && lowside) done = true;  // away from the lower cap
+			}
+			else
+			{
+				hi = mid;
+				if (count_only && !lowside) done = true;  // away from the upper cap
+			}
 		}
 	}
 	if (!active) return orig;
@@ -382,7 +396,7 @@ __global__ void __launch_bounds__(128) mstep_infprobs_kernel(MstepArgs a)
 				}
 			}
 			const MsParams P{ curprob, ip[k], sum, etf, etf * priord, 0.0, 0.0, epsilon };
-			const double res = ms_cappedgd_warp<0>(P, curprob, a.scalefactor, active, hit);
+			const double res = ms_cappedgd_warp<0>(P, curprob, a.scalefactor, active, hit, r.empty || !r.hasprior);
 			if (active) ip[k] = res;
 		}
 		double bestprob = 0;

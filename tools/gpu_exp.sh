@@ -1,1 +1,2 @@
-timeout 600 ncu --metrics gpu__time_duration.sum,smsp__inst_executed.sum,smsp__thread_inst_executed.sum --clock-control none -k regex:mstep -c 12 --csv --log-file gpurun_out/ms_launches.csv python bench.py --chroms 2 --steps 1 --warmup 1 --no-cpu-baseline > gpurun_out/ms_ncu.log 2>&1
+timeout 600 python -m pytest tests/test_mstep_gpu.py -m gpu -x -q > gpurun_out/exp_ms.log 2>&1
+timeout 900 python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/exp_a.log 2>&1
