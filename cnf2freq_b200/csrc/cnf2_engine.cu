@@ -772,7 +772,7 @@ extern "C" int cnf2_set_mstep_inputs(cnf2_engine* e, const double* relhaplo, con
 	CU(e->d_ratio.ensure((size_t)e->n_rows * e->max_mc));
 	CU(e->d_fw.ensure((size_t)e->n_rows * e->max_mc * 2));
 	CU(e->d_anyinfo.ensure(e->n_rows));
-	CU(e->d_hit.ensure(1));
+	CU(e->d_hit.ensure(2));
 	CU(e->d_msrows.ensure(e->n_rows));
 	for (size_t c = 0; c + 1 < e->chromstarts.size(); c++)
 	{
@@ -805,7 +805,8 @@ extern "C" int cnf2_begin_iteration(cnf2_engine* e)
 	return CNF2_OK;
 }
 
-extern "C" int cnf2_mstep(cnf2_engine* e, int32_t chrom, double scalefactor, double entropyfactor, int64_t* hitnnn)
+extern "C" int cnf2_mstep(cnf2_engine* e, int32_t chrom, double scalefactor, double entropyfactor, int64_t* hitnnn,
+                          int64_t* hitnnn_shared)
 {
 	if (!e) return CNF2_ERR_BAD_ARG;
 	if (!e->have_ms_inputs) return e->fail(CNF2_ERR_STATE, "cnf2_mstep: cnf2_set_mstep_inputs first");
@@ -815,7 +816,7 @@ extern "C" int cnf2_mstep(cnf2_engine* e, int32_t chrom, double scalefactor, dou
 	if (!slp) return e->fail(CNF2_ERR_STATE, "cnf2_mstep: cnf2_estep for this chromosome first (its statistics must still be in flight)");
 	Slot& sl = *slp;
 	cudaSetDevice(e->settings.device);
-	CU(cudaMemsetAsync(e->d_hit.p, 0, sizeof(unsigned long long), sl.stream));
+	CU(cudaMemsetAsync(e->d_hit.p, 0, 2 * sizeof(unsigned long long), sl.stream));
 	const int C = (int)e->chromstarts.size() - 1;
 	auto args = [&](int c, bool fresh) {
 		const size_t blk = (size_t)e->n_rows * e->chromstarts[c];
@@ -862,11 +863,12 @@ extern "C" int cnf2_mstep(cnf2_engine* e, int32_t chrom, double scalefactor, dou
 		}
 	}
 	e->carry_valid[chrom] = 1;
-	unsigned long long hit = 0;
-	CU(cudaMemcpyAsync(&hit, e->d_hit.p, sizeof(hit), cudaMemcpyDeviceToHost, sl.stream));
+	unsigned long long hit[2] = { 0, 0 };
+	CU(cudaMemcpyAsync(hit, e->d_hit.p, sizeof(hit), cudaMemcpyDeviceToHost, sl.stream));
 	CU(cudaStreamSynchronize(sl.stream));
 	CU(cudaGetLastError());
-	if (hitnnn) *hitnnn = (int64_t)hit;
+	if (hitnnn) *hitnnn = (int64_t)(hit[0] + hit[1]);
+	if (hitnnn_shared) *hitnnn_shared = (int64_t)hit[1];
 	return CNF2_OK;
 }
 

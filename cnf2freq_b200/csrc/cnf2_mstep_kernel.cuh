@@ -39,7 +39,7 @@ struct MstepArgs
 	double *carry_base, *carry_count;  // [n_rows][Mc]
 	double *ratio, *fw;                // scratch [n_rows][Mc], [n_rows][Mc][2]
 	uint8_t* anyinfo;                  // [n_rows]
-	unsigned long long* hitnnn;
+	unsigned long long* hitnnn;  // [0] rows only this rank holds, [1] shared rows (every rank counts those)
 	int32_t n_rows, n_shared, Mc;
 	int32_t fresh;  // 1: statistics come from the E-step block; 0: from the carry arrays
 	double scalefactor, entropyfactor;
@@ -420,7 +420,7 @@ __global__ void __launch_bounds__(128) mstep_infprobs_kernel(MstepArgs a)
 	{
 		a.alleles[idx] = al;
 		a.sure[idx] = su;
-		if (hit) atomicAdd(a.hitnnn, hit);
+		if (hit) atomicAdd(a.hitnnn + (row < a.n_shared ? 1 : 0), hit);
 	}
 }
 
@@ -526,7 +526,7 @@ __global__ void __launch_bounds__(128) mstep_haploweight_kernel(MstepArgs a)
 	if (active)
 	{
 		a.hw[idx] = res;
-		if (hit) atomicAdd(a.hitnnn, hit);
+		if (hit) atomicAdd(a.hitnnn + (row < a.n_shared ? 1 : 0), hit);
 	}
 	if (valid)
 	{

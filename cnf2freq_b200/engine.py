@@ -179,12 +179,13 @@ class Engine:
     def begin_iteration(self):
         self._check(self.lib.cnf2_begin_iteration(self.h))
 
-    def mstep(self, chrom, scalefactor, entropyfactor):
-        """The reference's M-step pass after chromosome `chrom`'s E-step; returns hitnnn."""
-        hit = ctypes.c_int64()
+    def mstep(self, chrom, scalefactor, entropyfactor, split=False):
+        """The reference's M-step pass after chromosome `chrom`'s E-step; returns hitnnn (split=True: (hitnnn, the
+        part of it from shared rows) -- see include/cnf2_engine.h for the multi-rank sum)."""
+        hit, sh = ctypes.c_int64(), ctypes.c_int64()
         self._check(self.lib.cnf2_mstep(self.h, ctypes.c_int32(chrom), ctypes.c_double(scalefactor),
-                                        ctypes.c_double(entropyfactor), ctypes.byref(hit)))
-        return int(hit.value)
+                                        ctypes.c_double(entropyfactor), ctypes.byref(hit), ctypes.byref(sh)))
+        return (int(hit.value), int(sh.value)) if split else int(hit.value)
 
     def get_params(self, chrom, alleles, sure, haploweight):
         self._check(self.lib.cnf2_get_params(self.h, ctypes.c_int32(chrom), _ptr(alleles), _ptr(sure), _ptr(haploweight)))

@@ -149,7 +149,10 @@ int cnf2_get_stats_packed(cnf2_engine* e, int32_t chrom, double* haplobase, doub
  * pass left behind.  The parameters are updated in place on the device (the next cnf2_estep of the chromosome uses
  * them without an upload); cnf2_get_params reads them back ([n_ind][n_markers] arrays, columns of `chrom`).
  * scalefactor / entropyfactor are the reference's globals (:3573-3574); *hitnnn receives the pass's count of capped
- * steps (:4022-4032), from which the caller runs the step-size control (:6373-6390).  Phase inversions (negshifter,
+ * steps (:4022-4032), from which the caller runs the step-size control (:6373-6390); with several ranks every rank
+ * updates its copy of the shared rows (the all-reduced statistics are identical everywhere) and *hitnnn_shared (may be
+ * NULL) is the part of *hitnnn those rows contributed: global hitnnn = sum over ranks of (hitnnn - hitnnn_shared) +
+ * hitnnn_shared.  Phase inversions (negshifter,
  * :6336-6340) are host logic and not part of this call: lastinved is taken as -1 (:6290).
  * cnf2_set_mstep_inputs: relhaplo (:889), prior markerdata / markersure (:880-881) as [n_ind][n_markers](x2) arrays,
  * and per individual hasprior (priormarkerdata.size() > 0), children (:5246-5259), empty, descendants.  Needs the
@@ -159,7 +162,8 @@ int cnf2_set_mstep_inputs(cnf2_engine* e, const double* relhaplo, const uint8_t*
                           const uint8_t* hasprior, const int32_t* children, const uint8_t* empty,
                           const int32_t* descendants);
 int cnf2_begin_iteration(cnf2_engine* e);
-int cnf2_mstep(cnf2_engine* e, int32_t chrom, double scalefactor, double entropyfactor, int64_t* hitnnn);
+int cnf2_mstep(cnf2_engine* e, int32_t chrom, double scalefactor, double entropyfactor, int64_t* hitnnn,
+               int64_t* hitnnn_shared);
 int cnf2_get_params(cnf2_engine* e, int32_t chrom, uint8_t* alleles, double* sure, double* haploweight);
 
 /* Block until everything enqueued by this engine has finished; returns the first asynchronous error. */
