@@ -76,101 +76,61 @@ __device__ __forceinline__ double ms_rcp(double x)
 	return (ax > 1e-290 && ax < 1e290) ? frcp(x) : 1.0 / x;
 }
 
-template <class F>
-__device__ __forceinline__ double ms_gauss15(F f, double a, double b)
+// log(y) for an ordinary positive y (no zero, subnormal, inf or NaN: the solver only takes logs of (1 - x) / x with x in
+// [eps, 1 - eps]).  The usual reduction y = 2^e m, m in [sqrt(1/2), sqrt(2)), log m = 2 atanh((m - 1) / (m + 1)) as an
+// odd series in u = 2 (m - 1) / (m + 1) with the division's residual added back; <= 1.2 ulp (checked against long
+// double over 2^-23..2^23 and around 1).  The library log costs three times the instructions in this loop: its
+// coefficients are 64-bit immediates (two moves each on sm_100) and it carries the special-case branches.  The series
+// coefficients 1 / ((2k + 1) 4^k) sit in constant memory and are read as instruction operands.
+__constant__ double MS_LC[10] = { 1.0 / 12,     1.0 / 80,     1.0 / 448,     1.0 / 2304,    1.0 / 11264,
+	                              1.0 / 53248,  1.0 / 245760, 1.0 / 1114112, 1.0 / 4980736, 1.0 / 22020096 };
+__constant__ double MS_LN2[2] = { 6.93147180369123816490e-01, 1.90821492927058770002e-10 };  // hi (21 trailing zero bits), lo
+__device__ __forceinline__ double ms_log(double y)
 {
-	const double x[8] = { 0.0,
-		                  0.2011940939974345223006283033946,
-		                  0.3941513470775633698972073709810,
-		                  0.5709721726085388475372267372539,
-		                  0.7244177313601700474161860546139,
-		                  0.8482065834104272162006483207742,
-		                  0.9372733924007059043077589477102,
-		                  0.9879925180204854284895657185866 };
-	const double w[8] = { 0.2025782419255612728806201999675,
-		                  0.1984314853271115764561183264438,
-		                  0.1861610000155622110268005618664,
-		                  0.1662692058169939335532008604812,
-		                  0.1395706779261543144478047945110,
-		                  0.1071592204671719350118695466859,
-		                  0.0703660474881081247092674164507,
-		                  0.0307532419961172683546283935772 };
-	const double avg = (a + b) * 0.5, scale = (b - a) * 0.5;
-	double result = f(avg) * w[0];
-#pragma unroll 1
-	for (int i = 1; i < 8; i++) result += (f(avg + scale * x[i]) + f(avg - scale * x[i])) * w[i];
-	return result * scale;
+	int hi = __double2hiint(y);
+	const int lo = __double2loint(y);
+	int e = (hi >> 20) - 1023;
+	hi = (hi & 0x000fffff) | 0x3ff00000;
+	if (hi >= 0x3ff6a09f) hi -= 0x00100000, e += 1;
+	const double m = __hiloint2double(hi, lo);
+	const double a = m - 1.0, r = frcp(m + 1.0);
+	const double h = a * r, u = h + h;
+	double res = a - u;
+	res += res;
+	res = fma(a, -u, res);  // 2 a - u (2 + a): what the rounded quotient leaves
+	const double c = r * res;
+	const double sq = u * u;
+	double p = MS_LC[9];
+#pragma unroll
+	for (int k = 8; k >= 0; k--) p = fma(p, sq, MS_LC[k]);
+	const double t = fma(u * sq, p, c);
+	const double ed = __hiloint2double(0x43300000, e ^ 0x80000000) - 4503601774854144.0;  // (double)e
+	return fma(ed, MS_LN2[0], u) + fma(ed, MS_LN2[1], t);
+}
+// fmin(fmax(v, lo), hi) of the reference for lo <= hi (a NaN v gives lo, as fmax does)
+__device__ __forceinline__ double ms_clamp(double v, double lo, double hi)
+{
+	v = !(v >= lo) ? lo : v;
+	return v > hi ? hi : v;
 }
 
-template <class G>
-__device__ __forceinline__ double ms_cappedgd(G gradient, double orig, double epsilon, double scalefactor, unsigned long long& hit)
+// The data term of the gradients at :4275 and :4688.  The reference writes it as a 15-term polynomial in c (current
+// value), h (the statistic), s (its total), x, log x and log(1 - x) over (c h + c s x - c s - h x)^2; the two logs only
+// enter through their difference, and collecting the terms gives
+//   numerator = A et + B + C x,  et = log(1 - x) - log(x) = log(1 / x - 1)   (the entropy term's own logarithm, :4288)
+//   A = c h (c - 1)(h - s),  B = c (h - s)(h - c s),  C = -(c s - h)^2,  denominator = (c (h - s) + (c s - h) x)^2
+// with A, B, C and the two denominator coefficients fixed per solve.  One logarithm and a dozen operations per
+// evaluation instead of two logarithms and ~60: fp64 log and the polynomial are what these kernels spent their time on.
+// The factored coefficients carry fewer cancellations than the expanded sum, so the value differs from the reference's
+// by the reference's own rounding of that sum (the parity tests hold the new parameters to 1e-9).
+__device__ __forceinline__ void ms_data_term(double c, double h, double s, double& A, double& B, double& C, double& d0, double& d1)
 {
-	unsigned long long dump = 0;
-	auto actual = [&](double val) {
-		val = fmin(fmax(val, epsilon), 1 - epsilon);
-		return ms_rcp(gradient(val));
-	};
-	const double lolim = ms_caplogit(epsilon, orig, epsilon, dump);
-	double lo = lolim - epsilon * 0.125;
-	const double hilim = ms_caplogit(1 - epsilon, orig, epsilon, dump);
-	double hi = hilim + epsilon * 0.125;
-	orig = ms_caplogit(orig, orig, epsilon, dump);
-	const double gradval = actual(orig);
-	if (!isfinite(gradval) || !scalefactor)
-	{
-		lo = orig;
-		hi = orig;
-	}
-	const bool lowside = gradval < 0;
-	if (lowside) hi = orig;
-	else lo = orig;
-#pragma unroll 1
-	for (int i = 0; i < 51 && scalefactor; i++)
-	{
-		if (lo > hilim || hi < lolim) break;
-		const double mid = (lo + hi) / 2;
-		double prel = 0;
-		const double g = actual(mid);
-		if (((g < 0) != lowside) || !isfinite(g)) prel = (scalefactor + 0.1) * 1.1;
-		else
-		{
-			double start = orig, end = mid;
-			if (start > end)
-			{
-				const double t = start;
-				start = end;
-				end = t;
-			}
-			if (end - start < 1e-10) break;
-			prel = ms_gauss15(actual, start, end);
-			if (end != mid) prel = -prel;
-			if (!isfinite(prel)) prel = (scalefactor + 0.1) * 1.1;
-		}
-		if (fabs(prel - scalefactor) < scalefactor * 1e-3) break;
-		if ((prel < scalefactor) != lowside) lo = mid;
-		else hi = mid;
-	}
-	if (!scalefactor)
-	{
-		lo = orig;
-		hi = orig;
-	}
-	return ms_caplogit((lo + hi) / 2, orig, epsilon, hit);
-}
-
-__device__ __forceinline__ double ms_sq(double v) { return v * v; }
-// Common part of the gradients at :4275 and :4688, terms in the reference's order, plus the entropy term's
-// log(1 / x - 1), returned through *et as log(1 - x) - log(x): the two logs are the data term's own (the reference
-// takes a third log of 1 / x - 1; the two forms differ by <= 2 ulp of the term).  fp64 log is what this kernel spends
-// its time on.
-__device__ __forceinline__ double ms_gcore(double c, double h, double s, double x, double* et)
-{
-	const double lx = log(x), l1 = log(1 - x);
-	*et = l1 - lx;
-	return -(-ms_sq(c * h) * lx + ms_sq(c * h) * l1 + ms_sq(c) * h * s * lx - ms_sq(c) * h * s * l1 - ms_sq(c) * h * s - ms_sq(c * s) * x +
-	         ms_sq(c * s) + c * ms_sq(h) * lx - c * ms_sq(h) * l1 + c * ms_sq(h) + 2 * c * h * s * x - c * h * s * lx + c * h * s * l1 -
-	         c * h * s - ms_sq(h) * x) *
-	       ms_rcp(ms_sq(c * h + c * s * x - c * s - h * x));
+	const double hs = h - s, csh = c * s - h;
+	A = c * h * (c - 1) * hs;
+	B = c * hs * (h - c * s);
+	C = -(csh * csh);
+	d0 = c * hs;
+	d1 = csh;
 }
 
 // ---- the warp-cooperative form of cappedgd ----
@@ -178,35 +138,59 @@ __device__ __forceinline__ double ms_gcore(double c, double h, double s, double 
 // own) and, for about a third of the steps, a 15-point integral.  Lanes take their integral steps at different
 // iterations, so a lane-private solver makes the warp pay 16 evaluations on nearly every step; here the integrals
 // pending after a step are served two at a time, one per half-warp, its 15 points on 15 lanes with the owner's
-// parameters fetched by shuffle, and the owner sums the values in the reference's order.  Arithmetic per solve is
-// unchanged.
+// parameters read from shared memory, and the weighted values are summed over the half-warp by a shuffle tree (the
+// reference adds the eight weighted pairs one after the other; the tree differs from that by rounding only).
 struct MsParams
 {
-	double c, h, s;        // data term: (curprob, hzygcorred, sum) or (haploweight, haplobase, haplocount)
-	double p0, p1, p2, p3; // MODE 0: etf, etf * priord; MODE 1: (1 - similarity) * 1, ef, relskewterm, descendants
+	double A, B, C, d0, d1;  // ms_data_term of (curprob, hzygcorred, sum) or (haploweight, haplobase, haplocount)
+	double p0, p1, p2, p3;   // MODE 0: etf, etf * priord; MODE 1: (1 - similarity) * 1, ef, relskewterm, descendants
 	double eps;
 };
+__device__ __forceinline__ MsParams ms_params(double c, double h, double s, double p0, double p1, double p2, double p3, double eps)
+{
+	MsParams P;
+	ms_data_term(c, h, s, P.A, P.B, P.C, P.d0, P.d1);
+	P.p0 = p0, P.p1 = p1, P.p2 = p2, P.p3 = p3, P.eps = eps;
+	return P;
+}
 template <int MODE>
 __device__ __forceinline__ double ms_actual(const MsParams& P, double val)
 {
-	val = fmin(fmax(val, P.eps), 1 - P.eps);
-	double et;
-	double g = ms_gcore(P.c, P.h, P.s, val, &et);
+	val = ms_clamp(val, P.eps, 1 - P.eps);  // eps > 0: val, 1 - val and val - val^2 are ordinary positive numbers
+	const double den = fma(P.d1, val, P.d0);
+	double et, g;
 	if (MODE == 0)
 	{
+		et = ms_log((1 - val) * frcp(val));
+		g = -fma(P.A, et, fma(P.C, val, P.B)) * ms_rcp(den * den);
 		g += P.p0 * et;  // entropy term, :4288
 		g += P.p1;       // prior, :4289
 	}
-	else g += (P.p0 * (P.p1 * et) + (P.p2 - val) / (val - val * val) * P.p3);  // :4689-4692
+	else
+	{
+		const double t = frcp(val - val * val);  // 1 / (x (1 - x)); 1 / x - 1 = (1 - x)^2 t
+		et = ms_log((1 - val) * (1 - val) * t);
+		g = -fma(P.A, et, fma(P.C, val, P.B)) * ms_rcp(den * den);
+		g += (P.p0 * (P.p1 * et) + (P.p2 - val) * t * P.p3);  // :4689-4692
+	}
 	return ms_rcp(g);
 }
-__device__ __forceinline__ MsParams ms_fetch(const MsParams& P, int src)
+// A solve's parameters are staged in shared memory by their owner (once per solve) and read back by the half-warp
+// that serves one of its integrals: [parameter][thread of the block], so the owner's stores are conflict-free and a
+// half-warp's loads are broadcasts.
+constexpr int MS_BLOCK = 128, MS_NPAR = 10;
+__device__ __forceinline__ void ms_stage(double* sp, const MsParams& P)
 {
-	const unsigned FULL = 0xffffffffu;
+	sp[0 * MS_BLOCK] = P.A, sp[1 * MS_BLOCK] = P.B, sp[2 * MS_BLOCK] = P.C, sp[3 * MS_BLOCK] = P.d0, sp[4 * MS_BLOCK] = P.d1;
+	sp[5 * MS_BLOCK] = P.p0, sp[6 * MS_BLOCK] = P.p1, sp[7 * MS_BLOCK] = P.p2, sp[8 * MS_BLOCK] = P.p3, sp[9 * MS_BLOCK] = P.eps;
+}
+template <int MODE>
+__device__ __forceinline__ MsParams ms_fetch(const double* sp)
+{
 	MsParams Q;
-	Q.c = __shfl_sync(FULL, P.c, src), Q.h = __shfl_sync(FULL, P.h, src), Q.s = __shfl_sync(FULL, P.s, src);
-	Q.p0 = __shfl_sync(FULL, P.p0, src), Q.p1 = __shfl_sync(FULL, P.p1, src), Q.p2 = __shfl_sync(FULL, P.p2, src);
-	Q.p3 = __shfl_sync(FULL, P.p3, src), Q.eps = __shfl_sync(FULL, P.eps, src);
+	Q.A = sp[0 * MS_BLOCK], Q.B = sp[1 * MS_BLOCK], Q.C = sp[2 * MS_BLOCK], Q.d0 = sp[3 * MS_BLOCK], Q.d1 = sp[4 * MS_BLOCK];
+	Q.p0 = sp[5 * MS_BLOCK], Q.p1 = sp[6 * MS_BLOCK], Q.eps = sp[9 * MS_BLOCK];
+	Q.p2 = MODE ? sp[7 * MS_BLOCK] : 0.0, Q.p3 = MODE ? sp[8 * MS_BLOCK] : 0.0;
 	return Q;
 }
 // All 32 lanes call this together; `active` lanes get their solve's result (the others get `orig` back).
@@ -217,10 +201,14 @@ __device__ __forceinline__ MsParams ms_fetch(const MsParams& P, int src)
 // count is what the full solve would give.
 template <int MODE>
 __device__ __forceinline__ double ms_cappedgd_warp(const MsParams& P, double orig, double scalefactor, bool active, unsigned long long& hit,
-                                                   bool count_only = false)
+                                                   double* stage, bool count_only = false)
 {
 	const unsigned FULL = 0xffffffffu;
 	const int lane = threadIdx.x & 31, half = lane >> 4, q = lane & 15;
+	double* const wstage = stage + (threadIdx.x & ~31);  // this warp's 32 columns of the block's staging array
+	__syncwarp();
+	ms_stage(wstage + lane, P);
+	__syncwarp();
 	const double GX[8] = { 0.0,
 		                   0.2011940939974345223006283033946,
 		                   0.3941513470775633698972073709810,
@@ -238,7 +226,13 @@ __device__ __forceinline__ double ms_cappedgd_warp(const MsParams& P, double ori
 		                   0.0703660474881081247092674164507,
 		                   0.0307532419961172683546283935772 };
 	// this lane's quadrature point: q = 0 the centre, 1..7 centre + scale x_q, 8..14 centre - scale x_(q-7), 15 idle
-	const double myx = q == 0 ? 0.0 : (q < 8 ? GX[q & 7] : (q < 15 ? -GX[(q - 7) & 7] : 0.0));
+	double myx = 0, myw = 0;
+#pragma unroll
+	for (int k = 0; k < 8; k++)
+	{
+		if (q == k) myx = GX[k], myw = GW[k];
+		if (k && q == k + 7) myx = -GX[k];
+	}
 	unsigned long long dump = 0;
 	const double epsilon = P.eps;
 	double lolim = 0, hilim = 0, lo = 0, hi = 0;
@@ -296,21 +290,19 @@ __device__ __forceinline__ double ms_cappedgd_warp(const MsParams& P, double ori
 			if (o1 >= 0) mask &= mask - 1;
 			const int owner = half ? o1 : o0;  // the solve this half-warp serves (-1: none)
 			const int src = owner < 0 ? lane : owner;
-			const MsParams Q = ms_fetch(P, src);
+			const MsParams Q = ms_fetch<MODE>(wstage + src);
 			const double a0 = __shfl_sync(FULL, start, src), b0 = __shfl_sync(FULL, end, src);
 			const double avg = (a0 + b0) * 0.5, scale = (b0 - a0) * 0.5;
 			double f = 0;
 			if (owner >= 0 && q < 15) f = ms_actual<MODE>(Q, avg + scale * myx);
-			// the owner (any lane of the warp) gathers its half-warp's values in the reference's order
+			// (f(+x_q) + f(-x_q)) w_q on lanes q = 0..7 of each half, summed over those 8 lanes, handed to the owner
+			double tq = (f + __shfl_down_sync(FULL, f, 7, 16)) * myw;
+			if (q == 0) tq = f * myw;
+			tq += __shfl_xor_sync(FULL, tq, 1);
+			tq += __shfl_xor_sync(FULL, tq, 2);
+			tq += __shfl_xor_sync(FULL, tq, 4);
 			const bool mine = lane == o0 || lane == o1;
-			const int base = lane == o1 ? 16 : 0;
-			double result = __shfl_sync(FULL, f, base) * GW[0];
-#pragma unroll
-			for (int k = 1; k < 8; k++)
-			{
-				const double fp = __shfl_sync(FULL, f, base + k), fm = __shfl_sync(FULL, f, base + 7 + k);
-				result += (fp + fm) * GW[k];
-			}
+			const double result = __shfl_sync(FULL, tq, lane == o1 ? 16 : 0);
 			if (mine)
 			{
 				prel = result * ((end - start) * 0.5);
@@ -351,8 +343,9 @@ __device__ __forceinline__ StatsCell ms_cell(const MstepArgs& a, int row, int m)
 // processinfprobs (:4179-4323) for both sides of one (row, marker).  A statistic that is exactly 0 is an absent key
 // of the reference's small_map (the E-step never adds a zero).  infprobs/homozyg are not cleared here: the next
 // E-step of the chromosome zeroes its block.
-__global__ void __launch_bounds__(128) mstep_infprobs_kernel(MstepArgs a)
+__global__ void __launch_bounds__(MS_BLOCK) mstep_infprobs_kernel(MstepArgs a)
 {
+	__shared__ double stage[MS_NPAR][MS_BLOCK];
 	const size_t idx0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x, cells = (size_t)a.n_rows * a.Mc;
 	const bool valid = idx0 < cells;  // every lane stays for the warp-cooperative solver
 	const size_t idx = valid ? idx0 : cells - 1;
@@ -395,8 +388,8 @@ __global__ void __launch_bounds__(128) mstep_infprobs_kernel(MstepArgs a)
 					priord += log(priorprob) - log(1 - priorprob);
 				}
 			}
-			const MsParams P{ curprob, ip[k], sum, etf, etf * priord, 0.0, 0.0, epsilon };
-			const double res = ms_cappedgd_warp<0>(P, curprob, a.scalefactor, active, hit, r.empty || !r.hasprior);
+			const MsParams P = ms_params(curprob, ip[k], sum, etf, etf * priord, 0.0, 0.0, epsilon);
+			const double res = ms_cappedgd_warp<0>(P, curprob, a.scalefactor, active, hit, &stage[0][0], r.empty || !r.hasprior);
 			if (active) ip[k] = res;
 		}
 		double bestprob = 0;
@@ -477,8 +470,9 @@ __global__ void __launch_bounds__(128) mstep_relskew_kernel(MstepArgs a)
 
 // updatehaploweights (:4533-4734) for one (row, marker); the adjusted haplobase/haplocount are kept in the carry
 // arrays because the reference re-runs this on the chromosome after every later chromosome of the iteration.
-__global__ void __launch_bounds__(128) mstep_haploweight_kernel(MstepArgs a)
+__global__ void __launch_bounds__(MS_BLOCK) mstep_haploweight_kernel(MstepArgs a)
 {
+	__shared__ double stage[MS_NPAR][MS_BLOCK];
 	const size_t idx0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x, cells = (size_t)a.n_rows * a.Mc;
 	const bool valid = idx0 < cells;  // every lane stays for the warp-cooperative solver
 	const size_t idx = valid ? idx0 : cells - 1;
@@ -519,10 +513,10 @@ __global__ void __launch_bounds__(128) mstep_haploweight_kernel(MstepArgs a)
 			if (hb >= hc) hb = hc;
 		}
 	}
-	const MsParams P{ w, hb, hc, (1 - similarity) * 1, a.entropyfactor, active ? a.ratio[idx] : 0.0, (double)r.descendants,
-		              MS_MAXDIFF / (r.children + 1) };
+	const MsParams P = ms_params(w, hb, hc, (1 - similarity) * 1, a.entropyfactor, active ? a.ratio[idx] : 0.0, (double)r.descendants,
+	                             MS_MAXDIFF / (r.children + 1));
 	unsigned long long hit = 0;
-	const double res = ms_cappedgd_warp<1>(P, w, a.scalefactor, active, hit);
+	const double res = ms_cappedgd_warp<1>(P, w, a.scalefactor, active, hit, &stage[0][0]);
 	if (active)
 	{
 		a.hw[idx] = res;

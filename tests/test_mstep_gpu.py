@@ -112,6 +112,7 @@ def stationary(alleles, sure, infprobs, prioralleles, hasprior):
     ("f2_cross", dict(n_f2=9, n_chrom=2, mpc=21, seed=61)),
     ("fullsib", dict(n_fam=2, n_off=3, n_chrom=1, mpc=15, seed=62)),
     ("tangled", dict(n_chrom=2, mpc=17, seed=63)),
+    ("f2_cross", dict(n_f2=300, n_chrom=2, mpc=12, seed=64)),  # founders' statistics sum over hundreds of offspring
 ])
 def test_device_mstep_matches_oracle_on_random_pedigrees(eng, maker, kw):
     """Random parameters (locked phases, zero sureness, priors on some individuals): the oracle's M-step on the
