@@ -425,10 +425,18 @@ __global__ void __launch_bounds__(128) mstep_relskew_kernel(MstepArgs a)
 	if (row >= a.n_rows) return;
 	const int Mc = a.Mc;
 	bool any = false;
-	for (int m = 0; m < Mc && !any; m++)
+	for (int m0 = 0; m0 < Mc && !any; m0 += 16)  // 16 independent loads per round: a row without information is scanned to its end
 	{
-		const double hc = a.fresh ? *ms_cell(a, row, m).haplocount : a.carry_count[(size_t)row * Mc + m];
-		if (hc) any = true;
+		double hc[16];
+#pragma unroll
+		for (int j = 0; j < 16; j++)
+		{
+			const int m = min(m0 + j, Mc - 1);
+			hc[j] = a.fresh ? *ms_cell(a, row, m).haplocount : a.carry_count[(size_t)row * Mc + m];
+		}
+#pragma unroll
+		for (int j = 0; j < 16; j++)
+			if (hc[j]) any = true;
 	}
 	a.anyinfo[row] = any;
 	if (!any) return;
@@ -436,41 +444,100 @@ __global__ void __launch_bounds__(128) mstep_relskew_kernel(MstepArgs a)
 	const double* rh = a.relhaplo + (size_t)row * Mc;
 	double2* fw = reinterpret_cast<double2*>(a.fw) + (size_t)row * Mc;
 	double* ratio = a.ratio + (size_t)row * Mc;
+	// A thread walks its own row, so its loads are a dependent chain of cache misses unless they are issued ahead:
+	// RB markers are loaded at once, the next RB while the current ones are worked through.
+	constexpr int RB = 8;
 	double s0 = 0.5, s1 = 0.5;
-	for (int m = 0; m < Mc; m++)
+	double wc[RB], nc[RB];
+#pragma unroll
+	for (int j = 0; j < RB; j++)
 	{
-		const double w = hw[m];
-		s0 *= fabs(1 - w);
-		s1 *= fabs(0 - w);
-		fw[m] = make_double2(s0, s1);
-		if (s0 + s1 < 1e-10) s0 *= 1e20, s1 *= 1e20;
-		const double n = rh[m], nb = 1 - n;
-		const double t0 = s0 * n + s1 * nb, t1 = s1 * n + s0 * nb;
-		s0 = t0, s1 = t1;
+		wc[j] = j < Mc ? hw[j] : 0.0;
+		nc[j] = j < Mc ? rh[j] : 0.0;
+	}
+	for (int m0 = 0; m0 < Mc; m0 += RB)
+	{
+		double wn[RB], nn[RB];
+#pragma unroll
+		for (int j = 0; j < RB; j++)
+		{
+			const int m = m0 + RB + j;
+			wn[j] = m < Mc ? hw[m] : 0.0;
+			nn[j] = m < Mc ? rh[m] : 0.0;
+		}
+#pragma unroll
+		for (int j = 0; j < RB; j++)
+		{
+			const int m = m0 + j;
+			if (m < Mc)
+			{
+				const double w = wc[j];
+				s0 *= fabs(1 - w);
+				s1 *= fabs(0 - w);
+				fw[m] = make_double2(s0, s1);
+				if (s0 + s1 < 1e-10) s0 *= 1e20, s1 *= 1e20;
+				const double n = nc[j], nb = 1 - n;
+				const double t0 = s0 * n + s1 * nb, t1 = s1 * n + s0 * nb;
+				s0 = t0, s1 = t1;
+			}
+		}
+#pragma unroll
+		for (int j = 0; j < RB; j++) wc[j] = wn[j], nc[j] = nn[j];
 	}
 	s0 = s1 = 0.5;
 	{
 		const double2 f = fw[Mc - 1];
 		ratio[Mc - 1] = f.y / (f.x + f.y);
 	}
-	for (int m = Mc - 2; m >= 0; m--)
+	// backwards: step t handles marker m = Mc - 2 - t with hw[m + 1], relhaplo[m] and the stored forward pair of m
+	const int steps = Mc - 1;
+	double2 fc[RB];
+#pragma unroll
+	for (int j = 0; j < RB; j++)
 	{
-		const double w = hw[m + 1];
-		s0 *= fabs(1 - w);
-		s1 *= fabs(0 - w);
-		const double n = rh[m], nb = 1 - n;
-		const double t0 = s0 * n + s1 * nb, t1 = s1 * n + s0 * nb;
-		s0 = t0, s1 = t1;
-		if (s0 + s1 < 1e-10) s0 *= 1e20, s1 *= 1e20;
-		const double2 f = fw[m];
-		const double r0 = s0 * f.x, r1 = s1 * f.y;
-		ratio[m] = r1 / (r0 + r1);
+		const int m = Mc - 2 - j;
+		wc[j] = j < steps ? hw[m + 1] : 0.0;
+		nc[j] = j < steps ? rh[m] : 0.0;
+		fc[j] = j < steps ? fw[m] : make_double2(0.0, 0.0);
+	}
+	for (int t0 = 0; t0 < steps; t0 += RB)
+	{
+		double wn[RB], nn[RB];
+		double2 fn[RB];
+#pragma unroll
+		for (int j = 0; j < RB; j++)
+		{
+			const int t = t0 + RB + j, m = Mc - 2 - t;
+			wn[j] = t < steps ? hw[m + 1] : 0.0;
+			nn[j] = t < steps ? rh[m] : 0.0;
+			fn[j] = t < steps ? fw[m] : make_double2(0.0, 0.0);
+		}
+#pragma unroll
+		for (int j = 0; j < RB; j++)
+		{
+			const int t = t0 + j, m = Mc - 2 - t;
+			if (t < steps)
+			{
+				const double w = wc[j];
+				s0 *= fabs(1 - w);
+				s1 *= fabs(0 - w);
+				const double n = nc[j], nb = 1 - n;
+				const double t0v = s0 * n + s1 * nb, t1v = s1 * n + s0 * nb;
+				s0 = t0v, s1 = t1v;
+				if (s0 + s1 < 1e-10) s0 *= 1e20, s1 *= 1e20;
+				const double2 f = fc[j];
+				const double r0 = s0 * f.x, r1 = s1 * f.y;
+				ratio[m] = r1 / (r0 + r1);
+			}
+		}
+#pragma unroll
+		for (int j = 0; j < RB; j++) wc[j] = wn[j], nc[j] = nn[j], fc[j] = fn[j];
 	}
 }
 
 // updatehaploweights (:4533-4734) for one (row, marker); the adjusted haplobase/haplocount are kept in the carry
 // arrays because the reference re-runs this on the chromosome after every later chromosome of the iteration.
-__global__ void __launch_bounds__(MS_BLOCK) mstep_haploweight_kernel(MstepArgs a)
+__global__ void __launch_bounds__(MS_BLOCK, 6) mstep_haploweight_kernel(MstepArgs a)
 {
 	__shared__ double stage[MS_NPAR][MS_BLOCK];
 	const size_t idx0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x, cells = (size_t)a.n_rows * a.Mc;
