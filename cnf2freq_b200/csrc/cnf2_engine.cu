@@ -235,6 +235,18 @@ extern "C" void cnf2_destroy(cnf2_engine* e)
 	if (!e) return;
 	cudaSetDevice(e->settings.device);
 	if (e->stream) cudaStreamSynchronize(e->stream);
+#ifdef CNF2_MS_HIST
+	{
+		unsigned long long h[2][64];
+		cudaMemcpyFromSymbol(h, ms_hist, sizeof(h));
+		for (int k = 0; k < 2; k++)
+		{
+			fprintf(stderr, "ms_hist mode %d:", k);
+			for (int i = 0; i < 64; i++) fprintf(stderr, " %llu", h[k][i]);
+			fprintf(stderr, "\n");
+		}
+	}
+#endif
 	e->d_alleles.release();
 	e->d_sure.release();
 	e->d_hw.release();

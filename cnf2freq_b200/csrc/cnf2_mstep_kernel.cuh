@@ -199,6 +199,9 @@ __device__ __forceinline__ MsParams ms_fetch(const double* sp)
 // beyond the cap (:4022-4032), i.e. every bisection decision towards the cap; the first decision away from it (or a
 // stop at the first midpoint, which lies halfway to the cap) rules it out, so such a solve ends there.  Exact: the
 // count is what the full solve would give.
+#ifdef CNF2_MS_HIST
+__device__ unsigned long long ms_hist[2][64];
+#endif
 template <int MODE>
 __device__ __forceinline__ double ms_cappedgd_warp(const MsParams& P, double orig, double scalefactor, bool active, unsigned long long& hit,
                                                    double* stage, bool count_only = false)
@@ -237,6 +240,9 @@ __device__ __forceinline__ double ms_cappedgd_warp(const MsParams& P, double ori
 	const double epsilon = P.eps;
 	double lolim = 0, hilim = 0, lo = 0, hi = 0;
 	bool lowside = false, done = !active;
+#ifdef CNF2_MS_HIST
+	int myit = 0;
+#endif
 	if (active)
 	{
 		lolim = ms_caplogit(epsilon, orig, epsilon, dump);
@@ -258,12 +264,17 @@ __device__ __forceinline__ double ms_cappedgd_warp(const MsParams& P, double ori
 #pragma unroll 1
 	for (int i = 0; i < 51; i++)
 	{
-		if (!done && (lo > hilim || hi < lolim)) done = true;
+		// lo == hi: the interval has collapsed (a non-finite 1 / gradient at the start, :4131, or scalefactor 0); every
+		// further step of the reference sets lo or hi to their common midpoint again, so the result is already fixed
+		if (!done && (lo > hilim || hi < lolim || lo == hi)) done = true;
 		if (__all_sync(FULL, done)) break;
 		double mid = 0, prel = 0, start = 0, end = 0;
 		bool pending = false;
 		if (!done)
 		{
+#ifdef CNF2_MS_HIST
+			myit++;
+#endif
 			mid = (lo + hi) / 2;
 			const double g = ms_actual<MODE>(P, mid);
 			if (((g < 0) != lowside) || !isfinite(g)) prel = (scalefactor + 0.1) * 1.1;
@@ -325,6 +336,9 @@ __device__ __forceinline__ double ms_cappedgd_warp(const MsParams& P, double ori
 			}
 		}
 	}
+#ifdef CNF2_MS_HIST
+	if (active) atomicAdd(&ms_hist[MODE][myit], 1ull);
+#endif
 	if (!active) return orig;
 	if (!scalefactor)
 	{
