@@ -67,13 +67,13 @@ __device__ __forceinline__ double ms_caplogit(double intended, double orig, doub
 	return intended;
 }
 
-// 1 / x on the solver's inner loop (two per gradient evaluation): frcp (~1 ulp) where x is an ordinary number, the IEEE
+// 1 / x on the solver's inner loop: frcp (~1 ulp) where x is an ordinary number, the IEEE
 // division where it is not, so that 1 / 0 = inf and non-finite gradients keep steering the bisection as they do in
 // the reference (:4131, :4144).
 __device__ __forceinline__ double ms_rcp(double x)
 {
-	const double ax = fabs(x);
-	return (ax > 1e-290 && ax < 1e290) ? frcp(x) : 1.0 / x;
+	const unsigned ex = ((unsigned)__double2hiint(x) >> 20) & 0x7ffu;
+	return (ex - 64u < 1920u) ? frcp(x) : 1.0 / x;  // |x| in [2^-959, 2^961): x and 1 / x are both ordinary numbers
 }
 
 // log(y) for an ordinary positive y (no zero, subnormal, inf or NaN: the solver only takes logs of (1 - x) / x with x in
@@ -157,23 +157,22 @@ template <int MODE>
 __device__ __forceinline__ double ms_actual(const MsParams& P, double val)
 {
 	val = ms_clamp(val, P.eps, 1 - P.eps);  // eps > 0: val, 1 - val and val - val^2 are ordinary positive numbers
-	const double den = fma(P.d1, val, P.d0);
-	double et, g;
+	const double den = fma(P.d1, val, P.d0), D = den * den;
+	double et, c;  // gradient = -N / D + c with N = A et + B + C x; what the solver integrates is 1 / gradient = D / (c D - N):
+	               // one reciprocal, and the same 0 / inf / NaN as the reference's two divisions when D or the gradient is 0
 	if (MODE == 0)
 	{
 		et = ms_log((1 - val) * frcp(val));
-		g = -fma(P.A, et, fma(P.C, val, P.B)) * ms_rcp(den * den);
-		g += P.p0 * et;  // entropy term, :4288
-		g += P.p1;       // prior, :4289
+		c = fma(P.p0, et, P.p1);  // entropy term and prior, :4288-4289
 	}
 	else
 	{
 		const double t = frcp(val - val * val);  // 1 / (x (1 - x)); 1 / x - 1 = (1 - x)^2 t
 		et = ms_log((1 - val) * (1 - val) * t);
-		g = -fma(P.A, et, fma(P.C, val, P.B)) * ms_rcp(den * den);
-		g += (P.p0 * (P.p1 * et) + (P.p2 - val) * t * P.p3);  // :4689-4692
+		c = fma(P.p0, P.p1 * et, (P.p2 - val) * t * P.p3);  // :4689-4692
 	}
-	return ms_rcp(g);
+	const double N = fma(P.A, et, fma(P.C, val, P.B));
+	return D * ms_rcp(fma(c, D, -N));
 }
 // A solve's parameters are staged in shared memory by their owner (once per solve) and read back by the half-warp
 // that serves one of its integrals: [parameter][thread of the block], so the owner's stores are conflict-free and a
