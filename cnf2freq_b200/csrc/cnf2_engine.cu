@@ -70,6 +70,8 @@ struct cnf2_engine
 	std::string error;
 	cudaStream_t stream = nullptr;  // copies of parameters, marks, microbenchmarks
 	cudaStream_t comm = nullptr;    // the all-reduce hook runs here, in call order
+	cudaStream_t side = nullptr;    // M-step: the relskew chains of a pass run here, beside processinfprobs
+	cudaEvent_t ms_fork = nullptr, ms_join = nullptr;
 	Slot slots[NSLOT];
 	int next_slot = 0, last_slot = -1;
 	int n_slots = 2;  // E-steps in flight (CNF2_SLOTS, 1..NSLOT)
@@ -198,6 +200,13 @@ extern "C" int cnf2_create(cnf2_engine** out, const cnf2_settings* settings)
 	if ((ce = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(ce, "cudaStreamCreate");
 	if ((ce = cudaStreamCreateWithFlags(&e->comm, cudaStreamNonBlocking)) != cudaSuccess) return bail(ce, "cudaStreamCreate");
 	if ((ce = cudaEventCreateWithFlags(&e->params_ready, cudaEventDisableTiming)) != cudaSuccess) return bail(ce, "cudaEventCreate");
+	{
+		int lo_prio = 0, hi_prio = 0;
+		cudaDeviceGetStreamPriorityRange(&lo_prio, &hi_prio);
+		if ((ce = cudaStreamCreateWithPriority(&e->side, cudaStreamNonBlocking, hi_prio)) != cudaSuccess) return bail(ce, "cudaStreamCreate");
+	}
+	if ((ce = cudaEventCreateWithFlags(&e->ms_fork, cudaEventDisableTiming)) != cudaSuccess) return bail(ce, "cudaEventCreate");
+	if ((ce = cudaEventCreateWithFlags(&e->ms_join, cudaEventDisableTiming)) != cudaSuccess) return bail(ce, "cudaEventCreate");
 	for (Slot& sl : e->slots)
 	{
 		if ((ce = cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(ce, "cudaStreamCreate");
@@ -263,6 +272,9 @@ extern "C" void cnf2_destroy(cnf2_engine* e)
 		if (sl.stream) cudaStreamDestroy(sl.stream);
 	}
 	if (e->comm) cudaStreamSynchronize(e->comm), cudaStreamDestroy(e->comm);
+	if (e->side) cudaStreamSynchronize(e->side), cudaStreamDestroy(e->side);
+	if (e->ms_fork) cudaEventDestroy(e->ms_fork);
+	if (e->ms_join) cudaEventDestroy(e->ms_join);
 	e->d_units.release();
 	for (cudaEvent_t m : e->marks)
 		if (m) cudaEventDestroy(m);
@@ -781,9 +793,9 @@ extern "C" int cnf2_set_mstep_inputs(cnf2_engine* e, const double* relhaplo, con
 	CU(e->d_priorsure.ensure(total));
 	CU(e->d_carry_base.ensure(total));
 	CU(e->d_carry_count.ensure(total));
-	CU(e->d_ratio.ensure((size_t)e->n_rows * e->max_mc));
+	CU(e->d_ratio.ensure((size_t)e->n_rows * e->markerpos.size()));  // per chromosome block: a pass computes them all before it uses them
 	CU(e->d_fw.ensure((size_t)e->n_rows * e->max_mc * 2));
-	CU(e->d_anyinfo.ensure(e->n_rows));
+	CU(e->d_anyinfo.ensure((size_t)e->n_rows * (e->chromstarts.size() - 1)));
 	CU(e->d_hit.ensure(2));
 	CU(e->d_msrows.ensure(e->n_rows));
 	for (size_t c = 0; c + 1 < e->chromstarts.size(); c++)
@@ -845,9 +857,9 @@ extern "C" int cnf2_mstep(cnf2_engine* e, int32_t chrom, double scalefactor, dou
 		a.stats_local = sl.stats_local(Mc);
 		a.carry_base = e->d_carry_base.p + blk;
 		a.carry_count = e->d_carry_count.p + blk;
-		a.ratio = e->d_ratio.p;
+		a.ratio = e->d_ratio.p + blk;
 		a.fw = e->d_fw.p;
-		a.anyinfo = e->d_anyinfo.p;
+		a.anyinfo = e->d_anyinfo.p + (size_t)e->n_rows * c;
 		a.hitnnn = e->d_hit.p;
 		a.n_rows = e->n_rows;
 		a.n_shared = e->n_shared;
@@ -860,19 +872,28 @@ extern "C" int cnf2_mstep(cnf2_engine* e, int32_t chrom, double scalefactor, dou
 	if (e->n_rows > 0)
 	{
 		// processinfprobs only has statistics for this chromosome; updatehaploweights also walks the chromosomes whose
-		// pass came earlier in the iteration, with the haplobase / haplocount that pass left behind (:6239-6367)
+		// pass came earlier in the iteration, with the haplobase / haplocount that pass left behind (:6239-6367).
+		// The relskew chains (one thread per row, latency-bound) read haploweight and haplocount only, which
+		// processinfprobs does not touch: they run on a side stream beside it, one chromosome after the other.
+		auto in_pass = [&](int c) { return c == chrom || e->carry_valid[c]; };
+		const unsigned gr = (unsigned)((e->n_rows + 127) / 128);
+		CU(cudaEventRecord(e->ms_fork, sl.stream));
+		CU(cudaStreamWaitEvent(e->side, e->ms_fork, 0));
+		for (int c = 0; c < C; c++)
+			if (in_pass(c)) mstep_relskew_kernel<<<gr, 128, 0, e->side>>>(args(c, c == chrom));
+		CU(cudaEventRecord(e->ms_join, e->side));
+		{
+			const MstepArgs a = args(chrom, true);
+			mstep_infprobs_kernel<<<(unsigned)(((size_t)e->n_rows * a.Mc + 127) / 128), 128, 0, sl.stream>>>(a);
+		}
+		CU(cudaStreamWaitEvent(sl.stream, e->ms_join, 0));
 		for (int c = 0; c < C; c++)
 		{
-			const bool fresh = c == chrom;
-			if (!fresh && !e->carry_valid[c]) continue;
-			const MstepArgs a = args(c, fresh);
-			const size_t cells = (size_t)e->n_rows * a.Mc;
-			const unsigned gc = (unsigned)((cells + 127) / 128), gr = (unsigned)((e->n_rows + 127) / 128);
-			if (fresh) mstep_infprobs_kernel<<<gc, 128, 0, sl.stream>>>(a);
-			mstep_relskew_kernel<<<gr, 128, 0, sl.stream>>>(a);
-			mstep_haploweight_kernel<<<gc, 128, 0, sl.stream>>>(a);
-			CU(cudaGetLastError());
+			if (!in_pass(c)) continue;
+			const MstepArgs a = args(c, c == chrom);
+			mstep_haploweight_kernel<<<(unsigned)(((size_t)e->n_rows * a.Mc + 127) / 128), 128, 0, sl.stream>>>(a);
 		}
+		CU(cudaGetLastError());
 	}
 	e->carry_valid[chrom] = 1;
 	unsigned long long hit[2] = { 0, 0 };
