@@ -11,6 +11,7 @@
 // boost::math::quadrature::gauss<double, 15>) is the same arithmetic in the same order as the reference; the only
 // difference is the device's log().  lastinved is -1 (no phase inversion in flight, :6290), so breakathalf is false.
 #pragma once
+#include <type_traits>
 #include "cnf2_tables.cuh"
 
 namespace cnf2
@@ -290,35 +291,58 @@ __device__ __forceinline__ double ms_cappedgd_warp(const MsParams& P, double ori
 				else pending = true;
 			}
 		}
-		// integrals of the lanes that need one, two per round
+		// integrals of the lanes that need one: two per round (one per half-warp), two rounds at a time while there are
+		// enough of them -- a round is one long dependent fp64 chain per lane, a second independent one fills its gaps
 		unsigned mask = __ballot_sync(FULL, pending);
+		auto rounds = [&](auto nu, const int* own) {
+			constexpr int NU = decltype(nu)::value;
+			double f[NU], tq[NU];
+#pragma unroll
+			for (int u = 0; u < NU; u++)
+			{
+				const int owner = half ? own[2 * u + 1] : own[2 * u];  // the solve this half-warp serves (-1: none)
+				const int src = owner < 0 ? lane : owner;
+				const MsParams Q = ms_fetch<MODE>(wstage + src);
+				const double a0 = __shfl_sync(FULL, start, src), b0 = __shfl_sync(FULL, end, src);
+				const double avg = (a0 + b0) * 0.5, scale = (b0 - a0) * 0.5;
+				const double v = ms_actual<MODE>(Q, avg + scale * myx);
+				f[u] = (owner >= 0 && q < 15) ? v : 0.0;
+			}
+			// (f(+x_q) + f(-x_q)) w_q on lanes q = 0..7 of each half, summed over those 8 lanes, handed to the owner
+#pragma unroll
+			for (int u = 0; u < NU; u++)
+			{
+				tq[u] = (f[u] + __shfl_down_sync(FULL, f[u], 7, 16)) * myw;
+				if (q == 0) tq[u] = f[u] * myw;
+			}
+#pragma unroll
+			for (int d = 1; d < 8; d <<= 1)
+#pragma unroll
+				for (int u = 0; u < NU; u++) tq[u] += __shfl_xor_sync(FULL, tq[u], d);
+#pragma unroll
+			for (int u = 0; u < NU; u++)
+			{
+				const bool mine = lane == own[2 * u] || lane == own[2 * u + 1];
+				const double result = __shfl_sync(FULL, tq[u], lane == own[2 * u + 1] ? 16 : 0);
+				if (mine)
+				{
+					prel = result * ((end - start) * 0.5);
+					if (end != mid) prel = -prel;
+					if (!isfinite(prel)) prel = (scalefactor + 0.1) * 1.1;
+				}
+			}
+		};
 		while (mask)
 		{
-			const int o0 = __ffs(mask) - 1;
-			mask &= mask - 1;
-			const int o1 = mask ? __ffs(mask) - 1 : -1;
-			if (o1 >= 0) mask &= mask - 1;
-			const int owner = half ? o1 : o0;  // the solve this half-warp serves (-1: none)
-			const int src = owner < 0 ? lane : owner;
-			const MsParams Q = ms_fetch<MODE>(wstage + src);
-			const double a0 = __shfl_sync(FULL, start, src), b0 = __shfl_sync(FULL, end, src);
-			const double avg = (a0 + b0) * 0.5, scale = (b0 - a0) * 0.5;
-			double f = 0;
-			if (owner >= 0 && q < 15) f = ms_actual<MODE>(Q, avg + scale * myx);
-			// (f(+x_q) + f(-x_q)) w_q on lanes q = 0..7 of each half, summed over those 8 lanes, handed to the owner
-			double tq = (f + __shfl_down_sync(FULL, f, 7, 16)) * myw;
-			if (q == 0) tq = f * myw;
-			tq += __shfl_xor_sync(FULL, tq, 1);
-			tq += __shfl_xor_sync(FULL, tq, 2);
-			tq += __shfl_xor_sync(FULL, tq, 4);
-			const bool mine = lane == o0 || lane == o1;
-			const double result = __shfl_sync(FULL, tq, lane == o1 ? 16 : 0);
-			if (mine)
+			int own[4];
+#pragma unroll
+			for (int u = 0; u < 4; u++)
 			{
-				prel = result * ((end - start) * 0.5);
-				if (end != mid) prel = -prel;
-				if (!isfinite(prel)) prel = (scalefactor + 0.1) * 1.1;
+				own[u] = mask ? __ffs(mask) - 1 : -1;
+				mask &= mask - 1;
 			}
+			if (own[2] >= 0) rounds(std::integral_constant<int, 2>(), own);
+			else rounds(std::integral_constant<int, 1>(), own);
 		}
 		if (!done)
 		{
