@@ -113,12 +113,16 @@ def stationary(alleles, sure, infprobs, prioralleles, hasprior):
     ("fullsib", dict(n_fam=2, n_off=3, n_chrom=1, mpc=15, seed=62)),
     ("tangled", dict(n_chrom=2, mpc=17, seed=63)),
     ("f2_cross", dict(n_f2=300, n_chrom=2, mpc=12, seed=64)),  # founders' statistics sum over hundreds of offspring
+    ("f2_cross", dict(n_f2=7, n_chrom=2, mpc=13, seed=65, sf=0.0)),       # scalefactor 0: nothing moves (:4119, :4153)
+    ("tangled", dict(n_chrom=2, mpc=11, seed=66, sf=0.4, ent=0.3)),       # long steps (caps hit), weaker entropy term
 ])
 def test_device_mstep_matches_oracle_on_random_pedigrees(eng, maker, kw):
     """Random parameters (locked phases, zero sureness, priors on some individuals): the oracle's M-step on the
     statistics the engine's E-step produced, pass by pass, against cnf2_mstep."""
     import randomped
     from cases import STATS, engine_problem
+    kw = dict(kw)
+    sf, ent = kw.pop("sf", 0.013), kw.pop("ent", 1.0)
     pb = getattr(randomped, maker)(**kw)
     rng = np.random.default_rng(kw["seed"])
     K, M, C = pb.K, pb.M, pb.C
@@ -134,13 +138,14 @@ def test_device_mstep_matches_oracle_on_random_pedigrees(eng, maker, kw):
         eng.set_params(c, al, su, hw)
     eng.set_mstep_inputs(relhaplo, prioral, priorsure, hasprior, children, pb.empty, pb.descendants)
     eng.begin_iteration()
-    sf, ent = 0.013, 1.0
     active = np.ones(K, np.uint8)
     active[0] = 0
     hb, hc = np.zeros((K, M)), np.zeros((K, M))  # haplobase / haplocount as the reference's vectors hold them
     ral, rsu, rhw = al.copy(), su.copy(), hw.copy()
     tie = np.zeros((K, M), bool)
+    used_sf = []
     for c in range(C):
+        used_sf.append(sf)
         eng.estep(c)
         st = dict(haplobase=np.zeros((K, M)), haplocount=np.zeros((K, M)), infprobs=np.zeros((K, M, 2, 2)), homozyg=np.zeros((K, M, 2)))
         eng.get_stats(c, **st)
@@ -163,4 +168,4 @@ def test_device_mstep_matches_oracle_on_random_pedigrees(eng, maker, kw):
     assert np.array_equal(al[ok], ral[ok])
     assert_close(su[ok], rsu[ok], "markersure", rtol=RTOL, atol=ATOL)
     assert_close(hw[ok], rhw[ok], "haploweight", rtol=RTOL, atol=ATOL)
-    assert not np.array_equal(hw, pb.haploweight)
+    assert (not any(used_sf)) == np.array_equal(hw, pb.haploweight)
