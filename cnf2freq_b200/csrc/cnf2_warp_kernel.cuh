@@ -681,11 +681,13 @@ __global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wa)
 				for (int t = 0; t < n; t++)
 				{
 					const int m = m0 + t;
+					double r0 = 0, r1 = 0;  // asked for ahead of the stores below, used after the emission
+					if (m < E) r0 = a.rec0[m], r1 = a.rec1[m];
 					store_alpha(alpha + (size_t)m * (NUMSHIFTS * NUMTYPES / 2), p, lane);
 					if ((lane & 3) == 0) kexp[(size_t)m * NUMSHIFTS + s] = ka;
 					emit16(p, w.qh + t * QS, lane);
 					rescale16(p, ka);
-					if (m < E) transition16(p, a.rec0[m], a.rec1[m]);
+					if (m < E) transition16(p, r0, r1);
 				}
 			}
 		}
@@ -836,6 +838,8 @@ __global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wa)
 				}
 #endif
 				__syncwarp();
+				double r0 = 0, r1 = 0;  // for the step to marker m - 1, asked for ahead of the transfer
+				if (m > 0) r0 = a.rec0[m - 1], r1 = a.rec1[m - 1];
 #ifndef CNF2_X_NOTRANSFER
 				// transfer into the EM sufficient statistics (:5875-5904, moveinfprobs :3577-3597, movehaplos :3599-3616)
 				transfer_out(w, w.tot, t, m, lane);
@@ -844,7 +848,7 @@ __global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wa)
 				{
 					emit16(b, w.qh + t * QS, lane);
 					rescale16(b, kb);
-					transition16(b, a.rec0[m - 1], a.rec1[m - 1]);
+					transition16(b, r0, r1);
 				}
 				__syncwarp();
 			}
