@@ -754,6 +754,8 @@ __global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wa)
 			__syncwarp();
 			raw_commit(w, raw, lane);
 			for (int i = lane; i < n * QS; i += 32) w.qh[i] = qs[(size_t)m0 * QS + i];
+			// the stash and the alphas of the units in flight are far larger than L2: ask for the next block's lines now
+			if (m0 >= WB && lane * 16 < WB * QS) asm volatile("prefetch.global.L2 [%0];" ::"l"(qs + (size_t)(m0 - WB) * QS + lane * 16));
 			// homozygous with equal sureness (:1235, :3488), per (slot, marker) of the batch
 			const bool homi = (lane / WB) < NSLOTS && u.row[(lane / WB) % NSLOTS] >= 0 && raw.al.x == raw.al.y && raw.su.x == raw.su.y;
 			const unsigned homb = __ballot_sync(FULL, homi);
@@ -790,6 +792,7 @@ __global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wa)
 				{
 					load_alpha(alpha + (size_t)(m - 1) * (NUMSHIFTS * NUMTYPES / 2), an, lane);
 					kan = kexp[(size_t)(m - 1) * NUMSHIFTS + s];
+					if (m > WB) asm volatile("prefetch.global.L2 [%0];" ::"l"(alpha + (size_t)(m - 1 - WB) * (NUMSHIFTS * NUMTYPES / 2) + lane * 8));
 				}
 				const int gp = w.gpmust[t];
 				if (gp != w.listtag) warp_lists(w, u, gp, lane);
