@@ -549,12 +549,13 @@ extern "C" int cnf2_set_pedigree(cnf2_engine* e, int32_t n_ind, const int32_t* p
 			fprintf(stderr, "cnf2: warp kernel %d warps per SM, %zu B shared memory per warp (tables %d + %d entries)\n", per_sm,
 			        warp_smem_bytes(e->cap0, e->cap1, e->cls), e->cap0, e->cap1);
 	}
+	// E-steps still in flight read d_units: they finish before the table is replaced
+	for (Slot& sl : e->slots) CU(cudaStreamSynchronize(sl.stream));
 	CU(e->d_units.ensure(e->units.size()));
 	if (!e->units.empty())
 		CU(cudaMemcpyAsync(e->d_units.p, e->units.data(), e->units.size() * sizeof(Unit), cudaMemcpyHostToDevice, e->stream));
 	for (Slot& sl : e->slots)
 	{
-		CU(cudaStreamSynchronize(sl.stream));
 		CU(sl.loglik.ensure(e->units.size() * 2));
 		CU(sl.counter.ensure(4));
 		CU(sl.literal.ensure(e->units.size()));

@@ -16,7 +16,10 @@
 
 namespace cnf2
 {
-constexpr double MS_MAXDIFF = (double)0.000005f;  // const float maxdiff, :228
+constexpr float MS_MAXDIFF = 0.000005f;  // const float maxdiff, :228
+// `1 - maxdiff` (:4667) and `maxdiff / (children + 1)` (:4242, :4703) are float arithmetic in the reference
+constexpr double MS_ONE_MINUS_MAXDIFF = (double)(1.0f - MS_MAXDIFF);
+__device__ __forceinline__ double ms_epsilon(int children) { return (double)(MS_MAXDIFF / (float)(children + 1)); }
 
 struct MstepRow  // per statistics row
 {
@@ -393,7 +396,7 @@ __global__ void __launch_bounds__(MS_BLOCK) mstep_infprobs_kernel(MstepArgs a)
 	double2 su = a.sure[idx];
 	const uchar2 pal = r.hasprior ? a.prioralleles[idx] : make_uchar2(0, 0);
 	const double2 psu = r.hasprior ? a.priorsure[idx] : make_double2(0, 0);
-	const double epsilon = MS_MAXDIFF / (r.children + 1), etf = 1 * a.entropyfactor;
+	const double epsilon = ms_epsilon(r.children), etf = 1 * a.entropyfactor;
 	unsigned long long hit = 0;
 #pragma unroll 1
 	for (int side = 0; side < 2; side++)
@@ -607,7 +610,7 @@ __global__ void __launch_bounds__(MS_BLOCK, 6) mstep_haploweight_kernel(MstepArg
 		}
 		else
 		{
-			if (similarity >= 1 - MS_MAXDIFF) similarity = 1 - MS_MAXDIFF;
+			if (similarity >= MS_ONE_MINUS_MAXDIFF) similarity = MS_ONE_MINUS_MAXDIFF;
 			double count = hc;
 			hb -= count * w;
 			count = count - similarity * count;
@@ -618,7 +621,7 @@ __global__ void __launch_bounds__(MS_BLOCK, 6) mstep_haploweight_kernel(MstepArg
 		}
 	}
 	const MsParams P = ms_params(w, hb, hc, (1 - similarity) * 1, a.entropyfactor, active ? a.ratio[idx] : 0.0, (double)r.descendants,
-	                             MS_MAXDIFF / (r.children + 1));
+	                             ms_epsilon(r.children));
 	unsigned long long hit = 0;
 	const double res = ms_cappedgd_warp<1>(P, w, a.scalefactor, active, hit, &stage[0][0]);
 	if (active)

@@ -60,6 +60,17 @@ def _ptr(a):
     return None if a is None else a.ctypes.data_as(ctypes.c_void_p)
 
 
+def _buf(a, dtype, size, what):
+    """A caller-owned array the library reads or fills through a raw pointer: dtype, C-contiguity and element count are
+    checked here, because the C side cannot."""
+    if a is None:
+        return None
+    if not isinstance(a, np.ndarray) or a.dtype != dtype or not a.flags.c_contiguous or a.size != size:
+        raise EngineError(f"{what}: needs a C-contiguous numpy array of {np.dtype(dtype).name} with {size} elements, got "
+                          f"{type(a).__name__}" + (f" {a.dtype} size {a.size} contiguous={a.flags.c_contiguous}" if isinstance(a, np.ndarray) else ""))
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
 class Engine:
     """One engine = one GPU (one rank).  Method names follow the C ABI."""
 
@@ -143,38 +154,56 @@ class Engine:
     def set_params_packed(self, chrom, alleles, sure, haploweight):
         """Row-ordered (row_ids()) arrays of this chromosome only: alleles u8 [n_rows][Mc][2], sure f64 [n_rows][Mc][2],
         haploweight f64 [n_rows][Mc]."""
-        for a, dt in ((alleles, np.uint8), (sure, np.float64), (haploweight, np.float64)):
-            if a.dtype != dt or not a.flags.c_contiguous:
-                raise EngineError("set_params_packed: arrays must be C-contiguous of the documented dtype")
-        self._check(self.lib.cnf2_set_params_packed(self.h, ctypes.c_int32(chrom), _ptr(alleles), _ptr(sure), _ptr(haploweight)))
+        n = self.n_rows() * self.mc(chrom)
+        self._check(self.lib.cnf2_set_params_packed(self.h, ctypes.c_int32(chrom), _buf(alleles, np.uint8, 2 * n, "set_params_packed alleles"),
+                                                    _buf(sure, np.float64, 2 * n, "set_params_packed sure"),
+                                                    _buf(haploweight, np.float64, n, "set_params_packed haploweight")))
 
     def estep(self, chrom):
         self._check(self.lib.cnf2_estep(self.h, ctypes.c_int32(chrom)))
 
+    def mc(self, chrom):
+        return int(self.chromstarts[chrom + 1]) - int(self.chromstarts[chrom])
+
+    def n_rows(self):
+        n = ctypes.c_int32()
+        self._check(self.lib.cnf2_row_count(self.h, ctypes.byref(n)))
+        return int(n.value)
+
     def get_stats(self, chrom, haplobase=None, haplocount=None, infprobs=None, homozyg=None, loglik=None):
-        self._check(self.lib.cnf2_get_stats(self.h, ctypes.c_int32(chrom), _ptr(haplobase), _ptr(haplocount),
-                                            _ptr(infprobs), _ptr(homozyg), _ptr(loglik)))
+        km = self.n_ind * self.n_markers
+        self._check(self.lib.cnf2_get_stats(self.h, ctypes.c_int32(chrom), _buf(haplobase, np.float64, km, "get_stats haplobase"),
+                                            _buf(haplocount, np.float64, km, "get_stats haplocount"),
+                                            _buf(infprobs, np.float64, 4 * km, "get_stats infprobs"),
+                                            _buf(homozyg, np.float64, 2 * km, "get_stats homozyg"),
+                                            _buf(loglik, np.float64, 2 * self.n_dous * self.n_chrom, "get_stats loglik")))
 
     def row_ids(self):
         """Individual id of every statistics row of this engine (shared rows first)."""
-        n = ctypes.c_int32()
-        self._check(self.lib.cnf2_row_count(self.h, ctypes.byref(n)))
-        ids = np.zeros(n.value, np.int32)
-        if n.value:
+        n = self.n_rows()
+        ids = np.zeros(n, np.int32)
+        if n:
             self._check(self.lib.cnf2_row_ids(self.h, _ptr(ids)))
         return ids
 
     def get_stats_packed(self, chrom, haplobase=None, haplocount=None, infprobs=None, homozyg=None, loglik=None):
         """Row-ordered contiguous blocks ([n_rows][Mc]...; see include/cnf2_engine.h): unstrided device -> host copies."""
-        self._check(self.lib.cnf2_get_stats_packed(self.h, ctypes.c_int32(chrom), _ptr(haplobase), _ptr(haplocount),
-                                                   _ptr(infprobs), _ptr(homozyg), _ptr(loglik)))
+        n = self.n_rows() * self.mc(chrom)
+        self._check(self.lib.cnf2_get_stats_packed(self.h, ctypes.c_int32(chrom), _buf(haplobase, np.float64, n, "get_stats_packed haplobase"),
+                                                   _buf(haplocount, np.float64, n, "get_stats_packed haplocount"),
+                                                   _buf(infprobs, np.float64, 4 * n, "get_stats_packed infprobs"),
+                                                   _buf(homozyg, np.float64, 2 * n, "get_stats_packed homozyg"),
+                                                   _buf(loglik, np.float64, 2 * self.n_dous, "get_stats_packed loglik")))
 
     # -- M-step on the device (rows a6 / f1) ---------------------------------------------------------
     def set_mstep_inputs(self, relhaplo, prioralleles, priorsure, hasprior, children, empty, descendants):
         c = np.ascontiguousarray
+        km, k = self.n_ind * self.n_markers, self.n_ind
         self._check(self.lib.cnf2_set_mstep_inputs(
-            self.h, _ptr(c(relhaplo, np.float64)), _ptr(c(prioralleles, np.uint8)), _ptr(c(priorsure, np.float64)),
-            _ptr(c(hasprior, np.uint8)), _ptr(c(children, np.int32)), _ptr(c(empty, np.uint8)), _ptr(c(descendants, np.int32))))
+            self.h, _buf(c(relhaplo, np.float64), np.float64, km, "relhaplo"), _buf(c(prioralleles, np.uint8), np.uint8, 2 * km, "prioralleles"),
+            _buf(c(priorsure, np.float64), np.float64, 2 * km, "priorsure"), _buf(c(hasprior, np.uint8), np.uint8, k, "hasprior"),
+            _buf(c(children, np.int32), np.int32, k, "children"), _buf(c(empty, np.uint8), np.uint8, k, "empty"),
+            _buf(c(descendants, np.int32), np.int32, k, "descendants")))
 
     def begin_iteration(self):
         self._check(self.lib.cnf2_begin_iteration(self.h))
@@ -188,7 +217,10 @@ class Engine:
         return (int(hit.value), int(sh.value)) if split else int(hit.value)
 
     def get_params(self, chrom, alleles, sure, haploweight):
-        self._check(self.lib.cnf2_get_params(self.h, ctypes.c_int32(chrom), _ptr(alleles), _ptr(sure), _ptr(haploweight)))
+        km = self.n_ind * self.n_markers
+        self._check(self.lib.cnf2_get_params(self.h, ctypes.c_int32(chrom), _buf(alleles, np.uint8, 2 * km, "get_params alleles"),
+                                             _buf(sure, np.float64, 2 * km, "get_params sure"),
+                                             _buf(haploweight, np.float64, km, "get_params haploweight")))
 
     def sync(self):
         self._check(self.lib.cnf2_sync(self.h))

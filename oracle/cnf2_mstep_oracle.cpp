@@ -21,7 +21,7 @@
 
 namespace
 {
-const double MAXDIFF = (double)0.000005f;  // const float maxdiff, cnF2freq.cpp:228
+const float MAXDIFF = 0.000005f;  // const float maxdiff, cnF2freq.cpp:228: `1 - maxdiff` and `maxdiff / int` are FLOAT arithmetic in the reference
 
 struct Ctl
 {
@@ -227,7 +227,7 @@ void processinfprobs(Ind& d, int j, int side, double entropyfactor, Ctl& ctl)
 		if (curmarker != 0) curprob = std::fabs((curmarker == allele ? 1 : 0) - d.sure[j * 2 + side]);
 		const double hzygcorred = ip[a];
 		const double etf = 1 * ef;
-		const double epsilon = MAXDIFF / (d.children + 1);
+		const double epsilon = MAXDIFF / (d.children + 1);  // float division, :4242
 		double priord = 0, priorprob = 0.5;
 		if (priorval != 0)
 		{

@@ -21,6 +21,7 @@
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <vector>
@@ -579,7 +580,11 @@ void estep_individual(Problem& P, int jidx, int root, int chrom, const Outputs& 
 					for (auto& kv : ip->second[side])
 					{
 						if (kv.first >= 1 && kv.first <= 2)
-							out.infprobs[(((size_t)rel * M + marker) * 2 + side) * 2 + kv.first - 1] += kv.second * norm;
+						{
+							const double add = kv.second * norm;
+#pragma omp atomic update
+							out.infprobs[(((size_t)rel * M + marker) * 2 + side) * 2 + kv.first - 1] += add;
+						}
 					}
 					ip->second[side].clear();
 				}
@@ -593,7 +598,10 @@ void estep_individual(Problem& P, int jidx, int root, int chrom, const Outputs& 
 					const float maxdiff = 0.000005;  // :228
 					double b1 = hp->second[0] + exp(-400) * maxdiff * maxdiff * 0.5;
 					double b2 = hp->second[1] + exp(-400) * maxdiff * maxdiff * 0.5;
-					out.haplobase[(size_t)rel * M + marker] += b1 / (b1 + b2) * desc;
+					const double add = b1 / (b1 + b2) * desc;
+#pragma omp atomic update
+					out.haplobase[(size_t)rel * M + marker] += add;
+#pragma omp atomic update
 					out.haplocount[(size_t)rel * M + marker] += desc;
 				}
 				hp->second[0] = 0;
@@ -635,8 +643,14 @@ int cnf2_oracle_estep(int K, int M, int C, int n_dous, const int32_t* par, const
 	P.sure = sure;
 	P.haploweight = haploweight;
 	Outputs out{ haplobase, haplocount, infprobs, homozyg, loglik, counters };
+	// CNF2_ORACLE_THREADS > 1 (opt-in, for sampled checks at full size): units run in parallel; rows shared between units
+	// are then summed in a nondeterministic order (atomic adds), rows only one unit adds to are unaffected.  The sticky
+	// founder flags must already be steady (cnf2_oracle_steady_founder) in that mode.
+	int nthreads = 1;
+	if (const char* t = getenv("CNF2_ORACLE_THREADS")) nthreads = std::max(1, atoi(t));
 	for (int c = 0; c < C; c++)
 	{
+#pragma omp parallel for schedule(dynamic, 1) num_threads(nthreads) if (nthreads > 1)
 		for (int j = 0; j < n_dous; j++)
 		{
 			Sweeps keep;

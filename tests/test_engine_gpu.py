@@ -1,6 +1,8 @@
 """Parity of the CUDA engine (through the C ABI) with the reference: against the golden fixtures the
 reference binary wrote, and against the CPU oracle on seeded inputs.  Tolerance: 1e-9 relative (fp64),
 as BASELINE.json's north_star states."""
+import os
+
 import numpy as np
 import pytest
 
@@ -152,6 +154,33 @@ def test_full_size_chromosome_properties(eng):
             acc[k] += part[k]
     for k in STATS:
         assert_close(acc[k], whole[k], f"linearity:{k}", rtol=1e-9, atol=1e-12)
+
+
+@pytest.mark.parametrize("maker,kw,n_sample,own", [
+    # BASELINE.json configs[2] at full size for one chromosome; an F2's own row and its two implicit F1 parents' rows
+    # receive contributions from its own unit only (cnF2freq.cpp:5283-5295, :5893-5902)
+    ("f2_flat", dict(n_f2=2000, n_chrom=1, markers_per_chrom=1000, spacing_cM=0.1, missing=0.2, seed=3), 16, 3),
+    # configs[3]'s pedigree shape at the size bench.py --workload fullsib runs per chromosome
+    ("fullsib_flat", dict(n_fam=66, n_off=20, n_chrom=1, markers_per_chrom=400, spacing_cM=0.02, missing=0.05, seed=4), 16, 1),
+])
+def test_full_size_sampled_parity(eng, monkeypatch, maker, kw, n_sample, own):
+    """Full-size E-step on the GPU; the oracle on the pedigree reduced to a seeded sample of the analysed individuals.
+    The log-likelihood pair and the statistics rows only the sampled unit adds to must agree to 1e-9."""
+    from cnf2freq_b200 import synth
+    d = getattr(synth, maker)(**kw)
+    pb = ol.Problem(d["par"], d["empty"], d["founder"], d["gen"], d["descendants"], d["dous"], d["markerpos"],
+                    d["chromstarts"], d["genrec"], d["alleles"], d["sure"], d["haploweight"])
+    whole = run_engine(eng, pb, shared=d["shared"])
+    rng = np.random.default_rng(1234)
+    pick = np.sort(rng.choice(len(pb.dous), n_sample, replace=False))
+    sub = ol.Problem(d["par"], d["empty"], d["founder"], d["gen"], d["descendants"], pb.dous[pick], d["markerpos"],
+                     d["chromstarts"], d["genrec"], d["alleles"], d["sure"], d["haploweight"])
+    monkeypatch.setenv("CNF2_ORACLE_THREADS", str(os.cpu_count() or 1))  # units in parallel; own rows are unaffected by the order
+    ref = ol.oracle_estep(sub)
+    assert_close(whole["loglik"][pick], ref["loglik"], f"{maker}: sampled loglik", rtol=RTOL, atol=1e-9)
+    rows = np.concatenate([pb.dous[pick] + k for k in range(own)])  # f2_flat ids: the F2, its F1 father, its F1 mother
+    for k in STATS:
+        assert_close(whole[k][rows], ref[k][rows], f"{maker}: sampled own rows {k}", rtol=RTOL, atol=ATOL)
 
 
 def test_no_analysed_individuals(eng):

@@ -151,7 +151,7 @@ def test_two_gpus_em_pass_equals_the_unsharded_mstep(tmp_path, maker, kw):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     import torch.multiprocessing as mp
-    from test_mstep_gpu import ATOL, stationary
+    from test_mstep_gpu import ATOL, MAX_MASKED, stationary
     from test_mstep_gpu import RTOL as MRTOL
     world = 2
     mp.spawn(_em_worker, args=(world, _free_port(), maker, kw, str(tmp_path)), nprocs=world, join=True)
@@ -188,7 +188,8 @@ def test_two_gpus_em_pass_equals_the_unsharded_mstep(tmp_path, maker, kw):
         for k in merged:
             merged[k][rows] = p[k][rows]
     ok = ~tie
-    assert ok.sum() > 0.5 * ok.size
+    print(f"masked as exact ties: {int(tie.sum())} of {tie.size} cells ({tie.mean():.4%})")
+    assert tie.mean() < MAX_MASKED, f"{tie.mean():.3%} of the cells masked as ties"
     assert np.array_equal(merged["alleles"][ok], ral[ok])
     assert_close(merged["sure"][ok], rsu[ok], "markersure", rtol=MRTOL, atol=ATOL)
     assert_close(merged["haploweight"][ok], rhw[ok], "haploweight", rtol=MRTOL, atol=ATOL)

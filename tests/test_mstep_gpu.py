@@ -104,8 +104,12 @@ def stationary(alleles, sure, infprobs, prioralleles, hasprior):
         for k in range(2):
             cur = np.where(alleles[:, :, side] != 0, np.abs((alleles[:, :, side] == k + 1).astype(float) - sure[:, :, side]), 0.5)
             noprior = (prioralleles[:, :, side] == 0) | (hasprior[:, None] == 0)
-            tie |= (ip[:, :, k] != 0) & noprior & (np.abs(ip[:, :, k] - tot * cur) <= 1e-6 * tot)
+            tie |= (ip[:, :, k] != 0) & noprior & (np.abs(ip[:, :, k] - tot * cur) <= TIE_REL * tot)
     return tie
+
+
+TIE_REL = 1e-12    # the tie itself up to the E-step's own rounding; not a neighbourhood of it
+MAX_MASKED = 0.05  # at most this fraction of the cells may be left out as ties
 
 
 @pytest.mark.parametrize("maker,kw", [
@@ -115,6 +119,10 @@ def stationary(alleles, sure, infprobs, prioralleles, hasprior):
     ("f2_cross", dict(n_f2=300, n_chrom=2, mpc=12, seed=64)),  # founders' statistics sum over hundreds of offspring
     ("f2_cross", dict(n_f2=7, n_chrom=2, mpc=13, seed=65, sf=0.0)),       # scalefactor 0: nothing moves (:4119, :4153)
     ("tangled", dict(n_chrom=2, mpc=11, seed=66, sf=0.4, ent=0.3)),       # long steps (caps hit), weaker entropy term
+    # markersure in (0, 1e-5) and children + 1 not a power of two: the float arithmetic of `1 - maxdiff` (:4667) and
+    # `maxdiff / (children + 1)` (:4242, :4703) shows in these cells
+    ("f2_cross", dict(n_f2=11, n_chrom=2, mpc=15, seed=67, tiny=True)),
+    ("fullsib", dict(n_fam=2, n_off=4, n_chrom=1, mpc=19, seed=68, tiny=True)),
 ])
 def test_device_mstep_matches_oracle_on_random_pedigrees(eng, maker, kw):
     """Random parameters (locked phases, zero sureness, priors on some individuals): the oracle's M-step on the
@@ -122,16 +130,19 @@ def test_device_mstep_matches_oracle_on_random_pedigrees(eng, maker, kw):
     import randomped
     from cases import STATS, engine_problem
     kw = dict(kw)
-    sf, ent = kw.pop("sf", 0.013), kw.pop("ent", 1.0)
+    sf, ent, tiny = kw.pop("sf", 0.013), kw.pop("ent", 1.0), kw.pop("tiny", False)
     pb = getattr(randomped, maker)(**kw)
     rng = np.random.default_rng(kw["seed"])
     K, M, C = pb.K, pb.M, pb.C
+    if tiny:
+        sel = (rng.random((K, M, 2)) < 0.3) & (pb.alleles != 0)
+        pb.sure[sel] = rng.uniform(0.0, 1e-5, (K, M, 2))[sel]
     relhaplo = rng.uniform(0.6, 1.0, (K, M))
     hasprior = (rng.random(K) < 0.7).astype(np.uint8)
     prioral = pb.alleles.copy()
     prioral[rng.random((K, M)) < 0.2] = 0
     priorsure = np.where(rng.random((K, M, 2)) < 0.1, 0.0, rng.uniform(0.0, 0.3, (K, M, 2)))
-    children = rng.integers(0, 4, K).astype(np.int32)
+    children = (rng.choice([2, 4, 5], K) if tiny else rng.integers(0, 4, K)).astype(np.int32)
     engine_problem(eng, pb, shared=np.zeros(0, np.int32))
     al, su, hw = pb.alleles.copy(), pb.sure.copy(), pb.haploweight.copy()
     for c in range(C):
@@ -164,7 +175,8 @@ def test_device_mstep_matches_oracle_on_random_pedigrees(eng, maker, kw):
     for c in range(C):
         eng.get_params(c, al, su, hw)
     ok = ~tie
-    assert ok.sum() > 0.5 * ok.size
+    print(f"masked as exact ties: {int(tie.sum())} of {tie.size} cells ({tie.mean():.4%})")
+    assert tie.mean() < MAX_MASKED, f"{tie.mean():.3%} of the cells masked as ties"
     assert np.array_equal(al[ok], ral[ok])
     assert_close(su[ok], rsu[ok], "markersure", rtol=RTOL, atol=ATOL)
     assert_close(hw[ok], rhw[ok], "haploweight", rtol=RTOL, atol=ATOL)
