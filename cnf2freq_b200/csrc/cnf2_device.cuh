@@ -26,7 +26,7 @@ constexpr int SEXMARKER = 9;  // cnF2freq.cpp:226
 //   [14,42)  infprobs[slot][realf2n][allele-1]
 //   [42,44)  homozyg[allele-1]
 constexpr int ACC_HAPLOS = 0, ACC_INF = 14, ACC_HZ = 42, NACC = 44;
-constexpr int STATS_PER_CELL = 8;  // haplobase, haplocount, infprobs[2][2], homozyg[2]
+constexpr int STATS_PER_CELL = 9;  // haplobase, haplocount, infprobs[2][2], homozyg[2], negshift
 
 // One analysed individual = one focus tree (what fixtrees leaves in reltree / reltreeordered / relmap /
 // relmapshift, cnF2freq.cpp:3099-3187), built on the host by cnf2_set_pedigree.
@@ -57,6 +57,10 @@ struct Unit
 	// parents' subtrees that some surviving (x, g) pair uses (bit cfg of cfgmask[p])
 	uint32_t xmask2[4];
 	unsigned long long cfgmask[2];
+	// turn scoring (updatenegshifts, cnF2freq.cpp:3640-3715): weight of the slot's negshift contribution -- 1 for the
+	// root and the two parents (:3665-3671), 1 / children of the parent for its parents and only when gen >= 2
+	// (:3673-3686), 0 when the pointer chain to the slot is broken
+	double nsscale[NSLOTS];
 };
 
 // Shared-memory view handed to the emission routine.

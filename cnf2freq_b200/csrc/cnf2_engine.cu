@@ -410,6 +410,12 @@ extern "C" int cnf2_set_pedigree(cnf2_engine* e, int32_t n_ind, const int32_t* p
 		else e->runs.push_back(Run{ r, e->rowid[r], 1 });
 	}
 
+	// individ::children as doit rebuilds it from the analysed individuals of the whole run (:5246-5259)
+	std::vector<int32_t> nchildren(n_ind, 0);
+	for (int j = 0; j < n_all_dous; j++)
+		for (int lev1 = 0; lev1 < 2; lev1++)
+			if (const int p = parents[all_dous[j] * 2 + lev1]) nchildren[p]++;
+
 	// focus trees (fixtrees, :3099-3187)
 	e->units.assign(n_dous, Unit{});
 	for (int j = 0; j < n_dous; j++)
@@ -458,6 +464,18 @@ extern "C" int cnf2_set_pedigree(cnf2_engine* e, int32_t n_ind, const int32_t* p
 		u.shiftend = (uint8_t)(gen[ind] < 2 ? 2 : NUMSHIFTS);  // :5359
 		u.out = j;
 		u.descendants = (double)descendants[ind];
+		// updatenegshifts (:3662-3687): who receives a phase-inversion score from this unit, and its weight
+		for (int k = 0; k < NSLOTS; k++) u.nsscale[k] = 0;
+		u.nsscale[0] = 1;
+		for (int lev1 = 0; lev1 < 2; lev1++)
+		{
+			const int sp = 1 + lev1 * 3;
+			if (!ids[sp]) continue;
+			u.nsscale[sp] = 1;
+			if (gen[ind] < 2) continue;
+			for (int lev2 = 0; lev2 < 2; lev2++)
+				if (ids[sp + 1 + lev2]) u.nsscale[sp + 1 + lev2] = 1.0 / nchildren[ids[sp]];
+		}
 		{
 			const int ign = u.flag2ignore;
 			u.gfixmask = (uint8_t)((ign >> 1) & (NUMTYPES - 1));
@@ -966,6 +984,53 @@ extern "C" int cnf2_get_stats_packed(cnf2_engine* e, int32_t chrom, double* hapl
 	}
 	if (loglik && !e->units.empty())
 		CU(cudaMemcpyAsync(loglik, sl.loglik.p, e->units.size() * 2 * sizeof(double), cudaMemcpyDeviceToHost, sl.stream));
+	CU(cudaStreamSynchronize(sl.stream));
+	CU(cudaGetLastError());
+	return CNF2_OK;
+}
+
+static Slot* slot_of(cnf2_engine* e, int32_t chrom)
+{
+	for (Slot& o : e->slots)
+		if (chrom >= 0 && o.chrom == chrom) return &o;
+	return nullptr;
+}
+
+extern "C" int cnf2_get_negshift(cnf2_engine* e, int32_t chrom, double* negshift)
+{
+	if (!e || !negshift) return CNF2_ERR_BAD_ARG;
+	Slot* slp = slot_of(e, chrom);
+	if (!slp) return e->fail(CNF2_ERR_STATE, "cnf2_get_negshift: cnf2_estep for this chromosome first (only the E-steps in flight are kept)");
+	Slot& sl = *slp;
+	cudaSetDevice(e->settings.device);
+	const size_t M = e->markerpos.size(), c0 = e->chromstarts[chrom], Mc = e->mc(chrom);
+	for (const Run& r : e->runs)
+	{
+		const bool sh = r.row0 < e->n_shared;
+		const StatsCell src = sh ? stats_cell(sl.stats_shared(), e->n_shared, Mc, r.row0, 0)
+		                         : stats_cell(sl.stats_local((int)Mc), e->n_rows - e->n_shared, Mc, r.row0 - e->n_shared, 0);
+		CU(cudaMemcpy2DAsync(negshift + (size_t)r.id0 * M + c0, M * 8, src.negshift, Mc * 8, Mc * 8, r.n, cudaMemcpyDeviceToHost, sl.stream));
+	}
+	CU(cudaStreamSynchronize(sl.stream));
+	CU(cudaGetLastError());
+	return CNF2_OK;
+}
+
+extern "C" int cnf2_get_negshift_packed(cnf2_engine* e, int32_t chrom, double* negshift)
+{
+	if (!e || !negshift) return CNF2_ERR_BAD_ARG;
+	Slot* slp = slot_of(e, chrom);
+	if (!slp) return e->fail(CNF2_ERR_STATE, "cnf2_get_negshift_packed: cnf2_estep for this chromosome first (only the E-steps in flight are kept)");
+	Slot& sl = *slp;
+	cudaSetDevice(e->settings.device);
+	const size_t Mc = e->mc(chrom);
+	for (int blk = 0; blk < 2; blk++)
+	{
+		const size_t nr = blk ? (size_t)(e->n_rows - e->n_shared) : (size_t)e->n_shared, row0 = blk ? (size_t)e->n_shared : 0;
+		if (!nr) continue;
+		const double* base = blk ? sl.stats_local((int)Mc) : sl.stats_shared();
+		CU(cudaMemcpyAsync(negshift + row0 * Mc, base + 8 * nr * Mc, nr * Mc * 8, cudaMemcpyDeviceToHost, sl.stream));
+	}
 	CU(cudaStreamSynchronize(sl.stream));
 	CU(cudaGetLastError());
 	return CNF2_OK;

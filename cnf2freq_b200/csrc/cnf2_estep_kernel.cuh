@@ -32,15 +32,15 @@ struct EstepArgs
 
 // Statistics of nr rows x Mc markers, one array per statistic so that each can be copied straight into
 // the caller's per-individual vectors: haplobase [nr][Mc], haplocount [nr][Mc], infprobs [nr][Mc][2][2],
-// homozyg [nr][Mc][2]  (8 doubles per cell in total).
+// homozyg [nr][Mc][2], negshift [nr][Mc]  (9 doubles per cell in total).
 struct StatsCell
 {
-	double *haplobase, *haplocount, *infprobs, *homozyg;
+	double *haplobase, *haplocount, *infprobs, *homozyg, *negshift;
 };
 __host__ __device__ __forceinline__ StatsCell stats_cell(double* base, size_t nr, size_t Mc, size_t idx, size_t m)
 {
 	const size_t cell = idx * Mc + m, plane = nr * Mc;
-	return StatsCell{ base + cell, base + plane + cell, base + 2 * plane + cell * 4, base + 6 * plane + cell * 2 };
+	return StatsCell{ base + cell, base + plane + cell, base + 2 * plane + cell * 4, base + 6 * plane + cell * 2, base + 8 * plane + cell };
 }
 
 struct __align__(16) Smem
@@ -51,6 +51,9 @@ struct __align__(16) Smem
 	double tot[NACC];
 	double Ls[NUMSHIFTS];
 	double beta[NUMSHIFTS * NUMTYPES];
+	double aplus[NUMSHIFTS * NUMTYPES];     // turn scoring: alpha after the emission at the current marker
+	double Bs[NUMSHIFTS], Fp[NUMSHIFTS];    // log-factors of beta / alpha+
+	double raw[8 * NUMSHIFTS];              // rawvals[turn][shift], -1 = not scored (:5678-5681)
 	unsigned short queue[NUMSHIFTS * 64];
 	uchar2 A[NSLOTS * TILE];
 	Unit unit;
@@ -339,6 +342,76 @@ __global__ void __launch_bounds__(NTHREADS, 1) estep_kernel(EstepArgs a)
 			for (int t = tend - 1; t >= 0; t--)
 			{
 				const int m = tile * TILE + t;
+				const double* src = alpha + ((size_t)m * NUMSHIFTS + shift) * NUMTYPES;
+				const double Fm = alphafac[(size_t)m * NUMSHIFTS + shift];
+				// beta of this shift mode, readable by every lane of the warp (and, for the turns, by the other warps)
+				sm.beta[shift * NUMTYPES + lane] = b0;
+				sm.beta[shift * NUMTYPES + lane + 32] = b1;
+				// ---- turn scoring (cnF2freq.cpp:5668-5757, DOTOULBAR 0) and updatenegshifts (:3640-3715) ----
+				{
+					double a0 = 0, a1 = 0, Fp = 0;
+					if (active)
+					{
+						a0 = src[lane], a1 = src[lane + 32], Fp = Fm;
+						emit_step(c, t, lane, shift, a0, a1, Fp);  // alpha+ and its factor: pad 2 of fwbw (:2248-2251)
+					}
+					sm.aplus[shift * NUMTYPES + lane] = a0;
+					sm.aplus[shift * NUMTYPES + lane + 32] = a1;
+					if (lane == 0) sm.Bs[shift] = B, sm.Fp[shift] = Fp;
+					__syncthreads();
+					const float minfturn = (float)(-50000.0 + factor);
+					for (int tn = 0; tn < 8; tn++)
+					{
+						const int g = tn == 0 ? 0 : tn == 7 ? 64 : 1 << (tn - 1);  // turn of slot tn (7: the root)
+						double rv = -1;
+						if (active && !(g & (u.flag2ignore >> 1)))
+						{
+							const int mask = g & 54, fms = (g >> 6) | ((g & 1) ? 2 : 0) | ((g & 8) ? 4 : 0);  // aroundturner, :506-508
+							const int s2 = shift ^ fms;
+							double fac = sm.Fp[shift];
+							if (!(fac < minfturn))
+							{
+								const double sum = warp_sum(sm.aplus[shift * NUMTYPES + (lane ^ mask)] * sm.beta[s2 * NUMTYPES + lane] +
+								                            sm.aplus[shift * NUMTYPES + ((lane + 32) ^ mask)] * sm.beta[s2 * NUMTYPES + lane + 32]);
+								fac += sm.Bs[s2];
+								if (sum <= 0) fac = MINFACTOR_D;
+								else fac -= log(1.0 / sum);
+							}
+							rv = exp(fac - factor);
+							if (!isfinite(rv)) rv = rv > 1e300 ? 1e300 : 0;
+						}
+						if (lane == 0) sm.raw[tn * NUMSHIFTS + shift] = rv;
+					}
+					__syncthreads();
+					if (tid < NSLOTS && u.row[tid] >= 0 && u.nsscale[tid] != 0)
+					{
+						const int slot = tid, tn = slot == 0 ? 7 : slot;
+						double l[2];
+						bool valid[2];
+						for (int q = 0; q < 2; q++)
+						{
+							const int tq = q ? tn : 0;
+							double val = 0;
+							valid[q] = false;
+							for (int s = 0; s < NUMSHIFTS; s++)
+							{
+								const double r = sm.raw[tq * NUMSHIFTS + s];
+								if (r < 0) continue;
+								val += r;
+								valid[q] = true;
+							}
+							if (!isfinite(val) || val < 1e-174) val = 1e-174;
+							l[q] = log(val);
+						}
+						const int srow = u.relrow[u.slotrel[slot]];
+						const StatsCell cell = srow < a.n_shared ? stats_cell(a.stats_shared, a.n_shared, Mc, srow, m)
+						                                         : stats_cell(a.stats_local, a.n_local, Mc, srow - a.n_shared, m);
+						double add = 0;
+						if (valid[0]) add += l[0] * u.nsscale[slot];
+						if (valid[1]) add -= l[1] * u.nsscale[slot];
+						atomicAdd(cell.negshift, add);
+					}
+				}
 				if (contributing)
 				{
 					int hom = 0;
@@ -351,12 +424,6 @@ __global__ void __launch_bounds__(NTHREADS, 1) estep_kernel(EstepArgs a)
 						const double2 su = sm.S[slot * TILE + t];
 						if (al.x == al.y && su.x == su.y) hom |= 1 << i;
 					}
-					const double* src = alpha + ((size_t)m * NUMSHIFTS + shift) * NUMTYPES;
-					const double Fm = alphafac[(size_t)m * NUMSHIFTS + shift];
-					// beta of this shift mode, readable by every lane of the warp
-					sm.beta[shift * NUMTYPES + lane] = b0;
-					sm.beta[shift * NUMTYPES + lane + 32] = b1;
-					__syncwarp();
 					// The surviving (g, flag2) pairs are sparse and differ from lane to lane, so they are first
 					// compacted into a per-warp queue (ballot + prefix count) and then handed out one per lane.
 					unsigned short* q = sm.queue + shift * 64;
@@ -410,7 +477,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) estep_kernel(EstepArgs a)
 				// transfer into the EM sufficient statistics (:5875-5904, moveinfprobs :3577-3597, movehaplos :3599-3616)
 				if (tid < u.nrel) transfer_stats(a, u, sm.tot, sm.HW, tid, t, m);
 				// beta for the previous marker: adjustprobs at m, then the transition (:2390-2396)
-				if (active && m > 0)
+				if (m > 0)  // every shift mode: a turn pairs alpha+ of one mode with beta of another (initfwbw(..., 2), :1988)
 				{
 					emit_step(c, t, lane, shift, b0, b1, B);
 					transition(b0, b1, a.rec0[m - 1], a.rec1[m - 1]);

@@ -31,6 +31,37 @@ __device__ __forceinline__ double frcp(double x)
 	r = fma(fma(-x, r, 1.0), r, r);
 	return r;
 }
+// log(y) for an ordinary positive y (no zero, subnormal, inf or NaN: the solver only takes logs of (1 - x) / x with x in
+// [eps, 1 - eps]).  The usual reduction y = 2^e m, m in [sqrt(1/2), sqrt(2)), log m = 2 atanh((m - 1) / (m + 1)) as an
+// odd series in u = 2 (m - 1) / (m + 1) with the division's residual added back; <= 1.2 ulp (checked against long
+// double over 2^-23..2^23 and around 1).  The library log costs three times the instructions in this loop: its
+// coefficients are 64-bit immediates (two moves each on sm_100) and it carries the special-case branches.  The series
+// coefficients 1 / ((2k + 1) 4^k) sit in constant memory and are read as instruction operands.
+__constant__ double MS_LC[10] = { 1.0 / 12,     1.0 / 80,     1.0 / 448,     1.0 / 2304,    1.0 / 11264,
+	                              1.0 / 53248,  1.0 / 245760, 1.0 / 1114112, 1.0 / 4980736, 1.0 / 22020096 };
+__constant__ double MS_LN2[2] = { 6.93147180369123816490e-01, 1.90821492927058770002e-10 };  // hi (21 trailing zero bits), lo
+__device__ __forceinline__ double ms_log(double y)
+{
+	int hi = __double2hiint(y);
+	const int lo = __double2loint(y);
+	int e = (hi >> 20) - 1023;
+	hi = (hi & 0x000fffff) | 0x3ff00000;
+	if (hi >= 0x3ff6a09f) hi -= 0x00100000, e += 1;
+	const double m = __hiloint2double(hi, lo);
+	const double a = m - 1.0, r = frcp(m + 1.0);
+	const double h = a * r, u = h + h;
+	double res = a - u;
+	res += res;
+	res = fma(a, -u, res);  // 2 a - u (2 + a): what the rounded quotient leaves
+	const double c = r * res;
+	const double sq = u * u;
+	double p = MS_LC[9];
+#pragma unroll
+	for (int k = 8; k >= 0; k--) p = fma(p, sq, MS_LC[k]);
+	const double t = fma(u * sq, p, c);
+	const double ed = __hiloint2double(0x43300000, e ^ 0x80000000) - 4503601774854144.0;  // (double)e
+	return fma(ed, MS_LN2[0], u) + fma(ed, MS_LN2[1], t);
+}
 // NodeTab (cnf2_device.cuh) with two reciprocals per allele position instead of three divisions
 __device__ __forceinline__ NodeTab make_nodetab_fast(uchar2 a, double2 s, double hw)
 {

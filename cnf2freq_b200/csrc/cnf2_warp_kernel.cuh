@@ -68,6 +68,7 @@ struct __align__(16) WarpSmem
 	unsigned char cst[32], ccn[32]; // per (parent, phase bit, meiosis bits) class: first entry and number of entries
 	int nE, nE0, nX0, nX1, listtag; // nX0 / nX1: entries of parent 0 / 1 with phase bit x & 1 = 0
 	int ntr, rootmask;
+	double* nsptr[NSLOTS];         // turn scoring: negshift cell of the slot's occupant at marker 0 (null: no contribution)
 	int homslot[WB], gpmust[WB];
 	Unit unit;
 	// followed by the posterior tables of the current marker, sized by the host for the pedigree (WarpArgs::cap0/cap1):
@@ -381,6 +382,17 @@ __device__ __forceinline__ void transfer_setup(WarpSmem& w, const EstepArgs& a, 
 		w.rootmask = rm;
 		w.ntr = nout;
 	}
+	if (lane < NSLOTS)
+	{
+		double* p = nullptr;
+		if (u.row[lane] >= 0 && u.nsscale[lane] != 0)
+		{
+			const int srow = u.relrow[u.slotrel[lane]];
+			const bool sh = srow < a.n_shared;
+			p = stats_cell(sh ? a.stats_shared : a.stats_local, sh ? a.n_shared : a.n_local, a.Mc, sh ? srow : srow - a.n_shared, 0).negshift;
+		}
+		w.nsptr[lane] = p;
+	}
 }
 __device__ __forceinline__ void transfer_out(const WarpSmem& w, const double* __restrict__ tot, int t, int m, int lane)
 {
@@ -471,6 +483,94 @@ __device__ __forceinline__ void emit16(double (&p)[16], const double* __restrict
 		const double2 q0 = Q0[j];
 		p[j] *= c0a * q0.x + c1a * q0.y;
 		p[j + 8] *= c0b * q0.x + c1b * q0.y;
+	}
+}
+// the emission values themselves (the factors emit16 multiplies by)
+__device__ __forceinline__ void emis16(double (&ev)[16], const double* __restrict__ q, int lane)
+{
+#pragma unroll
+	for (int i = 0; i < 16; i++) ev[i] = 1.0;
+	emit16(ev, q, lane);
+}
+
+// Turn scoring of one marker (cnF2freq.cpp:5668-5757 with DOTOULBAR 0: the turns of at most one bit; aroundturner
+// :498-554; quickanalyze with classicstop(marker, -1), :1960-2018) and updatenegshifts (:3640-3715).
+//   rawvals[turn][s] = exp(F+_s + B_s' + log sum_k alpha+_s[k ^ mask] beta_s'[k] - factor),  s' = s ^ flagmodeshift
+// with alpha+ = alpha- (x) emission.  Turn of slot k: a grandparent slot (2, 3, 5, 6) flips state bit k - 1 (bits 1, 2
+// inside the lane, bits 4, 5 one and two lanes apart), a parent slot (1, 4) flips shift bit 1 / 2 (8 / 16 lanes apart),
+// the root flips shift bit 0 (4 lanes apart).  D index: 0 no turn, k the turn of slot k, 7 the root's.
+// ap: alpha+ without its power of two (exponent ka per shift), b: beta (exponent kb), scale 2^kf * efrem = exp(-factor).
+__device__ __forceinline__ void warp_turns(const WarpSmem& w, const Unit& u, const double (&ap)[16], const double (&b)[16], int ka, int kb,
+                                           int kf, double efrem, int m, int lane)
+{
+	const unsigned FULL = 0xffffffffu;
+	double D[8];
+#pragma unroll
+	for (int j = 0; j < 8; j++) D[j] = 0;
+#pragma unroll
+	for (int i = 0; i < 16; i++)
+	{
+		D[0] = fma(ap[i], b[i], D[0]);
+		D[2] = fma(ap[i ^ 2], b[i], D[2]);  // slot 2: state bit 1
+		D[3] = fma(ap[i ^ 4], b[i], D[3]);  // slot 3: state bit 2
+		D[5] = fma(__shfl_xor_sync(FULL, ap[i], 1), b[i], D[5]);   // slot 5: state bit 4
+		D[6] = fma(__shfl_xor_sync(FULL, ap[i], 2), b[i], D[6]);   // slot 6: state bit 5
+		D[7] = fma(ap[i], __shfl_xor_sync(FULL, b[i], 4), D[7]);   // root: shift bit 0
+		D[1] = fma(ap[i], __shfl_xor_sync(FULL, b[i], 8), D[1]);   // slot 1: shift bit 1
+		D[4] = fma(ap[i], __shfl_xor_sync(FULL, b[i], 16), D[4]);  // slot 4: shift bit 2
+	}
+	{
+		const int k7 = __shfl_xor_sync(FULL, kb, 4), k1 = __shfl_xor_sync(FULL, kb, 8), k4 = __shfl_xor_sync(FULL, kb, 16);
+		auto pow2 = [&](int kbx) -> double {
+			const int ke = ka + kbx + kf;
+			// out of range below: the term underflows as exp() does in the reference; above (never in practice): its 1e300 cap (:5724)
+			return ke < -1000 ? 0.0 : ke > 1000 ? 1e300 : __hiloint2double((1023 + ke) << 20, 0) * efrem;
+		};
+		const double s0 = pow2(kb);
+		D[0] *= s0, D[2] *= s0, D[3] *= s0, D[5] *= s0, D[6] *= s0;
+		D[7] *= pow2(k7), D[1] *= pow2(k1), D[4] *= pow2(k4);
+	}
+	// sum over the warp (the shift modes that are not in use carry alpha = 0): halving exchange, then lane L holds
+	// turn (L >> 2) & 7 in the order of bits 4, 3, 2
+	double v4[4], v2[2], v1;
+	{
+		const bool hi = lane & 16;
+#pragma unroll
+		for (int j = 0; j < 4; j++)
+		{
+			const double keep = hi ? D[j + 4] : D[j], send = hi ? D[j] : D[j + 4];
+			v4[j] = keep + __shfl_xor_sync(FULL, send, 16);
+		}
+	}
+	{
+		const bool hi = lane & 8;
+#pragma unroll
+		for (int j = 0; j < 2; j++)
+		{
+			const double keep = hi ? v4[j + 2] : v4[j], send = hi ? v4[j] : v4[j + 2];
+			v2[j] = keep + __shfl_xor_sync(FULL, send, 8);
+		}
+	}
+	{
+		const bool hi = lane & 4;
+		const double keep = hi ? v2[1] : v2[0], send = hi ? v2[0] : v2[1];
+		v1 = keep + __shfl_xor_sync(FULL, send, 4);
+	}
+	v1 += __shfl_xor_sync(FULL, v1, 2);
+	v1 += __shfl_xor_sync(FULL, v1, 1);
+	const int tn = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+	if (!isfinite(v1) || v1 < 1e-174) v1 = 1e-174;  // :3655
+	const double lv = ms_log(v1);
+	const double l0 = __shfl_sync(FULL, lv, 0);
+	if ((lane & 3) == 0 && tn)
+	{
+		const int slot = tn == 7 ? 0 : tn;
+		double* const p = w.nsptr[slot];
+		if (p)
+		{
+			const bool scored = slot == 0 || !((u.flag2ignore >> slot) & 1);  // `g & (flag2ignore >> 1)`, :5684
+			atomicAdd(p + m, (l0 - (scored ? lv : 0.0)) * u.nsscale[slot]);
+		}
 	}
 }
 
@@ -788,6 +888,15 @@ __global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wa)
 #pragma unroll
 					for (int i = 0; i < 16; i++) W[i] = an[i] * (b[i] * sc);
 				}
+#ifndef CNF2_X_NOTURNS
+				{
+					double ev[16];
+					emis16(ev, w.qh + t * QS, lane);
+#pragma unroll
+					for (int i = 0; i < 16; i++) an[i] *= ev[i];  // alpha+ (unnormalised); alpha- is not needed any more
+					warp_turns(w, u, an, b, kan, kb, kf, efrem, m, lane);
+				}
+#endif
 				if (m > 0)
 				{
 					load_alpha(alpha + (size_t)(m - 1) * (NUMSHIFTS * NUMTYPES / 2), an, lane);

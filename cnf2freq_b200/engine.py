@@ -18,7 +18,7 @@ SYMBOLS = [
     "cnf2_set_params", "cnf2_estep", "cnf2_set_allreduce", "cnf2_set_shared_rows", "cnf2_get_stats", "cnf2_sync",
     "cnf2_last_estep_ms", "cnf2_last_estep_launches", "cnf2_stream", "cnf2_measure_peaks", "cnf2_mark",
     "cnf2_elapsed_ms", "cnf2_row_count", "cnf2_row_ids", "cnf2_get_stats_packed", "cnf2_set_params_packed", "cnf2_set_mstep_inputs",
-    "cnf2_begin_iteration", "cnf2_mstep", "cnf2_get_params",
+    "cnf2_begin_iteration", "cnf2_mstep", "cnf2_get_params", "cnf2_get_negshift", "cnf2_get_negshift_packed",
 ]
 
 
@@ -178,6 +178,15 @@ class Engine:
                                             _buf(homozyg, np.float64, 2 * km, "get_stats homozyg"),
                                             _buf(loglik, np.float64, 2 * self.n_dous * self.n_chrom, "get_stats loglik")))
 
+    def get_negshift(self, chrom, negshift):
+        """Phase-inversion scores of the chromosome's E-step into negshift f64 [n_ind][n_markers] (columns of `chrom`)."""
+        self._check(self.lib.cnf2_get_negshift(self.h, ctypes.c_int32(chrom),
+                                               _buf(negshift, np.float64, self.n_ind * self.n_markers, "get_negshift")))
+
+    def get_negshift_packed(self, chrom, negshift):
+        self._check(self.lib.cnf2_get_negshift_packed(self.h, ctypes.c_int32(chrom),
+                                                      _buf(negshift, np.float64, self.n_rows() * self.mc(chrom), "get_negshift_packed")))
+
     def row_ids(self):
         """Individual id of every statistics row of this engine (shared rows first)."""
         n = self.n_rows()
@@ -256,9 +265,11 @@ class Engine:
         K, M, C = self.n_ind, self.n_markers, self.n_chrom
         if out is None:
             out = dict(haplobase=np.zeros((K, M)), haplocount=np.zeros((K, M)), infprobs=np.zeros((K, M, 2, 2)),
-                       homozyg=np.zeros((K, M, 2)), loglik=np.zeros((self.n_dous, C, 2)))
+                       homozyg=np.zeros((K, M, 2)), loglik=np.zeros((self.n_dous, C, 2)), negshift=np.zeros((K, M)))
         for c in range(C):
             self.set_params(c, alleles, sure, haploweight)
             self.estep(c)
             self.get_stats(c, out["haplobase"], out["haplocount"], out["infprobs"], out["homozyg"], out["loglik"])
+            if "negshift" in out:
+                self.get_negshift(c, out["negshift"])
         return out

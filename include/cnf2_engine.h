@@ -110,8 +110,8 @@ int cnf2_estep(cnf2_engine* e, int32_t chrom);
 
 /* Optional exchange step between ranks (the stale MPI reduce at cnF2freq.cpp:6241-6256): called by
  * cnf2_estep after the kernels are enqueued, with the device buffer holding the statistics rows of the
- * individuals listed in cnf2_set_shared_rows (8 doubles per (row, marker): haplobase, haplocount,
- * infprobs[0][1], [0][2], [1][1], [1][2], homozyg[0], homozyg[1]).  The hook must enqueue a sum-all-reduce
+ * individuals listed in cnf2_set_shared_rows (9 doubles per (row, marker): haplobase, haplocount,
+ * infprobs[0][1], [0][2], [1][1], [1][2], homozyg[0], homozyg[1], negshift).  The hook must enqueue a sum-all-reduce
  * over `count` doubles in place on `cuda_stream` (e.g. ncclAllReduce / torch.distributed.all_reduce).  The
  * engine passes one and the same stream for every call, so collectives are issued in cnf2_estep call order. */
 typedef int (*cnf2_allreduce_fn)(void* ctx, double* device_buf, size_t count, void* cuda_stream);
@@ -139,6 +139,17 @@ int cnf2_row_count(cnf2_engine* e, int32_t* n_rows);
 int cnf2_row_ids(cnf2_engine* e, int32_t* ids);
 int cnf2_get_stats_packed(cnf2_engine* e, int32_t chrom, double* haplobase, double* haplocount, double* infprobs,
                           double* homozyg, double* loglik);
+
+/* Phase-inversion scores of the chromosome's E-step (row f2 of SURVEY.md section 8): what the turn scoring
+ * (cnF2freq.cpp:5668-5757, aroundturner :498-554; the DOTOULBAR 0 path: the 8 turns of at most one individual) and
+ * updatenegshifts (:3640-3715) add to individ::negshift (:891) -- for every member of an analysed individual's focus
+ * tree log(sum_s rawvals[no turn][s]) - log(sum_s rawvals[turn of that member][s]), divided by the parent's number of
+ * analysed children for grandparents.  cnf2_estep always computes them (HAPLOTYPING && !early && !full, :5668);
+ * shared rows are summed over ranks with the other statistics.  [n_ind][n_markers] (columns of `chrom`, rows this
+ * engine touches) or, packed, [n_rows][Mc] in cnf2_row_ids order.  The reference zeroes negshift after each
+ * iteration's dump (:8187); here every E-step starts from zero. */
+int cnf2_get_negshift(cnf2_engine* e, int32_t chrom, double* negshift);
+int cnf2_get_negshift_packed(cnf2_engine* e, int32_t chrom, double* negshift);
 
 /* ---- M-step on the device ------------------------------------------------
  * cnf2_mstep makes the pass of cnF2freq.cpp:6356-6367 that the reference runs after chromosome `chrom`'s E-step:

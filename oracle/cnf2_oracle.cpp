@@ -469,7 +469,103 @@ struct Outputs
 	double* homozyg;     // [K][M][2]
 	double* loglik;      // [n_dous][C][2]  (max_s L_s, logsumexp_s L_s) -- the pair printed at :5399-5401
 	long long* counters; // [2] terms tried (after ignoreflag2), terms kept (val > -200); may be null
+	double* negshift;    // [K][M] phase-inversion scores (:3640-3715); may be null (no turn scoring)
+	const int32_t* children;  // [K] individ::children as doit rebuilds it (:5246-5259); needed with negshift
 };
+
+
+// doanalyze<aroundturner>(classicstop(-1000 - marker, -1), flag2 = -1) for shift mode s (cnF2freq.cpp:1936-2018 with
+// genotype -1 -> pad 2; realanalyze<4 | 2> :2229-2266 applies the turner and stops; aroundturner :498-554): alpha+ of
+// shift s at the marker, permuted by the turn mask, against beta of shift s ^ flagmodeshift.
+double turn_term(const Env& e0, int root, Sweeps& sw, int c0, int c1, int marker, int turn, double minfactor_d)
+{
+	const float minfactor = (float)minfactor_d;
+	const int s = e0.shift;
+	const int mask = turn & 54;                                                   // :506
+	const int fms = (turn >> 6) | ((turn & 1) ? 2 : 0) | ((turn & 8) ? 4 : 0);   // :507-508
+	double factor = sw.f(s, marker, 2);
+	double probs[NUMTYPES];
+	const double* a = sw.at(s, marker, 2);
+	if (factor < minfactor) return factor;                                       // :1966
+	for (int i = 0; i < NUMTYPES; i++) probs[i ^ mask] = a[i];                    // turner, :531-545
+	const int s2 = s ^ fms;                                                       // :548
+	Env e2 = e0;
+	e2.shift = s2;
+	runsweeps(e2, root, sw, c0, c1);                                              // initfwbw(..., 2) for the new shift mode, :1988
+	if (factor < minfactor) return factor;
+	const double* b = sw.at(s2, marker, 1);
+	double sum = 0;
+	for (int k = 0; k < NUMTYPES; k++)
+	{
+		probs[k] *= b[k];
+		sum += probs[k];
+	}
+	factor += sw.f(s2, marker, 1);
+	if (sum <= 0) factor = MINFACTOR;
+	else
+	{
+		sum = 1 / sum;
+		factor -= log(sum);
+	}
+	return factor;
+}
+
+// The turn scoring of one marker (cnF2freq.cpp:5668-5757 with DOTOULBAR 0: only the 8 turns of at most one bit) and
+// updatenegshifts (:3640-3715).
+void score_turns(Problem& P, const Env& e, const Tree& t, int root, Sweeps& sw, int c0, int c1, int marker, int shiftend,
+                 double factor, const Outputs& out)
+{
+	constexpr int NUMTURNS = 128;
+	const int M = P.M;
+	for (int g = 0; g < NUMTURNS; g++)
+	{
+		if (g & (t.flag2ignore >> 1)) continue;
+		if (__builtin_popcount(g & 127) > 1) continue;  // !DOTOULBAR, :5690-5698
+		bool valid = false;
+		double rawvals[NUMSHIFTS];
+		for (int s = 0; s < NUMSHIFTS; s++) rawvals[s] = -1;
+		for (int s = 0; s < shiftend; s++)
+		{
+			if (s & t.shiftignore) continue;
+			Env es = e;
+			es.shift = s;
+			const double rawer = turn_term(es, root, sw, c0, c1, marker, g, -50000 + factor) - factor;
+			valid = true;
+			const double expval = exp(rawer);
+			if (!std::isfinite(expval)) rawvals[s] = expval > 1e300 ? 1e300 : 0;
+			else rawvals[s] = expval;
+		}
+		if (!valid) continue;
+		// updatenegshifts, :3640-3715
+		double val = 0;
+		for (int s = 0; s < shiftend; s++)
+		{
+			if (s & t.shiftignore) continue;
+			if (rawvals[s] < 0) continue;
+			val += rawvals[s];
+		}
+		if (!std::isfinite(val) || val < 1e-174) val = 1e-174;
+		int g2 = g;
+		if (!g) g2 = (1 << 15) - 1;
+		auto add = [&](int ind, int bit, int div) {
+			double v = log(val) * (1.0 - ((g >> bit) & 1) * 2) * ((g2 >> bit) & 1);
+			if (div) v = v / div;
+#pragma omp atomic update
+			out.negshift[(size_t)ind * M + marker] += v;
+		};
+		add(root, 6, 0);
+		const int p0 = P.par[root * 2], p1 = P.par[root * 2 + 1];
+		if (p0) add(p0, 0, 0);
+		if (p1) add(p1, 3, 0);
+		if (P.gen[root] >= 2)
+		{
+			if (p0 && P.par[p0 * 2]) add(P.par[p0 * 2], 1, out.children[p0]);
+			if (p0 && P.par[p0 * 2 + 1]) add(P.par[p0 * 2 + 1], 2, out.children[p0]);
+			if (p1 && P.par[p1 * 2]) add(P.par[p1 * 2], 4, out.children[p1]);
+			if (p1 && P.par[p1 * 2 + 1]) add(P.par[p1 * 2 + 1], 5, out.children[p1]);
+		}
+	}
+}
 
 void estep_individual(Problem& P, int jidx, int root, int chrom, const Outputs& out, Sweeps* keep)
 {
@@ -560,6 +656,7 @@ void estep_individual(Problem& P, int jidx, int root, int chrom, const Outputs& 
 				}
 			}
 		}
+		if (out.negshift) score_turns(P, e, t, root, sw, c0, c1, marker, shiftend, factor, out);  // :5668-5871
 		// :5875-5904
 		double sum = 0;
 		for (auto& kv : sc.infprobs[root][0]) sum += kv.second;
@@ -620,12 +717,14 @@ extern "C"
 // founder is in/out: fixtrees' sticky side effect (:3176) is applied in analysis order.
 // fwbw_dous_index >= 0 additionally copies that individual's sweeps for chromosome fwbw_chrom into
 // fwbw [8][Mc][3][64] / fwbwfactors [8][Mc][3] / fwbwmask [8].
+// negshift [K][M] (zeroed by the caller; null = no turn scoring) accumulates the phase-inversion scores; children [K]
+// is individ::children as doit rebuilds it from the analysed individuals (:5246-5259).
 int cnf2_oracle_estep(int K, int M, int C, int n_dous, const int32_t* par, const uint8_t* empty, uint8_t* founder,
                       const int32_t* gen, const int32_t* descendants, const int32_t* dous, const double* markerpos,
                       const uint32_t* chromstarts, const double* genrec, const uint8_t* alleles, const double* sure,
                       const double* haploweight, double* haplobase, double* haplocount, double* infprobs,
                       double* homozyg, double* loglik, long long* counters, int fwbw_dous_index, int fwbw_chrom,
-                      double* fwbw, double* fwbwfactors, int32_t* fwbwmask)
+                      double* fwbw, double* fwbwfactors, int32_t* fwbwmask, double* negshift, const int32_t* children)
 {
 	Problem P;
 	P.K = K;
@@ -642,7 +741,7 @@ int cnf2_oracle_estep(int K, int M, int C, int n_dous, const int32_t* par, const
 	P.alleles = alleles;
 	P.sure = sure;
 	P.haploweight = haploweight;
-	Outputs out{ haplobase, haplocount, infprobs, homozyg, loglik, counters };
+	Outputs out{ haplobase, haplocount, infprobs, homozyg, loglik, counters, negshift, children };
 	// CNF2_ORACLE_THREADS > 1 (opt-in, for sampled checks at full size): units run in parallel; rows shared between units
 	// are then summed in a nondeterministic order (atomic adds), rows only one unit adds to are unaffected.  The sticky
 	// founder flags must already be steady (cnf2_oracle_steady_founder) in that mode.

@@ -58,6 +58,9 @@ def collect(prefix, stdout, it, fwbw_individuals):
         for k in stats:
             stats[k][:, cs[c]:cs[c + 1]] = st[k][:, cs[c]:cs[c + 1]]
     out.update(stats)
+    # phase-inversion scores as the whole doit() left them (accumulated by updatenegshifts, cnF2freq.cpp:3640-3715;
+    # nothing after the E-step touches them until main() zeroes them at :8187)
+    out["negshift"] = read_dump(f"{prefix}.iter{it}.state")["negshift"]
     # printed log-likelihood pairs of this iteration: lines come chromosome by chromosome, in dous order
     lines = [LINE.match(l) for l in stdout.splitlines()]
     lines = [m for m in lines if m]

@@ -67,12 +67,22 @@ def steady_founder(pb):
     return f
 
 
-def oracle_estep(pb, fwbw_for=None, counters=False):
-    """Runs the oracle E-step.  Returns dict(haplobase, haplocount, infprobs, homozyg, loglik, founder[, fwbw...])."""
+def doit_children(par, dous):
+    """individ::children as doit rebuilds it from the analysed individuals (cnF2freq.cpp:5246-5259)."""
+    par = np.asarray(par)
+    ch = np.bincount(par[np.asarray(dous, np.int64)].ravel(), minlength=par.shape[0]).astype(np.int32)
+    ch[0] = 0
+    return ch
+
+
+def oracle_estep(pb, fwbw_for=None, counters=False, all_dous=None):
+    """Runs the oracle E-step.  Returns dict(haplobase, haplocount, infprobs, homozyg, negshift, loglik, founder[, fwbw...]).
+    all_dous: the analysed individuals of the whole run when pb.dous is a sample of them (children counts)."""
     K, M, C, nd = pb.K, pb.M, pb.C, len(pb.dous)
     out = dict(
         haplobase=np.zeros((K, M)), haplocount=np.zeros((K, M)), infprobs=np.zeros((K, M, 2, 2)),
-        homozyg=np.zeros((K, M, 2)), loglik=np.zeros((nd, C, 2)), founder=pb.founder.copy())
+        homozyg=np.zeros((K, M, 2)), negshift=np.zeros((K, M)), loglik=np.zeros((nd, C, 2)), founder=pb.founder.copy())
+    children = doit_children(pb.par, pb.dous if all_dous is None else all_dous)
     cnt = np.zeros(2, np.int64) if counters else None
     fj, fc = (-1, -1) if fwbw_for is None else fwbw_for
     fw = ff = fm = None
@@ -86,7 +96,7 @@ def oracle_estep(pb, fwbw_for=None, counters=False):
         _p(out["founder"]), _p(pb.gen), _p(pb.descendants), _p(pb.dous), _p(pb.markerpos), _p(pb.chromstarts),
         _p(pb.genrec), _p(pb.alleles), _p(pb.sure), _p(pb.haploweight), _p(out["haplobase"]), _p(out["haplocount"]),
         _p(out["infprobs"]), _p(out["homozyg"]), _p(out["loglik"]), _p(cnt), ctypes.c_int(fj), ctypes.c_int(fc),
-        _p(fw), _p(ff), _p(fm))
+        _p(fw), _p(ff), _p(fm), _p(out["negshift"]), _p(children))
     assert rc == 0
     if counters:
         out["counters"] = cnt

@@ -178,6 +178,9 @@ def test_device_mstep_matches_oracle_on_random_pedigrees(eng, maker, kw):
     print(f"masked as exact ties: {int(tie.sum())} of {tie.size} cells ({tie.mean():.4%})")
     assert tie.mean() < MAX_MASKED, f"{tie.mean():.3%} of the cells masked as ties"
     assert np.array_equal(al[ok], ral[ok])
-    assert_close(su[ok], rsu[ok], "markersure", rtol=RTOL, atol=ATOL)
-    assert_close(hw[ok], rhw[ok], "haploweight", rtol=RTOL, atol=ATOL)
+    # tiny: the solver's end point is a probability within 1e-5 of 1, compared at 1e-9 like every posterior; markersure
+    # is its complement (1 - p), so the same absolute error is a larger relative one there
+    atol = 1e-9 if tiny else ATOL
+    assert_close(su[ok], rsu[ok], "markersure", rtol=RTOL, atol=atol)
+    assert_close(hw[ok], rhw[ok], "haploweight", rtol=RTOL, atol=atol)
     assert (not any(used_sf)) == np.array_equal(hw, pb.haploweight)

@@ -20,6 +20,9 @@ def test_oracle_statistics_match_reference(name):
         assert_close(out[k], g[k], f"{name}:{k}", rtol=1e-12)
     # the reference prints the log-likelihood pair with 6 decimals (cnF2freq.cpp:5399-5401)
     assert_close(out["loglik"], g["loglik_printed"], f"{name}:loglik", rtol=0, atol=6e-7)
+    # turn scoring + updatenegshifts (row f2; :5668-5757, :3640-3715).  Scores are sums of log(val) terms that cancel to
+    # rounding where a turn changes nothing, hence the absolute part
+    assert_close(out["negshift"], g["negshift"], f"{name}:negshift", rtol=1e-12, atol=1e-13)
 
 
 @pytest.mark.parametrize("name", GOLDEN_CASES)
