@@ -11,6 +11,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <set>
 #include <string>
 #include <vector>
 
@@ -72,6 +73,11 @@ struct cnf2_engine
 	cudaStream_t comm = nullptr;    // the all-reduce hook runs here, in call order
 	cudaStream_t side = nullptr;    // M-step: the relskew chains of a pass run here, beside processinfprobs
 	cudaEvent_t ms_fork = nullptr, ms_join = nullptr;
+	// M-step passes and phase inversions update parameters of several chromosomes from different streams: each waits for
+	// the one before it through this event, and so does everything that reads parameters afterwards
+	cudaEvent_t ms_chain = nullptr;
+	bool chain_set = false;
+
 	Slot slots[NSLOT];
 	int next_slot = 0, last_slot = -1;
 	int n_slots = 2;  // E-steps in flight (CNF2_SLOTS, 1..NSLOT)
@@ -108,8 +114,19 @@ struct cnf2_engine
 	DevBuf<uchar2> d_prioral;
 	DevBuf<MstepRow> d_msrows;
 	DevBuf<uint8_t> d_anyinfo;
-	DevBuf<unsigned long long> d_hit;
+	DevBuf<EmCtl> d_ctl;
+	DevBuf<double> d_minval;
+	DevBuf<int32_t> d_minstart, d_invrows, d_invstart;
 	std::vector<uint8_t> carry_valid;
+	int32_t n_dous_total = 0;
+	// phase-inversion candidates of the iteration (negshiftcands, :5261; host logic of :6270-6340)
+	std::vector<int32_t> parents;                // [n_ind][2]
+	std::vector<std::vector<int32_t>> kids;      // analysed children (individ::kids, :5246-5259)
+	struct Cand { int32_t id; double val; int32_t start; bool operator<(const Cand& o) const { return id != o.id ? id < o.id : val != o.val ? val < o.val : start < o.start; } };
+	std::vector<std::set<Cand>> cands;           // per chromosome
+	std::vector<std::vector<double>> minval_c;   // per chromosome: minima of this iteration by individual id (empty: none yet)
+	std::vector<std::vector<int32_t>> minstart_c;
+	DevBuf<double> d_gmin;                       // [n_ind][2] exchange buffer between ranks
 	bool have_ms_inputs = false;
 	std::vector<double> h_loglik;
 
@@ -134,6 +151,16 @@ struct cnf2_engine
 		return fail(CNF2_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
 	}
 	int mc(int chrom) const { return (int)(chromstarts[chrom + 1] - chromstarts[chrom]); }
+	int wait_chain(cudaStream_t st)
+	{
+		if (!chain_set) return 0;
+		return cuda(cudaStreamWaitEvent(st, ms_chain, 0), "cudaStreamWaitEvent(ms_chain)");
+	}
+	int mark_chain(cudaStream_t st)
+	{
+		chain_set = true;
+		return cuda(cudaEventRecord(ms_chain, st), "cudaEventRecord(ms_chain)");
+	}
 };
 
 #define CU(call)                                      \
@@ -207,6 +234,7 @@ extern "C" int cnf2_create(cnf2_engine** out, const cnf2_settings* settings)
 	}
 	if ((ce = cudaEventCreateWithFlags(&e->ms_fork, cudaEventDisableTiming)) != cudaSuccess) return bail(ce, "cudaEventCreate");
 	if ((ce = cudaEventCreateWithFlags(&e->ms_join, cudaEventDisableTiming)) != cudaSuccess) return bail(ce, "cudaEventCreate");
+	if ((ce = cudaEventCreateWithFlags(&e->ms_chain, cudaEventDisableTiming)) != cudaSuccess) return bail(ce, "cudaEventCreate");
 	for (Slot& sl : e->slots)
 	{
 		if ((ce = cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(ce, "cudaStreamCreate");
@@ -275,7 +303,12 @@ extern "C" void cnf2_destroy(cnf2_engine* e)
 	if (e->side) cudaStreamSynchronize(e->side), cudaStreamDestroy(e->side);
 	if (e->ms_fork) cudaEventDestroy(e->ms_fork);
 	if (e->ms_join) cudaEventDestroy(e->ms_join);
+	if (e->ms_chain) cudaEventDestroy(e->ms_chain);
 	e->d_units.release();
+	e->d_relhaplo.release(), e->d_carry_base.release(), e->d_carry_count.release(), e->d_ratio.release(), e->d_fw.release();
+	e->d_priorsure.release(), e->d_prioral.release(), e->d_msrows.release(), e->d_anyinfo.release(), e->d_ctl.release();
+	e->d_gmin.release();
+	e->d_minval.release(), e->d_minstart.release(), e->d_invrows.release(), e->d_invstart.release();
 	for (cudaEvent_t m : e->marks)
 		if (m) cudaEventDestroy(m);
 	if (e->params_ready) cudaEventDestroy(e->params_ready);
@@ -579,6 +612,12 @@ extern "C" int cnf2_set_pedigree(cnf2_engine* e, int32_t n_ind, const int32_t* p
 		CU(sl.literal.ensure(e->units.size()));
 	}
 	e->h_loglik.assign(e->units.size() * 2, 0.0);
+	e->n_dous_total = n_all_dous;
+	e->parents.assign(parents, parents + (size_t)n_ind * 2);
+	e->kids.assign(n_ind, {});
+	for (int j = 0; j < n_all_dous; j++)
+		for (int lev1 = 0; lev1 < 2; lev1++)
+			if (const int p = parents[all_dous[j] * 2 + lev1]) e->kids[p].push_back(all_dous[j]);
 	CU(cudaStreamSynchronize(e->stream));
 	std::fill(e->have_params.begin(), e->have_params.end(), 0);
 	for (Slot& sl : e->slots) sl.chrom = -1;
@@ -610,6 +649,7 @@ static int set_params_impl(cnf2_engine* e, int32_t chrom, const uint8_t* alleles
 	CU(e->d_alleles.ensure(total));
 	CU(e->d_sure.ensure(total));
 	CU(e->d_hw.ensure(total));
+	if (int rc = e->wait_chain(e->stream)) return rc;
 	if (packed)
 	{
 		// row-ordered contiguous blocks [n_rows][Mc]: one unstrided copy per array
@@ -657,6 +697,13 @@ extern "C" int cnf2_set_params_packed(cnf2_engine* e, int32_t chrom, const uint8
 	return set_params_impl(e, chrom, alleles, sure, haploweight, true);
 }
 
+static Slot* slot_of(cnf2_engine* e, int32_t chrom)
+{
+	for (Slot& o : e->slots)
+		if (chrom >= 0 && o.chrom == chrom) return &o;
+	return nullptr;
+}
+
 extern "C" int cnf2_estep(cnf2_engine* e, int32_t chrom)
 {
 	if (!e) return CNF2_ERR_BAD_ARG;
@@ -680,6 +727,7 @@ extern "C" int cnf2_estep(cnf2_engine* e, int32_t chrom)
 	sl.n_shared = e->n_shared;
 	sl.chrom = chrom;
 	CU(cudaStreamWaitEvent(sl.stream, e->params_ready, 0));
+	if (int rc = e->wait_chain(sl.stream)) return rc;  // the parameters an earlier M-step pass or phase inversion is still writing
 	CU(cudaEventRecord(sl.ev0, sl.stream));
 	CU(cudaMemsetAsync(sl.stats.p, 0, (size_t)e->n_rows * Mc * STATS_PER_CELL * sizeof(double), sl.stream));
 	CU(cudaMemsetAsync(sl.counter.p, 0, 4 * sizeof(unsigned int), sl.stream));
@@ -751,6 +799,7 @@ extern "C" int cnf2_sync(cnf2_engine* e)
 	cudaSetDevice(e->settings.device);
 	for (Slot& sl : e->slots) CU(cudaStreamSynchronize(sl.stream));
 	CU(cudaStreamSynchronize(e->comm));
+	CU(cudaStreamSynchronize(e->side));
 	CU(cudaStreamSynchronize(e->stream));
 	CU(cudaGetLastError());
 	return CNF2_OK;
@@ -813,9 +862,18 @@ extern "C" int cnf2_set_mstep_inputs(cnf2_engine* e, const double* relhaplo, con
 	CU(e->d_carry_base.ensure(total));
 	CU(e->d_carry_count.ensure(total));
 	CU(e->d_ratio.ensure((size_t)e->n_rows * e->markerpos.size()));  // per chromosome block: a pass computes them all before it uses them
-	CU(e->d_fw.ensure((size_t)e->n_rows * e->max_mc * 2));
+	CU(e->d_fw.ensure(total * 2));  // per chromosome: the chains of every chromosome of a pass run in one launch
 	CU(e->d_anyinfo.ensure((size_t)e->n_rows * (e->chromstarts.size() - 1)));
-	CU(e->d_hit.ensure(2));
+	if (!e->d_ctl.p)
+	{
+		CU(e->d_ctl.ensure(1));
+		EmCtl init{};
+		init.scalefactor = 0.013;  // :3573
+		init.entropyfactor = 1;    // :3574
+		CU(cudaMemcpyAsync(e->d_ctl.p, &init, sizeof(init), cudaMemcpyHostToDevice, e->stream));
+	}
+	CU(e->d_minval.ensure(e->n_rows));
+	CU(e->d_minstart.ensure(e->n_rows));
 	CU(e->d_msrows.ensure(e->n_rows));
 	for (size_t c = 0; c + 1 < e->chromstarts.size(); c++)
 	{
@@ -845,83 +903,351 @@ extern "C" int cnf2_begin_iteration(cnf2_engine* e)
 {
 	if (!e) return CNF2_ERR_BAD_ARG;
 	std::fill(e->carry_valid.begin(), e->carry_valid.end(), 0);  // doit zeroes haplobase / haplocount, :5222-5234
+	const size_t C = e->chromstarts.empty() ? 0 : e->chromstarts.size() - 1;
+	e->cands.assign(C, {});       // negshiftcands is local to doit (:5261)
+	e->minval_c.assign(C, {});    // negshift is zeroed after every iteration's dump (:8187)
+	e->minstart_c.assign(C, {});
 	return CNF2_OK;
 }
 
-extern "C" int cnf2_mstep(cnf2_engine* e, int32_t chrom, double scalefactor, double entropyfactor, int64_t* hitnnn,
-                          int64_t* hitnnn_shared)
+// One M-step pass behind chromosome `chrom`'s E-step, enqueued on that E-step's stream.  set: scalefactor / entropyfactor
+// handed in (cnf2_mstep); control: run the step-size control of :6373-6390 on the device (cnf2_mstep_pass).
+static int enqueue_pass(cnf2_engine* e, int32_t chrom, int any, int set, double sf, double ent, int control, Slot** out_slot)
 {
-	if (!e) return CNF2_ERR_BAD_ARG;
 	if (!e->have_ms_inputs) return e->fail(CNF2_ERR_STATE, "cnf2_mstep: cnf2_set_mstep_inputs first");
 	Slot* slp = nullptr;
 	for (Slot& o : e->slots)
 		if (chrom >= 0 && o.chrom == chrom) slp = &o;
 	if (!slp) return e->fail(CNF2_ERR_STATE, "cnf2_mstep: cnf2_estep for this chromosome first (its statistics must still be in flight)");
 	Slot& sl = *slp;
+	*out_slot = slp;
 	cudaSetDevice(e->settings.device);
-	CU(cudaMemsetAsync(e->d_hit.p, 0, 2 * sizeof(unsigned long long), sl.stream));
 	const int C = (int)e->chromstarts.size() - 1;
-	auto args = [&](int c, bool fresh) {
-		const size_t blk = (size_t)e->n_rows * e->chromstarts[c];
-		const int Mc = e->mc(c);
-		MstepArgs a{};
-		a.alleles = e->d_alleles.p + blk;
-		a.sure = e->d_sure.p + blk;
-		a.hw = e->d_hw.p + blk;
-		a.relhaplo = e->d_relhaplo.p + blk;
-		a.prioralleles = e->d_prioral.p + blk;
-		a.priorsure = e->d_priorsure.p + blk;
-		a.rows = e->d_msrows.p;
-		a.stats_shared = sl.stats_shared();
-		a.stats_local = sl.stats_local(Mc);
-		a.carry_base = e->d_carry_base.p + blk;
-		a.carry_count = e->d_carry_count.p + blk;
-		a.ratio = e->d_ratio.p + blk;
-		a.fw = e->d_fw.p;
-		a.anyinfo = e->d_anyinfo.p + (size_t)e->n_rows * c;
-		a.hitnnn = e->d_hit.p;
-		a.n_rows = e->n_rows;
-		a.n_shared = e->n_shared;
-		a.Mc = Mc;
-		a.fresh = fresh ? 1 : 0;
-		a.scalefactor = scalefactor;
-		a.entropyfactor = entropyfactor;
-		return a;
-	};
+	if (int rc = e->wait_chain(sl.stream)) return rc;
+	ms_begin_kernel<<<1, 1, 0, sl.stream>>>(e->d_ctl.p, any, set, sf, ent);
 	if (e->n_rows > 0)
 	{
+		MstepArgs g{};
+		g.alleles = e->d_alleles.p;
+		g.sure = e->d_sure.p;
+		g.hw = e->d_hw.p;
+		g.relhaplo = e->d_relhaplo.p;
+		g.prioralleles = e->d_prioral.p;
+		g.priorsure = e->d_priorsure.p;
+		g.rows = e->d_msrows.p;
+		g.stats_shared = sl.stats_shared();
+		g.stats_local = sl.stats_local(e->mc(chrom));
+		g.carry_base = e->d_carry_base.p;
+		g.carry_count = e->d_carry_count.p;
+		g.ratio = e->d_ratio.p;
+		g.fw = e->d_fw.p;
+		g.anyinfo = e->d_anyinfo.p;
+		g.ctl = e->d_ctl.p;
+		g.n_rows = e->n_rows;
+		g.n_shared = e->n_shared;
 		// processinfprobs only has statistics for this chromosome; updatehaploweights also walks the chromosomes whose
 		// pass came earlier in the iteration, with the haplobase / haplocount that pass left behind (:6239-6367).
-		// The relskew chains (one thread per row, latency-bound) read haploweight and haplocount only, which
-		// processinfprobs does not touch: they run on a side stream beside it, one chromosome after the other.
-		auto in_pass = [&](int c) { return c == chrom || e->carry_valid[c]; };
+		// The relskew chains (one thread per (row, chromosome), latency-bound) read haploweight and haplocount only, which
+		// processinfprobs does not touch: they run on a side stream beside it.
+		std::vector<int> in_pass;
+		for (int c = 0; c < C; c++)
+			if (c == chrom || e->carry_valid[c]) in_pass.push_back(c);
+		std::vector<MstepPass> launches;
+		for (size_t i = 0; i < in_pass.size(); i += MS_MAXLIST)
+		{
+			MstepPass p{};
+			p.g = g;
+			p.fresh_index = -1;
+			p.n = (int)std::min<size_t>(MS_MAXLIST, in_pass.size() - i);
+			for (int k = 0; k < p.n; k++)
+			{
+				const int c = in_pass[i + k];
+				p.c0[k] = (int32_t)e->chromstarts[c];
+				p.Mc[k] = e->mc(c);
+				p.cidx[k] = c;
+				if (c == chrom) p.fresh_index = k;
+			}
+			launches.push_back(p);
+		}
 		const unsigned gr = (unsigned)((e->n_rows + 127) / 128);
 		CU(cudaEventRecord(e->ms_fork, sl.stream));
 		CU(cudaStreamWaitEvent(e->side, e->ms_fork, 0));
-		for (int c = 0; c < C; c++)
-			if (in_pass(c)) mstep_relskew_kernel<<<gr, 128, 0, e->side>>>(args(c, c == chrom));
+		for (const MstepPass& p : launches) mstep_relskew_kernel<<<dim3(gr, p.n), 128, 0, e->side>>>(p);
 		CU(cudaEventRecord(e->ms_join, e->side));
 		{
-			const MstepArgs a = args(chrom, true);
+			MstepArgs a = g;
+			const size_t off = (size_t)e->n_rows * e->chromstarts[chrom];
+			a.alleles += off, a.sure += off, a.hw += off, a.relhaplo += off, a.prioralleles += off, a.priorsure += off;
+			a.Mc = e->mc(chrom);
+			a.fresh = 1;
 			mstep_infprobs_kernel<<<(unsigned)(((size_t)e->n_rows * a.Mc + 127) / 128), 128, 0, sl.stream>>>(a);
 		}
 		CU(cudaStreamWaitEvent(sl.stream, e->ms_join, 0));
-		for (int c = 0; c < C; c++)
+		for (const MstepPass& p : launches)
 		{
-			if (!in_pass(c)) continue;
-			const MstepArgs a = args(c, c == chrom);
-			mstep_haploweight_kernel<<<(unsigned)(((size_t)e->n_rows * a.Mc + 127) / 128), 128, 0, sl.stream>>>(a);
+			int maxmc = 0;
+			for (int k = 0; k < p.n; k++) maxmc = std::max(maxmc, p.Mc[k]);
+			mstep_haploweight_kernel<<<dim3((unsigned)(((size_t)e->n_rows * maxmc + 127) / 128), p.n), 128, 0, sl.stream>>>(p);
 		}
 		CU(cudaGetLastError());
 	}
 	e->carry_valid[chrom] = 1;
-	unsigned long long hit[2] = { 0, 0 };
-	CU(cudaMemcpyAsync(hit, e->d_hit.p, sizeof(hit), cudaMemcpyDeviceToHost, sl.stream));
+	int reduced = 0;
+	if (control && e->allreduce && e->n_shared > 0)
+	{
+		// global hitnnn = sum over ranks of the local counts + the shared rows' count (identical on every rank)
+		ms_pack_kernel<<<1, 1, 0, sl.stream>>>(e->d_ctl.p);
+		CU(cudaEventRecord(sl.tail, sl.stream));
+		CU(cudaStreamWaitEvent(e->comm, sl.tail, 0));
+		const int rc = e->allreduce(e->allreduce_ctx, &e->d_ctl.p->hit_local_d, 1, (void*)e->comm);
+		if (rc) return e->fail(CNF2_ERR_CUDA, "cnf2_mstep_pass: all-reduce hook failed");
+		CU(cudaEventRecord(sl.done, e->comm));
+		CU(cudaStreamWaitEvent(sl.stream, sl.done, 0));
+		reduced = 1;
+	}
+	ms_end_kernel<<<1, 1, 0, sl.stream>>>(e->d_ctl.p, reduced, control);
+	CU(cudaGetLastError());
+	return e->mark_chain(sl.stream);
+}
+
+extern "C" int cnf2_mstep(cnf2_engine* e, int32_t chrom, double scalefactor, double entropyfactor, int64_t* hitnnn,
+                          int64_t* hitnnn_shared)
+{
+	if (!e) return CNF2_ERR_BAD_ARG;
+	Slot* sl = nullptr;
+	const int rc = enqueue_pass(e, chrom, 0, 1, scalefactor, entropyfactor, 0, &sl);
+	if (rc) return rc;
+	EmCtl c{};
+	CU(cudaMemcpyAsync(&c, e->d_ctl.p, sizeof(c), cudaMemcpyDeviceToHost, sl->stream));
+	CU(cudaStreamSynchronize(sl->stream));
+	CU(cudaGetLastError());
+	if (hitnnn) *hitnnn = (int64_t)(c.hit[0] + c.hit[1]);
+	if (hitnnn_shared) *hitnnn_shared = (int64_t)c.hit[1];
+	return CNF2_OK;
+}
+
+extern "C" int cnf2_mstep_pass(cnf2_engine* e, int32_t chrom, int32_t any_inversion)
+{
+	if (!e) return CNF2_ERR_BAD_ARG;
+	Slot* sl = nullptr;
+	return enqueue_pass(e, chrom, any_inversion ? 1 : 0, 0, 0.0, 0.0, 1, &sl);
+}
+
+extern "C" int cnf2_set_em_state(cnf2_engine* e, double scalefactor, double entropyfactor, int32_t oldhitnnn, int32_t oldhitnnn2)
+{
+	if (!e) return CNF2_ERR_BAD_ARG;
+	if (!e->have_ms_inputs) return e->fail(CNF2_ERR_STATE, "cnf2_set_em_state: cnf2_set_mstep_inputs first");
+	cudaSetDevice(e->settings.device);
+	CU(cnf2_sync(e) == CNF2_OK ? cudaSuccess : cudaErrorUnknown);
+	EmCtl c{};
+	c.scalefactor = scalefactor;
+	c.entropyfactor = entropyfactor;
+	c.oldhitnnn = oldhitnnn;
+	c.oldhitnnn2 = oldhitnnn2;
+	c.n_dous_total = e->n_dous_total;
+	CU(cudaMemcpyAsync(e->d_ctl.p, &c, sizeof(c), cudaMemcpyHostToDevice, e->stream));
+	CU(cudaStreamSynchronize(e->stream));
+	return CNF2_OK;
+}
+
+extern "C" int cnf2_get_em_state(cnf2_engine* e, double* scalefactor, double* entropyfactor, int32_t* oldhitnnn, int32_t* oldhitnnn2,
+                                 int64_t* hitnnn_last)
+{
+	if (!e) return CNF2_ERR_BAD_ARG;
+	if (!e->have_ms_inputs) return e->fail(CNF2_ERR_STATE, "cnf2_get_em_state: cnf2_set_mstep_inputs first");
+	cudaSetDevice(e->settings.device);
+	{
+		const int rc = cnf2_sync(e);
+		if (rc) return rc;
+	}
+	EmCtl c{};
+	CU(cudaMemcpy(&c, e->d_ctl.p, sizeof(c), cudaMemcpyDeviceToHost));
+	if (scalefactor) *scalefactor = c.scalefactor;
+	if (entropyfactor) *entropyfactor = c.entropyfactor;
+	if (oldhitnnn) *oldhitnnn = c.oldhitnnn;
+	if (oldhitnnn2) *oldhitnnn2 = c.oldhitnnn2;
+	if (hitnnn_last) *hitnnn_last = (int64_t)c.hitnnn_last;
+	return CNF2_OK;
+}
+
+extern "C" int cnf2_negshift_minima(cnf2_engine* e, int32_t chrom, double* minval, int32_t* minstart)
+{
+	if (!e || !minval || !minstart) return CNF2_ERR_BAD_ARG;
+	Slot* slp = nullptr;
+	for (Slot& o : e->slots)
+		if (chrom >= 0 && o.chrom == chrom) slp = &o;
+	if (!slp) return e->fail(CNF2_ERR_STATE, "cnf2_negshift_minima: cnf2_estep for this chromosome first (its statistics must still be in flight)");
+	Slot& sl = *slp;
+	cudaSetDevice(e->settings.device);
+	if (e->n_rows == 0) return CNF2_OK;
+	CU(e->d_minval.ensure(e->n_rows));
+	CU(e->d_minstart.ensure(e->n_rows));
+	const int Mc = e->mc(chrom);
+	negshift_minima_kernel<<<(unsigned)((e->n_rows * 32 + 127) / 128), 128, 0, sl.stream>>>(sl.stats_shared(), sl.stats_local(Mc), e->n_rows,
+	                                                                                     e->n_shared, Mc, e->d_minval.p, e->d_minstart.p);
+	CU(cudaGetLastError());
+	CU(cudaMemcpyAsync(minval, e->d_minval.p, (size_t)e->n_rows * sizeof(double), cudaMemcpyDeviceToHost, sl.stream));
+	CU(cudaMemcpyAsync(minstart, e->d_minstart.p, (size_t)e->n_rows * sizeof(int32_t), cudaMemcpyDeviceToHost, sl.stream));
 	CU(cudaStreamSynchronize(sl.stream));
 	CU(cudaGetLastError());
-	if (hitnnn) *hitnnn = (int64_t)(hit[0] + hit[1]);
-	if (hitnnn_shared) *hitnnn_shared = (int64_t)hit[1];
 	return CNF2_OK;
+}
+
+extern "C" int cnf2_apply_inversions(cnf2_engine* e, int32_t chrom, const int32_t* ids, const int32_t* minstart, int32_t n)
+{
+	if (!e || n < 0 || (n > 0 && (!ids || !minstart))) return CNF2_ERR_BAD_ARG;
+	if (!e->have_ms_inputs) return e->fail(CNF2_ERR_STATE, "cnf2_apply_inversions: cnf2_set_mstep_inputs first");
+	if (chrom < 0 || chrom + 1 >= (int)e->chromstarts.size()) return e->fail(CNF2_ERR_BAD_ARG, "cnf2_apply_inversions: bad chromosome");
+	cudaSetDevice(e->settings.device);
+	const int Mc = e->mc(chrom);
+	std::vector<int32_t> rows, starts;
+	for (int k = 0; k < n; k++)
+	{
+		if (ids[k] <= 0 || ids[k] >= e->n_ind) return e->fail(CNF2_ERR_BAD_ARG, "cnf2_apply_inversions: id out of range");
+		if (minstart[k] < 0 || minstart[k] >= Mc) return e->fail(CNF2_ERR_BAD_ARG, "cnf2_apply_inversions: marker out of range");
+		if (e->rowof[ids[k]] < 0) continue;  // not held by this rank
+		rows.push_back(e->rowof[ids[k]]);
+		starts.push_back(minstart[k]);
+	}
+	if (rows.empty()) return CNF2_OK;
+	// the chromosome's haplobase / haplocount: the E-step's block while its pass has not run, the carried copy afterwards
+	Slot* slp = nullptr;
+	for (Slot& o : e->slots)
+		if (o.chrom == chrom) slp = &o;
+	const bool fresh = !e->carry_valid[chrom];
+	if (fresh && !slp) return e->fail(CNF2_ERR_STATE, "cnf2_apply_inversions: no statistics of this chromosome (cnf2_estep first)");
+	// behind the last pass / inversion (and, for fresh statistics, behind the chromosome's E-step); ahead of the next ones
+	cudaStream_t st = e->stream;
+	if (int rc = e->wait_chain(st)) return rc;
+	if (slp)
+	{
+		CU(cudaEventRecord(slp->tail, slp->stream));
+		CU(cudaStreamWaitEvent(st, slp->tail, 0));
+	}
+	CU(e->d_invrows.ensure(rows.size()));
+	CU(e->d_invstart.ensure(rows.size()));
+	CU(cudaMemcpyAsync(e->d_invrows.p, rows.data(), rows.size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+	CU(cudaMemcpyAsync(e->d_invstart.p, starts.data(), starts.size() * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+	MstepArgs a{};
+	const size_t off = (size_t)e->n_rows * e->chromstarts[chrom];
+	a.hw = e->d_hw.p + off;
+	a.carry_base = e->d_carry_base.p + off;
+	a.carry_count = e->d_carry_count.p + off;
+	a.stats_shared = slp ? slp->stats_shared() : nullptr;
+	a.stats_local = slp ? slp->stats_local(Mc) : nullptr;
+	a.n_rows = e->n_rows;
+	a.n_shared = e->n_shared;
+	a.Mc = Mc;
+	a.fresh = fresh ? 1 : 0;
+	apply_inversions_kernel<<<(unsigned)rows.size(), 128, 0, st>>>(a, e->d_invrows.p, e->d_invstart.p, (int)rows.size());
+	CU(cudaGetLastError());
+	if (int rc = e->mark_chain(st)) return rc;
+	if (slp) CU(cudaStreamWaitEvent(slp->stream, e->ms_chain, 0));  // the chromosome's own pass reads what was just flipped
+	CU(cudaStreamSynchronize(st));  // rows / starts are host vectors of this call
+	return CNF2_OK;
+}
+
+// individ::arerelated (cnF2freq.cpp:916-946): within two generations up the pointer chains, or sharing an analysed child
+static bool arerelated(const cnf2_engine* e, int a, int b, std::vector<int> stack, int gens)
+{
+	if (gens > 2) return false;
+	if (b == a) return true;
+	if (std::find(stack.begin(), stack.end(), a) != stack.end()) return false;
+	stack.push_back(a);
+	if (stack.size() == 1)
+	{
+		if (b && arerelated(e, b, a, stack, gens + 1)) return true;
+	}
+	for (int k = 0; k < 2; k++)
+		if (const int p = e->parents[(size_t)a * 2 + k])
+			if (arerelated(e, p, b, stack, gens + 1)) return true;
+	for (int i : e->kids[a])
+		for (int j : e->kids[b])
+			if (i == j) return true;
+	return false;
+}
+
+extern "C" int cnf2_em_pass(cnf2_engine* e, int32_t chrom, int32_t* inv_ids, int32_t* inv_markers, int32_t cap, int32_t* n_inv)
+{
+	if (!e) return CNF2_ERR_BAD_ARG;
+	if (!e->have_ms_inputs) return e->fail(CNF2_ERR_STATE, "cnf2_em_pass: cnf2_set_mstep_inputs first");
+	const int C = (int)e->chromstarts.size() - 1;
+	if (chrom < 0 || chrom >= C) return e->fail(CNF2_ERR_BAD_ARG, "cnf2_em_pass: bad chromosome");
+	if ((int)e->cands.size() != C) return e->fail(CNF2_ERR_STATE, "cnf2_em_pass: cnf2_begin_iteration first");
+	Slot* slp = slot_of(e, chrom);
+	if (!slp) return e->fail(CNF2_ERR_STATE, "cnf2_em_pass: cnf2_estep for this chromosome first (its statistics must still be in flight)");
+	cudaSetDevice(e->settings.device);
+	// minval / minstart of this chromosome for every individual (:6272-6284), the same on every rank
+	{
+		std::vector<double> mv(e->n_rows);
+		std::vector<int32_t> ms(e->n_rows);
+		if (int rc = cnf2_negshift_minima(e, chrom, mv.data(), ms.data())) return rc;
+		const int Mc = e->mc(chrom);
+		std::vector<double> g((size_t)e->n_ind * 2, 0.0);  // (minval, Mc - minstart): zero = no candidate
+		const bool exchange = e->allreduce != nullptr;
+		for (int r = exchange ? e->n_shared : 0; r < e->n_rows; r++)
+			g[(size_t)e->rowid[r] * 2] = mv[r], g[(size_t)e->rowid[r] * 2 + 1] = (double)(Mc - ms[r]);
+		if (exchange)
+		{
+			// rows only one rank holds: everybody else contributes zeros to the sum; shared rows are identical everywhere
+			CU(e->d_gmin.ensure(g.size()));
+			CU(cudaMemcpyAsync(e->d_gmin.p, g.data(), g.size() * sizeof(double), cudaMemcpyHostToDevice, e->comm));
+			if (e->allreduce(e->allreduce_ctx, e->d_gmin.p, g.size(), (void*)e->comm)) return e->fail(CNF2_ERR_CUDA, "cnf2_em_pass: all-reduce hook failed");
+			CU(cudaMemcpyAsync(g.data(), e->d_gmin.p, g.size() * sizeof(double), cudaMemcpyDeviceToHost, e->comm));
+			CU(cudaStreamSynchronize(e->comm));
+			for (int r = 0; r < e->n_shared; r++)
+				g[(size_t)e->rowid[r] * 2] = mv[r], g[(size_t)e->rowid[r] * 2 + 1] = (double)(Mc - ms[r]);
+		}
+		e->minval_c[chrom].assign(e->n_ind, -1e-10);
+		e->minstart_c[chrom].assign(e->n_ind, Mc);
+		for (int id = 1; id < e->n_ind; id++)
+			if (g[(size_t)id * 2 + 1] != 0)
+			{
+				e->minval_c[chrom][id] = g[(size_t)id * 2];
+				e->minstart_c[chrom][id] = Mc - (int32_t)g[(size_t)id * 2 + 1];
+			}
+	}
+	// candidates, at most one per individual and chromosome (:6270-6327): individuals in id order, every chromosome each
+	for (int id = 1; id < e->n_ind; id++)
+		for (int c = 0; c < C; c++)
+		{
+			if (e->minval_c[c].empty()) continue;
+			const int Mc = e->mc(c), minstart = e->minstart_c[c][id];
+			if (!(minstart + 1 < Mc)) continue;  // :6301 (none, or the last marker)
+			const cnf2_engine::Cand our{ id, e->minval_c[c][id], minstart };
+			bool anymatch = false;
+			for (auto it = e->cands[c].begin(); it != e->cands[c].end();)
+			{
+				bool erase = false;
+				if (arerelated(e, it->id, our.id, {}, 0))  // inferiorrelated, :3415-3435
+				{
+					if (it->val > our.val) erase = true;
+					else anymatch = true;
+				}
+				if (erase) it = e->cands[c].erase(it);
+				else ++it;
+			}
+			if (!anymatch && rand() / (RAND_MAX / 5)) e->cands[c].insert(our);  // :6319
+		}
+	// negshifter on every candidate of every chromosome (:6336-6340)
+	bool any = false;
+	int n_out = 0;
+	for (int c = 0; c < C; c++)
+	{
+		if (e->cands[c].empty()) continue;
+		any = true;
+		std::vector<int32_t> ids, starts;
+		for (const auto& cd : e->cands[c])
+		{
+			ids.push_back(cd.id);
+			starts.push_back(cd.start);
+			if (inv_ids && inv_markers && n_out < cap) inv_ids[n_out] = cd.id, inv_markers[n_out] = (int32_t)e->chromstarts[c] + cd.start + 1;
+			n_out++;
+		}
+		if (int rc = cnf2_apply_inversions(e, c, ids.data(), starts.data(), (int32_t)ids.size())) return rc;
+	}
+	if (n_inv) *n_inv = n_out;
+	return cnf2_mstep_pass(e, chrom, any ? 1 : 0);
 }
 
 extern "C" int cnf2_get_params(cnf2_engine* e, int32_t chrom, uint8_t* alleles, double* sure, double* haploweight)
@@ -932,6 +1258,7 @@ extern "C" int cnf2_get_params(cnf2_engine* e, int32_t chrom, uint8_t* alleles, 
 	cudaSetDevice(e->settings.device);
 	const size_t M = e->markerpos.size(), c0 = e->chromstarts[chrom], Mc = e->mc(chrom);
 	const size_t blk = (size_t)e->n_rows * (e->resident ? c0 : 0);
+	if (int rc = e->wait_chain(e->stream)) return rc;
 	for (const Run& r : e->runs)
 	{
 		const size_t dst = (size_t)r.id0 * M + c0, src = blk + (size_t)r.row0 * Mc;
@@ -987,13 +1314,6 @@ extern "C" int cnf2_get_stats_packed(cnf2_engine* e, int32_t chrom, double* hapl
 	CU(cudaStreamSynchronize(sl.stream));
 	CU(cudaGetLastError());
 	return CNF2_OK;
-}
-
-static Slot* slot_of(cnf2_engine* e, int32_t chrom)
-{
-	for (Slot& o : e->slots)
-		if (chrom >= 0 && o.chrom == chrom) return &o;
-	return nullptr;
 }
 
 extern "C" int cnf2_get_negshift(cnf2_engine* e, int32_t chrom, double* negshift)

@@ -28,6 +28,19 @@ struct MstepRow  // per statistics row
 	uint8_t empty, hasprior, pad[2];
 };
 
+// The EM control state of the reference (scalefactor / entropyfactor :3573-3574, the hitnnn history :6373-6390), kept on
+// the device so that a pass needs no host round trip.
+struct EmCtl
+{
+	double scalefactor, entropyfactor;
+	double sf_pass;               // scalefactor of the pass in flight: 0 while phase inversions are applied (:6339-6341)
+	double hit_local_d;           // local hits as a double: the all-reduce slot between ranks
+	unsigned long long hit[2];    // hits of the pass: [0] rows only this rank holds, [1] shared rows (every rank counts those)
+	long long hitnnn_last;        // global hitnnn of the last finished pass
+	int32_t oldhitnnn, oldhitnnn2;
+	int32_t n_dous_total, any;
+};
+
 struct MstepArgs
 {
 	// parameters of the chromosome, [n_rows][Mc] blocks (in/out)
@@ -43,11 +56,32 @@ struct MstepArgs
 	double *carry_base, *carry_count;  // [n_rows][Mc]
 	double *ratio, *fw;                // scratch [n_rows][Mc], [n_rows][Mc][2]
 	uint8_t* anyinfo;                  // [n_rows]
-	unsigned long long* hitnnn;  // [0] rows only this rank holds, [1] shared rows (every rank counts those)
+	EmCtl* ctl;
 	int32_t n_rows, n_shared, Mc;
 	int32_t fresh;  // 1: statistics come from the E-step block; 0: from the carry arrays
-	double scalefactor, entropyfactor;
 };
+
+// One launch serves every chromosome of a pass (the fresh one and the ones carried from earlier in the iteration, which
+// the reference's block walks again, :6239-6367): blockIdx.y picks the chromosome.  `g` holds the genome-wide base
+// pointers (chromosome c's block starts n_rows * c0 cells in; anyinfo at n_rows * index).
+constexpr int MS_MAXLIST = 24;
+struct MstepPass
+{
+	MstepArgs g;
+	int32_t n, fresh_index;  // chromosomes in this launch; which of them is the fresh one (-1: none)
+	int32_t c0[MS_MAXLIST], Mc[MS_MAXLIST], cidx[MS_MAXLIST];
+};
+__device__ __forceinline__ MstepArgs ms_view(const MstepPass& p, int k)
+{
+	MstepArgs a = p.g;
+	const size_t off = (size_t)a.n_rows * p.c0[k];
+	a.alleles += off, a.sure += off, a.hw += off, a.relhaplo += off, a.prioralleles += off, a.priorsure += off;
+	a.carry_base += off, a.carry_count += off, a.ratio += off, a.fw += 2 * off;
+	a.anyinfo += (size_t)a.n_rows * p.cidx[k];
+	a.Mc = p.Mc[k];
+	a.fresh = k == p.fresh_index;
+	return a;
+}
 
 __device__ __forceinline__ double ms_caplogit(double intended, double orig, double epsilon, unsigned long long& hit)
 {
@@ -353,7 +387,7 @@ __device__ __forceinline__ StatsCell ms_cell(const MstepArgs& a, int row, int m)
 // processinfprobs (:4179-4323) for both sides of one (row, marker).  A statistic that is exactly 0 is an absent key
 // of the reference's small_map (the E-step never adds a zero).  infprobs/homozyg are not cleared here: the next
 // E-step of the chromosome zeroes its block.
-__global__ void __launch_bounds__(MS_BLOCK) mstep_infprobs_kernel(MstepArgs a)
+__global__ void __launch_bounds__(MS_BLOCK, 5) mstep_infprobs_kernel(MstepArgs a)
 {
 	__shared__ double stage[MS_NPAR][MS_BLOCK];
 	const size_t idx0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x, cells = (size_t)a.n_rows * a.Mc;
@@ -366,7 +400,8 @@ __global__ void __launch_bounds__(MS_BLOCK) mstep_infprobs_kernel(MstepArgs a)
 	double2 su = a.sure[idx];
 	const uchar2 pal = r.hasprior ? a.prioralleles[idx] : make_uchar2(0, 0);
 	const double2 psu = r.hasprior ? a.priorsure[idx] : make_double2(0, 0);
-	const double epsilon = ms_epsilon(r.children), etf = 1 * a.entropyfactor;
+	const double scalefactor = a.ctl->sf_pass;
+	const double epsilon = ms_epsilon(r.children), etf = 1 * a.ctl->entropyfactor;
 	unsigned long long hit = 0;
 #pragma unroll 1
 	for (int side = 0; side < 2; side++)
@@ -399,7 +434,7 @@ __global__ void __launch_bounds__(MS_BLOCK) mstep_infprobs_kernel(MstepArgs a)
 				}
 			}
 			const MsParams P = ms_params(curprob, ip[k], sum, etf, etf * priord, 0.0, 0.0, epsilon);
-			const double res = ms_cappedgd_warp<0>(P, curprob, a.scalefactor, active, hit, &stage[0][0], r.empty || !r.hasprior);
+			const double res = ms_cappedgd_warp<0>(P, curprob, scalefactor, active, hit, &stage[0][0], r.empty || !r.hasprior);
 			if (active) ip[k] = res;
 		}
 		double bestprob = 0;
@@ -423,14 +458,15 @@ __global__ void __launch_bounds__(MS_BLOCK) mstep_infprobs_kernel(MstepArgs a)
 	{
 		a.alleles[idx] = al;
 		a.sure[idx] = su;
-		if (hit) atomicAdd(a.hitnnn + (row < a.n_shared ? 1 : 0), hit);
+		if (hit) atomicAdd(a.ctl->hit + (row < a.n_shared ? 1 : 0), hit);
 	}
 }
 
 // relskewhmm (:4325-4467, realhmm): one thread per row walks the chromosome forward (stores the two forward values per
 // marker) and backward (ratio = P(state 1)); anyinfo = some haplocount of the chromosome is non-zero (:4560-4565).
-__global__ void __launch_bounds__(128) mstep_relskew_kernel(MstepArgs a)
+__global__ void __launch_bounds__(128) mstep_relskew_kernel(MstepPass pass)
 {
+	const MstepArgs a = ms_view(pass, blockIdx.y);
 	const int row = blockIdx.x * blockDim.x + threadIdx.x;
 	if (row >= a.n_rows) return;
 	const int Mc = a.Mc;
@@ -547,9 +583,11 @@ __global__ void __launch_bounds__(128) mstep_relskew_kernel(MstepArgs a)
 
 // updatehaploweights (:4533-4734) for one (row, marker); the adjusted haplobase/haplocount are kept in the carry
 // arrays because the reference re-runs this on the chromosome after every later chromosome of the iteration.
-__global__ void __launch_bounds__(MS_BLOCK, 6) mstep_haploweight_kernel(MstepArgs a)
+__global__ void __launch_bounds__(MS_BLOCK, 6) mstep_haploweight_kernel(MstepPass pass)
 {
 	__shared__ double stage[MS_NPAR][MS_BLOCK];
+	const MstepArgs a = ms_view(pass, blockIdx.y);
+	if ((size_t)blockIdx.x * blockDim.x >= (size_t)a.n_rows * a.Mc) return;  // the grid is sized for the longest chromosome of the pass
 	const size_t idx0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x, cells = (size_t)a.n_rows * a.Mc;
 	const bool valid = idx0 < cells;  // every lane stays for the warp-cooperative solver
 	const size_t idx = valid ? idx0 : cells - 1;
@@ -590,19 +628,100 @@ __global__ void __launch_bounds__(MS_BLOCK, 6) mstep_haploweight_kernel(MstepArg
 			if (hb >= hc) hb = hc;
 		}
 	}
-	const MsParams P = ms_params(w, hb, hc, (1 - similarity) * 1, a.entropyfactor, active ? a.ratio[idx] : 0.0, (double)r.descendants,
+	const MsParams P = ms_params(w, hb, hc, (1 - similarity) * 1, a.ctl->entropyfactor, active ? a.ratio[idx] : 0.0, (double)r.descendants,
 	                             ms_epsilon(r.children));
 	unsigned long long hit = 0;
-	const double res = ms_cappedgd_warp<1>(P, w, a.scalefactor, active, hit, &stage[0][0]);
+	const double res = ms_cappedgd_warp<1>(P, w, a.ctl->sf_pass, active, hit, &stage[0][0]);
 	if (active)
 	{
 		a.hw[idx] = res;
-		if (hit) atomicAdd(a.hitnnn + (row < a.n_shared ? 1 : 0), hit);
+		if (hit) atomicAdd(a.ctl->hit + (row < a.n_shared ? 1 : 0), hit);
 	}
 	if (valid)
 	{
 		a.carry_base[idx] = hb;
 		a.carry_count[idx] = hc;
+	}
+}
+
+// ---- EM control on the device ----
+// Start of a pass: the effective scalefactor (0 while phase inversions are applied, :6339-6341) and zeroed hit counters.
+// explicit_sf >= 0... the synchronous cnf2_mstep hands scalefactor / entropyfactor in (set = 1).
+__global__ void ms_begin_kernel(EmCtl* c, int any, int set, double sf, double ent)
+{
+	if (set) c->scalefactor = sf, c->entropyfactor = ent;
+	c->any = any;
+	c->sf_pass = any ? 0.0 : c->scalefactor;
+	c->hit[0] = c->hit[1] = 0;
+	c->hit_local_d = 0;
+}
+__global__ void ms_pack_kernel(EmCtl* c) { c->hit_local_d = (double)c->hit[0]; }
+// End of a pass: the step-size control of cnF2freq.cpp:6373-6390.  reduced: hit_local_d holds the sum over ranks of the
+// local counts; control = 0 leaves scalefactor and the history alone (cnf2_mstep: the caller runs the control).
+__global__ void ms_end_kernel(EmCtl* c, int reduced, int control)
+{
+	const long long hitnnn = (reduced ? (long long)c->hit_local_d : (long long)c->hit[0]) + (long long)c->hit[1];
+	c->hitnnn_last = hitnnn;
+	if (!control) return;
+	const double oldscalefactor = c->scalefactor;
+	double sf = c->any ? 0.0 : oldscalefactor;  // :6341
+	const bool badhit = hitnnn > max(c->oldhitnnn, c->oldhitnnn2);
+	if (badhit) sf /= 1.1;
+	const bool goodhit = (double)hitnnn < max(min(c->oldhitnnn, c->oldhitnnn2), c->n_dous_total / NSLOTS) * 0.99;
+	if (goodhit) sf *= 1.21;
+	sf *= 0.997;
+	if (c->any) sf = oldscalefactor;
+	else
+	{
+		c->oldhitnnn2 = c->oldhitnnn;
+		c->oldhitnnn = (int32_t)hitnnn;
+	}
+	c->scalefactor = sf;
+}
+
+// ---- phase inversions (row f2): candidates and their application ----
+// Per row: the most negative phase-inversion score of the chromosome below -1e-10 and the first marker holding it
+// (cnF2freq.cpp:6272-6284); minstart = Mc when there is none.  One warp per row.
+__global__ void __launch_bounds__(128) negshift_minima_kernel(const double* stats_shared, const double* stats_local, int n_rows, int n_shared,
+                                                              int Mc, double* minval, int32_t* minstart)
+{
+	const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+	if (row >= n_rows) return;
+	const bool sh = row < n_shared;
+	const size_t nr = sh ? n_shared : n_rows - n_shared;
+	const double* ns = (sh ? stats_shared : stats_local) + 8 * nr * Mc + (size_t)(sh ? row : row - n_shared) * Mc;
+	double best = -1e-10;
+	int at = Mc;
+	for (int m = lane; m < Mc; m += 32)
+	{
+		const double v = ns[m];
+		if (v < best) best = v, at = m;  // strict: the first of equal minima in this lane
+	}
+	for (int o = 16; o > 0; o >>= 1)
+	{
+		const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+		const int oa = __shfl_xor_sync(0xffffffffu, at, o);
+		if (ob < best || (ob == best && oa < at)) best = ob, at = oa;
+	}
+	if (lane == 0) minval[row] = best, minstart[row] = at;
+}
+// negshifter (:3437-3459): from the marker after minstart to the chromosome's end the phase is inverted: haploweight
+// -> 1 - haploweight, haplobase -> haplocount - haplobase.  One block per candidate.
+__global__ void __launch_bounds__(128) apply_inversions_kernel(MstepArgs a, const int32_t* rows, const int32_t* minstart, int n)
+{
+	const int k = blockIdx.x;
+	if (k >= n) return;
+	const int row = rows[k];
+	for (int m = minstart[k] + 1 + threadIdx.x; m < a.Mc; m += blockDim.x)
+	{
+		const size_t idx = (size_t)row * a.Mc + m;
+		a.hw[idx] = 1.0 - a.hw[idx];
+		if (a.fresh)
+		{
+			const StatsCell cell = ms_cell(a, row, m);
+			*cell.haplobase = *cell.haplocount - *cell.haplobase;
+		}
+		else a.carry_base[idx] = a.carry_count[idx] - a.carry_base[idx];
 	}
 }
 }  // namespace cnf2

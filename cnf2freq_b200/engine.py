@@ -19,6 +19,7 @@ SYMBOLS = [
     "cnf2_last_estep_ms", "cnf2_last_estep_launches", "cnf2_stream", "cnf2_measure_peaks", "cnf2_mark",
     "cnf2_elapsed_ms", "cnf2_row_count", "cnf2_row_ids", "cnf2_get_stats_packed", "cnf2_set_params_packed", "cnf2_set_mstep_inputs",
     "cnf2_begin_iteration", "cnf2_mstep", "cnf2_get_params", "cnf2_get_negshift", "cnf2_get_negshift_packed",
+    "cnf2_set_em_state", "cnf2_get_em_state", "cnf2_mstep_pass", "cnf2_negshift_minima", "cnf2_apply_inversions", "cnf2_em_pass",
 ]
 
 
@@ -224,6 +225,44 @@ class Engine:
         self._check(self.lib.cnf2_mstep(self.h, ctypes.c_int32(chrom), ctypes.c_double(scalefactor),
                                         ctypes.c_double(entropyfactor), ctypes.byref(hit), ctypes.byref(sh)))
         return (int(hit.value), int(sh.value)) if split else int(hit.value)
+
+    # -- the EM loop on the device (rows a6 / f1 / f2): step-size control, phase inversions ------------------
+    def set_em_state(self, scalefactor=0.013, entropyfactor=1.0, oldhitnnn=0, oldhitnnn2=0):
+        self._check(self.lib.cnf2_set_em_state(self.h, ctypes.c_double(scalefactor), ctypes.c_double(entropyfactor),
+                                               ctypes.c_int32(int(oldhitnnn)), ctypes.c_int32(int(oldhitnnn2))))
+
+    def get_em_state(self):
+        """(scalefactor, entropyfactor, oldhitnnn, oldhitnnn2, hitnnn of the last pass); waits for the passes in flight."""
+        sf, ent = ctypes.c_double(), ctypes.c_double()
+        o1, o2, hit = ctypes.c_int32(), ctypes.c_int32(), ctypes.c_int64()
+        self._check(self.lib.cnf2_get_em_state(self.h, ctypes.byref(sf), ctypes.byref(ent), ctypes.byref(o1), ctypes.byref(o2),
+                                               ctypes.byref(hit)))
+        return float(sf.value), float(ent.value), int(o1.value), int(o2.value), int(hit.value)
+
+    def mstep_pass(self, chrom, any_inversion=False):
+        self._check(self.lib.cnf2_mstep_pass(self.h, ctypes.c_int32(chrom), ctypes.c_int32(1 if any_inversion else 0)))
+
+    def negshift_minima(self, chrom):
+        """(minval f64 [n_rows], minstart i32 [n_rows]) in row_ids() order; minstart = Mc where no score is below -1e-10."""
+        n = self.n_rows()
+        mv, ms = np.zeros(n, np.float64), np.zeros(n, np.int32)
+        self._check(self.lib.cnf2_negshift_minima(self.h, ctypes.c_int32(chrom), _ptr(mv), _ptr(ms)))
+        return mv, ms
+
+    def apply_inversions(self, chrom, ids, minstart):
+        ids = np.ascontiguousarray(ids, np.int32)
+        minstart = np.ascontiguousarray(minstart, np.int32)
+        if len(ids) != len(minstart):
+            raise EngineError("apply_inversions: ids and minstart differ in length")
+        self._check(self.lib.cnf2_apply_inversions(self.h, ctypes.c_int32(chrom), _ptr(ids), _ptr(minstart), ctypes.c_int32(len(ids))))
+
+    def em_pass(self, chrom, cap=4096):
+        """The reference's block behind a chromosome's E-step (candidates, inversions, M-step pass, step-size control);
+        returns the applied inversions as a list of (individual id, first inverted marker)."""
+        ids, mk, n = np.zeros(cap, np.int32), np.zeros(cap, np.int32), ctypes.c_int32()
+        self._check(self.lib.cnf2_em_pass(self.h, ctypes.c_int32(chrom), _ptr(ids), _ptr(mk), ctypes.c_int32(cap), ctypes.byref(n)))
+        k = min(int(n.value), cap)
+        return list(zip(ids[:k].tolist(), mk[:k].tolist()))
 
     def get_params(self, chrom, alleles, sure, haploweight):
         km = self.n_ind * self.n_markers

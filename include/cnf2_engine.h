@@ -163,8 +163,9 @@ int cnf2_get_negshift_packed(cnf2_engine* e, int32_t chrom, double* negshift);
  * steps (:4022-4032), from which the caller runs the step-size control (:6373-6390); with several ranks every rank
  * updates its copy of the shared rows (the all-reduced statistics are identical everywhere) and *hitnnn_shared (may be
  * NULL) is the part of *hitnnn those rows contributed: global hitnnn = sum over ranks of (hitnnn - hitnnn_shared) +
- * hitnnn_shared.  Phase inversions (negshifter,
- * :6336-6340) are host logic and not part of this call: lastinved is taken as -1 (:6290).
+ * hitnnn_shared.  Phase inversions (negshifter, :6336-6340) are applied with cnf2_apply_inversions before the
+ * pass; a pass that follows inversions runs with scalefactor 0 (:6341), where lastinved (:6290, the breakathalf
+ * argument of cappedgd) has no effect.
  * cnf2_set_mstep_inputs: relhaplo (:889), prior markerdata / markersure (:880-881) as [n_ind][n_markers](x2) arrays,
  * and per individual hasprior (priormarkerdata.size() > 0), children (:5246-5259), empty, descendants.  Needs the
  * parameters of all chromosomes resident.  cnf2_begin_iteration forgets the carried haplobase / haplocount
@@ -176,6 +177,40 @@ int cnf2_begin_iteration(cnf2_engine* e);
 int cnf2_mstep(cnf2_engine* e, int32_t chrom, double scalefactor, double entropyfactor, int64_t* hitnnn,
                int64_t* hitnnn_shared);
 int cnf2_get_params(cnf2_engine* e, int32_t chrom, uint8_t* alleles, double* sure, double* haploweight);
+
+/* ---- the EM loop without host round trips (rows a6 / f1 / f2) ---------------------------------------------------
+ * The reference's step-size control (cnF2freq.cpp:6333-6392: scalefactor /= 1.1 on a bad pass, *= 1.21 on a good one,
+ * *= 0.997 always, from hitnnn and its two-pass history oldhitnnn / oldhitnnn2, :4004-4005) lives on the device:
+ * cnf2_set_em_state uploads the globals (scalefactor :3573 = 0.013, entropyfactor :3574 = 1, history 0 at start),
+ * cnf2_mstep_pass enqueues -- asynchronously, behind chromosome `chrom`'s E-step -- the same pass as cnf2_mstep with
+ * the device's scalefactor, sums hitnnn over ranks (through the cnf2_set_allreduce hook) and runs the control;
+ * cnf2_get_em_state waits and reads the state back (hitnnn_last: the global count of the last pass, the number
+ * printed at :6392).  any_inversion != 0: the pass of an iteration in which phase inversions were applied -- it
+ * runs with scalefactor 0 and leaves scalefactor and the history as they were (:6339-6341, :6385).
+ *
+ * Phase inversions (negshifter :3437-3459; candidates :6270-6327): cnf2_negshift_minima gives, per row of
+ * cnf2_row_ids, the most negative phase-inversion score of the chromosome below -1e-10 and the first marker holding
+ * it (chromosome-relative; = Mc when there is none), i.e. minval / minstart of :6272-6284.  Which candidates to keep
+ * is host logic (inferiorrelated :3415-3435 over related individuals and libc rand(), :6319); cnf2_apply_inversions
+ * applies the kept ones to the device-resident state: haploweight -> 1 - haploweight and haplobase -> haplocount -
+ * haplobase from the marker after minstart to the chromosome's end (ids this engine does not hold are skipped).
+ * Call it before the cnf2_mstep_pass of the same pass, as the reference does (:6336-6340). */
+int cnf2_set_em_state(cnf2_engine* e, double scalefactor, double entropyfactor, int32_t oldhitnnn, int32_t oldhitnnn2);
+int cnf2_get_em_state(cnf2_engine* e, double* scalefactor, double* entropyfactor, int32_t* oldhitnnn, int32_t* oldhitnnn2,
+                      int64_t* hitnnn_last);
+int cnf2_mstep_pass(cnf2_engine* e, int32_t chrom, int32_t any_inversion);
+int cnf2_negshift_minima(cnf2_engine* e, int32_t chrom, double* minval, int32_t* minstart);
+int cnf2_apply_inversions(cnf2_engine* e, int32_t chrom, const int32_t* ids, const int32_t* minstart, int32_t n);
+
+/* The whole block the reference runs after a chromosome's E-step (cnF2freq.cpp:6239-6392) in one call: phase-inversion
+ * candidates of every chromosome analysed so far in this iteration (minima exchanged between ranks through the
+ * cnf2_set_allreduce hook; inferiorrelated / arerelated :916-946 and rand() on the host, in the reference's order:
+ * individuals by id, chromosomes inside), negshifter on all of them, then cnf2_mstep_pass.  The applied inversions
+ * are returned for the "Inv: <id> <marker>" lines (:3450; marker = the first inverted one, over all chromosomes; at
+ * most cap entries are written, *n_inv is the full count).  Uses libc rand() exactly as the reference does (:6319),
+ * so a host that never seeds or calls rand() elsewhere reproduces the reference binary's decisions.
+ * cnf2_begin_iteration forgets the candidates (negshiftcands is local to doit, :5261). */
+int cnf2_em_pass(cnf2_engine* e, int32_t chrom, int32_t* inv_ids, int32_t* inv_markers, int32_t cap, int32_t* n_inv);
 
 /* Block until everything enqueued by this engine has finished; returns the first asynchronous error. */
 int cnf2_sync(cnf2_engine* e);

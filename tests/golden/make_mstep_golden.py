@@ -1,8 +1,9 @@
-"""Golden fixtures of the M-step (row a6 / f1) from the REFERENCE's own code: for whole EM iterations of
+"""Golden fixtures of the M-step (rows a6 / f1 / f2) from the REFERENCE's own code: for whole EM iterations of
 oracle/_ref/cnf2ref (single-threaded) the parameters before doit(), the EM statistics as they stood before each
-chromosome's M-step pass ("FIRST PASS" hook of oracle/ref_driver.cpp), and the parameters + step-size scalars after
-doit().  Only iterations without phase inversions are kept (negshift > -1e-10 everywhere).  Only runs where
-/root/reference exists; the fixtures are committed.
+chromosome's M-step pass ("FIRST PASS" hook of oracle/ref_driver.cpp), the phase-inversion scores (negshift) and the
+inversions the reference applied in each pass (its "Inv: <id> <marker>" lines, cnF2freq.cpp:3450), and the
+parameters + step-size scalars after doit().  mstep_demo / mstep_f2 hold iterations without inversions,
+mstep_inv_* iterations with them.  Only runs where /root/reference exists; the fixtures are committed.
 
 usage: python tests/golden/make_mstep_golden.py
 """
@@ -24,16 +25,35 @@ REF = os.environ.get("CNF2_REFERENCE_DIR", "/root/reference")
 BIN = os.path.join(ROOT, "oracle", "_ref", "cnf2ref")
 
 
-def collect(prefix, iterations):
+def passes(stdout, C):
+    """Per pass (one per chromosome per iteration, closed by the "Scale factor now" line, :6392): the inversions applied."""
+    out, cur = [], []
+    for line in stdout.splitlines():
+        if line.startswith("Inv: "):
+            n, p = line.split()[1:3]
+            cur.append((int(n), int(p)))
+        elif line.startswith("Scale factor now"):
+            out.append(cur)
+            cur = []
+    return out
+
+
+def collect(prefix, iterations, stdout=None, allow_inversions=False):
     prob = read_dump(prefix + ".problem")
     C = len(prob["chromstarts"]) - 1
+    inv = passes(stdout, C) if stdout is not None else None
     out = dict(par=np.stack([prob["par0"], prob["par1"]], axis=1).astype(np.int32), exists=prob["exists"], empty=prob["empty"],
                hasprior=prob["hasprior"], descendants=prob["descendants"], dous=prob["dous"],
                chromstarts=prob["chromstarts"].astype(np.uint32), iterations=np.asarray(iterations), gen=prob["gen"],
                markerpos=prob["markerposes"], genrec=prob["genrec"])
     for it in iterations:
         a, b = read_dump(f"{prefix}.iter{it}.params"), read_dump(f"{prefix}.iter{it}.state")
-        assert b["negshift"].min() > -1e-10, "phase inversion in this iteration"
+        assert allow_inversions or b["negshift"].min() > -1e-10, "phase inversion in this iteration"
+        out[f"it{it}_negshift"] = b["negshift"]
+        if inv is not None:
+            for c in range(C):
+                lst = inv[(it - 1) * C + c]
+                out[f"it{it}_c{c}_inv"] = np.asarray(lst, np.int32).reshape(-1, 2)
         for k in ("alleles", "sure", "haploweight", "relhaplo", "prioralleles", "priorsure", "scalars", "founder"):
             out[f"it{it}_before_{k}"] = a[k]
         for k in ("alleles", "sure", "haploweight", "scalars", "children"):  # children is rebuilt inside doit (:5246-5259)
@@ -57,7 +77,21 @@ def main():
         args = ["--mapfile", tmp + "/f2.map", "--pedfile", tmp + "/f2.ped", "--genfile", tmp + "/f2.gen"]
         subprocess.run([BIN] + args + ["--count", "3", "--dump", tmp + "/f2"], env=env, capture_output=True, check=True)
         np.savez_compressed(os.path.join(HERE, "mstep_f2.npz"), **collect(tmp + "/f2", [1, 2]))
-    for n in ("mstep_demo.npz", "mstep_f2.npz"):
+        # iterations in which the reference inverts phases (demo: 6, 8, 9, 10; two-chromosome full-sib families: from 2 on)
+        args = ["--mapfile", f"{REF}/demoplantimpute.map", "--pedfile", f"{REF}/demoplantimpute.ped", "--genfile",
+                f"{REF}/demoplantimpute.gen"]
+        r = subprocess.run([BIN] + args + ["--count", "12", "--dump", tmp + "/inv"], env=env, capture_output=True, text=True, check=True)
+        g = collect(tmp + "/inv", list(range(1, 12)), r.stdout, True)
+        assert any(len(g[f"it{it}_c0_inv"]) for it in range(1, 12))
+        np.savez_compressed(os.path.join(HERE, "mstep_inv_demo.npz"), **g)
+        sim = synth.simulate_fullsib(n_fam=2, n_off=3, n_chrom=2, markers_per_chrom=12, spacing_cM=2.0, missing=0.1, seed=4)
+        synth.write_alpha_files(tmp + "/fs", sim)
+        args = ["--mapfile", tmp + "/fs.map", "--pedfile", tmp + "/fs.ped", "--genfile", tmp + "/fs.gen"]
+        r = subprocess.run([BIN] + args + ["--count", "7", "--dump", tmp + "/fs"], env=env, capture_output=True, text=True, check=True)
+        g = collect(tmp + "/fs", list(range(1, 7)), r.stdout, True)
+        assert any(len(g[f"it{it}_c{c}_inv"]) for it in range(1, 7) for c in range(2))
+        np.savez_compressed(os.path.join(HERE, "mstep_inv_fullsib.npz"), **g)
+    for n in ("mstep_demo.npz", "mstep_f2.npz", "mstep_inv_demo.npz", "mstep_inv_fullsib.npz"):
         print(n, os.path.getsize(os.path.join(HERE, n)), "bytes")
 
 
