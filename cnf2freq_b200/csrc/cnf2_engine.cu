@@ -60,6 +60,7 @@ struct Slot
 	DevBuf<unsigned int> counter;
 	int chrom = -1;
 	int n_shared = 0;
+	bool timed = false;  // ev0 / ev1 hold a launch whose duration has not been added to the engine's totals yet
 	double* stats_shared() { return stats.p; }
 	double* stats_local(int Mc) { return stats.p + (size_t)n_shared * Mc * STATS_PER_CELL; }
 };
@@ -137,6 +138,9 @@ struct cnf2_engine
 	cudaEvent_t marks[4] = { nullptr, nullptr, nullptr, nullptr };
 	cudaEvent_t params_ready = nullptr;  // behind the last cnf2_set_params copies on `stream`
 	int last_launches = 0;
+	double estep_ms_sum = 0;  // device time of the E-step kernels (ev0 -> ev1 of every cnf2_estep), see cnf2_estep_times
+	int64_t estep_ms_n = 0;
+	int64_t n_kernels = 0;    // kernels launched by this engine since the last reset
 	cnf2_allreduce_fn allreduce = nullptr;
 	void* allreduce_ctx = nullptr;
 
@@ -151,6 +155,17 @@ struct cnf2_engine
 		return fail(CNF2_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
 	}
 	int mc(int chrom) const { return (int)(chromstarts[chrom + 1] - chromstarts[chrom]); }
+	int collect_time(Slot& sl)
+	{
+		if (!sl.timed) return 0;
+		float ms = 0;
+		if (int rc = cuda(cudaEventSynchronize(sl.ev1), "cudaEventSynchronize(ev1)")) return rc;
+		if (int rc = cuda(cudaEventElapsedTime(&ms, sl.ev0, sl.ev1), "cudaEventElapsedTime")) return rc;
+		estep_ms_sum += ms;
+		estep_ms_n++;
+		sl.timed = false;
+		return 0;
+	}
 	int wait_chain(cudaStream_t st)
 	{
 		if (!chain_set) return 0;
@@ -726,6 +741,7 @@ extern "C" int cnf2_estep(cnf2_engine* e, int32_t chrom)
 	CU(sl.stats.ensure((size_t)e->n_rows * e->max_mc * STATS_PER_CELL));
 	sl.n_shared = e->n_shared;
 	sl.chrom = chrom;
+	if (int rc = e->collect_time(sl)) return rc;  // the launch this slot held before (n_slots E-steps ago): long finished
 	CU(cudaStreamWaitEvent(sl.stream, e->params_ready, 0));
 	if (int rc = e->wait_chain(sl.stream)) return rc;  // the parameters an earlier M-step pass or phase inversion is still writing
 	CU(cudaEventRecord(sl.ev0, sl.stream));
@@ -770,6 +786,7 @@ extern "C" int cnf2_estep(cnf2_engine* e, int32_t chrom)
 			const size_t smem = warp_smem_bytes(e->cap0, e->cap1, e->cls);
 			if (e->cls) warp_estep_kernel<true><<<grid, 32, smem, sl.stream>>>(wa);
 			else warp_estep_kernel<false><<<grid, 32, smem, sl.stream>>>(wa);
+			e->n_kernels++;
 			CU(cudaGetLastError());
 			e->last_launches++;
 			a.unit_list = sl.literal.p;
@@ -777,10 +794,12 @@ extern "C" int cnf2_estep(cnf2_engine* e, int32_t chrom)
 			a.counter = sl.counter.p + 2;
 		}
 		estep_kernel<<<std::max(1, std::min(e->n_ctas_literal, n_units)), NTHREADS, sizeof(Smem), sl.stream>>>(a);
+		e->n_kernels++;
 		CU(cudaGetLastError());
 		e->last_launches++;
 	}
 	CU(cudaEventRecord(sl.ev1, sl.stream));
+	sl.timed = true;
 	if (e->allreduce && e->n_shared > 0)
 	{
 		// the hook runs on one stream for all slots, so every rank issues its collectives in the order of its cnf2_estep calls
@@ -847,11 +866,9 @@ extern "C" int cnf2_get_stats(cnf2_engine* e, int32_t chrom, double* haplobase, 
 	return CNF2_OK;
 }
 
-extern "C" int cnf2_set_mstep_inputs(cnf2_engine* e, const double* relhaplo, const uint8_t* prioralleles, const double* priorsure,
-                                     const uint8_t* hasprior, const int32_t* children, const uint8_t* empty,
-                                     const int32_t* descendants)
+// device arrays of the M-step: every chromosome's block, the control state
+static int ms_alloc(cnf2_engine* e)
 {
-	if (!e || !relhaplo || !prioralleles || !priorsure || !hasprior || !children || !empty || !descendants) return CNF2_ERR_BAD_ARG;
 	if (e->chromstarts.empty() || e->rowof.empty()) return e->fail(CNF2_ERR_STATE, "cnf2_set_mstep_inputs: set_map and set_pedigree first");
 	if (!e->resident) return e->fail(CNF2_ERR_STATE, "cnf2_set_mstep_inputs: the M-step needs the parameters of all chromosomes resident");
 	cudaSetDevice(e->settings.device);
@@ -870,22 +887,20 @@ extern "C" int cnf2_set_mstep_inputs(cnf2_engine* e, const double* relhaplo, con
 		EmCtl init{};
 		init.scalefactor = 0.013;  // :3573
 		init.entropyfactor = 1;    // :3574
+		init.n_dous_total = e->n_dous_total;
 		CU(cudaMemcpyAsync(e->d_ctl.p, &init, sizeof(init), cudaMemcpyHostToDevice, e->stream));
 	}
 	CU(e->d_minval.ensure(e->n_rows));
 	CU(e->d_minstart.ensure(e->n_rows));
 	CU(e->d_msrows.ensure(e->n_rows));
-	for (size_t c = 0; c + 1 < e->chromstarts.size(); c++)
-	{
-		const size_t c0 = e->chromstarts[c], Mc = e->mc((int)c), blk = (size_t)e->n_rows * c0;
-		for (const Run& r : e->runs)
-		{
-			const size_t src = (size_t)r.id0 * M + c0, dst = blk + (size_t)r.row0 * Mc;
-			CU(cudaMemcpy2DAsync(e->d_relhaplo.p + dst, Mc * 8, relhaplo + src, M * 8, Mc * 8, r.n, cudaMemcpyHostToDevice, e->stream));
-			CU(cudaMemcpy2DAsync(e->d_prioral.p + dst, Mc * 2, prioralleles + src * 2, M * 2, Mc * 2, r.n, cudaMemcpyHostToDevice, e->stream));
-			CU(cudaMemcpy2DAsync(e->d_priorsure.p + dst, Mc * 16, priorsure + src * 2, M * 16, Mc * 16, r.n, cudaMemcpyHostToDevice, e->stream));
-		}
-	}
+	return CNF2_OK;
+}
+
+extern "C" int cnf2_set_mstep_rows(cnf2_engine* e, const uint8_t* hasprior, const int32_t* children, const uint8_t* empty,
+                                   const int32_t* descendants)
+{
+	if (!e || !hasprior || !children || !empty || !descendants) return CNF2_ERR_BAD_ARG;
+	if (int rc = ms_alloc(e)) return rc;
 	std::vector<MstepRow> rows(e->n_rows);
 	for (int32_t r = 0; r < e->n_rows; r++)
 	{
@@ -897,6 +912,44 @@ extern "C" int cnf2_set_mstep_inputs(cnf2_engine* e, const double* relhaplo, con
 	e->carry_valid.assign(e->chromstarts.size() - 1, 0);
 	e->have_ms_inputs = true;
 	return CNF2_OK;
+}
+
+extern "C" int cnf2_set_mstep_chrom_packed(cnf2_engine* e, int32_t chrom, const double* relhaplo, const uint8_t* prioralleles,
+                                           const double* priorsure)
+{
+	if (!e || !relhaplo || !prioralleles || !priorsure) return CNF2_ERR_BAD_ARG;
+	if (int rc = ms_alloc(e)) return rc;
+	if (chrom < 0 || chrom + 1 >= (int)e->chromstarts.size()) return e->fail(CNF2_ERR_BAD_ARG, "cnf2_set_mstep_chrom_packed: bad chromosome");
+	const size_t Mc = e->mc(chrom), n = (size_t)e->n_rows * Mc, blk = (size_t)e->n_rows * e->chromstarts[chrom];
+	if (int rc = e->wait_chain(e->stream)) return rc;
+	CU(cudaMemcpyAsync(e->d_relhaplo.p + blk, relhaplo, n * 8, cudaMemcpyHostToDevice, e->stream));
+	CU(cudaMemcpyAsync(e->d_prioral.p + blk, prioralleles, n * 2, cudaMemcpyHostToDevice, e->stream));
+	CU(cudaMemcpyAsync(e->d_priorsure.p + blk, priorsure, n * 16, cudaMemcpyHostToDevice, e->stream));
+	CU(cudaEventRecord(e->params_ready, e->stream));
+	if (!e->settings.async_params) CU(cudaStreamSynchronize(e->stream));
+	return CNF2_OK;
+}
+
+extern "C" int cnf2_set_mstep_inputs(cnf2_engine* e, const double* relhaplo, const uint8_t* prioralleles, const double* priorsure,
+                                     const uint8_t* hasprior, const int32_t* children, const uint8_t* empty,
+                                     const int32_t* descendants)
+{
+	if (!e || !relhaplo || !prioralleles || !priorsure || !hasprior || !children || !empty || !descendants) return CNF2_ERR_BAD_ARG;
+	if (int rc = ms_alloc(e)) return rc;
+	const size_t M = e->markerpos.size();
+	for (size_t c = 0; c + 1 < e->chromstarts.size(); c++)
+	{
+		const size_t c0 = e->chromstarts[c], Mc = e->mc((int)c), blk = (size_t)e->n_rows * c0;
+		for (const Run& r : e->runs)
+		{
+			const size_t src = (size_t)r.id0 * M + c0, dst = blk + (size_t)r.row0 * Mc;
+			CU(cudaMemcpy2DAsync(e->d_relhaplo.p + dst, Mc * 8, relhaplo + src, M * 8, Mc * 8, r.n, cudaMemcpyHostToDevice, e->stream));
+			CU(cudaMemcpy2DAsync(e->d_prioral.p + dst, Mc * 2, prioralleles + src * 2, M * 2, Mc * 2, r.n, cudaMemcpyHostToDevice, e->stream));
+			CU(cudaMemcpy2DAsync(e->d_priorsure.p + dst, Mc * 16, priorsure + src * 2, M * 16, Mc * 16, r.n, cudaMemcpyHostToDevice, e->stream));
+		}
+	}
+	CU(cudaStreamSynchronize(e->stream));
+	return cnf2_set_mstep_rows(e, hasprior, children, empty, descendants);
 }
 
 extern "C" int cnf2_begin_iteration(cnf2_engine* e)
@@ -925,6 +978,7 @@ static int enqueue_pass(cnf2_engine* e, int32_t chrom, int any, int set, double 
 	const int C = (int)e->chromstarts.size() - 1;
 	if (int rc = e->wait_chain(sl.stream)) return rc;
 	ms_begin_kernel<<<1, 1, 0, sl.stream>>>(e->d_ctl.p, any, set, sf, ent);
+	e->n_kernels++;
 	if (e->n_rows > 0)
 	{
 		MstepArgs g{};
@@ -972,7 +1026,7 @@ static int enqueue_pass(cnf2_engine* e, int32_t chrom, int any, int set, double 
 		const unsigned gr = (unsigned)((e->n_rows + 127) / 128);
 		CU(cudaEventRecord(e->ms_fork, sl.stream));
 		CU(cudaStreamWaitEvent(e->side, e->ms_fork, 0));
-		for (const MstepPass& p : launches) mstep_relskew_kernel<<<dim3(gr, p.n), 128, 0, e->side>>>(p);
+		for (const MstepPass& p : launches) e->n_kernels++, mstep_relskew_kernel<<<dim3(gr, p.n), 128, 0, e->side>>>(p);
 		CU(cudaEventRecord(e->ms_join, e->side));
 		{
 			MstepArgs a = g;
@@ -981,6 +1035,7 @@ static int enqueue_pass(cnf2_engine* e, int32_t chrom, int any, int set, double 
 			a.Mc = e->mc(chrom);
 			a.fresh = 1;
 			mstep_infprobs_kernel<<<(unsigned)(((size_t)e->n_rows * a.Mc + 127) / 128), 128, 0, sl.stream>>>(a);
+			e->n_kernels++;
 		}
 		CU(cudaStreamWaitEvent(sl.stream, e->ms_join, 0));
 		for (const MstepPass& p : launches)
@@ -988,6 +1043,7 @@ static int enqueue_pass(cnf2_engine* e, int32_t chrom, int any, int set, double 
 			int maxmc = 0;
 			for (int k = 0; k < p.n; k++) maxmc = std::max(maxmc, p.Mc[k]);
 			mstep_haploweight_kernel<<<dim3((unsigned)(((size_t)e->n_rows * maxmc + 127) / 128), p.n), 128, 0, sl.stream>>>(p);
+			e->n_kernels++;
 		}
 		CU(cudaGetLastError());
 	}
@@ -997,6 +1053,7 @@ static int enqueue_pass(cnf2_engine* e, int32_t chrom, int any, int set, double 
 	{
 		// global hitnnn = sum over ranks of the local counts + the shared rows' count (identical on every rank)
 		ms_pack_kernel<<<1, 1, 0, sl.stream>>>(e->d_ctl.p);
+		e->n_kernels++;
 		CU(cudaEventRecord(sl.tail, sl.stream));
 		CU(cudaStreamWaitEvent(e->comm, sl.tail, 0));
 		const int rc = e->allreduce(e->allreduce_ctx, &e->d_ctl.p->hit_local_d, 1, (void*)e->comm);
@@ -1006,6 +1063,7 @@ static int enqueue_pass(cnf2_engine* e, int32_t chrom, int any, int set, double 
 		reduced = 1;
 	}
 	ms_end_kernel<<<1, 1, 0, sl.stream>>>(e->d_ctl.p, reduced, control);
+	e->n_kernels++;
 	CU(cudaGetLastError());
 	return e->mark_chain(sl.stream);
 }
@@ -1085,6 +1143,7 @@ extern "C" int cnf2_negshift_minima(cnf2_engine* e, int32_t chrom, double* minva
 	const int Mc = e->mc(chrom);
 	negshift_minima_kernel<<<(unsigned)((e->n_rows * 32 + 127) / 128), 128, 0, sl.stream>>>(sl.stats_shared(), sl.stats_local(Mc), e->n_rows,
 	                                                                                     e->n_shared, Mc, e->d_minval.p, e->d_minstart.p);
+	e->n_kernels++;
 	CU(cudaGetLastError());
 	CU(cudaMemcpyAsync(minval, e->d_minval.p, (size_t)e->n_rows * sizeof(double), cudaMemcpyDeviceToHost, sl.stream));
 	CU(cudaMemcpyAsync(minstart, e->d_minstart.p, (size_t)e->n_rows * sizeof(int32_t), cudaMemcpyDeviceToHost, sl.stream));
@@ -1140,6 +1199,7 @@ extern "C" int cnf2_apply_inversions(cnf2_engine* e, int32_t chrom, const int32_
 	a.Mc = Mc;
 	a.fresh = fresh ? 1 : 0;
 	apply_inversions_kernel<<<(unsigned)rows.size(), 128, 0, st>>>(a, e->d_invrows.p, e->d_invstart.p, (int)rows.size());
+	e->n_kernels++;
 	CU(cudaGetLastError());
 	if (int rc = e->mark_chain(st)) return rc;
 	if (slp) CU(cudaStreamWaitEvent(slp->stream, e->ms_chain, 0));  // the chromosome's own pass reads what was just flipped
@@ -1353,6 +1413,48 @@ extern "C" int cnf2_get_negshift_packed(cnf2_engine* e, int32_t chrom, double* n
 	}
 	CU(cudaStreamSynchronize(sl.stream));
 	CU(cudaGetLastError());
+	return CNF2_OK;
+}
+
+extern "C" int cnf2_estep_times(cnf2_engine* e, double* sum_ms, int64_t* n_launches, int64_t* n_kernels, int32_t reset)
+{
+	if (!e) return CNF2_ERR_BAD_ARG;
+	cudaSetDevice(e->settings.device);
+	for (Slot& sl : e->slots)
+		if (int rc = e->collect_time(sl)) return rc;
+	if (sum_ms) *sum_ms = e->estep_ms_sum;
+	if (n_launches) *n_launches = e->estep_ms_n;
+	if (n_kernels) *n_kernels = e->n_kernels;
+	if (reset) e->estep_ms_sum = 0, e->estep_ms_n = 0, e->n_kernels = 0;
+	return CNF2_OK;
+}
+
+extern "C" int cnf2_mstep_counters(cnf2_engine* e, uint64_t* evals, int32_t reset)
+{
+	if (!e) return CNF2_ERR_BAD_ARG;
+	if (!e->have_ms_inputs) return e->fail(CNF2_ERR_STATE, "cnf2_mstep_counters: cnf2_set_mstep_inputs first");
+	cudaSetDevice(e->settings.device);
+	if (int rc = cnf2_sync(e)) return rc;
+	EmCtl c{};
+	CU(cudaMemcpy(&c, e->d_ctl.p, sizeof(c), cudaMemcpyDeviceToHost));
+	if (evals) evals[0] = c.evals[0], evals[1] = c.evals[1];
+	if (reset) CU(cudaMemset(&e->d_ctl.p->evals[0], 0, sizeof(c.evals)));
+	return CNF2_OK;
+}
+
+extern "C" int cnf2_get_params_packed(cnf2_engine* e, int32_t chrom, uint8_t* alleles, double* sure, double* haploweight)
+{
+	if (!e) return CNF2_ERR_BAD_ARG;
+	if (chrom < 0 || chrom >= (int)e->have_params.size() || !e->have_params[chrom])
+		return e->fail(CNF2_ERR_STATE, "cnf2_get_params_packed: no parameters of this chromosome on the device");
+	cudaSetDevice(e->settings.device);
+	const size_t c0 = e->chromstarts[chrom], Mc = e->mc(chrom), n = (size_t)e->n_rows * Mc;
+	const size_t blk = (size_t)e->n_rows * (e->resident ? c0 : 0);
+	if (int rc = e->wait_chain(e->stream)) return rc;
+	if (alleles) CU(cudaMemcpyAsync(alleles, e->d_alleles.p + blk, n * 2, cudaMemcpyDeviceToHost, e->stream));
+	if (sure) CU(cudaMemcpyAsync(sure, e->d_sure.p + blk, n * 16, cudaMemcpyDeviceToHost, e->stream));
+	if (haploweight) CU(cudaMemcpyAsync(haploweight, e->d_hw.p + blk, n * 8, cudaMemcpyDeviceToHost, e->stream));
+	CU(cudaStreamSynchronize(e->stream));
 	return CNF2_OK;
 }
 

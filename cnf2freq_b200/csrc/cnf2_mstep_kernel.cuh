@@ -39,6 +39,9 @@ struct EmCtl
 	long long hitnnn_last;        // global hitnnn of the last finished pass
 	int32_t oldhitnnn, oldhitnnn2;
 	int32_t n_dous_total, any;
+	// measurement (bench.py's M-step roofline): gradient evaluations the solves made since the last reset --
+	// [0] processinfprobs (MODE 0), [1] updatehaploweights (MODE 1); 15 per integral, 1 per midpoint and start
+	unsigned long long evals[2];
 };
 
 struct MstepArgs
@@ -211,7 +214,7 @@ __device__ unsigned long long ms_hist[2][64];
 #endif
 template <int MODE>
 __device__ __forceinline__ double ms_cappedgd_warp(const MsParams& P, double orig, double scalefactor, bool active, unsigned long long& hit,
-                                                   double* stage, bool count_only = false)
+                                                   double* stage, unsigned& evals, bool count_only = false)
 {
 	const unsigned FULL = 0xffffffffu;
 	const int lane = threadIdx.x & 31, half = lane >> 4, q = lane & 15;
@@ -258,6 +261,7 @@ __device__ __forceinline__ double ms_cappedgd_warp(const MsParams& P, double ori
 		hi = hilim + epsilon * 0.125;
 		orig = ms_caplogit(orig, orig, epsilon, dump);
 		const double gradval = ms_actual<MODE>(P, orig);
+		evals++;
 		if (!isfinite(gradval) || !scalefactor)
 		{
 			lo = orig;
@@ -284,6 +288,7 @@ __device__ __forceinline__ double ms_cappedgd_warp(const MsParams& P, double ori
 #endif
 			mid = (lo + hi) / 2;
 			const double g = ms_actual<MODE>(P, mid);
+			evals++;
 			if (((g < 0) != lowside) || !isfinite(g)) prel = (scalefactor + 0.1) * 1.1;
 			else
 			{
@@ -295,7 +300,7 @@ __device__ __forceinline__ double ms_cappedgd_warp(const MsParams& P, double ori
 					end = t;
 				}
 				if (end - start < 1e-10) done = true;
-				else pending = true;
+				else pending = true, evals += 15;
 			}
 		}
 		// integrals of the lanes that need one: two per round (one per half-warp), two rounds at a time while there are
@@ -403,6 +408,7 @@ __global__ void __launch_bounds__(MS_BLOCK, 5) mstep_infprobs_kernel(MstepArgs a
 	const double scalefactor = a.ctl->sf_pass;
 	const double epsilon = ms_epsilon(r.children), etf = 1 * a.ctl->entropyfactor;
 	unsigned long long hit = 0;
+	unsigned evals = 0;
 #pragma unroll 1
 	for (int side = 0; side < 2; side++)
 	{
@@ -434,7 +440,7 @@ __global__ void __launch_bounds__(MS_BLOCK, 5) mstep_infprobs_kernel(MstepArgs a
 				}
 			}
 			const MsParams P = ms_params(curprob, ip[k], sum, etf, etf * priord, 0.0, 0.0, epsilon);
-			const double res = ms_cappedgd_warp<0>(P, curprob, scalefactor, active, hit, &stage[0][0], r.empty || !r.hasprior);
+			const double res = ms_cappedgd_warp<0>(P, curprob, scalefactor, active, hit, &stage[0][0], evals, r.empty || !r.hasprior);
 			if (active) ip[k] = res;
 		}
 		double bestprob = 0;
@@ -460,6 +466,8 @@ __global__ void __launch_bounds__(MS_BLOCK, 5) mstep_infprobs_kernel(MstepArgs a
 		a.sure[idx] = su;
 		if (hit) atomicAdd(a.ctl->hit + (row < a.n_shared ? 1 : 0), hit);
 	}
+	evals = __reduce_add_sync(0xffffffffu, evals);
+	if ((threadIdx.x & 31) == 0 && evals) atomicAdd(a.ctl->evals + 0, (unsigned long long)evals);
 }
 
 // relskewhmm (:4325-4467, realhmm): one thread per row walks the chromosome forward (stores the two forward values per
@@ -631,7 +639,10 @@ __global__ void __launch_bounds__(MS_BLOCK, 6) mstep_haploweight_kernel(MstepPas
 	const MsParams P = ms_params(w, hb, hc, (1 - similarity) * 1, a.ctl->entropyfactor, active ? a.ratio[idx] : 0.0, (double)r.descendants,
 	                             ms_epsilon(r.children));
 	unsigned long long hit = 0;
-	const double res = ms_cappedgd_warp<1>(P, w, a.ctl->sf_pass, active, hit, &stage[0][0]);
+	unsigned evals = 0;
+	const double res = ms_cappedgd_warp<1>(P, w, a.ctl->sf_pass, active, hit, &stage[0][0], evals);
+	evals = __reduce_add_sync(0xffffffffu, evals);
+	if ((threadIdx.x & 31) == 0 && evals) atomicAdd(a.ctl->evals + 1, (unsigned long long)evals);
 	if (active)
 	{
 		a.hw[idx] = res;

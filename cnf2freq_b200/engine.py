@@ -20,6 +20,7 @@ SYMBOLS = [
     "cnf2_elapsed_ms", "cnf2_row_count", "cnf2_row_ids", "cnf2_get_stats_packed", "cnf2_set_params_packed", "cnf2_set_mstep_inputs",
     "cnf2_begin_iteration", "cnf2_mstep", "cnf2_get_params", "cnf2_get_negshift", "cnf2_get_negshift_packed",
     "cnf2_set_em_state", "cnf2_get_em_state", "cnf2_mstep_pass", "cnf2_negshift_minima", "cnf2_apply_inversions", "cnf2_em_pass",
+    "cnf2_set_mstep_rows", "cnf2_set_mstep_chrom_packed", "cnf2_get_params_packed", "cnf2_estep_times", "cnf2_mstep_counters",
 ]
 
 
@@ -215,6 +216,21 @@ class Engine:
             _buf(c(children, np.int32), np.int32, k, "children"), _buf(c(empty, np.uint8), np.uint8, k, "empty"),
             _buf(c(descendants, np.int32), np.int32, k, "descendants")))
 
+    def set_mstep_rows(self, hasprior, children, empty, descendants):
+        c, k = np.ascontiguousarray, self.n_ind
+        self._check(self.lib.cnf2_set_mstep_rows(
+            self.h, _buf(c(hasprior, np.uint8), np.uint8, k, "hasprior"), _buf(c(children, np.int32), np.int32, k, "children"),
+            _buf(c(empty, np.uint8), np.uint8, k, "empty"), _buf(c(descendants, np.int32), np.int32, k, "descendants")))
+
+    def set_mstep_chrom_packed(self, chrom, relhaplo, prioralleles, priorsure):
+        """Row-ordered arrays of this chromosome: relhaplo f64 [n_rows][Mc], prioralleles u8 [n_rows][Mc][2], priorsure f64
+        [n_rows][Mc][2]."""
+        n = self.n_rows() * self.mc(chrom)
+        self._check(self.lib.cnf2_set_mstep_chrom_packed(
+            self.h, ctypes.c_int32(chrom), _buf(relhaplo, np.float64, n, "set_mstep_chrom_packed relhaplo"),
+            _buf(prioralleles, np.uint8, 2 * n, "set_mstep_chrom_packed prioralleles"),
+            _buf(priorsure, np.float64, 2 * n, "set_mstep_chrom_packed priorsure")))
+
     def begin_iteration(self):
         self._check(self.lib.cnf2_begin_iteration(self.h))
 
@@ -269,6 +285,24 @@ class Engine:
         self._check(self.lib.cnf2_get_params(self.h, ctypes.c_int32(chrom), _buf(alleles, np.uint8, 2 * km, "get_params alleles"),
                                              _buf(sure, np.float64, 2 * km, "get_params sure"),
                                              _buf(haploweight, np.float64, km, "get_params haploweight")))
+
+    def get_params_packed(self, chrom, alleles, sure, haploweight):
+        n = self.n_rows() * self.mc(chrom)
+        self._check(self.lib.cnf2_get_params_packed(self.h, ctypes.c_int32(chrom), _buf(alleles, np.uint8, 2 * n, "get_params_packed alleles"),
+                                                    _buf(sure, np.float64, 2 * n, "get_params_packed sure"),
+                                                    _buf(haploweight, np.float64, n, "get_params_packed haploweight")))
+
+    def estep_times(self, reset=False):
+        """(summed device ms of the E-step kernels, their launches, kernels of any kind launched) since the last reset."""
+        ms, n, k = ctypes.c_double(), ctypes.c_int64(), ctypes.c_int64()
+        self._check(self.lib.cnf2_estep_times(self.h, ctypes.byref(ms), ctypes.byref(n), ctypes.byref(k), ctypes.c_int32(1 if reset else 0)))
+        return float(ms.value), int(n.value), int(k.value)
+
+    def mstep_counters(self, reset=False):
+        """Gradient evaluations of the step solver since the last reset: (processinfprobs, updatehaploweights)."""
+        ev = (ctypes.c_uint64 * 2)()
+        self._check(self.lib.cnf2_mstep_counters(self.h, ev, ctypes.c_int32(1 if reset else 0)))
+        return int(ev[0]), int(ev[1])
 
     def sync(self):
         self._check(self.lib.cnf2_sync(self.h))

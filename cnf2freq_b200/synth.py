@@ -204,3 +204,96 @@ def fullsib_flat(n_fam, n_off, n_chrom, markers_per_chrom, spacing_cM=0.02, miss
     return dict(par=par, empty=empty, founder=founder, gen=gen, descendants=desc, dous=np.asarray(dous, np.int32),
                 markerpos=pos, chromstarts=cs, genrec=np.full(3, -1.0 / 50), alleles=alleles, sure=sure, haploweight=hw,
                 shared=np.zeros(0, np.int32))
+
+
+class F2Shard:
+    """One rank's part of an F2 design of `n_total` analysed individuals (cfg3 / cfg5 shapes): `lines` inbred founder lines
+    (2: line A all `2`, line B all `1` -- the F2 intercross of cfg3; more: homozygous with allele frequency 0.5, biparental
+    families of `fam_size` F2s each -- cfg5).  The pedigree arrays cover the whole design (ids: 0 none, 1..lines the
+    founders, then per F2 itself, its F1 father, its F1 mother: the implicit `empty` F1s of readalphaped,
+    cnF2freq.cpp:6515-6527); genotypes exist only for the `count` F2s from `first` on, and parameters are produced per
+    chromosome in a caller-given row order (the engine's cnf2_row_ids) -- the packed form of the C ABI, so no
+    [n_ind][n_markers] array is ever built.  State as the reference holds it during its EM iterations (see f2_flat)."""
+
+    def __init__(self, n_total, first, count, n_chrom, markers_per_chrom, spacing_cM=0.1, missing=0.2, seed=3, lines=2,
+                 fam_size=None):
+        self.pos, self.cs = make_map(n_chrom, markers_per_chrom, spacing_cM)
+        M = self.pos.shape[0]
+        L = self.L = lines
+        self.first, self.count, self.M = first, count, M
+        fam_size = fam_size or n_total
+        if L == 2:
+            self.line = np.stack([np.full(M, 2, np.uint8), np.full(M, 1, np.uint8)])
+        else:
+            self.line = np.random.default_rng([seed, 1 << 20]).integers(1, 3, size=(L, M)).astype(np.uint8)
+        fam = np.arange(n_total) // fam_size
+        self.pa = (fam % L).astype(np.int64)
+        self.pb = ((fam + 1 + fam // L) % L).astype(np.int64)
+        self.pb = np.where(self.pb == self.pa, (self.pb + 1) % L, self.pb)
+        rng = np.random.default_rng([seed, first])
+        self.g = np.zeros((count, M, 2), np.uint8)
+        loc = np.arange(first, first + count)
+        for f in np.unique(fam[loc]):
+            sel = np.nonzero(fam[loc] == f)[0]
+            f1 = np.stack([self.line[self.pa[loc[sel[0]]]], self.line[self.pb[loc[sel[0]]]]])
+            self.g[sel, :, 0] = _gametes(rng, f1, self.pos, self.cs, len(sel))
+            self.g[sel, :, 1] = _gametes(rng, f1, self.pos, self.cs, len(sel))
+        self.g[rng.random((count, M)) < missing] = 0
+        K = 1 + L + 3 * n_total
+        self.base = 1 + L
+        f2 = self.base + 3 * np.arange(n_total)
+        self.par = np.zeros((K, 2), np.int32)
+        self.par[f2, 0], self.par[f2, 1] = f2 + 1, f2 + 2
+        for off in (1, 2):
+            self.par[f2 + off, 0], self.par[f2 + off, 1] = 1 + self.pa, 1 + self.pb
+        self.empty = np.zeros(K, np.uint8)
+        self.empty[0] = self.empty[f2 + 1] = self.empty[f2 + 2] = 1
+        self.gen = np.zeros(K, np.int32)
+        self.gen[f2], self.gen[f2 + 1], self.gen[f2 + 2] = 2, 1, 1
+        self.descendants = np.zeros(K, np.int32)
+        self.descendants[f2] = 1
+        self.founder = np.zeros(K, np.uint8)
+        self.founder[1:1 + L] = 1
+        self.all_dous = f2.astype(np.int32)
+        self.dous = self.all_dous[first:first + count].copy()
+        self.shared = np.arange(1, 1 + L, dtype=np.int32)
+        self.genrec = np.full(3, -1.0 / 50)
+        self.hasprior = (1 - self.empty).astype(np.uint8)   # readalphadata copies the genotypes it reads (:6664-6665)
+        # individ::children: counted over everybody in postmarkerdata (:3257-3263), then once more over the analysed
+        # individuals by each doit (:5246-5259, never reset): the value during the first EM iteration
+        self.children = (np.bincount(self.par.ravel(), minlength=K) + np.bincount(self.par[self.all_dous].ravel(), minlength=K)).astype(np.int32)
+        self.children[0] = 0
+
+    def params(self, ids, c, out=None):
+        """(alleles u8 [R][Mc][2], sure f64 [R][Mc][2], haploweight f64 [R][Mc]) of chromosome c for the rows `ids`."""
+        cols = slice(int(self.cs[c]), int(self.cs[c + 1]))
+        Mc, R = cols.stop - cols.start, len(ids)
+        al, su, hw = out if out is not None else (np.zeros((R, Mc, 2), np.uint8), np.zeros((R, Mc, 2)), np.zeros((R, Mc)))
+        ids = np.asarray(ids, np.int64)
+        al[...], su[...], hw[...] = 0, 0, 0.5
+        rf = np.nonzero((ids >= 1) & (ids < self.base))[0]
+        al[rf] = self.line[ids[rf] - 1][:, cols, None]
+        su[rf] = 0.02
+        gk, off = (ids - self.base) // 3, (ids - self.base) % 3
+        k = gk - self.first
+        own = (ids >= self.base) & (k >= 0) & (k < self.count)
+        r2 = np.nonzero(own & (off == 0))[0]
+        a = self.g[k[r2], cols]
+        al[r2] = a
+        su[r2] = np.where((a == 0), 0.0, 0.02)
+        r1 = np.nonzero(own & (off != 0))[0]
+        al[r1, :, 0] = self.line[self.pa[gk[r1]]][:, cols]   # fixkid (:1469-1487): a homozygous parent's allele, sureness 0.5
+        al[r1, :, 1] = self.line[self.pb[gk[r1]]][:, cols]
+        su[r1] = 0.5
+        hw[r1, 0] = 0.0   # phase locked at the first marker of the chromosome (lockhaplos, :3045-3079)
+        return al, su, hw
+
+    def priors(self, ids, c, out=None):
+        """(relhaplo, prior alleles, prior markersure) of chromosome c: relhaplo 0.5 (:2496), priors = the genotypes as read."""
+        cols = int(self.cs[c + 1]) - int(self.cs[c])
+        rel, al, su = out if out is not None else (np.zeros((len(ids), cols)), np.zeros((len(ids), cols, 2), np.uint8), np.zeros((len(ids), cols, 2)))
+        self.params(ids, c, out=(al, su, rel))   # rel doubles as the haploweight scratch
+        noprior = self.hasprior[np.asarray(ids, np.int64)] == 0
+        al[noprior], su[noprior] = 0, 0
+        rel[...] = 0.5
+        return rel, al, su

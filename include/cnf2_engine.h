@@ -173,10 +173,21 @@ int cnf2_get_negshift_packed(cnf2_engine* e, int32_t chrom, double* negshift);
 int cnf2_set_mstep_inputs(cnf2_engine* e, const double* relhaplo, const uint8_t* prioralleles, const double* priorsure,
                           const uint8_t* hasprior, const int32_t* children, const uint8_t* empty,
                           const int32_t* descendants);
+/* The same inputs in two parts, for hosts that keep their arrays in the engine's row order (cnf2_row_ids): the per-individual
+ * attributes ([n_ind] arrays), and per chromosome relhaplo [n_rows][Mc], prior markerdata [n_rows][Mc][2], prior markersure
+ * [n_rows][Mc][2] as three unstrided host -> device copies (page-locked buffers with cnf2_settings.async_params stay in
+ * flight like cnf2_set_params_packed's). */
+int cnf2_set_mstep_rows(cnf2_engine* e, const uint8_t* hasprior, const int32_t* children, const uint8_t* empty,
+                        const int32_t* descendants);
+int cnf2_set_mstep_chrom_packed(cnf2_engine* e, int32_t chrom, const double* relhaplo, const uint8_t* prioralleles,
+                                const double* priorsure);
 int cnf2_begin_iteration(cnf2_engine* e);
 int cnf2_mstep(cnf2_engine* e, int32_t chrom, double scalefactor, double entropyfactor, int64_t* hitnnn,
                int64_t* hitnnn_shared);
 int cnf2_get_params(cnf2_engine* e, int32_t chrom, uint8_t* alleles, double* sure, double* haploweight);
+/* The chromosome's parameters in the engine's row order: alleles [n_rows][Mc][2], sure [n_rows][Mc][2], haploweight
+ * [n_rows][Mc] -- what the per-iteration dump (cnF2freq.cpp:8157-8192) prints, as three unstrided device -> host copies. */
+int cnf2_get_params_packed(cnf2_engine* e, int32_t chrom, uint8_t* alleles, double* sure, double* haploweight);
 
 /* ---- the EM loop without host round trips (rows a6 / f1 / f2) ---------------------------------------------------
  * The reference's step-size control (cnF2freq.cpp:6333-6392: scalefactor /= 1.1 on a bad pass, *= 1.21 on a good one,
@@ -219,6 +230,14 @@ int cnf2_sync(cnf2_engine* e);
  * on the engine's stream), number of kernel launches it made, and the engine's stream handle. */
 int cnf2_last_estep_ms(cnf2_engine* e, float* ms);
 int cnf2_last_estep_launches(cnf2_engine* e, int32_t* n);
+/* Device time of the E-step kernels summed over the cnf2_estep calls since the last reset (CUDA events on each launch's
+ * own stream, so a launch that shares the GPU with other launches or with an M-step pass counts its full duration), their
+ * number, and the number of kernels of any kind this engine launched.  Waits for the launches in flight. */
+int cnf2_estep_times(cnf2_engine* e, double* sum_ms, int64_t* n_launches, int64_t* n_kernels, int32_t reset);
+/* Gradient evaluations of the step solver (cappedgd, cnF2freq.cpp:4040-4177: one at the start, one per bisection midpoint,
+ * 15 per Gauss-Legendre integral) since the last reset: evals[0] processinfprobs, evals[1] updatehaploweights.  Waits
+ * for the passes in flight. */
+int cnf2_mstep_counters(cnf2_engine* e, uint64_t* evals, int32_t reset);
 void* cnf2_stream(cnf2_engine* e);
 /* CUDA events on the engine's stream: cnf2_mark records event `slot` (0..3); cnf2_elapsed_ms waits for
  * event `to` and returns the device time between two recorded events. */
