@@ -561,7 +561,7 @@ def roofline_of(res, hbm_peak, peaks_present):
     by = im * BYTES_PER_INDMARKER / (res["launch_ms"] * 1e-3) * 1e-9
     per_im, cap = traffic_from_profile()
     # M-step kernels: gradient evaluations counted on the device over the timed iterations
-    ev0, ev1 = res["evals"]
+    ev0, ev1, n_conf, n_rej = res["evals"]
     steps = len(res["it_ms"])
     ms_fl = (ev0 * FLOP_PER_GRADIENT[0] + ev1 * FLOP_PER_GRADIENT[1]) / max(1, steps)
     t_left = max(1e-9, res["step_ms"] - res["estep_ms"])  # what an iteration costs beyond its E-steps run back to back
@@ -583,6 +583,7 @@ def roofline_of(res, hbm_peak, peaks_present):
         "mstep": {"kernel": "cnf2::mstep_infprobs_kernel + cnf2::mstep_haploweight_kernel (cappedgd solves)", "bound": "fp64",
                   "gradient_evaluations_per_iteration": [ev0 / max(1, steps), ev1 / max(1, steps)],
                   "flop_per_gradient": list(FLOP_PER_GRADIENT), "flop_per_iteration": ms_fl,
+                  "solves_on_integral_free_steps_per_iteration": {"confirmed": n_conf / max(1, steps), "sent_back": n_rej / max(1, steps)},
                   "ms_per_iteration_beyond_esteps": t_left, "achieved": ms_fl / (t_left * 1e-3) * 1e-12, "peak": dfma_tflops,
                   "unit": "TFLOP/s", "frac": ms_fl / (t_left * 1e-3) * 1e-12 / dfma_tflops,
                   "note": "time = EM iteration - its E-steps run back to back (the passes overlap the next chromosomes' E-steps, so this is "

@@ -55,8 +55,9 @@ struct Slot
 {
 	cudaStream_t stream = nullptr;
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr, done = nullptr, tail = nullptr;  // kernels start / end, all-reduce done, mark join
-	DevBuf<double> alpha, alphafac, qstash, stats, loglik;
-	DevBuf<int32_t> kexp, literal;
+	DevBuf<double> alpha, qstash, ckalpha, stats, loglik;  // warp kernel: alpha ring, sweep-table ring, checkpoints
+	DevBuf<double> lit_alpha, lit_fac;                       // literal kernel: alpha and its log-factor per marker
+	DevBuf<int32_t> kexp, ckexp, literal;
 	DevBuf<unsigned int> counter;
 	int chrom = -1;
 	int n_shared = 0;
@@ -108,6 +109,8 @@ struct cnf2_engine
 	int cls = 0;               // CLS when some unit's rule-2 mask is all ones (class sums in use)
 	int n_ctas_literal = 0;
 	bool literal_only = false;  // debugging / A-B switch: CNF2_LITERAL=1 runs every unit through the literal kernel
+	int seg_override = 0;       // CNF2_SEG: cap on the markers per segment of the warp kernel's alpha ring (experiments, tests)
+	size_t ring_budget = 0;     // CNF2_RING_MB: bytes the ring of one in-flight E-step may take (0: 12 GiB)
 	DevBuf<Unit> d_units;
 	// M-step (row a6): inputs the E-step does not need, carried haplobase/haplocount, scratch
 	DevBuf<double> d_relhaplo, d_carry_base, d_carry_count, d_ratio, d_fw;
@@ -276,6 +279,9 @@ extern "C" int cnf2_create(cnf2_engine** out, const cnf2_settings* settings)
 	const char* lit = getenv("CNF2_LITERAL");
 	e->literal_only = lit && lit[0] == '1';
 	if (const char* cp = getenv("CNF2_CTAS_PER_SM")) e->settings.ctas_per_sm = atoi(cp);
+	e->seg_override = settings->segment;
+	if (const char* cp = getenv("CNF2_SEG")) e->seg_override = atoi(cp);
+	if (const char* cp = getenv("CNF2_RING_MB")) e->ring_budget = (size_t)atoll(cp) << 20;
 	if (settings->in_flight > 0) e->n_slots = std::min(NSLOT, (int)settings->in_flight);
 	if (const char* ns = getenv("CNF2_SLOTS")) e->n_slots = std::max(1, std::min(NSLOT, atoi(ns)));
 	*out = e;
@@ -306,8 +312,9 @@ extern "C" void cnf2_destroy(cnf2_engine* e)
 	for (Slot& sl : e->slots)
 	{
 		if (sl.stream) cudaStreamSynchronize(sl.stream);
-		sl.alpha.release(), sl.alphafac.release(), sl.qstash.release(), sl.stats.release(), sl.loglik.release();
-		sl.kexp.release(), sl.literal.release(), sl.counter.release();
+		sl.alpha.release(), sl.qstash.release(), sl.ckalpha.release(), sl.stats.release(), sl.loglik.release();
+		sl.lit_alpha.release(), sl.lit_fac.release();
+		sl.kexp.release(), sl.ckexp.release(), sl.literal.release(), sl.counter.release();
 		if (sl.ev0) cudaEventDestroy(sl.ev0);
 		if (sl.ev1) cudaEventDestroy(sl.ev1);
 		if (sl.done) cudaEventDestroy(sl.done);
@@ -733,11 +740,32 @@ extern "C" int cnf2_estep(cnf2_engine* e, int32_t chrom)
 	e->next_slot = (e->next_slot + 1) % e->n_slots;
 	for (Slot& o : e->slots)
 		if (o.chrom == chrom) o.chrom = -1;
-	const int n_ctas = std::max(1, std::min(std::max(e->n_ctas_warp, e->n_ctas_literal), n_units));
-	CU(sl.alpha.ensure((size_t)n_ctas * e->max_mc * NUMSHIFTS * NUMTYPES));
-	CU(sl.alphafac.ensure((size_t)std::max(1, std::min(e->n_ctas_literal, n_units)) * e->max_mc * NUMSHIFTS));
-	CU(sl.kexp.ensure((size_t)n_ctas * e->max_mc * NUMSHIFTS));
-	CU(sl.qstash.ensure((size_t)n_ctas * e->max_mc * QS));
+	// Scratch of the sweeps.  The warp kernel keeps, per resident warp, a ring of `seg` markers (alpha before each marker's
+	// emission for the 8 shift modes, its exponents, the marker's sweep table: 4,672 B per marker) and one alpha checkpoint per
+	// segment; a chromosome longer than `seg` is walked segment by segment, its alphas recomputed from the checkpoints
+	// (see warp_estep_kernel).  seg = the whole chromosome while the ring stays within the budget, so the footprint does not
+	// grow with the chromosome beyond that.  The literal kernel (a few CTAs, rare units) keeps every marker.
+	const int n_warps = std::max(1, std::min(e->n_ctas_warp, n_units));
+	const int n_lit = std::max(1, std::min(e->n_ctas_literal, n_units));
+	const size_t ring_per_marker = (size_t)NUMSHIFTS * NUMTYPES * 8 + NUMSHIFTS * 4 + QS * 8;
+	int seg = ((Mc + WB - 1) / WB) * WB;
+	{
+		const size_t budget = e->ring_budget ? e->ring_budget : (size_t)12 << 30;
+		const size_t fit = budget / ((size_t)n_warps * ring_per_marker);
+		if ((size_t)seg > fit) seg = (int)std::max<size_t>(WB, fit / WB * WB);
+		if (e->seg_override > 0) seg = std::min(seg, std::max(WB, e->seg_override / WB * WB));
+	}
+	const int nseg = (Mc + seg - 1) / seg;
+	if (!e->literal_only)
+	{
+		CU(sl.alpha.ensure((size_t)n_warps * seg * NUMSHIFTS * NUMTYPES));
+		CU(sl.kexp.ensure((size_t)n_warps * seg * NUMSHIFTS));
+		CU(sl.qstash.ensure((size_t)n_warps * seg * QS));
+		CU(sl.ckalpha.ensure((size_t)n_warps * nseg * NUMSHIFTS * NUMTYPES));
+		CU(sl.ckexp.ensure((size_t)n_warps * nseg * NUMSHIFTS));
+	}
+	CU(sl.lit_alpha.ensure((size_t)n_lit * e->max_mc * NUMSHIFTS * NUMTYPES));
+	CU(sl.lit_fac.ensure((size_t)n_lit * e->max_mc * NUMSHIFTS));
 	CU(sl.stats.ensure((size_t)e->n_rows * e->max_mc * STATS_PER_CELL));
 	sl.n_shared = e->n_shared;
 	sl.chrom = chrom;
@@ -764,7 +792,7 @@ extern "C" int cnf2_estep(cnf2_engine* e, int32_t chrom)
 		a.ld = Mc;
 		a.counter = sl.counter.p;
 		a.alpha = sl.alpha.p;
-		a.alphafac = sl.alphafac.p;
+		a.alphafac = nullptr;
 		a.stats_shared = sl.stats_shared();
 		a.stats_local = sl.stats_local(Mc);
 		a.n_shared = e->n_shared;
@@ -777,6 +805,11 @@ extern "C" int cnf2_estep(cnf2_engine* e, int32_t chrom)
 			// one warp per unit; units it cannot take (founder roots, out-of-range parameters) are listed for the literal kernel
 			wa.kexp = sl.kexp.p;
 			wa.qstash = sl.qstash.p;
+			wa.ckalpha = sl.ckalpha.p;
+			wa.ckexp = sl.ckexp.p;
+			wa.seg = seg;
+			wa.nseg = nseg;
+			wa.turns = 1;
 			wa.literal_units = sl.literal.p;
 			wa.literal_count = sl.counter.p + 1;
 			wa.cap0 = e->cap0;
@@ -793,6 +826,8 @@ extern "C" int cnf2_estep(cnf2_engine* e, int32_t chrom)
 			a.list_count = sl.counter.p + 1;
 			a.counter = sl.counter.p + 2;
 		}
+		a.alpha = sl.lit_alpha.p;
+		a.alphafac = sl.lit_fac.p;
 		estep_kernel<<<std::max(1, std::min(e->n_ctas_literal, n_units)), NTHREADS, sizeof(Smem), sl.stream>>>(a);
 		e->n_kernels++;
 		CU(cudaGetLastError());
@@ -1437,8 +1472,8 @@ extern "C" int cnf2_mstep_counters(cnf2_engine* e, uint64_t* evals, int32_t rese
 	if (int rc = cnf2_sync(e)) return rc;
 	EmCtl c{};
 	CU(cudaMemcpy(&c, e->d_ctl.p, sizeof(c), cudaMemcpyDeviceToHost));
-	if (evals) evals[0] = c.evals[0], evals[1] = c.evals[1];
-	if (reset) CU(cudaMemset(&e->d_ctl.p->evals[0], 0, sizeof(c.evals)));
+	if (evals) evals[0] = c.evals[0], evals[1] = c.evals[1], evals[2] = c.closing[0], evals[3] = c.closing[1];
+	if (reset) CU(cudaMemset(&e->d_ctl.p->evals[0], 0, sizeof(c.evals) + sizeof(c.closing)));
 	return CNF2_OK;
 }
 

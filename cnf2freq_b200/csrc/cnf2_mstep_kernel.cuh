@@ -42,7 +42,26 @@ struct EmCtl
 	// measurement (bench.py's M-step roofline): gradient evaluations the solves made since the last reset --
 	// [0] processinfprobs (MODE 0), [1] updatehaploweights (MODE 1); 15 per integral, 1 per midpoint and start
 	unsigned long long evals[2];
+	// solves that ended on integral-free steps (see ms_cappedgd_warp): [0] confirmed by the closing integral, [1] sent back
+	unsigned long long closing[2];
 };
+struct MsCount
+{
+	unsigned evals = 0, confirmed = 0, rejected = 0;
+};
+__device__ __forceinline__ void ms_count_flush(EmCtl* ctl, int mode, MsCount c)
+{
+	const unsigned FULL = 0xffffffffu;
+	c.evals = __reduce_add_sync(FULL, c.evals);
+	c.confirmed = __reduce_add_sync(FULL, c.confirmed);
+	c.rejected = __reduce_add_sync(FULL, c.rejected);
+	if ((threadIdx.x & 31) == 0)
+	{
+		if (c.evals) atomicAdd(ctl->evals + mode, (unsigned long long)c.evals);
+		if (c.confirmed) atomicAdd(ctl->closing + 0, (unsigned long long)c.confirmed);
+		if (c.rejected) atomicAdd(ctl->closing + 1, (unsigned long long)c.rejected);
+	}
+}
 
 struct MstepArgs
 {
@@ -214,7 +233,7 @@ __device__ unsigned long long ms_hist[2][64];
 #endif
 template <int MODE>
 __device__ __forceinline__ double ms_cappedgd_warp(const MsParams& P, double orig, double scalefactor, bool active, unsigned long long& hit,
-                                                   double* stage, unsigned& evals, bool count_only = false)
+                                                   double* stage, MsCount& cnt, bool count_only = false)
 {
 	const unsigned FULL = 0xffffffffu;
 	const int lane = threadIdx.x & 31, half = lane >> 4, q = lane & 15;
@@ -249,10 +268,7 @@ __device__ __forceinline__ double ms_cappedgd_warp(const MsParams& P, double ori
 	unsigned long long dump = 0;
 	const double epsilon = P.eps;
 	double lolim = 0, hilim = 0, lo = 0, hi = 0;
-	bool lowside = false, done = !active;
-#ifdef CNF2_MS_HIST
-	int myit = 0;
-#endif
+	bool lowside = false, fin = !active;
 	if (active)
 	{
 		lolim = ms_caplogit(epsilon, orig, epsilon, dump);
@@ -261,7 +277,7 @@ __device__ __forceinline__ double ms_cappedgd_warp(const MsParams& P, double ori
 		hi = hilim + epsilon * 0.125;
 		orig = ms_caplogit(orig, orig, epsilon, dump);
 		const double gradval = ms_actual<MODE>(P, orig);
-		evals++;
+		cnt.evals++;
 		if (!isfinite(gradval) || !scalefactor)
 		{
 			lo = orig;
@@ -270,26 +286,53 @@ __device__ __forceinline__ double ms_cappedgd_warp(const MsParams& P, double ori
 		lowside = gradval < 0;
 		if (lowside) hi = orig;
 		else lo = orig;
-		if (!scalefactor) done = true;
+		if (!scalefactor) fin = true;
 	}
+	// Integral-free steps.  A step whose midpoint lies on the near side of the gradient's sign change costs the reference a
+	// 15-point integral only to learn that the flow has not yet run for `scalefactor` (prel < scalefactor -> move on).  Where
+	// the flow converges on a stationary point of the objective, or runs into the cap, EVERY such step of the solve says
+	// so, because the integral diverges towards the stationary point -- and in the later EM iterations that is four solves
+	// in five, each with ~25 integrals.  Once a step has fallen well short (prel < scalefactor / 4) or overshot the sign
+	// change, the solve therefore goes on WITHOUT the integrals, taking "short" for granted: the same midpoints, the same
+	// interval updates, bit for bit the reference's.  At its end one integral from the start to the near end of the final
+	// interval -- at least as long as any the skipped steps would have taken -- settles it: short by a margin (< 0.9
+	// scalefactor, every sample of the integrand of one sign) confirms the result; otherwise the solve returns to the state
+	// in which it left the reference's schedule and repeats those steps with their integrals.  (Measured and dropped: a
+	// secant-slope estimate of how close the flow gets to the stationary point, to keep the ordinary solves out of this
+	// mode -- the solves sent back cost what they cost either way; and one integral over the whole way to the cap as a
+	// short cut for the solves that end there -- it misses a stationary point hidden within ~1e-6 of the cap.)
+	bool skip = false, banned = count_only, verify = false, skipped = false;
+	int myi = 0, smyi = 0;
+	double slo = 0, shi = 0;
+#ifdef CNF2_MS_NOSKIP
+	banned = true;
+#endif
+#ifdef CNF2_MS_HIST
+	int myit = 0;
+#endif
 #pragma unroll 1
-	for (int i = 0; i < 51; i++)
+	for (int round = 0; round < 120; round++)
 	{
 		// lo == hi: the interval has collapsed (a non-finite 1 / gradient at the start, :4131, or scalefactor 0); every
 		// further step of the reference sets lo or hi to their common midpoint again, so the result is already fixed
-		if (!done && (lo > hilim || hi < lolim || lo == hi)) done = true;
-		if (__all_sync(FULL, done)) break;
+		if (!fin && !verify && (myi >= 51 || lo > hilim || hi < lolim || lo == hi))
+		{
+			if (skipped) verify = true;
+			else fin = true;
+		}
+		if (__all_sync(FULL, fin)) break;
 		double mid = 0, prel = 0, start = 0, end = 0;
-		bool pending = false;
-		if (!done)
+		bool pending = false, typea = false, stepping = !fin && !verify;
+		if (stepping)
 		{
 #ifdef CNF2_MS_HIST
 			myit++;
 #endif
+			myi++;
 			mid = (lo + hi) / 2;
-			const double g = ms_actual<MODE>(P, mid);
-			evals++;
-			if (((g < 0) != lowside) || !isfinite(g)) prel = (scalefactor + 0.1) * 1.1;
+			const double gmid = ms_actual<MODE>(P, mid);
+			cnt.evals++;
+			if (((gmid < 0) != lowside) || !isfinite(gmid)) prel = (scalefactor + 0.1) * 1.1, typea = true;
 			else
 			{
 				start = orig, end = mid;
@@ -299,16 +342,36 @@ __device__ __forceinline__ double ms_cappedgd_warp(const MsParams& P, double ori
 					start = end;
 					end = t;
 				}
-				if (end - start < 1e-10) done = true;
-				else pending = true, evals += 15;
+				if (end - start < 1e-10)
+				{
+					stepping = false;
+					if (skipped) verify = true;
+					else fin = true;
+				}
+				else if (skip) skipped = true;  // prel = 0: taken to fall short of scalefactor, settled at the end
+				else pending = true, cnt.evals += 15;
 			}
+		}
+		else if (verify)
+		{
+			mid = lowside ? hi : lo;  // the near end of the final interval
+			start = orig, end = mid;
+			if (start > end)
+			{
+				const double t = start;
+				start = end;
+				end = t;
+			}
+			pending = true, cnt.evals += 15;
 		}
 		// integrals of the lanes that need one: two per round (one per half-warp), two rounds at a time while there are
 		// enough of them -- a round is one long dependent fp64 chain per lane, a second independent one fills its gaps
 		unsigned mask = __ballot_sync(FULL, pending);
+		bool samesign = false;
 		auto rounds = [&](auto nu, const int* own) {
 			constexpr int NU = decltype(nu)::value;
 			double f[NU], tq[NU];
+			unsigned pos[NU], neg[NU];
 #pragma unroll
 			for (int u = 0; u < NU; u++)
 			{
@@ -319,6 +382,8 @@ __device__ __forceinline__ double ms_cappedgd_warp(const MsParams& P, double ori
 				const double avg = (a0 + b0) * 0.5, scale = (b0 - a0) * 0.5;
 				const double v = ms_actual<MODE>(Q, avg + scale * myx);
 				f[u] = (owner >= 0 && q < 15) ? v : 0.0;
+				pos[u] = __ballot_sync(FULL, f[u] > 0);
+				neg[u] = __ballot_sync(FULL, f[u] < 0);
 			}
 			// (f(+x_q) + f(-x_q)) w_q on lanes q = 0..7 of each half, summed over those 8 lanes, handed to the owner
 #pragma unroll
@@ -335,12 +400,15 @@ __device__ __forceinline__ double ms_cappedgd_warp(const MsParams& P, double ori
 			for (int u = 0; u < NU; u++)
 			{
 				const bool mine = lane == own[2 * u] || lane == own[2 * u + 1];
-				const double result = __shfl_sync(FULL, tq[u], lane == own[2 * u + 1] ? 16 : 0);
+				const bool second = lane == own[2 * u + 1];
+				const double result = __shfl_sync(FULL, tq[u], second ? 16 : 0);
 				if (mine)
 				{
 					prel = result * ((end - start) * 0.5);
 					if (end != mid) prel = -prel;
 					if (!isfinite(prel)) prel = (scalefactor + 0.1) * 1.1;
+					const unsigned sh = second ? 16 : 0;
+					samesign = ((pos[u] >> sh) & 0x7fffu) == 0x7fffu || ((neg[u] >> sh) & 0x7fffu) == 0x7fffu;
 				}
 			}
 		};
@@ -356,18 +424,36 @@ __device__ __forceinline__ double ms_cappedgd_warp(const MsParams& P, double ori
 			if (own[2] >= 0) rounds(std::integral_constant<int, 2>(), own);
 			else rounds(std::integral_constant<int, 1>(), own);
 		}
-		if (!done)
+		const bool shortby = samesign && prel >= 0 && prel < 0.9 * scalefactor;
+		if (verify)
 		{
-			if (fabs(prel - scalefactor) < scalefactor * 1e-3) done = true;
+			verify = false;
+			if (shortby) fin = true, cnt.confirmed++;
+			else
+			{
+				cnt.rejected++;
+				lo = slo, hi = shi, myi = smyi;  // back to where the solve left the reference's schedule
+				skip = skipped = false;
+				banned = true;
+			}
+		}
+		else if (stepping)
+		{
+			if (fabs(prel - scalefactor) < scalefactor * 1e-3) fin = true;
 			else if ((prel < scalefactor) != lowside)
 			{
 				lo = mid;
-				if (count_only && lowside) done = true;  // away from the lower cap
+				if (count_only && lowside) fin = true;  // away from the lower cap
 			}
 			else
 			{
 				hi = mid;
-				if (count_only && !lowside) done = true;  // away from the upper cap
+				if (count_only && !lowside) fin = true;  // away from the upper cap
+			}
+			if (!fin && !skip && !banned && (typea || prel < 0.25 * scalefactor))
+			{
+				skip = true;
+				slo = lo, shi = hi, smyi = myi;
 			}
 		}
 	}
@@ -408,7 +494,7 @@ __global__ void __launch_bounds__(MS_BLOCK, 5) mstep_infprobs_kernel(MstepArgs a
 	const double scalefactor = a.ctl->sf_pass;
 	const double epsilon = ms_epsilon(r.children), etf = 1 * a.ctl->entropyfactor;
 	unsigned long long hit = 0;
-	unsigned evals = 0;
+	MsCount cnt;
 #pragma unroll 1
 	for (int side = 0; side < 2; side++)
 	{
@@ -440,7 +526,7 @@ __global__ void __launch_bounds__(MS_BLOCK, 5) mstep_infprobs_kernel(MstepArgs a
 				}
 			}
 			const MsParams P = ms_params(curprob, ip[k], sum, etf, etf * priord, 0.0, 0.0, epsilon);
-			const double res = ms_cappedgd_warp<0>(P, curprob, scalefactor, active, hit, &stage[0][0], evals, r.empty || !r.hasprior);
+			const double res = ms_cappedgd_warp<0>(P, curprob, scalefactor, active, hit, &stage[0][0], cnt, r.empty || !r.hasprior);
 			if (active) ip[k] = res;
 		}
 		double bestprob = 0;
@@ -466,8 +552,7 @@ __global__ void __launch_bounds__(MS_BLOCK, 5) mstep_infprobs_kernel(MstepArgs a
 		a.sure[idx] = su;
 		if (hit) atomicAdd(a.ctl->hit + (row < a.n_shared ? 1 : 0), hit);
 	}
-	evals = __reduce_add_sync(0xffffffffu, evals);
-	if ((threadIdx.x & 31) == 0 && evals) atomicAdd(a.ctl->evals + 0, (unsigned long long)evals);
+	ms_count_flush(a.ctl, 0, cnt);
 }
 
 // relskewhmm (:4325-4467, realhmm): one thread per row walks the chromosome forward (stores the two forward values per
@@ -639,10 +724,9 @@ __global__ void __launch_bounds__(MS_BLOCK, 6) mstep_haploweight_kernel(MstepPas
 	const MsParams P = ms_params(w, hb, hc, (1 - similarity) * 1, a.ctl->entropyfactor, active ? a.ratio[idx] : 0.0, (double)r.descendants,
 	                             ms_epsilon(r.children));
 	unsigned long long hit = 0;
-	unsigned evals = 0;
-	const double res = ms_cappedgd_warp<1>(P, w, a.ctl->sf_pass, active, hit, &stage[0][0], evals);
-	evals = __reduce_add_sync(0xffffffffu, evals);
-	if ((threadIdx.x & 31) == 0 && evals) atomicAdd(a.ctl->evals + 1, (unsigned long long)evals);
+	MsCount cnt;
+	const double res = ms_cappedgd_warp<1>(P, w, a.ctl->sf_pass, active, hit, &stage[0][0], cnt);
+	ms_count_flush(a.ctl, 1, cnt);
 	if (active)
 	{
 		a.hw[idx] = res;
@@ -692,7 +776,11 @@ __global__ void ms_end_kernel(EmCtl* c, int reduced, int control)
 
 // ---- phase inversions (row f2): candidates and their application ----
 // Per row: the most negative phase-inversion score of the chromosome below -1e-10 and the first marker holding it
-// (cnF2freq.cpp:6272-6284); minstart = Mc when there is none.  One warp per row.
+// (cnF2freq.cpp:6272-6284); minstart = Mc when there is none.  One warp per row.  "Holding it": within the rounding noise
+// of the scores (differences of logarithms of O(1) sums: 1e-15 absolute, 1e-12 relative) of the minimum.  The reference
+// adds an individual's scores in one fixed order at every marker, so markers carrying the same information tie (or differ
+// in the last bit the same way every run) and the first one wins; here the contributions arrive through atomics in any
+// order.  Documented tie: minima closer than that are taken at the first marker.
 __global__ void __launch_bounds__(128) negshift_minima_kernel(const double* stats_shared, const double* stats_local, int n_rows, int n_shared,
                                                               int Mc, double* minval, int32_t* minstart)
 {
@@ -702,19 +790,27 @@ __global__ void __launch_bounds__(128) negshift_minima_kernel(const double* stat
 	const size_t nr = sh ? n_shared : n_rows - n_shared;
 	const double* ns = (sh ? stats_shared : stats_local) + 8 * nr * Mc + (size_t)(sh ? row : row - n_shared) * Mc;
 	double best = -1e-10;
+	for (int m = lane; m < Mc; m += 32) best = fmin(best, ns[m]);
+	for (int o = 16; o > 0; o >>= 1) best = fmin(best, __shfl_xor_sync(0xffffffffu, best, o));
 	int at = Mc;
-	for (int m = lane; m < Mc; m += 32)
+	double val = best;
+	if (best < -1e-10)
 	{
-		const double v = ns[m];
-		if (v < best) best = v, at = m;  // strict: the first of equal minima in this lane
+		const double thr = best + fmax(1e-15, -best * 1e-12);  // best < 0: slightly above the minimum
+		for (int m0 = 0; m0 < Mc && at == Mc; m0 += 32)
+		{
+			const int m = m0 + lane;
+			const double v = m < Mc ? ns[m] : 0.0;
+			const unsigned hit = __ballot_sync(0xffffffffu, m < Mc && v <= thr);
+			if (hit)
+			{
+				const int src = __ffs(hit) - 1;
+				at = m0 + src;
+				val = __shfl_sync(0xffffffffu, v, src);
+			}
+		}
 	}
-	for (int o = 16; o > 0; o >>= 1)
-	{
-		const double ob = __shfl_xor_sync(0xffffffffu, best, o);
-		const int oa = __shfl_xor_sync(0xffffffffu, at, o);
-		if (ob < best || (ob == best && oa < at)) best = ob, at = oa;
-	}
-	if (lane == 0) minval[row] = best, minstart[row] = at;
+	if (lane == 0) minval[row] = val, minstart[row] = at;
 }
 // negshifter (:3437-3459): from the marker after minstart to the chromosome's end the phase is inverted: haploweight
 // -> 1 - haploweight, haplobase -> haplocount - haplobase.  One block per candidate.

@@ -485,91 +485,124 @@ __device__ __forceinline__ void emit16(double (&p)[16], const double* __restrict
 		p[j + 8] *= c0b * q0.x + c1b * q0.y;
 	}
 }
-// the emission values themselves (the factors emit16 multiplies by)
-__device__ __forceinline__ void emis16(double (&ev)[16], const double* __restrict__ q, int lane)
+// fp64 tensor-core step of the turn scoring: C[8][8] += A[8][4] B[4][8] (mma.sync m8n8k4).  Lane T supplies
+// A[T / 4][T % 4] and B[T % 4][T / 4] and holds C[T / 4][2 (T % 4)], C[T / 4][2 (T % 4) + 1].
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b)
 {
-#pragma unroll
-	for (int i = 0; i < 16; i++) ev[i] = 1.0;
-	emit16(ev, q, lane);
+	asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 
-// Turn scoring of one marker (cnF2freq.cpp:5668-5757 with DOTOULBAR 0: the turns of at most one bit; aroundturner
-// :498-554; quickanalyze with classicstop(marker, -1), :1960-2018) and updatenegshifts (:3640-3715).
+// One marker of the backward pass, fused: W = alpha- beta exp(F- + B - factor) into shared memory for the posterior
+// (:1963-2018, :5499-5508), and the turn scoring (cnF2freq.cpp:5668-5757 with DOTOULBAR 0: the turns of at most one
+// individual; aroundturner :498-554; quickanalyze with classicstop(marker, -1), :1960-2018; updatenegshifts :3640-3715):
 //   rawvals[turn][s] = exp(F+_s + B_s' + log sum_k alpha+_s[k ^ mask] beta_s'[k] - factor),  s' = s ^ flagmodeshift
-// with alpha+ = alpha- (x) emission.  Turn of slot k: a grandparent slot (2, 3, 5, 6) flips state bit k - 1 (bits 1, 2
-// inside the lane, bits 4, 5 one and two lanes apart), a parent slot (1, 4) flips shift bit 1 / 2 (8 / 16 lanes apart),
-// the root flips shift bit 0 (4 lanes apart).  D index: 0 no turn, k the turn of slot k, 7 the root's.
-// ap: alpha+ without its power of two (exponent ka per shift), b: beta (exponent kb), scale 2^kf * efrem = exp(-factor).
-__device__ __forceinline__ void warp_turns(const WarpSmem& w, const Unit& u, const double (&ap)[16], const double (&b)[16], int ka, int kb,
-                                           int kf, double efrem, int m, int lane)
+// with alpha+ = alpha- (x) emission, streamed state by state so that neither W nor alpha+ nor the emission values are
+// ever held as 16-value register arrays.
+//   * the root's turn and the two parents' turns flip a SHIFT bit (s' = s ^ 1, 2, 4): together with the unturned sum they
+//     are four entries per row of the 8 x 8 matrix C[s][s'] = sum_g alpha+_s[g] beta_s'[g], a contraction over the 64
+//     states.  In the sweeps' layout (lane = shift * 4 + state bits 4-5, registers = state bits 0-3) a lane's alpha+ and
+//     beta values of one register index ARE the A and B fragments of mma.sync.m8n8k4.f64: 16 tensor-core steps, no
+//     shuffle, and the sum over the four lanes of a shift mode comes with it.
+//   * the grandparents' turns flip a state bit: bits 1, 2 inside the lane (register renaming), bits 4, 5 one and two lanes
+//     apart -- alpha+ goes through shared memory (xbuf, the posterior tables' space, dead at this point) once.
+// an: alpha- (power of two kan per shift mode), b: beta (kb), sc: the scale of W (0 for a shift mode that does not
+// contribute), 2^kf * efrem = exp(-factor).
+__device__ __forceinline__ void warp_w_and_turns(WarpSmem& w, const Unit& u, const double (&an)[16], const double (&b)[16], double sc, int kan,
+                                                 int kb, int kf, double efrem, const double* __restrict__ q, double2* __restrict__ xbuf, int m,
+                                                 int lane, bool turns)
 {
 	const unsigned FULL = 0xffffffffu;
-	double D[8];
+	const int s = lane >> 2, gh = lane & 3;
+	const int s0 = s & 1, s1 = (s >> 1) & 1, s2 = s >> 2;
+	const double2 R = *reinterpret_cast<const double2*>(q + 64 + s0 * 2);
+	const double2* Q1 = reinterpret_cast<const double2*>(q + (((2 + s2) * 8) + gh * 2) * 2);
+	const double2* Q0 = reinterpret_cast<const double2*>(q + (s1 * 8) * 2);
+	const double2 qa = Q1[0], qb = Q1[1];
+	const double c0a = R.x * qa.x, c1a = R.y * qa.y, c0b = R.x * qb.x, c1b = R.y * qb.y;
+	const int wbase = ws_base(gh << 4) ^ s;
+	double C0 = 0, C1 = 0, D2 = 0, D3 = 0;
 #pragma unroll
-	for (int j = 0; j < 8; j++) D[j] = 0;
-#pragma unroll
-	for (int i = 0; i < 16; i++)
+	for (int j = 0; j < 8; j++)
 	{
-		D[0] = fma(ap[i], b[i], D[0]);
-		D[2] = fma(ap[i ^ 2], b[i], D[2]);  // slot 2: state bit 1
-		D[3] = fma(ap[i ^ 4], b[i], D[3]);  // slot 3: state bit 2
-		D[5] = fma(__shfl_xor_sync(FULL, ap[i], 1), b[i], D[5]);   // slot 5: state bit 4
-		D[6] = fma(__shfl_xor_sync(FULL, ap[i], 2), b[i], D[6]);   // slot 6: state bit 5
-		D[7] = fma(ap[i], __shfl_xor_sync(FULL, b[i], 4), D[7]);   // root: shift bit 0
-		D[1] = fma(ap[i], __shfl_xor_sync(FULL, b[i], 8), D[1]);   // slot 1: shift bit 1
-		D[4] = fma(ap[i], __shfl_xor_sync(FULL, b[i], 16), D[4]);  // slot 4: shift bit 2
-	}
-	{
-		const int k7 = __shfl_xor_sync(FULL, kb, 4), k1 = __shfl_xor_sync(FULL, kb, 8), k4 = __shfl_xor_sync(FULL, kb, 16);
-		auto pow2 = [&](int kbx) -> double {
-			const int ke = ka + kbx + kf;
-			// out of range below: the term underflows as exp() does in the reference; above (never in practice): its 1e300 cap (:5724)
-			return ke < -1000 ? 0.0 : ke > 1000 ? 1e300 : __hiloint2double((1023 + ke) << 20, 0) * efrem;
-		};
-		const double s0 = pow2(kb);
-		D[0] *= s0, D[2] *= s0, D[3] *= s0, D[5] *= s0, D[6] *= s0;
-		D[7] *= pow2(k7), D[1] *= pow2(k1), D[4] *= pow2(k4);
-	}
-	// sum over the warp (the shift modes that are not in use carry alpha = 0): halving exchange, then lane L holds
-	// turn (L >> 2) & 7 in the order of bits 4, 3, 2
-	double v4[4], v2[2], v1;
-	{
-		const bool hi = lane & 16;
-#pragma unroll
-		for (int j = 0; j < 4; j++)
+		w.Ws[wbase ^ ws_base(j)] = an[j] * (b[j] * sc);
+		w.Ws[wbase ^ ws_base(j + 8)] = an[j + 8] * (b[j + 8] * sc);
+		if (turns)
 		{
-			const double keep = hi ? D[j + 4] : D[j], send = hi ? D[j] : D[j + 4];
-			v4[j] = keep + __shfl_xor_sync(FULL, send, 16);
+			const double2 q0 = Q0[j];
+			const double alo = an[j] * (c0a * q0.x + c1a * q0.y), ahi = an[j + 8] * (c0b * q0.x + c1b * q0.y);  // alpha+ of states j, j + 8
+			dmma884(C0, C1, alo, b[j]);
+			dmma884(C0, C1, ahi, b[j + 8]);
+			D2 = fma(alo, b[j ^ 2], fma(ahi, b[(j ^ 2) + 8], D2));  // slot 2: state bit 1
+			D3 = fma(alo, b[j ^ 4], fma(ahi, b[(j ^ 4) + 8], D3));  // slot 3: state bit 2
+			xbuf[j * 32 + lane] = make_double2(alo, ahi);
 		}
 	}
-	{
-		const bool hi = lane & 8;
+	if (!turns) return;
+	__syncwarp();
+	double D5 = 0, D6 = 0;
 #pragma unroll
-		for (int j = 0; j < 2; j++)
-		{
-			const double keep = hi ? v4[j + 2] : v4[j], send = hi ? v4[j] : v4[j + 2];
-			v2[j] = keep + __shfl_xor_sync(FULL, send, 8);
-		}
-	}
+	for (int j = 0; j < 8; j++)
 	{
-		const bool hi = lane & 4;
-		const double keep = hi ? v2[1] : v2[0], send = hi ? v2[0] : v2[1];
-		v1 = keep + __shfl_xor_sync(FULL, send, 4);
+		const double2 x1 = xbuf[j * 32 + (lane ^ 1)], x2 = xbuf[j * 32 + (lane ^ 2)];
+		D5 = fma(x1.x, b[j], fma(x1.y, b[j + 8], D5));  // slot 5: state bit 4
+		D6 = fma(x2.x, b[j], fma(x2.y, b[j + 8], D6));  // slot 6: state bit 5
 	}
-	v1 += __shfl_xor_sync(FULL, v1, 2);
-	v1 += __shfl_xor_sync(FULL, v1, 1);
-	const int tn = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+	auto pow2 = [&](int kbx) -> double {
+		const int ke = kan + kbx + kf;
+		// out of range below: the term underflows as exp() does in the reference; above (never in practice): its 1e300 cap (:5724)
+		return ke < -1000 ? 0.0 : ke > 1000 ? 1e300 : __hiloint2double((1023 + ke) << 20, 0) * efrem;
+	};
+	// C0, C1 = C[s][2 gh], C[s][2 gh + 1]: column c is the unturned sum for c = s, the root's turn for c = s ^ 1, slot 1's for
+	// c = s ^ 2, slot 4's for c = s ^ 4.  jj = gh ^ (s >> 1) says which pair this lane holds; the pair moves to lane position jj.
+	{
+		const int kA = __shfl_sync(FULL, kb, gh * 8), kB = __shfl_sync(FULL, kb, gh * 8 + 4);
+		C0 *= pow2(kA), C1 *= pow2(kB);
+	}
+	const int jj = gh ^ (s >> 1);
+	double pA = s0 ? C1 : C0, pB = s0 ? C0 : C1;  // pA: column with (c ^ s) even = 2 jj, pB: column 2 jj + 1
+	if (jj) pB = 0.0;                             // c ^ s = 3, 5, 7: not a turn that is scored here
+	if (jj == 3) pA = 0.0;                        // c ^ s = 6
+	{
+		const int src = (lane & ~3) | (gh ^ (s >> 1));  // position jj = gh of the receiving lane
+		pA = __shfl_sync(FULL, pA, src);
+		pB = __shfl_sync(FULL, pB, src);
+	}
+	// the four in-lane / in-shift sums over the four lanes of the shift mode: gh = 0 ends with D2, 1 with D5, 2 with D3, 3 with D6
+	double pC;
+	{
+		const bool hi1 = gh & 1, hi2 = gh & 2;
+		const double k0 = hi1 ? D5 : D2, t0 = hi1 ? D2 : D5, k1 = hi1 ? D6 : D3, t1 = hi1 ? D3 : D6;
+		const double v0 = k0 + __shfl_xor_sync(FULL, t0, 1), v1 = k1 + __shfl_xor_sync(FULL, t1, 1);
+		pC = (hi2 ? v1 : v0) + __shfl_xor_sync(FULL, hi2 ? v0 : v1, 2);
+		pC *= pow2(kb);
+	}
+	// sum over the shift modes (those not in use carry alpha = 0); every group of four lanes ends with all totals:
+	//   gh 0: (none, root, slot 2)   gh 1: (slot 1, -, slot 5)   gh 2: (slot 4, -, slot 3)   gh 3: (-, -, slot 6)
+#pragma unroll
+	for (int o = 4; o < 32; o <<= 1)
+	{
+		pA += __shfl_xor_sync(FULL, pA, o);
+		pB += __shfl_xor_sync(FULL, pB, o);
+		pC += __shfl_xor_sync(FULL, pC, o);
+	}
+	// one logarithm per lane: shift group 0 takes the first value of its position, group 1 the second, group 2 the third
+	double v1 = s == 0 ? pA : s == 1 ? pB : pC;
 	if (!isfinite(v1) || v1 < 1e-174) v1 = 1e-174;  // :3655
 	const double lv = ms_log(v1);
 	const double l0 = __shfl_sync(FULL, lv, 0);
-	if ((lane & 3) == 0 && tn)
+	int slot = -1;  // the tree slot whose turn this lane holds
+	if (s == 0) slot = gh == 1 ? 1 : gh == 2 ? 4 : -1;
+	else if (s == 1) slot = gh == 0 ? 0 : -1;
+	else if (s == 2) slot = gh == 0 ? 2 : gh == 1 ? 5 : gh == 2 ? 3 : 6;
+	if (slot >= 0)
 	{
-		const int slot = tn == 7 ? 0 : tn;
 		double* const p = w.nsptr[slot];
 		if (p)
 		{
 			const bool scored = slot == 0 || !((u.flag2ignore >> slot) & 1);  // `g & (flag2ignore >> 1)`, :5684
+#ifndef CNF2_X_NONSATOMIC
 			atomicAdd(p + m, (l0 - (scored ? lv : 0.0)) * u.nsscale[slot]);
+#endif
 		}
 	}
 }
@@ -703,20 +736,32 @@ __device__ __forceinline__ void warp_lists(WarpSmem& w, const Unit& u, int gpmus
 
 struct WarpArgs
 {
-	EstepArgs e;             // alpha scratch: [n_warps][Mc][512] doubles in store_alpha's layout
-	int32_t* kexp;           // [n_warps][Mc][NUMSHIFTS] power-of-two exponent of the stored alpha
-	double* qstash;          // [n_warps][Mc][QS] sweep-emission tables (forward pass -> backward pass)
+	EstepArgs e;             // e.alpha: alpha ring [n_warps][seg][512] doubles in store_alpha's layout (alpha before each marker's emission)
+	int32_t* kexp;           // [n_warps][seg][NUMSHIFTS] power-of-two exponent of the stored alpha
+	double* qstash;          // [n_warps][seg][QS] sweep-emission tables (forward pass -> backward pass)
+	double* ckalpha;         // [n_warps][nseg][512] checkpoints: alpha before the first marker of segments 1.. (slot 0 unused)
+	int32_t* ckexp;          // [n_warps][nseg][NUMSHIFTS]
+	int32_t seg, nseg;       // markers per segment (a multiple of WB), segments per chromosome
 	int32_t* literal_units;  // units the literal kernel has to do
 	unsigned int* literal_count;
 	int32_t cap0, cap1;      // capacity (entries) of the posterior tables of parent 0 / parent 1
 	int32_t cls;             // CLS when the class sums are in use (some unit has an all-ones rule-2 mask), else 0
+	int32_t turns;           // score the phase-inversion turns (HAPLOTYPING && !early && !full, :5668)
 };
+constexpr size_t XBUF_BYTES = 8 * 32 * sizeof(double2);  // warp_w_and_turns' exchange buffer lives in the posterior tables' space
 __host__ __device__ inline size_t warp_smem_bytes(int cap0, int cap1, int cls)
 {
-	return sizeof(WarpSmem) + ((size_t)cap0 * 2 * T0W + (size_t)cap1 * 2 * T1W + cls) * sizeof(double);
+	const size_t tables = ((size_t)cap0 * 2 * T0W + (size_t)cap1 * 2 * T1W + cls) * sizeof(double);
+	return sizeof(WarpSmem) + (tables > XBUF_BYTES ? tables : XBUF_BYTES);
 }
 
 // AGG: built with the class-sum form for units without rule-2 coupling (picked by the host when the pedigree has any)
+//
+// Memory of the sweeps (row a5): the forward pass keeps alpha only at the start of every segment of `seg` markers (a
+// checkpoint: 4 KB per segment) and, for the chromosome's LAST segment, for every marker in a per-warp ring of `seg`
+// entries.  The backward pass walks the segments from the last to the first; before it enters a segment it re-runs the
+// forward sweep over it from the checkpoint, filling the ring.  With seg >= Mc that is the plain store-everything
+// schedule (one segment, nothing recomputed); the host picks seg so that the ring fits its budget whatever Mc is.
 template <bool AGG>
 __global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wa)
 {
@@ -725,13 +770,17 @@ __global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wa)
 	double* const tab0 = reinterpret_cast<double*>(smem_raw + sizeof(WarpSmem));
 	double* const tab1 = tab0 + (size_t)wa.cap0 * 2 * T0W;
 	double* const cls = tab1 + (size_t)wa.cap1 * 2 * T1W;
+	double2* const xbuf = reinterpret_cast<double2*>(tab0);
 	const EstepArgs& a = wa.e;
 	const unsigned FULL = 0xffffffffu;
 	const int lane = threadIdx.x, s = lane >> 2;
-	const int Mc = a.Mc, E = Mc - 1;
-	double2* const alpha = reinterpret_cast<double2*>(a.alpha) + (size_t)blockIdx.x * Mc * (NUMSHIFTS * NUMTYPES / 2);
-	int32_t* const kexp = wa.kexp + (size_t)blockIdx.x * Mc * NUMSHIFTS;
-	double* const qs = wa.qstash + (size_t)blockIdx.x * Mc * QS;
+	const int Mc = a.Mc, E = Mc - 1, SEG = wa.seg, nseg = wa.nseg;
+	constexpr int AV = NUMSHIFTS * NUMTYPES / 2;  // double2 per stored alpha
+	double2* const alpha = reinterpret_cast<double2*>(a.alpha) + (size_t)blockIdx.x * SEG * AV;
+	int32_t* const kexp = wa.kexp + (size_t)blockIdx.x * SEG * NUMSHIFTS;
+	double* const qs = wa.qstash + (size_t)blockIdx.x * SEG * QS;
+	double2* const ckalpha = reinterpret_cast<double2*>(wa.ckalpha) + (size_t)blockIdx.x * nseg * AV;
+	int32_t* const ckexp = wa.ckexp + (size_t)blockIdx.x * nseg * NUMSHIFTS;
 
 	for (int i = lane; i < NCOL * NACCP; i += 32) w.acc[i] = 0;
 
@@ -755,41 +804,54 @@ __global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wa)
 		bool literal = u.founder[0] != 0;  // a root "at the top" never recurses (:1120): literal kernel
 		const bool active = s < u.shiftend && !(s & u.shiftignore);
 
-		// ---- forward sweep (initfwbw + realanalyze<STORE|FORWARD>, cnF2freq.cpp:2086-2107) ----
-		double p[16];
-#pragma unroll
-		for (int i = 0; i < 16; i++) p[i] = active ? 1.0 / NUMTYPES : 0.0;  // EVENGEN, :2100-2104
+		// the forward sweep over markers [mb, me) from (p, ka) (realanalyze<STORE|FORWARD>, cnF2freq.cpp:2086-2107); stash: alpha
+		// before each marker, its exponents and the marker's sweep table go to ring entry (marker - mb); check: parameters outside
+		// the regular range end the sweep (the unit is the literal kernel's)
+		double p[16];  // the forward vector; in the backward pass: alpha before the current marker's emission
 		int ka = 0;
-		if (!literal)
-		{
-			RawItem raw = raw_load(u, a, 0, min(WB, Mc), lane);
-			for (int m0 = 0; m0 < Mc; m0 += WB)
+		auto forward = [&](const int mb, const int me, const bool stash, const bool check) -> bool {
+			RawItem raw = raw_load(u, a, mb, min(WB, me - mb), lane);
+			for (int m0 = mb; m0 < me; m0 += WB)
 			{
-				const int n = min(WB, Mc - m0);
+				const int n = min(WB, me - m0);
 				__syncwarp();
 				const bool bad = raw_commit(w, raw, lane);
-				if (m0 + WB < Mc) raw = raw_load(u, a, m0 + WB, min(WB, Mc - m0 - WB), lane);
-				if (__any_sync(FULL, bad))
-				{
-					literal = true;
-					break;
-				}
+				if (m0 + WB < me) raw = raw_load(u, a, m0 + WB, min(WB, me - m0 - WB), lane);
+				if (check && __any_sync(FULL, bad)) return false;
 				__syncwarp();
 				if ((lane >> 3) < n) sweep_family<WB>(u, w.A, w.nt, lane >> 3, lane & 7, w.qh + (lane >> 3) * QS);
 				__syncwarp();
-				for (int i = lane; i < n * QS; i += 32) qs[(size_t)m0 * QS + i] = w.qh[i];
+				if (stash)
+					for (int i = lane; i < n * QS; i += 32) qs[(size_t)(m0 - mb) * QS + i] = w.qh[i];
 				for (int t = 0; t < n; t++)
 				{
 					const int m = m0 + t;
 					double r0 = 0, r1 = 0;  // asked for ahead of the stores below, used after the emission
 					if (m < E) r0 = a.rec0[m], r1 = a.rec1[m];
-					store_alpha(alpha + (size_t)m * (NUMSHIFTS * NUMTYPES / 2), p, lane);
-					if ((lane & 3) == 0) kexp[(size_t)m * NUMSHIFTS + s] = ka;
+					if (stash)
+					{
+						store_alpha(alpha + (size_t)(m - mb) * AV, p, lane);
+						if ((lane & 3) == 0) kexp[(size_t)(m - mb) * NUMSHIFTS + s] = ka;
+					}
 					emit16(p, w.qh + t * QS, lane);
 					rescale16(p, ka);
 					if (m < E) transition16(p, r0, r1);
 				}
 			}
+			return true;
+		};
+
+		// ---- forward pass (initfwbw, :2086-2107): checkpoints at the segment starts, the last segment into the ring ----
+#pragma unroll
+		for (int i = 0; i < 16; i++) p[i] = active ? 1.0 / NUMTYPES : 0.0;  // EVENGEN, :2100-2104
+		for (int sg = 0; sg < nseg && !literal; sg++)
+		{
+			if (sg > 0)
+			{
+				store_alpha(ckalpha + (size_t)sg * AV, p, lane);
+				if ((lane & 3) == 0) ckexp[sg * NUMSHIFTS + s] = ka;
+			}
+			if (!forward(sg * SEG, min(Mc, (sg + 1) * SEG), sg == nseg - 1, true)) literal = true;
 		}
 		if (literal)
 		{
@@ -807,16 +869,21 @@ __global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wa)
 			L = sum > 0 ? (double)ka * LN2 + log(sum) : MINFACTOR_D;
 		}
 		double factor = -1e15, realfactor = 0;  // :5373-5403
-		double Ls[NUMSHIFTS];
-#pragma unroll
-		for (int j = 0; j < NUMSHIFTS; j++)
 		{
-			Ls[j] = __shfl_sync(FULL, L, j * 4);
-			if (j < u.shiftend && !(j & u.shiftignore)) factor = fmax(factor, Ls[j]);
-		}
+			const unsigned actmask = __ballot_sync(FULL, active);
 #pragma unroll
-		for (int j = 0; j < NUMSHIFTS; j++)
-			if (j < u.shiftend && !(j & u.shiftignore)) realfactor += exp(Ls[j] - factor);
+			for (int j = 0; j < NUMSHIFTS; j++)
+			{
+				const double Lj = __shfl_sync(FULL, L, j * 4);
+				if ((actmask >> (j * 4)) & 1) factor = fmax(factor, Lj);
+			}
+#pragma unroll
+			for (int j = 0; j < NUMSHIFTS; j++)
+			{
+				const double Lj = __shfl_sync(FULL, L, j * 4);
+				if ((actmask >> (j * 4)) & 1) realfactor += exp(Lj - factor);
+			}
+		}
 		const double maxfactor = factor;
 		if (!(maxfactor > MINFACTOR_D))
 		{
@@ -843,126 +910,137 @@ __global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wa)
 #pragma unroll
 		for (int i = 0; i < 16; i++) b[i] = 1.0;  // :2111-2114
 		int kb = 0;
-		const int mlast = ((Mc - 1) / WB) * WB;
-		RawItem raw = raw_load(u, a, mlast, Mc - mlast, lane);
-		double an[16];
-		load_alpha(alpha + (size_t)(Mc - 1) * (NUMSHIFTS * NUMTYPES / 2), an, lane);
-		int kan = kexp[(size_t)(Mc - 1) * NUMSHIFTS + s];
-		for (int m0 = mlast; m0 >= 0; m0 -= WB)
+		for (int sg = nseg - 1; sg >= 0; sg--)
 		{
-			const int n = min(WB, Mc - m0);
-			__syncwarp();
-			raw_commit(w, raw, lane);
-			for (int i = lane; i < n * QS; i += 32) w.qh[i] = qs[(size_t)m0 * QS + i];
-			// the stash and the alphas of the units in flight are far larger than L2: ask for the next block's lines now
-			if (m0 >= WB && lane * 16 < WB * QS) asm volatile("prefetch.global.L2 [%0];" ::"l"(qs + (size_t)(m0 - WB) * QS + lane * 16));
-			// homozygous with equal sureness (:1235, :3488), per (slot, marker) of the batch
-			const bool homi = (lane / WB) < NSLOTS && u.row[(lane / WB) % NSLOTS] >= 0 && raw.al.x == raw.al.y && raw.su.x == raw.su.y;
-			const unsigned homb = __ballot_sync(FULL, homi);
-			if (m0 >= WB) raw = raw_load(u, a, m0 - WB, WB, lane);
-			if (lane < WB)
+			const int mb = sg * SEG, me = min(Mc, mb + SEG);
+			if (sg != nseg - 1)
 			{
-				int hs = 0, hom = 0, gp = 0;
-				for (int k = 0; k < NSLOTS; k++)
-					if ((homb >> (k * WB + lane)) & 1)
-					{
-						hs |= 1 << k;
-						hom |= 1 << u.slotrel[k];
-					}
-				for (int i = 0; i < u.nrel; i++)  // rule 3 (:3488-3493) of the relatives whose rule does not involve the shift mode
-					if (((hom >> i) & 1) && u.relshift[i] == 0) gp |= u.relfilter[i];
-				w.homslot[lane] = hs;
-				w.gpmust[lane] = gp;
+				// the segment's alphas are not in the ring: forward again from its checkpoint
+				if (sg > 0)
+				{
+					load_alpha(ckalpha + (size_t)sg * AV, p, lane);
+					ka = ckexp[sg * NUMSHIFTS + s];
+				}
+				else
+				{
+#pragma unroll
+					for (int i = 0; i < 16; i++) p[i] = active ? 1.0 / NUMTYPES : 0.0;
+					ka = 0;
+				}
+				__syncwarp();
+				forward(mb, me, true, false);
 			}
-			__syncwarp();
-			for (int t = n - 1; t >= 0; t--)
+			const int mlast = mb + ((me - 1 - mb) / WB) * WB;
+			RawItem raw = raw_load(u, a, mlast, me - mlast, lane);
+			load_alpha(alpha + (size_t)(me - 1 - mb) * AV, p, lane);
+			int kan = kexp[(size_t)(me - 1 - mb) * NUMSHIFTS + s];
+			for (int m0 = mlast; m0 >= mb; m0 -= WB)
 			{
-				const int m = m0 + t;
-				// W = alpha beta exp(F- + B - factor) (:1963-2018, :5499-5508); the factors are k ln 2 here
-				double W[16];
-				{
-					double sc = 0;
-					const int ke = kan + kb + kf;
-					if (contributing && !((double)kan * LN2 + 5.0 < minfactor) && ke > -860 && ke < 860)
-						sc = __hiloint2double((1023 + ke) << 20, 0) * efrem;
-#pragma unroll
-					for (int i = 0; i < 16; i++) W[i] = an[i] * (b[i] * sc);
-				}
-#ifndef CNF2_X_NOTURNS
-				{
-					double ev[16];
-					emis16(ev, w.qh + t * QS, lane);
-#pragma unroll
-					for (int i = 0; i < 16; i++) an[i] *= ev[i];  // alpha+ (unnormalised); alpha- is not needed any more
-					warp_turns(w, u, an, b, kan, kb, kf, efrem, m, lane);
-				}
-#endif
-				if (m > 0)
-				{
-					load_alpha(alpha + (size_t)(m - 1) * (NUMSHIFTS * NUMTYPES / 2), an, lane);
-					kan = kexp[(size_t)(m - 1) * NUMSHIFTS + s];
-					if (m > WB) asm volatile("prefetch.global.L2 [%0];" ::"l"(alpha + (size_t)(m - 1 - WB) * (NUMSHIFTS * NUMTYPES / 2) + lane * 8));
-				}
-				const int gp = w.gpmust[t];
-				if (gp != w.listtag) warp_lists(w, u, gp, lane);
-				if (lane < 2) root_constants(w.A[t], w.nt[t], lane, w.rootc);
-				else if (lane < 4)
-				{
-					const int sp = lane == 2 ? 1 : 4;
-					const bool there = u.row[sp] >= 0;
-					w.rootc[12 + (lane - 2) * 2 + 0] = there ? w.nt[sp * WB + t].W[0] : 1.0;
-					w.rootc[12 + (lane - 2) * 2 + 1] = there ? w.nt[sp * WB + t].W[1] : 1.0;
-				}
-#pragma unroll
-				for (int i = 0; i < 16; i++) w.Ws[(ws_base((lane & 3) << 4) ^ s) ^ ws_base(i)] = W[i];
+				const int n = min(WB, me - m0);
 				__syncwarp();
+				raw_commit(w, raw, lane);
+				for (int i = lane; i < n * QS; i += 32) w.qh[i] = qs[(size_t)(m0 - mb) * QS + i];
+				// the stash and the alphas of the units in flight are far larger than L2: ask for the next block's lines now
+				if (m0 >= mb + WB && lane * 16 < WB * QS) asm volatile("prefetch.global.L2 [%0];" ::"l"(qs + (size_t)(m0 - mb - WB) * QS + lane * 16));
+				// homozygous with equal sureness (:1235, :3488), per (slot, marker) of the batch
+				const bool homi = (lane / WB) < NSLOTS && u.row[(lane / WB) % NSLOTS] >= 0 && raw.al.x == raw.al.y && raw.su.x == raw.su.y;
+				const unsigned homb = __ballot_sync(FULL, homi);
+				if (m0 >= mb + WB) raw = raw_load(u, a, m0 - WB, WB, lane);
+				if (lane < WB)
+				{
+					int hs = 0, hom = 0, gp = 0;
+					for (int k = 0; k < NSLOTS; k++)
+						if ((homb >> (k * WB + lane)) & 1)
+						{
+							hs |= 1 << k;
+							hom |= 1 << u.slotrel[k];
+						}
+					for (int i = 0; i < u.nrel; i++)  // rule 3 (:3488-3493) of the relatives whose rule does not involve the shift mode
+						if (((hom >> i) & 1) && u.relshift[i] == 0) gp |= u.relfilter[i];
+					w.homslot[lane] = hs;
+					w.gpmust[lane] = gp;
+				}
+				__syncwarp();
+				for (int t = n - 1; t >= 0; t--)
+				{
+					const int m = m0 + t;
+					// W = alpha beta exp(F- + B - factor) (:1963-2018, :5499-5508); the factors are k ln 2 here
+					{
+						double sc = 0;
+						const int ke = kan + kb + kf;
+						if (contributing && !((double)kan * LN2 + 5.0 < minfactor) && ke > -860 && ke < 860)
+							sc = __hiloint2double((1023 + ke) << 20, 0) * efrem;
+#ifdef CNF2_X_NOTURNS
+						warp_w_and_turns(w, u, p, b, sc, kan, kb, kf, efrem, w.qh + t * QS, xbuf, m, lane, false);
+#else
+						warp_w_and_turns(w, u, p, b, sc, kan, kb, kf, efrem, w.qh + t * QS, xbuf, m, lane, wa.turns != 0);
+#endif
+					}
+					if (m > mb)
+					{
+						load_alpha(alpha + (size_t)(m - 1 - mb) * AV, p, lane);
+						kan = kexp[(size_t)(m - 1 - mb) * NUMSHIFTS + s];
+						if (m > mb + WB) asm volatile("prefetch.global.L2 [%0];" ::"l"(alpha + (size_t)(m - 1 - WB - mb) * AV + lane * 8));
+					}
+					const int gp = w.gpmust[t];
+					if (gp != w.listtag) warp_lists(w, u, gp, lane);
+					if (lane < 2) root_constants(w.A[t], w.nt[t], lane, w.rootc);
+					else if (lane < 4)
+					{
+						const int sp = lane == 2 ? 1 : 4;
+						const bool there = u.row[sp] >= 0;
+						w.rootc[12 + (lane - 2) * 2 + 0] = there ? w.nt[sp * WB + t].W[0] : 1.0;
+						w.rootc[12 + (lane - 2) * 2 + 1] = there ? w.nt[sp * WB + t].W[1] : 1.0;
+					}
+					__syncwarp();
 #ifndef CNF2_X_NOTAB
-				for (int i = lane; i < 2 * w.nE; i += 32)
-				{
-					const int c = w.el[i >> 1];
-					const int pp = c >> 6, slot = (i >> 1) - (pp ? w.nE0 : 0);
-					post_entry1(u, w.A, w.nt, w.rootc, t, pp, c & 63, i & 1, pp ? tab1 + (slot * 2 + (i & 1)) * T1W : tab0 + (slot * 2 + (i & 1)) * T0W);
-				}
+					for (int i = lane; i < 2 * w.nE; i += 32)
+					{
+						const int c = w.el[i >> 1];
+						const int pp = c >> 6, slot = (i >> 1) - (pp ? w.nE0 : 0);
+						post_entry1(u, w.A, w.nt, w.rootc, t, pp, c & 63, i & 1, pp ? tab1 + (slot * 2 + (i & 1)) * T1W : tab0 + (slot * 2 + (i & 1)) * T0W);
+					}
 #endif
-				__syncwarp();
+					__syncwarp();
 #ifndef CNF2_X_NOPAIRS
-				if (agg)
-				{
-					class_sums(w, lane, tab0, tab1, cls);
+					if (agg)
+					{
+						class_sums(w, lane, tab0, tab1, cls);
+						__syncwarp();
+					}
+					warp_posterior_pairs<AGG>(w, u, w.homslot[t], lane, tab0, tab1, cls, agg);
+#endif
+					__syncwarp();
+#ifndef CNF2_X_NOREDUCE
+					// the warp reduces its accumulator columns; the reader clears what it read
+					for (int k = lane; k < NACC; k += 32)
+					{
+						double* col = w.acc + k;
+						double v0 = 0, v1 = 0;
+#pragma unroll
+						for (int j = 0; j < NCOL; j += 2)
+						{
+							v0 += col[j * NACCP], v1 += col[(j + 1) * NACCP];
+							col[j * NACCP] = 0, col[(j + 1) * NACCP] = 0;
+						}
+						w.tot[k] = v0 + v1;
+					}
+#endif
+					__syncwarp();
+					double r0 = 0, r1 = 0;  // for the step to marker m - 1, asked for ahead of the transfer
+					if (m > 0) r0 = a.rec0[m - 1], r1 = a.rec1[m - 1];
+#ifndef CNF2_X_NOTRANSFER
+					// transfer into the EM sufficient statistics (:5875-5904, moveinfprobs :3577-3597, movehaplos :3599-3616)
+					transfer_out(w, w.tot, t, m, lane);
+#endif
+					if (m > 0)
+					{
+						emit16(b, w.qh + t * QS, lane);
+						rescale16(b, kb);
+						transition16(b, r0, r1);
+					}
 					__syncwarp();
 				}
-				warp_posterior_pairs<AGG>(w, u, w.homslot[t], lane, tab0, tab1, cls, agg);
-#endif
-				__syncwarp();
-#ifndef CNF2_X_NOREDUCE
-				// the warp reduces its accumulator columns; the reader clears what it read
-				for (int k = lane; k < NACC; k += 32)
-				{
-					double* col = w.acc + k;
-					double v0 = 0, v1 = 0;
-#pragma unroll
-					for (int j = 0; j < NCOL; j += 2)
-					{
-						v0 += col[j * NACCP], v1 += col[(j + 1) * NACCP];
-						col[j * NACCP] = 0, col[(j + 1) * NACCP] = 0;
-					}
-					w.tot[k] = v0 + v1;
-				}
-#endif
-				__syncwarp();
-				double r0 = 0, r1 = 0;  // for the step to marker m - 1, asked for ahead of the transfer
-				if (m > 0) r0 = a.rec0[m - 1], r1 = a.rec1[m - 1];
-#ifndef CNF2_X_NOTRANSFER
-				// transfer into the EM sufficient statistics (:5875-5904, moveinfprobs :3577-3597, movehaplos :3599-3616)
-				transfer_out(w, w.tot, t, m, lane);
-#endif
-				if (m > 0)
-				{
-					emit16(b, w.qh + t * QS, lane);
-					rescale16(b, kb);
-					transition16(b, r0, r1);
-				}
-				__syncwarp();
 			}
 		}
 	}

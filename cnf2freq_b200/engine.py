@@ -11,7 +11,8 @@ import os
 import numpy as np
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG, "lib", "libcnf2_engine.so")
+# CNF2_ENGINE_LIB: another build of the same library (A/B experiments, instrumented builds); never a CPU path
+LIB_PATH = os.environ.get("CNF2_ENGINE_LIB") or os.path.join(_PKG, "lib", "libcnf2_engine.so")
 
 SYMBOLS = [
     "cnf2_default_settings", "cnf2_create", "cnf2_destroy", "cnf2_last_error", "cnf2_set_map", "cnf2_set_pedigree",
@@ -26,7 +27,7 @@ SYMBOLS = [
 
 class Settings(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int32) for n in
-                ("numgen", "selfing", "relskewstates", "haplotyping", "doinfprobs", "device", "ctas_per_sm", "async_params", "in_flight", "reserved")]
+                ("numgen", "selfing", "relskewstates", "haplotyping", "doinfprobs", "device", "ctas_per_sm", "async_params", "in_flight", "segment")]
 
 
 ALLREDUCE_FN = ctypes.CFUNCTYPE(ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p)
@@ -76,7 +77,7 @@ def _buf(a, dtype, size, what):
 class Engine:
     """One engine = one GPU (one rank).  Method names follow the C ABI."""
 
-    def __init__(self, device=0, ctas_per_sm=0, async_params=False, in_flight=0):
+    def __init__(self, device=0, ctas_per_sm=0, async_params=False, in_flight=0, segment=0):
         self.lib = load_library()
         s = Settings()
         self.lib.cnf2_default_settings(ctypes.byref(s))
@@ -84,6 +85,7 @@ class Engine:
         s.ctas_per_sm = ctas_per_sm
         s.async_params = 1 if async_params else 0
         s.in_flight = in_flight
+        s.segment = segment
         self.h = ctypes.c_void_p()
         rc = self.lib.cnf2_create(ctypes.byref(self.h), ctypes.byref(s))
         if rc != 0:
@@ -299,10 +301,11 @@ class Engine:
         return float(ms.value), int(n.value), int(k.value)
 
     def mstep_counters(self, reset=False):
-        """Gradient evaluations of the step solver since the last reset: (processinfprobs, updatehaploweights)."""
-        ev = (ctypes.c_uint64 * 2)()
+        """Step-solver counters since the last reset: gradient evaluations of (processinfprobs, updatehaploweights), solves
+        ended on integral-free steps (confirmed by the closing integral, sent back)."""
+        ev = (ctypes.c_uint64 * 4)()
         self._check(self.lib.cnf2_mstep_counters(self.h, ev, ctypes.c_int32(1 if reset else 0)))
-        return int(ev[0]), int(ev[1])
+        return int(ev[0]), int(ev[1]), int(ev[2]), int(ev[3])
 
     def sync(self):
         self._check(self.lib.cnf2_sync(self.h))

@@ -58,7 +58,9 @@ typedef struct cnf2_settings
 	                          1: copies from page-locked buffers stay in flight -- keep the arrays unchanged until the
 	                          chromosome's cnf2_get_stats* or cnf2_sync returns */
 	int32_t in_flight;     /* E-steps kept in flight (their statistics stay readable): 0 = default (2), up to 4 */
-	int32_t reserved;
+	int32_t segment;       /* markers per segment of the sweeps' scratch: the forward pass keeps alpha at segment starts only
+	                          and the backward pass recomputes a segment before it walks it, so the scratch does not grow with
+	                          the chromosome; 0 = the engine chooses (the whole chromosome while that fits its budget) */
 } cnf2_settings;
 
 /* Fills *s with the reference's HEAD settings (settings.h:3-47) and device 0. */
@@ -234,9 +236,10 @@ int cnf2_last_estep_launches(cnf2_engine* e, int32_t* n);
  * own stream, so a launch that shares the GPU with other launches or with an M-step pass counts its full duration), their
  * number, and the number of kernels of any kind this engine launched.  Waits for the launches in flight. */
 int cnf2_estep_times(cnf2_engine* e, double* sum_ms, int64_t* n_launches, int64_t* n_kernels, int32_t reset);
-/* Gradient evaluations of the step solver (cappedgd, cnF2freq.cpp:4040-4177: one at the start, one per bisection midpoint,
- * 15 per Gauss-Legendre integral) since the last reset: evals[0] processinfprobs, evals[1] updatehaploweights.  Waits
- * for the passes in flight. */
+/* Counters of the step solver (cappedgd, cnF2freq.cpp:4040-4177) since the last reset, four values: gradient evaluations
+ * (one at the start, one per bisection midpoint, 15 per Gauss-Legendre integral) of [0] processinfprobs and [1]
+ * updatehaploweights; solves that ended on integral-free steps and were [2] confirmed by their closing integral, [3] sent
+ * back to repeat those steps with their integrals (see ms_cappedgd_warp).  Waits for the passes in flight. */
 int cnf2_mstep_counters(cnf2_engine* e, uint64_t* evals, int32_t reset);
 void* cnf2_stream(cnf2_engine* e);
 /* CUDA events on the engine's stream: cnf2_mark records event `slot` (0..3); cnf2_elapsed_ms waits for

@@ -38,7 +38,7 @@ def passes(stdout, C):
     return out
 
 
-def collect(prefix, iterations, stdout=None, allow_inversions=False):
+def collect(prefix, iterations, stdout=None, allow_inversions=False, stats=True):
     prob = read_dump(prefix + ".problem")
     C = len(prob["chromstarts"]) - 1
     inv = passes(stdout, C) if stdout is not None else None
@@ -58,7 +58,7 @@ def collect(prefix, iterations, stdout=None, allow_inversions=False):
             out[f"it{it}_before_{k}"] = a[k]
         for k in ("alleles", "sure", "haploweight", "scalars", "children"):  # children is rebuilt inside doit (:5246-5259)
             out[f"it{it}_after_{k}"] = b[k]
-        for c in range(C):
+        for c in range(C if stats else 0):
             st = read_dump(f"{prefix}.iter{it}.chrom{c}.stats")
             for k in ("haplobase", "haplocount", "infprobs", "homozyg"):
                 out[f"it{it}_c{c}_{k}"] = st[k]
@@ -91,7 +91,18 @@ def main():
         g = collect(tmp + "/fs", list(range(1, 7)), r.stdout, True)
         assert any(len(g[f"it{it}_c{c}_inv"]) for it in range(1, 7) for c in range(2))
         np.savez_compressed(os.path.join(HERE, "mstep_inv_fullsib.npz"), **g)
-    for n in ("mstep_demo.npz", "mstep_f2.npz", "mstep_inv_demo.npz", "mstep_inv_fullsib.npz"):
+        # longer runs for the free-running EM loop test (no per-chromosome statistics: before / after / scores / inversions only)
+        sim = synth.simulate_f2(n_f2=16, n_chrom=2, markers_per_chrom=60, spacing_cM=0.8, missing=0.2, seed=13)
+        synth.write_alpha_files(tmp + "/rf2", sim)
+        args = ["--mapfile", tmp + "/rf2.map", "--pedfile", tmp + "/rf2.ped", "--genfile", tmp + "/rf2.gen"]
+        r = subprocess.run([BIN] + args + ["--count", "9", "--dump", tmp + "/rf2"], env=env, capture_output=True, text=True, check=True)
+        np.savez_compressed(os.path.join(HERE, "mstep_run_f2.npz"), **collect(tmp + "/rf2", list(range(1, 9)), r.stdout, True, stats=False))
+        sim = synth.simulate_fullsib(n_fam=6, n_off=4, n_chrom=1, markers_per_chrom=40, spacing_cM=1.0, missing=0.1, seed=14)
+        synth.write_alpha_files(tmp + "/rfs", sim)
+        args = ["--mapfile", tmp + "/rfs.map", "--pedfile", tmp + "/rfs.ped", "--genfile", tmp + "/rfs.gen"]
+        r = subprocess.run([BIN] + args + ["--count", "8", "--dump", tmp + "/rfs"], env=env, capture_output=True, text=True, check=True)
+        np.savez_compressed(os.path.join(HERE, "mstep_run_fullsib.npz"), **collect(tmp + "/rfs", list(range(1, 8)), r.stdout, True, stats=False))
+    for n in ("mstep_demo.npz", "mstep_f2.npz", "mstep_inv_demo.npz", "mstep_inv_fullsib.npz", "mstep_run_f2.npz", "mstep_run_fullsib.npz"):
         print(n, os.path.getsize(os.path.join(HERE, n)), "bytes")
 
 

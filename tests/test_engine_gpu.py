@@ -230,3 +230,50 @@ def test_packed_statistics_equal_the_scattered_ones(eng):
         eng.get_stats_packed(c, **pk2)
         for k in pk:
             assert_close(pk2[k], pk[k], "packed parameters:" + k, rtol=1e-12, atol=1e-15)  # atomics: order of summation
+
+
+@pytest.mark.parametrize("segment", [4, 8, 20])
+@pytest.mark.parametrize("maker,kw", [
+    (randomped.f2_cross, dict(n_f2=12, n_chrom=2, mpc=37, seed=11)),
+    (randomped.tangled, dict(n_chrom=1, mpc=70, seed=16, missing=0.5)),
+    (randomped.fullsib, dict(n_fam=1, n_off=3, n_chrom=2, mpc=26, seed=17)),
+])
+def test_segmented_sweeps_equal_the_oracle(maker, kw, segment):
+    """Row a5: alpha checkpoints + recompute.  With a segment shorter than the chromosome the forward pass keeps alpha at
+    segment starts only and the backward pass re-runs the forward sweep over each segment before it walks it; the
+    statistics, scores and log-likelihoods must not depend on the segment length (ragged last segments included)."""
+    from cnf2freq_b200.engine import Engine
+    pb = maker(**kw)
+    e = Engine(device=0, segment=segment)
+    try:
+        compare(run_engine(e, pb), ol.oracle_estep(pb), f"{maker.__name__}{kw} segment {segment}")
+    finally:
+        e.close()
+
+
+def test_multi_line_f2_design_matches_oracle(eng):
+    """The cfg5-shaped bench workload in small (synth.F2Shard: biparental F2 families from several inbred lines, founders
+    shared between families, F1s homozygous where their lines agree) against the oracle, through the packed-parameter
+    calls the bench uses."""
+    from cnf2freq_b200 import synth
+    s = synth.F2Shard(12, 0, 12, 2, 21, spacing_cM=0.7, missing=0.2, seed=5, lines=5, fam_size=3)
+    K, M, C = s.par.shape[0], s.M, 2
+    ids = np.arange(K)
+    al, su, hw = np.zeros((K, M, 2), np.uint8), np.zeros((K, M, 2)), np.zeros((K, M))
+    for c in range(C):
+        cols = slice(int(s.cs[c]), int(s.cs[c + 1]))
+        al[:, cols], su[:, cols], hw[:, cols] = s.params(ids, c)
+    al[0], su[0] = 0, 0
+    pb = ol.Problem(s.par, s.empty, s.founder, s.gen, s.descendants, s.dous, s.pos, s.cs, s.genrec, al, su, hw)
+    ref = ol.oracle_estep(pb)
+    engine_problem(eng, pb, shared=s.shared)
+    rows = eng.row_ids()
+    out = dict(haplobase=np.zeros((K, M)), haplocount=np.zeros((K, M)), infprobs=np.zeros((K, M, 2, 2)), homozyg=np.zeros((K, M, 2)),
+               loglik=np.zeros((len(s.dous), C, 2)), negshift=np.zeros((K, M)))
+    for c in range(C):
+        eng.set_params_packed(c, *[np.ascontiguousarray(x) for x in s.params(rows, c)])
+        eng.estep(c)
+        eng.get_stats(c, out["haplobase"], out["haplocount"], out["infprobs"], out["homozyg"], out["loglik"])
+        eng.get_negshift(c, out["negshift"])
+    compare(out, ref, "F2Shard lines=5")
+    eng.set_shared_rows(np.zeros(0, np.int32))

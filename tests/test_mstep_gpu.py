@@ -123,6 +123,12 @@ MAX_MASKED = 0.05  # at most this fraction of the cells may be left out as ties
     # `maxdiff / (children + 1)` (:4242, :4703) shows in these cells
     ("f2_cross", dict(n_f2=11, n_chrom=2, mpc=15, seed=67, tiny=True)),
     ("fullsib", dict(n_fam=2, n_off=4, n_chrom=1, mpc=19, seed=68, tiny=True)),
+    # the step size of the later EM iterations (scalefactor ~ 1): most solves converge on a stationary point or run into
+    # the cap -- the solver's integral-free steps and their closing integral (ms_cappedgd_warp) decide these
+    ("f2_cross", dict(n_f2=40, n_chrom=2, mpc=25, seed=69, sf=1.0)),
+    ("fullsib", dict(n_fam=3, n_off=4, n_chrom=1, mpc=31, seed=70, sf=1.0)),
+    ("tangled", dict(n_chrom=2, mpc=23, seed=71, sf=2.5)),
+    ("f2_cross", dict(n_f2=25, n_chrom=1, mpc=40, seed=72, sf=0.2, ent=2.0)),
 ])
 def test_device_mstep_matches_oracle_on_random_pedigrees(eng, maker, kw):
     """Random parameters (locked phases, zero sureness, priors on some individuals): the oracle's M-step on the
