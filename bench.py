@@ -389,7 +389,7 @@ def make_workload(a, workload, D, eng, pinned):
             raise SystemExit("bench.py: --workload fullsib is a single-GPU line")
         d = synth.fullsib_flat(max(1, n // 20), 20, C, mc, spacing_cM=0.02, missing=0.05, seed=4)
         K = d["par"].shape[0]
-        children = (np.bincount(d["par"].ravel(), minlength=K) + np.bincount(d["par"][d["dous"]].ravel(), minlength=K)).astype(np.int32)
+        children = np.bincount(d["par"][d["dous"]].ravel(), minlength=K).astype(np.int32)
         children[0] = 0
         src = dict(par=d["par"], empty=d["empty"], founder=d["founder"], gen=d["gen"], descendants=d["descendants"], dous=d["dous"],
                    all_dous=d["dous"], shared=d["shared"], pos=d["markerpos"], cs=d["chromstarts"], genrec=d["genrec"],

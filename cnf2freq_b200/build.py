@@ -7,7 +7,7 @@ ROOT = os.path.dirname(PKG)
 LIB = os.path.join(PKG, "lib", "libcnf2_engine.so")
 SOURCES = [os.path.join(PKG, "csrc", "cnf2_engine.cu")]
 HEADERS = [os.path.join(PKG, "csrc", h) for h in ("cnf2_device.cuh", "cnf2_estep_kernel.cuh", "cnf2_tables.cuh", "cnf2_warp_kernel.cuh",
-                                                   "cnf2_mstep_kernel.cuh")] + [
+                                                   "cnf2_mstep_kernel.cuh", "cnf2_preprocess.cuh")] + [
     os.path.join(ROOT, "include", "cnf2_engine.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-shared", "-Xcompiler",
               "-fPIC"]

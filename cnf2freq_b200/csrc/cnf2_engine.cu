@@ -1619,3 +1619,343 @@ extern "C" int cnf2_measure_peaks(cnf2_engine* e, double* dfma_tflops, double* c
 	cudaEventDestroy(t1);
 	return CNF2_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------
+// Row f3: postmarkerdata (cnF2freq.cpp:3191-3412).  The emission scans run on the device (cnf2_preprocess.cuh); the
+// sequential bookkeeping between them -- fixkid, the descendant counts, the per-marker allele evidence fixparents hands
+// to the parents and the corrections drawn from it, lockhaplos -- follows the reference's single-threaded order
+// (individuals by id, markers inside) on the host.
+#include "cnf2_preprocess.cuh"
+
+namespace
+{
+// individ::markervals[marker]: allele -> (count, probability), ordered by allele value like the reference's map; at most a
+// handful of distinct alleles ever appear
+struct AlleleEvidence
+{
+	struct Entry
+	{
+		int key, count;
+		double prob;
+	};
+	Entry e[4];
+	int n = 0;
+	Entry* find(int key)
+	{
+		for (int i = 0; i < n; i++)
+			if (e[i].key == key) return &e[i];
+		return nullptr;
+	}
+	bool insert(int key, int count, double prob)  // map::insert: keeps an existing entry
+	{
+		if (find(key)) return true;
+		if (n >= 4) return false;
+		int at = n++;
+		while (at > 0 && e[at - 1].key > key) e[at] = e[at - 1], at--;
+		e[at] = Entry{ key, count, prob };
+		return true;
+	}
+	void erase(int key)
+	{
+		for (int i = 0; i < n; i++)
+			if (e[i].key == key)
+			{
+				for (int j = i + 1; j < n; j++) e[j - 1] = e[j];
+				n--;
+				return;
+			}
+	}
+};
+
+double dosureval(int what, int count, double prob)  // :3082-3097
+{
+	(void)count;
+	if (prob == 0) return 0;
+	double toret = std::log(prob);
+	toret /= what;
+	toret *= 4;
+	toret = std::exp(toret);
+	toret /= (1 + toret);
+	return toret;
+}
+}  // namespace
+
+extern "C" int cnf2_preprocess(cnf2_engine* e, int32_t n_ind, const int32_t* parents, const uint8_t* exists, const uint8_t* empty,
+                               uint8_t* alleles, double* sure, double* haploweight, int32_t* descendants, int32_t* children,
+                               uint8_t* founder, cnf2_log_fn log, void* log_ctx)
+{
+	if (!e || !parents || !exists || !empty || !alleles || !sure || !haploweight || !descendants || !children || !founder || n_ind <= 0)
+		return e ? e->fail(CNF2_ERR_BAD_ARG, "cnf2_preprocess: null or empty argument") : CNF2_ERR_BAD_ARG;
+	if (e->chromstarts.empty()) return e->fail(CNF2_ERR_STATE, "cnf2_preprocess: cnf2_set_map first");
+	cudaSetDevice(e->settings.device);
+	const size_t K = n_ind, M = e->markerpos.size(), cells = K * M;
+	auto say = [&](int stream, const char* fmt, auto... args) {
+		if (!log) return;
+		char line[256];
+		snprintf(line, sizeof(line), fmt, args...);
+		log(log_ctx, stream, line);
+	};
+	DevBuf<uchar2> d_al;
+	DevBuf<double2> d_su;
+	DevBuf<double> d_hw, d_sq, d_sum;
+	DevBuf<int2> d_par;
+	DevBuf<uint8_t> d_exists, d_steady, d_ok, d_ign;
+	auto cleanup = [&]() {
+		d_al.release(), d_su.release(), d_hw.release(), d_sq.release(), d_sum.release(), d_par.release();
+		d_exists.release(), d_steady.release(), d_ok.release(), d_ign.release();
+	};
+#define PRE(call)                                    \
+	do                                               \
+	{                                                \
+		int rc_ = e->cuda((call), #call);            \
+		if (rc_)                                     \
+		{                                            \
+			cleanup();                               \
+			return rc_;                              \
+		}                                            \
+	} while (0)
+	PRE(d_al.ensure(cells));
+	PRE(d_su.ensure(cells));
+	PRE(d_hw.ensure(cells));
+	PRE(d_par.ensure(K));
+	PRE(d_exists.ensure(K));
+	PRE(d_steady.ensure(K));
+	PRE(d_ok.ensure(cells));
+	PRE(d_ign.ensure(K));
+	PRE(cudaMemcpy(d_par.p, parents, K * sizeof(int2), cudaMemcpyHostToDevice));
+	PRE(cudaMemcpy(d_exists.p, exists, K, cudaMemcpyHostToDevice));
+	// what fixtrees leaves in individ::founder (:3170-3177) and returns as flag2ignore (:3105-3167) for ANY individual
+	std::vector<uint8_t> steady(K, 0), ign(K, 0);
+	for (size_t ind = 1; ind < K; ind++)
+	{
+		if (!exists[ind]) continue;
+		int flag2ignore = 1;
+		bool any1 = false;
+		for (int lev1 = 0; lev1 < 2; lev1++)
+		{
+			const int l1 = parents[ind * 2 + lev1];
+			if (!l1) continue;
+			const int flag2index = 1 + lev1 * 3;
+			if (!empty[l1]) flag2ignore |= 1 << flag2index;
+			bool anypars = false;
+			for (int lev2 = 0; lev2 < 2; lev2++)
+			{
+				const int l2 = parents[(size_t)l1 * 2 + lev2];
+				if (!l2 || empty[l2]) continue;
+				flag2ignore |= 1 << (flag2index + lev2 + 1);
+				anypars = true;
+			}
+			if (anypars || !empty[l1]) any1 = true;
+		}
+		steady[ind] = any1 ? 0 : 1;
+		ign[ind] = (uint8_t)(flag2ignore ^ (NUMPATHS - 1));
+	}
+	PRE(cudaMemcpy(d_steady.p, steady.data(), K, cudaMemcpyHostToDevice));
+	PRE(cudaMemcpy(d_ign.p, ign.data(), K, cudaMemcpyHostToDevice));
+	PreArgs pa{};
+	pa.alleles = d_al.p, pa.sure = d_su.p, pa.hw = d_hw.p, pa.par = d_par.p, pa.steady = d_steady.p;
+	pa.K = (int32_t)K, pa.M = (int32_t)M;
+	auto upload = [&]() -> cudaError_t {
+		cudaError_t ce = cudaMemcpy(d_al.p, alleles, cells * 2, cudaMemcpyHostToDevice);
+		if (ce == cudaSuccess) ce = cudaMemcpy(d_su.p, sure, cells * 16, cudaMemcpyHostToDevice);
+		if (ce == cudaSuccess) ce = cudaMemcpy(d_hw.p, haploweight, cells * 8, cudaMemcpyHostToDevice);
+		return ce;
+	};
+	auto md = [&](size_t ind, size_t g, int side) -> uint8_t& { return alleles[(ind * M + g) * 2 + side]; };
+	auto ms = [&](size_t ind, size_t g, int side) -> double& { return sure[(ind * M + g) * 2 + side]; };
+	std::vector<AlleleEvidence> vals(cells);
+	std::vector<uint8_t> okmask(cells);
+	int any = 0, anyrem = 0;
+	do
+	{
+		for (size_t i = 1; i < K; i++) children[i] = 0;
+		// fixkid (:1469-1487): an unknown genotype takes the allele of a homozygous parent, sureness 0.5
+		for (size_t i = 1; i < K; i++)
+		{
+			if (!exists[i]) continue;
+			for (size_t g = 0; g < M; g++)
+			{
+				if (md(i, g, 0) != UNKNOWN || md(i, g, 1) != UNKNOWN) continue;
+				for (int p = 0; p < 2; p++)
+				{
+					const int par = parents[i * 2 + p];
+					if (!par || !exists[par]) continue;
+					if (md(par, g, 0) == UNKNOWN) continue;
+					if (md(par, g, 0) != md(par, g, 1)) continue;
+					md(i, g, p) = md(par, g, 0);
+					ms(i, g, p) = 0.5;
+				}
+			}
+		}
+		// descendants (:3228-3258): every individual sends its count (at least 1) up once more per round
+		{
+			std::vector<int> upsent(K, 0);
+			bool anychange;
+			do
+			{
+				anychange = false;
+				for (size_t i = 1; i < K; i++)
+				{
+					if (!exists[i]) continue;
+					int nowdesc = descendants[i];
+					if (!nowdesc) nowdesc = 1;
+					nowdesc -= upsent[i];
+					if (nowdesc > 0)
+					{
+						for (int p = 0; p < 2; p++)
+							if (const int par = parents[i * 2 + p])
+								if (exists[par]) descendants[par] += nowdesc;
+						upsent[i] += nowdesc;
+						anychange = true;
+					}
+				}
+			} while (anychange);
+			for (size_t i = 1; i < K; i++)
+				if (exists[i] && descendants[i] == 0) descendants[i] = 1;
+		}
+		// fixparents' scan on the device.  A genotype without any admissible interpretation is cleared (:1432-1437), which the
+		// scans of its descendants with a higher id see: the pass is repeated from the first clearing of a marker onwards.
+		std::vector<size_t> final_upto(M, 1);
+		std::vector<uint8_t> cleared(cells, 0);
+		for (;;)
+		{
+			PRE(upload());
+			pre_okmask_kernel<<<(unsigned)((cells + 127) / 128), 128, 0, e->stream>>>(pa, d_exists.p, d_ok.p);
+			e->n_kernels++;
+			PRE(cudaGetLastError());
+			PRE(cudaMemcpyAsync(okmask.data(), d_ok.p, cells, cudaMemcpyDeviceToHost, e->stream));
+			PRE(cudaStreamSynchronize(e->stream));
+			bool again = false;
+			for (size_t g = 0; g < M; g++)
+			{
+				size_t i = final_upto[g];
+				for (; i < K; i++)
+					if (exists[i] && !okmask[i * M + g] && !cleared[i * M + g]) break;
+				if (i < K)
+				{
+					say(1, "Clearing %d:%d (was %d,%d)\n", (int)i, (int)g, (int)md(i, g, 0), (int)md(i, g, 1));
+					md(i, g, 0) = md(i, g, 1) = UNKNOWN;
+					ms(i, g, 0) = ms(i, g, 1) = 0.0;
+					cleared[i * M + g] = 1;
+					final_upto[g] = i + 1;
+					again = true;
+				}
+				else final_upto[g] = K;
+			}
+			if (!again) break;
+		}
+		// the evidence fixparents hands to the parents (:1439-1466), individuals in id order
+		for (size_t i = 1; i < K; i++)
+		{
+			if (!exists[i]) continue;
+			for (int j = 0; j < 2; j++)
+				if (const int par = parents[i * 2 + j])
+					if (exists[par]) children[par]++;
+			for (size_t g = 0; g < M; g++)
+			{
+				const bool ok[2] = { (okmask[i * M + g] & 1) != 0 && !cleared[i * M + g], (okmask[i * M + g] & 2) != 0 && !cleared[i * M + g] };
+				if (ok[0] == ok[1]) continue;
+				for (int flag2 = 0; flag2 < 2; flag2++)
+				{
+					if (!ok[flag2]) continue;
+					for (int k = 0; k < 2; k++)
+					{
+						const int par = parents[i * 2 + k];
+						if (!par || !exists[par]) continue;
+						const int u = (k ^ flag2) & 1;
+						const int allele = md(i, g, u);
+						if (allele == UNKNOWN) continue;
+						double old1 = 1;
+						int old2 = 0;
+						AlleleEvidence& ev = vals[(size_t)par * M + g];
+						if (AlleleEvidence::Entry* en = ev.find(allele)) old1 = en->prob, old2 = en->count;
+						double probit = ms(i, g, 0) + ms(i, g, 1);
+						probit /= (1 - probit);
+						if (AlleleEvidence::Entry* en = ev.find(allele)) en->count = old2 + 1, en->prob = old1 * probit;
+						else ev.insert(allele, old2 + 1, old1 * probit);
+					}
+				}
+			}
+		}
+		// corrections (:3283-3351)
+		any = 0;
+		anyrem = 0;
+		for (size_t i = 1; i < K; i++)
+		{
+			if (!exists[i]) continue;
+			for (size_t g = 0; g < M; g++)
+			{
+				AlleleEvidence& ev = vals[i * M + g];
+				const int known = (md(i, g, 0) != UNKNOWN) + (md(i, g, 1) != UNKNOWN);
+				const int oldany = any;
+				if (known == 2) continue;
+				ev.erase(UNKNOWN);
+				if (md(i, g, 0) != UNKNOWN) ev.insert(md(i, g, 0), children[i], ms(i, g, 0));
+				if (md(i, g, 1) != UNKNOWN) ev.insert(md(i, g, 1), children[i], ms(i, g, 1));
+				if (ev.n >= 3) say(1, "Error, too many matches: %d\t%d\n", (int)i, (int)g);
+				if (ev.n == 2)
+				{
+					const int knowncount = ev.e[0].count + ev.e[1].count;
+					md(i, g, 0) = (uint8_t)ev.e[0].key;
+					md(i, g, 1) = (uint8_t)ev.e[1].key;
+					ms(i, g, 0) = dosureval(knowncount, ev.e[0].count, ev.e[0].prob);
+					ms(i, g, 1) = dosureval(knowncount, ev.e[1].count, ev.e[1].prob);
+					any++;
+				}
+				else if (ev.n == 1 && known == 0)
+				{
+					any++;
+					md(i, g, 0) = (uint8_t)ev.e[0].key;
+					md(i, g, 1) = UNKNOWN;
+					ms(i, g, 0) = dosureval(ev.e[0].count, ev.e[0].count, ev.e[0].prob);
+					ms(i, g, 1) = 0.0;
+				}
+				if (any != oldany)
+					say(0, "Correction at %d, marker %d (%d;%d) (%lf;%lf)\n", (int)i, (int)g, (int)md(i, g, 0), (int)md(i, g, 1), ms(i, g, 0), ms(i, g, 1));
+			}
+			for (size_t g = 0; g < M; g++)
+			{
+				if (md(i, g, 0) == SEXMARKER) std::swap(md(i, g, 0), md(i, g, 1));
+				vals[i * M + g].n = 0;
+			}
+		}
+		say(1, "Number of corrected genotypes: %d\n", any);
+	} while (any > anyrem);
+
+	// addvariance (:1489-1558) for every individual (fixtrees' sticky founder flag takes effect in id order, :3377), then
+	// lockhaplos (:3045-3079): the phase is locked at the marker of largest variance of each chromosome
+	for (size_t i = 1; i < K; i++) founder[i] = exists[i] ? steady[i] : 0;
+	PRE(upload());
+	PRE(d_sq.ensure(cells * 8));
+	PRE(d_sum.ensure(cells * 8));
+	pre_variance_kernel<<<(unsigned)((cells * 8 + 127) / 128), 128, 0, e->stream>>>(pa, d_exists.p, d_ign.p, d_sq.p, d_sum.p);
+	e->n_kernels++;
+	PRE(cudaGetLastError());
+	std::vector<double> psq(cells * 8), psum(cells * 8);
+	PRE(cudaMemcpyAsync(psq.data(), d_sq.p, cells * 8 * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+	PRE(cudaMemcpyAsync(psum.data(), d_sum.p, cells * 8 * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+	PRE(cudaStreamSynchronize(e->stream));
+	const size_t C = e->chromstarts.size() - 1;
+	for (size_t i = 1; i < K; i++)
+	{
+		if (!exists[i]) continue;
+		for (size_t c = 0; c < C; c++)
+		{
+			long bestpos = -1;
+			double bestvar = 0;
+			for (size_t j = e->chromstarts[c]; j != e->chromstarts[c + 1]; j++)
+			{
+				double sum = 0, sqsum = 0;
+				for (int k = 0; k < 8; k++) sum += psum[(i * M + j) * 8 + k], sqsum += psq[(i * M + j) * 8 + k];
+				const double variance = sum ? sqsum : 0.0;  // `if (!sum) return` leaves the vector's zero (:1553)
+				if (variance > bestvar) bestpos = (long)j, bestvar = variance;
+			}
+			if (bestpos == -1) continue;
+			say(0, "Fixing point: %d %d %d\n", (int)i, (int)c + 1, (int)bestpos);
+			haploweight[i * M + bestpos] = haploweight[i * M + bestpos] <= 0.5 ? 0 : 1;
+		}
+	}
+	cleanup();
+#undef PRE
+	return CNF2_OK;
+}

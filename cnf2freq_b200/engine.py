@@ -22,6 +22,7 @@ SYMBOLS = [
     "cnf2_begin_iteration", "cnf2_mstep", "cnf2_get_params", "cnf2_get_negshift", "cnf2_get_negshift_packed",
     "cnf2_set_em_state", "cnf2_get_em_state", "cnf2_mstep_pass", "cnf2_negshift_minima", "cnf2_apply_inversions", "cnf2_em_pass",
     "cnf2_set_mstep_rows", "cnf2_set_mstep_chrom_packed", "cnf2_get_params_packed", "cnf2_estep_times", "cnf2_mstep_counters",
+    "cnf2_preprocess",
 ]
 
 
@@ -31,6 +32,7 @@ class Settings(ctypes.Structure):
 
 
 ALLREDUCE_FN = ctypes.CFUNCTYPE(ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p)
+LOG_FN = ctypes.CFUNCTYPE(None, ctypes.c_void_p, ctypes.c_int32, ctypes.c_char_p)
 
 
 class EngineError(RuntimeError):
@@ -207,6 +209,22 @@ class Engine:
                                                    _buf(infprobs, np.float64, 4 * n, "get_stats_packed infprobs"),
                                                    _buf(homozyg, np.float64, 2 * n, "get_stats_packed homozyg"),
                                                    _buf(loglik, np.float64, 2 * self.n_dous, "get_stats_packed loglik")))
+
+    # -- pre-processing (row f3) ----------------------------------------------------------------------
+    def preprocess(self, parents, exists, empty, alleles, sure, haploweight, descendants=None, log=None):
+        """postmarkerdata (cnF2freq.cpp:3191-3412) on arrays as the readers left them; alleles / sure / haploweight are
+        updated in place.  Returns (descendants, children, founder).  log(stream, line) receives the progress lines."""
+        c = np.ascontiguousarray
+        parents, exists, empty = c(parents, np.int32), c(exists, np.uint8), c(empty, np.uint8)
+        k, km = parents.shape[0], parents.shape[0] * self.n_markers
+        desc = np.zeros(k, np.int32) if descendants is None else c(descendants, np.int32).copy()
+        children, founder = np.zeros(k, np.int32), np.zeros(k, np.uint8)
+        cb = LOG_FN((lambda ctx, stream, line: log(int(stream), line.decode())) if log else (lambda ctx, stream, line: None))
+        self._check(self.lib.cnf2_preprocess(
+            self.h, ctypes.c_int32(k), _ptr(parents), _buf(exists, np.uint8, k, "exists"), _buf(empty, np.uint8, k, "empty"),
+            _buf(alleles, np.uint8, 2 * km, "preprocess alleles"), _buf(sure, np.float64, 2 * km, "preprocess sure"),
+            _buf(haploweight, np.float64, km, "preprocess haploweight"), _ptr(desc), _ptr(children), _ptr(founder), cb, None))
+        return desc, children, founder
 
     # -- M-step on the device (rows a6 / f1) ---------------------------------------------------------
     def set_mstep_inputs(self, relhaplo, prioralleles, priorsure, hasprior, children, empty, descendants):

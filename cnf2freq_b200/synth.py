@@ -259,9 +259,8 @@ class F2Shard:
         self.shared = np.arange(1, 1 + L, dtype=np.int32)
         self.genrec = np.full(3, -1.0 / 50)
         self.hasprior = (1 - self.empty).astype(np.uint8)   # readalphadata copies the genotypes it reads (:6664-6665)
-        # individ::children: counted over everybody in postmarkerdata (:3257-3263), then once more over the analysed
-        # individuals by each doit (:5246-5259, never reset): the value during the first EM iteration
-        self.children = (np.bincount(self.par.ravel(), minlength=K) + np.bincount(self.par[self.all_dous].ravel(), minlength=K)).astype(np.int32)
+        # individ::children as every doit recounts it: analysed children only (:5226, :5246-5259)
+        self.children = np.bincount(self.par[self.all_dous].ravel(), minlength=K).astype(np.int32)
         self.children[0] = 0
 
     def params(self, ids, c, out=None):

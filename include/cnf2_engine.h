@@ -225,6 +225,24 @@ int cnf2_apply_inversions(cnf2_engine* e, int32_t chrom, const int32_t* ids, con
  * cnf2_begin_iteration forgets the candidates (negshiftcands is local to doit, :5261). */
 int cnf2_em_pass(cnf2_engine* e, int32_t chrom, int32_t* inv_ids, int32_t* inv_markers, int32_t cap, int32_t* n_inv);
 
+/* ---- pre-processing (row f3): postmarkerdata, cnF2freq.cpp:3191-3412 ----------------------------------------------------
+ * What the reference runs once between reading its inputs and the first EM iteration (main, :8083-8085, with
+ * CORRECTIONINFERENCE true): genotype inference for untyped relatives to a fixed point -- fixkid :1469-1487, fixparents
+ * :1392-1467 and the corrections drawn from the evidence it collects :3283-3351 --, the descendant and child counts
+ * (:3228-3277), addvariance :1489-1558 and lockhaplos :3045-3079 (the phase of every individual is locked at the marker of
+ * largest variance of each chromosome).  The two emission scans (fixparents: up to 64 x 128 emissions per individual-marker;
+ * addvariance: 2 x 2 x 2 x 64 x 64 x 2) run on the device for all individuals at once; the bookkeeping between them follows the
+ * reference's single-threaded order.  Needs cnf2_set_map.  All arrays are [n_ind](...) / [n_ind][n_markers](x2), caller
+ * owned: alleles / sure / haploweight in-out (as the readers left them -> as the first EM iteration finds them),
+ * descendants in-out (zero on entry for a fresh run), children and founder (fixtrees' sticky flag, :3170-3177: pass it to
+ * cnf2_set_pedigree) out.  exists: the individual exists (individer[] non-null).  log (may be NULL) receives the
+ * reference's progress lines ("Correction at", "Fixing point", to stdout = 0; "Number of corrected genotypes", "Clearing"
+ * to stderr = 1) in its order. */
+typedef void (*cnf2_log_fn)(void* ctx, int32_t stream, const char* line);
+int cnf2_preprocess(cnf2_engine* e, int32_t n_ind, const int32_t* parents, const uint8_t* exists, const uint8_t* empty,
+                    uint8_t* alleles, double* sure, double* haploweight, int32_t* descendants, int32_t* children,
+                    uint8_t* founder, cnf2_log_fn log, void* log_ctx);
+
 /* Block until everything enqueued by this engine has finished; returns the first asynchronous error. */
 int cnf2_sync(cnf2_engine* e);
 

@@ -28,6 +28,7 @@ namespace cnf2drv
 {
 static FILE* realstderr = nullptr;
 static std::string dumpprefix;
+static std::string statedumpfn;  // the per-iteration text dump of cnF2freq.cpp:8157-8192 (what main writes to --output)
 static bool dumpfwbw = false;
 static bool quiet = false;
 static int curiter = 0;
@@ -390,6 +391,7 @@ int main(int argc, char* argv[])
 		else if (a == "--count") COUNT = atoi(next().c_str());
 		else if (a == "--limit") limit = atoi(next().c_str());
 		else if (a == "--dump") dumpprefix = next();
+		else if (a == "--statedump") statedumpfn = next();
 		else if (a == "--dumpfwbw") dumpfwbw = true;
 		else if (a == "--quiet") quiet = true;
 		else if (a == "--mode") mode = next();
@@ -486,6 +488,32 @@ int main(int argc, char* argv[])
 				int len = sprintf(line, "TIME iter %d seconds %.6f individuals %zu markers %zu states %d threads %d\n", i, dt, analysed, M, NUMTYPES, omp_get_max_threads());
 				if (write(resultfd, line, len) < 0) return 3;
 			}
+		}
+		// cnF2freq.cpp:8157-8192: the state after every iteration, in main's formats
+		if (!statedumpfn.empty())
+		{
+			static FILE* sd = fopen(statedumpfn.c_str(), "w");
+			for (int i2 = 1; i2 <= maxn; i2++)
+			{
+				if (i2 > limit) continue;
+				individ* ind = individer[i2];
+				if (!ind || !ind->haplocount.size()) continue;
+				fprintf(sd, "%d %s\n", i2, ind->name.c_str());
+				for (unsigned int c = 0; c < chromstarts.size() - 1; c++)
+					for (unsigned int j = chromstarts[c]; j < chromstarts[c + 1]; j++)
+					{
+						if (ind->priormarkerdata.size() > j)
+							fprintf(sd, "%f\t%d\t%d\t\t%f\t%lf %lf %lf\t%d\t%d\t%lf\t%lf\n", ind->haploweight[j], ind->markerdata[j].first.value(),
+							        ind->markerdata[j].second.value(), ind->negshift[j], ind->markersure[j].first, ind->markersure[j].second,
+							        RELSKEWS ? ind->relhaplo[j] : 0, ind->priormarkerdata[j].first.value(), ind->priormarkerdata[j].second.value(),
+							        ind->priormarkersure[j].first, ind->priormarkersure[j].second);
+						else
+							fprintf(sd, "%f\t%d\t%d\t\t%f\t%lf %lf %lf\n", ind->haploweight[j], ind->markerdata[j].first.value(),
+							        ind->markerdata[j].second.value(), ind->negshift[j], ind->markersure[j].first, ind->markersure[j].second,
+							        RELSKEWS ? ind->relhaplo[j] : 0);
+					}
+			}
+			fflush(sd);
 		}
 		// cnF2freq.cpp:8187: negshift is reset after each iteration's dump
 		for (int i2 = 1; i2 <= maxn; i2++)

@@ -50,3 +50,21 @@ def test_no_cpu_fallback():
         pytest.skip("a GPU is present; the refusal path is exercised on the CPU box")
     with pytest.raises(engine.EngineError, match="no CPU path|no usable CUDA device"):
         engine.Engine()
+
+
+def test_host_program_builds_against_the_abi_and_refuses_to_run_without_a_gpu(tmp_path):
+    """host/cnf2freq_gpu (row f4) is the compiled C++ caller of include/cnf2_engine.h: it must build with g++ against the
+    header alone, parse the reference's input formats, and -- like the library -- have no CPU path."""
+    import subprocess
+    import torch
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    subprocess.check_call(["make", "-C", os.path.join(root, "host"), "cnf2freq_gpu"], stdout=subprocess.DEVNULL)
+    data = os.path.join(root, "tests", "golden", "host", "refdata")
+    r = subprocess.run([os.path.join(root, "host", "cnf2freq_gpu"), "--mapfile", data + "/demoplantimpute.map", "--pedfile",
+                        data + "/demoplantimpute.ped", "--genfile", data + "/demoplantimpute.gen", "--count", "1", "--output",
+                        str(tmp_path / "o")], capture_output=True, text=True)
+    assert "5/1 turned into 1 1 with 0.002121;0.474640" in r.stdout  # the read-count genotypes of the demo (:6599-6657)
+    if torch.cuda.is_available():
+        assert r.returncode == 0
+    else:
+        assert r.returncode != 0 and "no usable CUDA device" in r.stderr
