@@ -126,6 +126,8 @@ struct cnf2_engine
 	// phase-inversion candidates of the iteration (negshiftcands, :5261; host logic of :6270-6340)
 	std::vector<int32_t> parents;                // [n_ind][2]
 	std::vector<std::vector<int32_t>> kids;      // analysed children (individ::kids, :5246-5259)
+	std::vector<std::vector<int32_t>> allkids;   // every individual naming this one as a parent (inverse of the pointer chains)
+	std::vector<std::map<int32_t, std::pair<double, int32_t>>> candmap;  // per chromosome: id -> (val, start) of its candidate
 	struct Cand { int32_t id; double val; int32_t start; bool operator<(const Cand& o) const { return id != o.id ? id < o.id : val != o.val ? val < o.val : start < o.start; } };
 	std::vector<std::set<Cand>> cands;           // per chromosome
 	std::vector<std::vector<double>> minval_c;   // per chromosome: minima of this iteration by individual id (empty: none yet)
@@ -640,6 +642,11 @@ extern "C" int cnf2_set_pedigree(cnf2_engine* e, int32_t n_ind, const int32_t* p
 	for (int j = 0; j < n_all_dous; j++)
 		for (int lev1 = 0; lev1 < 2; lev1++)
 			if (const int p = parents[all_dous[j] * 2 + lev1]) e->kids[p].push_back(all_dous[j]);
+	e->allkids.assign(n_ind, {});
+	for (int i = 1; i < n_ind; i++)
+		for (int lev1 = 0; lev1 < 2; lev1++)
+			if (const int p = parents[i * 2 + lev1])
+				if (e->allkids[p].empty() || e->allkids[p].back() != i) e->allkids[p].push_back(i);
 	CU(cudaStreamSynchronize(e->stream));
 	std::fill(e->have_params.begin(), e->have_params.end(), 0);
 	for (Slot& sl : e->slots) sl.chrom = -1;
@@ -993,6 +1000,7 @@ extern "C" int cnf2_begin_iteration(cnf2_engine* e)
 	std::fill(e->carry_valid.begin(), e->carry_valid.end(), 0);  // doit zeroes haplobase / haplocount, :5222-5234
 	const size_t C = e->chromstarts.empty() ? 0 : e->chromstarts.size() - 1;
 	e->cands.assign(C, {});       // negshiftcands is local to doit (:5261)
+	e->candmap.assign(C, {});
 	e->minval_c.assign(C, {});    // negshift is zeroed after every iteration's dump (:8187)
 	e->minstart_c.assign(C, {});
 	return CNF2_OK;
@@ -1243,13 +1251,23 @@ extern "C" int cnf2_apply_inversions(cnf2_engine* e, int32_t chrom, const int32_
 }
 
 // individ::arerelated (cnF2freq.cpp:916-946): within two generations up the pointer chains, or sharing an analysed child
-static bool arerelated(const cnf2_engine* e, int a, int b, std::vector<int> stack, int gens)
+struct RelStack
+{
+	int v[4], n = 0;
+	bool has(int a) const
+	{
+		for (int i = 0; i < n; i++)
+			if (v[i] == a) return true;
+		return false;
+	}
+};
+static bool arerelated(const cnf2_engine* e, int a, int b, RelStack stack, int gens)
 {
 	if (gens > 2) return false;
 	if (b == a) return true;
-	if (std::find(stack.begin(), stack.end(), a) != stack.end()) return false;
-	stack.push_back(a);
-	if (stack.size() == 1)
+	if (stack.has(a)) return false;
+	stack.v[stack.n++] = a;
+	if (stack.n == 1)
 	{
 		if (b && arerelated(e, b, a, stack, gens + 1)) return true;
 	}
@@ -1262,13 +1280,47 @@ static bool arerelated(const cnf2_engine* e, int a, int b, std::vector<int> stac
 	return false;
 }
 
+// Everybody `a` for whom arerelated(a, our) can hold -- a superset, to be confirmed by arerelated itself: our, its
+// descendants and ancestors within two pointer steps, and whoever is tied to it through a shared analysed child at the levels
+// arerelated looks at (the other parents of our's analysed children and of its parents' analysed children, and their
+// descendants within two steps).  The reference scans all candidates of the chromosome for every individual; with
+// thousands of candidates that scan is quadratic, this list is a handful of individuals except for a founder line.
+static void related_superset(const cnf2_engine* e, int our, std::vector<int32_t>& out)
+{
+	out.clear();
+	auto down2 = [&](int x) {
+		out.push_back(x);
+		for (int k1 : e->allkids[x])
+		{
+			out.push_back(k1);
+			for (int k2 : e->allkids[k1]) out.push_back(k2);
+		}
+	};
+	down2(our);
+	for (int k = 0; k < 2; k++)
+		if (const int p = e->parents[(size_t)our * 2 + k])
+		{
+			out.push_back(p);
+			for (int kk = 0; kk < 2; kk++)
+				if (const int pp = e->parents[(size_t)p * 2 + kk]) out.push_back(pp);
+			for (int kid : e->kids[p])  // kids[q] and kids[a] share a child, q a parent of our
+				for (int k2 = 0; k2 < 2; k2++)
+					if (const int co = e->parents[(size_t)kid * 2 + k2]) out.push_back(co);
+		}
+	for (int kid : e->kids[our])  // kids[x] and kids[our] share a child for x = a, a parent of a, a grandparent of a
+		for (int k2 = 0; k2 < 2; k2++)
+			if (const int co = e->parents[(size_t)kid * 2 + k2]) down2(co);
+	std::sort(out.begin(), out.end());
+	out.erase(std::unique(out.begin(), out.end()), out.end());
+}
+
 extern "C" int cnf2_em_pass(cnf2_engine* e, int32_t chrom, int32_t* inv_ids, int32_t* inv_markers, int32_t cap, int32_t* n_inv)
 {
 	if (!e) return CNF2_ERR_BAD_ARG;
 	if (!e->have_ms_inputs) return e->fail(CNF2_ERR_STATE, "cnf2_em_pass: cnf2_set_mstep_inputs first");
 	const int C = (int)e->chromstarts.size() - 1;
 	if (chrom < 0 || chrom >= C) return e->fail(CNF2_ERR_BAD_ARG, "cnf2_em_pass: bad chromosome");
-	if ((int)e->cands.size() != C) return e->fail(CNF2_ERR_STATE, "cnf2_em_pass: cnf2_begin_iteration first");
+	if ((int)e->candmap.size() != C) return e->fail(CNF2_ERR_STATE, "cnf2_em_pass: cnf2_begin_iteration first");
 	Slot* slp = slot_of(e, chrom);
 	if (!slp) return e->fail(CNF2_ERR_STATE, "cnf2_em_pass: cnf2_estep for this chromosome first (its statistics must still be in flight)");
 	cudaSetDevice(e->settings.device);
@@ -1303,40 +1355,56 @@ extern "C" int cnf2_em_pass(cnf2_engine* e, int32_t chrom, int32_t* inv_ids, int
 			}
 	}
 	// candidates, at most one per individual and chromosome (:6270-6327): individuals in id order, every chromosome each
+	std::vector<int32_t> rel;
 	for (int id = 1; id < e->n_ind; id++)
+	{
+		bool have_rel = false;
 		for (int c = 0; c < C; c++)
 		{
 			if (e->minval_c[c].empty()) continue;
 			const int Mc = e->mc(c), minstart = e->minstart_c[c][id];
 			if (!(minstart + 1 < Mc)) continue;  // :6301 (none, or the last marker)
-			const cnf2_engine::Cand our{ id, e->minval_c[c][id], minstart };
+			const double ourval = e->minval_c[c][id];
+			auto& cm = e->candmap[c];
 			bool anymatch = false;
-			for (auto it = e->cands[c].begin(); it != e->cands[c].end();)
+			if (!cm.empty())
 			{
-				bool erase = false;
-				if (arerelated(e, it->id, our.id, {}, 0))  // inferiorrelated, :3415-3435
-				{
-					if (it->val > our.val) erase = true;
+				if (!have_rel) related_superset(e, id, rel), have_rel = true;
+				// inferiorrelated (:3415-3435) over the candidates that can be related at all
+				auto test = [&](std::map<int32_t, std::pair<double, int32_t>>::iterator it) {
+					if (!arerelated(e, it->first, id, RelStack{}, 0)) return;
+					if (it->second.first > ourval) cm.erase(it);
 					else anymatch = true;
-				}
-				if (erase) it = e->cands[c].erase(it);
-				else ++it;
+				};
+				if (rel.size() < cm.size())
+					for (int32_t a : rel)
+					{
+						auto it = cm.find(a);
+						if (it != cm.end()) test(it);
+					}
+				else
+					for (auto it = cm.begin(); it != cm.end();)
+					{
+						auto cur = it++;
+						if (std::binary_search(rel.begin(), rel.end(), cur->first)) test(cur);
+					}
 			}
-			if (!anymatch && rand() / (RAND_MAX / 5)) e->cands[c].insert(our);  // :6319
+			if (!anymatch && rand() / (RAND_MAX / 5)) cm[id] = { ourval, minstart };  // :6319
 		}
+	}
 	// negshifter on every candidate of every chromosome (:6336-6340)
 	bool any = false;
 	int n_out = 0;
 	for (int c = 0; c < C; c++)
 	{
-		if (e->cands[c].empty()) continue;
+		if (e->candmap[c].empty()) continue;
 		any = true;
 		std::vector<int32_t> ids, starts;
-		for (const auto& cd : e->cands[c])
+		for (const auto& cd : e->candmap[c])
 		{
-			ids.push_back(cd.id);
-			starts.push_back(cd.start);
-			if (inv_ids && inv_markers && n_out < cap) inv_ids[n_out] = cd.id, inv_markers[n_out] = (int32_t)e->chromstarts[c] + cd.start + 1;
+			ids.push_back(cd.first);
+			starts.push_back(cd.second.second);
+			if (inv_ids && inv_markers && n_out < cap) inv_ids[n_out] = cd.first, inv_markers[n_out] = (int32_t)e->chromstarts[c] + cd.second.second + 1;
 			n_out++;
 		}
 		if (int rc = cnf2_apply_inversions(e, c, ids.data(), starts.data(), (int32_t)ids.size())) return rc;

@@ -66,10 +66,11 @@ struct __align__(16) WarpSmem
 	unsigned char vmk[256];        // per (entry, root orientation): bit xo = rule 2 admits the other parent's x = xo
 	unsigned short ainfo[128];     // per entry: ws_base of its meiosis bits at the parent's place | x << 10
 	unsigned char cst[32], ccn[32]; // per (parent, phase bit, meiosis bits) class: first entry and number of entries
-	int nE, nE0, nX0, nX1, listtag; // nX0 / nX1: entries of parent 0 / 1 with phase bit x & 1 = 0
-	int ntr, rootmask;
+	int listtag;
+	short nE, nE0, nX0, nX1;        // nX0 / nX1: entries of parent 0 / 1 with phase bit x & 1 = 0
+	short ntr, rootmask;            // (sizes kept tight: 12 single-warp CTAs per SM need <= 18,432 B each)
 	double* nsptr[NSLOTS];         // turn scoring: negshift cell of the slot's occupant at marker 0 (null: no contribution)
-	int homslot[WB], gpmust[WB];
+	unsigned char homslot[WB], gpmust[WB];
 	Unit unit;
 	// followed by the posterior tables of the current marker, sized by the host for the pedigree (WarpArgs::cap0/cap1):
 	//   tab0[cap0][f][T0W]: Q(plain), rho0[1], rho0[2];  tab1[cap1][f][T1W]: Q(plain), rho1[1], rho1[2], Q(al,0)/Q(plain)
@@ -379,8 +380,8 @@ __device__ __forceinline__ void transfer_setup(WarpSmem& w, const EstepArgs& a, 
 		int rm = 0;
 		for (int slot = 0; slot < NSLOTS; slot++)
 			if (u.row[slot] >= 0 && u.slotrel[slot] == rootrel) rm |= 1 << slot;
-		w.rootmask = rm;
-		w.ntr = nout;
+		w.rootmask = (short)rm;
+		w.ntr = (short)nout;
 	}
 	if (lane < NSLOTS)
 	{
@@ -725,10 +726,10 @@ __device__ __forceinline__ void warp_lists(WarpSmem& w, const Unit& u, int gpmus
 	}
 	if (lane == 0)
 	{
-		w.nE = nE;
-		w.nE0 = nE0;
-		w.nX0 = nX[0];
-		w.nX1 = nX[1];
+		w.nE = (short)nE;
+		w.nE0 = (short)nE0;
+		w.nX0 = (short)nX[0];
+		w.nX1 = (short)nX[1];
 		w.listtag = gpmust;
 	}
 	__syncwarp();

@@ -291,6 +291,27 @@ int nccl_hook(void*, double* buf, size_t count, void* stream)
 	return ncclAllReduce(buf, buf, count, ncclDouble, ncclSum, g_comm, (cudaStream_t)stream) == ncclSuccess ? 0 : 1;
 }
 #endif
+
+// Sum of a host vector over the ranks (every rank contributes zeros for what it does not own): how rank 0 gets the rows
+// of the other ranks' individuals for the likelihood lines and the state dump.
+void sum_over_ranks(std::vector<double>& v, int world)
+{
+	if (world <= 1 || v.empty()) return;
+#ifdef CNF2_WITH_NCCL
+	static double* d = nullptr;
+	static size_t cap = 0;
+	if (cap < v.size())
+	{
+		if (d) cudaFree(d);
+		if (cudaMalloc(&d, v.size() * sizeof(double)) != cudaSuccess) die("cudaMalloc for the gather failed");
+		cap = v.size();
+	}
+	cudaMemcpy(d, v.data(), v.size() * sizeof(double), cudaMemcpyHostToDevice);
+	if (ncclAllReduce(d, d, v.size(), ncclDouble, ncclSum, g_comm, 0) != ncclSuccess) die("ncclAllReduce failed");
+	cudaStreamSynchronize(0);
+	cudaMemcpy(v.data(), d, v.size() * sizeof(double), cudaMemcpyDeviceToHost);
+#endif
+}
 }  // namespace
 
 int main(int argc, char* argv[])
@@ -492,6 +513,20 @@ int main(int argc, char* argv[])
 		if (!out) die("cannot open %s", outfn.c_str());
 	}
 	std::vector<double> loglik(mine.size() * (size_t)C * 2, 0.0);
+	// rows this rank reports in the gather: the ones only it touches, and (rank 0) the shared ones, which are equal everywhere
+	std::vector<uint8_t> owned(K, 0);
+	std::map<int, size_t> dou_pos;
+	for (size_t j = 0; j < dous.size(); j++) dou_pos[dous[j]] = j;
+	if (world > 1)
+	{
+		int32_t n_rows = 0;
+		CK(cnf2_row_count(eng, &n_rows));
+		std::vector<int32_t> rows(n_rows);
+		CK(cnf2_row_ids(eng, rows.data()));
+		for (int32_t id : rows) owned[id] = 1;
+		if (rank)
+			for (int32_t id : shared) owned[id] = 0;
+	}
 	std::vector<int32_t> inv_ids(4096), inv_markers(4096);
 	for (int it = 0; it < COUNT; it++)
 	{
@@ -512,12 +547,19 @@ int main(int argc, char* argv[])
 			{
 				if (c + ahead < C || ahead == 0) CK(cnf2_estep(eng, c + ahead));
 				CK(cnf2_get_stats(eng, c, nullptr, nullptr, nullptr, nullptr, loglik.data()));
+				std::vector<double> ll(dous.size() * 2, 0.0);  // in the order of the whole run's analysed individuals
 				for (size_t j = 0; j < mine.size(); j++)
 				{
+					const size_t at = world > 1 ? dou_pos[mine[j]] : j;
+					ll[at * 2] = loglik[(j * C + c) * 2], ll[at * 2 + 1] = loglik[(j * C + c) * 2 + 1];
+				}
+				sum_over_ranks(ll, world);
+				for (size_t j = 0; j < dous.size(); j++)
+				{
 					int f2i, shi;
-					tree_masks(mine[j], f2i, shi);
-					const int shiftend = inds[mine[j]].gen < 2 ? 2 : NUMSHIFTS;  // :5359
-					printf("%d,%03d,%03d: %lf\t%lf %d\n", mine[j], f2i, shi, loglik[(j * C + c) * 2], loglik[(j * C + c) * 2 + 1], shiftend);
+					tree_masks(dous[j], f2i, shi);
+					const int shiftend = inds[dous[j]].gen < 2 ? 2 : NUMSHIFTS;  // :5359
+					printf("%d,%03d,%03d: %lf\t%lf %d\n", dous[j], f2i, shi, ll[j * 2], ll[j * 2 + 1], shiftend);
 				}
 				for (int d : dous) fprintf(rep, "%s:%d\n\n", inds[d].name.c_str(), c + 1);  // :6183-6188 (the rows are empty at HEAD, :5873)
 				fflush(rep);
@@ -533,6 +575,33 @@ int main(int argc, char* argv[])
 				CK(cnf2_get_negshift(eng, c, negshift.data()));  // the chromosome's statistics block is reused by a later E-step
 			}
 			for (int c = 0; c < C; c++) CK(cnf2_get_params(eng, c, markerdata.data(), markersure.data(), haploweight.data()));
+			if (world > 1)
+			{
+				// every rank ends the iteration with the whole state: six values per (individual, marker), zeros where not owned
+				std::vector<double> pack(K * M * 6, 0.0);
+				for (size_t i = 1; i < K; i++)
+					if (owned[i])
+						for (size_t j = 0; j < M; j++)
+						{
+							const size_t x = i * M + j;
+							double* q = &pack[x * 6];
+							q[0] = haploweight[x], q[1] = markerdata[x * 2], q[2] = markerdata[x * 2 + 1], q[3] = markersure[x * 2], q[4] = markersure[x * 2 + 1];
+							q[5] = negshift[x];
+						}
+				std::vector<double> touched(K, 0.0);
+				for (size_t i = 1; i < K; i++) touched[i] = owned[i];
+				sum_over_ranks(pack, world);
+				sum_over_ranks(touched, world);
+				for (size_t i = 1; i < K; i++)
+					if (touched[i] > 0)
+						for (size_t j = 0; j < M; j++)
+						{
+							const size_t x = i * M + j;
+							const double* q = &pack[x * 6];
+							haploweight[x] = q[0], markerdata[x * 2] = (uint8_t)q[1], markerdata[x * 2 + 1] = (uint8_t)q[2], markersure[x * 2] = q[3];
+							markersure[x * 2 + 1] = q[4], negshift[x] = q[5];
+						}
+			}
 		}
 		fflush(stdout);
 		fflush(out);
