@@ -5,7 +5,7 @@
 // statements of doit (:5189-6410) that a drop-in has to keep:
 //
 //   cnf2freq_gpu --mapfile M --pedfile P --genfile G [--gigimapfile M --gigipedfile P] --count N [--limit L]
-//                [--output FILE] [--tmppath DIR]
+//                [--output FILE] [--tmppath DIR] [--deserialize FILE]
 //
 // --output FILE receives what the reference writes there: the state dump after every iteration (:8157-8192) and the last
 // iteration's per-chromosome report; stdout carries the progress lines (likelihoods :5399-5401, "Inv:" :3450, "Scale
@@ -272,6 +272,60 @@ void readgigidata(FILE* map, FILE* ped)
 	}
 }
 
+// deserialize (:7757-7832): resume from the state dumps of an earlier run (its --output file): for every `<n> <name>` header
+// of an individual known under that number and name, one line per marker `haploweight a b negshift sure1 sure2 ...`; later
+// dumps of the file overwrite earlier ones.  Reports the phase switches per individual as the reference does.
+void deserialize(FILE* in, const std::vector<int32_t>& children)
+{
+	const size_t M = markerposes.size();
+	char line[1024];
+	while (fgets(line, sizeof(line), in))
+	{
+		int n = 0, used = 0;
+		char name[255];
+		if (sscanf(line, "%d %254s %n", &n, name, &used) != 2 || line[used] != 0) continue;  // int_ >> word_ >> eoi
+		auto it = indmap.find(name);
+		if (n <= 0 || n >= (int)inds.size() || it == indmap.end() || it->second != n)
+		{
+			fprintf(stderr, "Supposed individual header not a header: %s", line);
+			continue;
+		}
+		int oldphase = 0, switches = 0;
+		for (size_t i = 0; i < M; i++)
+		{
+			double hw, ns, s1, s2;
+			int a, b;
+			if (!fgets(line, sizeof(line), in) || sscanf(line, "%lf %d %d %lf %lf %lf", &hw, &a, &b, &ns, &s1, &s2) != 6)
+			{
+				fprintf(stderr, "Reading haplotype for marker %zu for individual %s failed: %s", i, name, line);
+				continue;
+			}
+			const size_t x = (size_t)n * M + i;
+			haploweight[x] = hw;
+			uint8_t* md = &markerdata[x * 2];
+			bool inv = false, match = true;
+			if (!(md[0] == a && md[1] == b))
+			{
+				if (!(md[0] == b && md[1] == a))
+				{
+					fprintf(stderr, "Genotype mismatch for marker %zu for individual %s (%d,%d) to  (%d,%d)\n", i, name, md[0], md[1], a, b);
+					match = false;
+				}
+				else inv = true;
+			}
+			md[0] = (uint8_t)a, md[1] = (uint8_t)b;
+			markersure[x * 2] = s1, markersure[x * 2 + 1] = s2;
+			if (hw == 0.5 || a == b || !match) continue;
+			const int newphase = 1 + ((hw > 0.5) ^ inv);
+			if (oldphase && oldphase != newphase) switches++;
+			oldphase = newphase;
+		}
+		const Individ& ind = inds[n];
+		if (children[n] || (ind.pars[0] && !inds[ind.pars[0]].empty) || (ind.pars[1] && !inds[ind.pars[1]].empty))
+			printf("Switches %d %s\t%d\n", n, name, switches);
+	}
+}
+
 void log_line(void*, int32_t stream, const char* line)
 {
 	fputs(line, stream ? stderr : stdout);
@@ -316,7 +370,7 @@ void sum_over_ranks(std::vector<double>& v, int world)
 
 int main(int argc, char* argv[])
 {
-	std::string mapfn, pedfn, genfn, gigimap, gigiped, outfn, tmppath = ".";
+	std::string mapfn, pedfn, genfn, gigimap, gigiped, outfn, deserializefn, tmppath = ".";
 	int COUNT = 3, limit = INDCOUNT;  // :7961-7962
 	for (int i = 1; i < argc; i++)
 	{
@@ -334,7 +388,8 @@ int main(int argc, char* argv[])
 		else if (a == "--count") COUNT = atoi(next().c_str());
 		else if (a == "--limit") limit = atoi(next().c_str());
 		else if (a == "--tmppath") tmppath = next();
-		else die("unknown option %s (supported: --mapfile --pedfile --genfile --gigimapfile --gigipedfile --count --limit --output --tmppath)", a.c_str());
+		else if (a == "--deserialize") deserializefn = next();
+		else die("unknown option %s (supported: --mapfile --pedfile --genfile --gigimapfile --gigipedfile --count --limit --output --tmppath --deserialize)", a.c_str());
 	}
 	const int rank = getenv("RANK") ? atoi(getenv("RANK")) : 0, world = getenv("WORLD_SIZE") ? atoi(getenv("WORLD_SIZE")) : 1;
 	const int local_rank = getenv("LOCAL_RANK") ? atoi(getenv("LOCAL_RANK")) : rank;
@@ -401,6 +456,16 @@ int main(int argc, char* argv[])
 	// postmarkerdata (:8083-8085)
 	CK(cnf2_preprocess(eng, (int32_t)K, parents.data(), exists.data(), empty.data(), markerdata.data(), markersure.data(), haploweight.data(),
 	                   descendants.data(), children.data(), founder.data(), log_line, nullptr));
+
+	if (!deserializefn.empty())  // :8087-8093
+	{
+		FILE* f = fopen(deserializefn.c_str(), "rt");
+		if (!f) die("cannot open %s", deserializefn.c_str());
+		printf("deserialize started.\n");
+		deserialize(f, children);
+		fclose(f);
+		printf("deserialize finished.\n");
+	}
 
 	// analysed individuals of this rank: sibships dealt to the least loaded rank, the largest first (one rank: all of them)
 	std::vector<int32_t> mine, shared;

@@ -96,3 +96,26 @@ def test_host_program_reproduces_the_reference_run(binary, tmp_path, name):
         compare_lines(mine[:upto], ref[:upto], f"{name}: progress lines of postmarkerdata and the first iteration")
     report = [l for l in out.read_text().splitlines() if ":" in l]
     assert any(l.startswith("FIRST PASS: ") for l in report) and any(re.match(r"^\S+:1$", l) for l in report)
+
+
+def test_host_program_resumes_from_its_own_dump(binary, tmp_path):
+    """--deserialize (cnF2freq.cpp:7757-7832): the state dumps of an earlier run are read back after postmarkerdata; the
+    resumed run's first dump carries the earlier run's last haploweights, alleles and sureness, and continuing from it
+    gives what the uninterrupted run gives (step-size state apart: scalefactor restarts, as in the reference)."""
+    args, _, datadir, _ = CASES["f2"]
+    args = [os.path.join(datadir, a) if not a.startswith("--") else a for a in args]
+    first = tmp_path / "first.txt"
+    r = subprocess.run([binary] + args + ["--count", "3", "--output", str(first)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    second = tmp_path / "second.txt"
+    r = subprocess.run([binary] + args + ["--count", "1", "--deserialize", str(first), "--output", str(second)], capture_output=True,
+                       text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "deserialize finished." in r.stdout and "Switches " in r.stdout
+    dump = lambda p: [l for l in p.read_text().splitlines() if l.strip() and ":" not in l]
+    a, b = dump(first), dump(second)
+    per = len(a) // 3
+    assert len(b) == per
+    for x, y in zip(a[2 * per:], b):   # haploweight, alleles, (negshift is per run), sureness
+        tx, ty = x.split(), y.split()
+        assert tx[:3] == ty[:3] and tx[4:6] == ty[4:6], (x, y)

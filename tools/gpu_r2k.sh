@@ -17,6 +17,6 @@ G=tests/golden/host
 ./host/cnf2freq_gpu --mapfile $G/f2.map --pedfile $G/f2.ped --genfile $G/f2.gen --count 4 --output gpurun_out/r2k_host1.out > gpurun_out/r2k_host1.stdout 2>/dev/null; echo "host1 rc $?"
 rm -f /tmp/cnf2_nccl_id
 for R in 0 1; do RANK=$R WORLD_SIZE=2 LOCAL_RANK=$R CNF2_NCCL_ID_FILE=/tmp/cnf2_nccl_id timeout 300 ./host/cnf2freq_gpu_nccl --mapfile $G/f2.map --pedfile $G/f2.ped --genfile $G/f2.gen --count 4 --output gpurun_out/r2k_host2_r$R.out > gpurun_out/r2k_host2_r$R.stdout 2> gpurun_out/r2k_host2_r$R.stderr & done; wait; echo "host2 done"
-tail -3 gpurun_out/r2k_host2_r0.stderr gpurun_out/r2k_host2_r1.stderr
+tail -n 3 gpurun_out/r2k_host2_r0.stderr; tail -n 3 gpurun_out/r2k_host2_r1.stderr
 cmp gpurun_out/r2k_host1.out gpurun_out/r2k_host2_r0.out && echo "2-rank output identical to the 1-rank output"
 diff <(grep -v Creating gpurun_out/r2k_host1.stdout) <(grep -v Creating gpurun_out/r2k_host2_r0.stdout) | head -10
