@@ -208,7 +208,10 @@ __device__ __forceinline__ void sweep_family(const Unit& u, const uchar2* A, con
 			{
 				const int ma = j & 1, mb = j >> 1;
 				const int mkf = m ? mb : ma, mko = m ? ma : mb;
-				const double t0 = nb[0] * Go[0][mko] * Gf[0][mkf], t1 = nb[1] * Go[1][mko] * Gf[1][mkf];
+				// selects, not indexed reads: a runtime index would put the four 2 x 2 arrays into local memory
+				const double go0 = mko ? Go[0][1] : Go[0][0], go1 = mko ? Go[1][1] : Go[1][0];
+				const double gf0 = mkf ? Gf[0][1] : Gf[0][0], gf1 = mkf ? Gf[1][1] : Gf[1][0];
+				const double t0 = nb[0] * go0 * gf0, t1 = nb[1] * go1 * gf1;
 #pragma unroll
 				for (int s = 0; s < 2; s++) out[s][j] = t0 * np.W[m ^ s] + t1 * np.W[1 ^ m ^ s];
 			}

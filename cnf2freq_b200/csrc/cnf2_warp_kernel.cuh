@@ -977,12 +977,7 @@ __global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wa)
 						warp_w_and_turns(w, u, p, b, sc, kan, kb, kf, efrem, w.qh + t * QS, xbuf, m, lane, wa.turns != 0);
 #endif
 					}
-					if (m > mb)
-					{
-						load_alpha(alpha + (size_t)(m - 1 - mb) * AV, p, lane);
-						kan = kexp[(size_t)(m - 1 - mb) * NUMSHIFTS + s];
-						if (m > mb + WB) asm volatile("prefetch.global.L2 [%0];" ::"l"(alpha + (size_t)(m - 1 - WB - mb) * AV + lane * 8));
-					}
+					if (m > mb + WB) asm volatile("prefetch.global.L2 [%0];" ::"l"(alpha + (size_t)(m - 1 - WB - mb) * AV + lane * 8));
 					const int gp = w.gpmust[t];
 					if (gp != w.listtag) warp_lists(w, u, gp, lane);
 					if (lane < 2) root_constants(w.A[t], w.nt[t], lane, w.rootc);
@@ -1034,6 +1029,13 @@ __global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wa)
 					// transfer into the EM sufficient statistics (:5875-5904, moveinfprobs :3577-3597, movehaplos :3599-3616)
 					transfer_out(w, w.tot, t, m, lane);
 #endif
+					// alpha before the next marker to the left: asked for here, behind the posterior (whose loops need the registers),
+					// and in flight while beta takes its step
+					if (m > mb)
+					{
+						load_alpha(alpha + (size_t)(m - 1 - mb) * AV, p, lane);
+						kan = kexp[(size_t)(m - 1 - mb) * NUMSHIFTS + s];
+					}
 					if (m > 0)
 					{
 						emit16(b, w.qh + t * QS, lane);
