@@ -755,21 +755,24 @@ extern "C" int cnf2_estep(cnf2_engine* e, int32_t chrom)
 	const int n_warps = std::max(1, std::min(e->n_ctas_warp, n_units));
 	const int n_lit = std::max(1, std::min(e->n_ctas_literal, n_units));
 	const size_t ring_per_marker = (size_t)NUMSHIFTS * NUMTYPES * 8 + NUMSHIFTS * 4 + QS * 8;
-	int seg = ((Mc + WB - 1) / WB) * WB;
-	{
+	auto seg_for = [&](int mc) {
+		int sg = ((mc + WB - 1) / WB) * WB;
 		const size_t budget = e->ring_budget ? e->ring_budget : (size_t)12 << 30;
 		const size_t fit = budget / ((size_t)n_warps * ring_per_marker);
-		if ((size_t)seg > fit) seg = (int)std::max<size_t>(WB, fit / WB * WB);
-		if (e->seg_override > 0) seg = std::min(seg, std::max(WB, e->seg_override / WB * WB));
-	}
-	const int nseg = (Mc + seg - 1) / seg;
+		if ((size_t)sg > fit) sg = (int)std::max<size_t>(WB, fit / WB * WB);
+		if (e->seg_override > 0) sg = std::min(sg, std::max(WB, e->seg_override / WB * WB));
+		return sg;
+	};
+	const int seg = seg_for(Mc), nseg = (Mc + seg - 1) / seg;
 	if (!e->literal_only)
 	{
-		CU(sl.alpha.ensure((size_t)n_warps * seg * NUMSHIFTS * NUMTYPES));
-		CU(sl.kexp.ensure((size_t)n_warps * seg * NUMSHIFTS));
-		CU(sl.qstash.ensure((size_t)n_warps * seg * QS));
-		CU(sl.ckalpha.ensure((size_t)n_warps * nseg * NUMSHIFTS * NUMTYPES));
-		CU(sl.ckexp.ensure((size_t)n_warps * nseg * NUMSHIFTS));
+		// sized for the longest chromosome, so that no later E-step of the run allocates (seg and nseg grow with the length)
+		const int seg_max = seg_for(e->max_mc), nseg_max = (e->max_mc + seg_max - 1) / seg_max;
+		CU(sl.alpha.ensure((size_t)n_warps * seg_max * NUMSHIFTS * NUMTYPES));
+		CU(sl.kexp.ensure((size_t)n_warps * seg_max * NUMSHIFTS));
+		CU(sl.qstash.ensure((size_t)n_warps * seg_max * QS));
+		CU(sl.ckalpha.ensure((size_t)n_warps * nseg_max * NUMSHIFTS * NUMTYPES));
+		CU(sl.ckexp.ensure((size_t)n_warps * nseg_max * NUMSHIFTS));
 	}
 	CU(sl.lit_alpha.ensure((size_t)n_lit * e->max_mc * NUMSHIFTS * NUMTYPES));
 	CU(sl.lit_fac.ensure((size_t)n_lit * e->max_mc * NUMSHIFTS));
