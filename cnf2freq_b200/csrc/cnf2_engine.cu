@@ -128,6 +128,7 @@ struct cnf2_engine
 	std::vector<std::vector<int32_t>> kids;      // analysed children (individ::kids, :5246-5259)
 	std::vector<std::vector<int32_t>> allkids;   // every individual naming this one as a parent (inverse of the pointer chains)
 	std::vector<std::map<int32_t, std::pair<double, int32_t>>> candmap;  // per chromosome: id -> (val, start) of its candidate
+	std::vector<uint8_t> hasmin;                 // per individual: some chromosome of this iteration holds an inversion score for it
 	struct Cand { int32_t id; double val; int32_t start; bool operator<(const Cand& o) const { return id != o.id ? id < o.id : val != o.val ? val < o.val : start < o.start; } };
 	std::vector<std::set<Cand>> cands;           // per chromosome
 	std::vector<std::vector<double>> minval_c;   // per chromosome: minima of this iteration by individual id (empty: none yet)
@@ -1004,6 +1005,7 @@ extern "C" int cnf2_begin_iteration(cnf2_engine* e)
 	const size_t C = e->chromstarts.empty() ? 0 : e->chromstarts.size() - 1;
 	e->cands.assign(C, {});       // negshiftcands is local to doit (:5261)
 	e->candmap.assign(C, {});
+	e->hasmin.assign(e->n_ind, 0);
 	e->minval_c.assign(C, {});    // negshift is zeroed after every iteration's dump (:8187)
 	e->minstart_c.assign(C, {});
 	return CNF2_OK;
@@ -1355,12 +1357,14 @@ extern "C" int cnf2_em_pass(cnf2_engine* e, int32_t chrom, int32_t* inv_ids, int
 			{
 				e->minval_c[chrom][id] = g[(size_t)id * 2];
 				e->minstart_c[chrom][id] = Mc - (int32_t)g[(size_t)id * 2 + 1];
+				if (e->minstart_c[chrom][id] + 1 < Mc) e->hasmin[id] = 1;
 			}
 	}
 	// candidates, at most one per individual and chromosome (:6270-6327): individuals in id order, every chromosome each
 	std::vector<int32_t> rel;
 	for (int id = 1; id < e->n_ind; id++)
 	{
+		if (!e->hasmin[id]) continue;  // no chromosome offers a candidate for this individual (:6301)
 		bool have_rel = false;
 		for (int c = 0; c < C; c++)
 		{
