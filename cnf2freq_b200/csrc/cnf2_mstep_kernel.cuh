@@ -287,6 +287,14 @@ __device__ __forceinline__ double ms_cappedgd_warp(const MsParams& P, double ori
 		if (lowside) hi = orig;
 		else lo = orig;
 		if (!scalefactor) fin = true;
+		// count_only: all that is wanted is whether the final caplogitchange counts a hit (:4022-4032) -- the end point beyond
+		// the cap on the side the solve moves to, AND that cap on the near side of 0.5.  A cap at or beyond 0.5 (every solve
+		// that starts from 0.5, e.g. the untyped F1 rows of an F2 design) cannot count: the solve is over before it starts.
+		if (count_only && (lowside ? lolim <= 0.5 : hilim >= 0.5))
+		{
+			lo = hi = orig;
+			fin = true;
+		}
 	}
 	// Integral-free steps.  A step whose midpoint lies on the near side of the gradient's sign change costs the reference a
 	// 15-point integral only to learn that the flow has not yet run for `scalefactor` (prel < scalefactor -> move on).  Where
