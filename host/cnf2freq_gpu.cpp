@@ -5,7 +5,7 @@
 // statements of doit (:5189-6410) that a drop-in has to keep:
 //
 //   cnf2freq_gpu --mapfile M --pedfile P --genfile G [--gigimapfile M --gigipedfile P] --count N [--limit L]
-//                [--output FILE] [--tmppath DIR] [--deserialize FILE]
+//                [--output FILE] [--tmppath DIR] [--deserialize FILE] [--parse-only]
 //
 // --output FILE receives what the reference writes there: the state dump after every iteration (:8157-8192) and the last
 // iteration's per-chromosome report; stdout carries the progress lines (likelihoods :5399-5401, "Inv:" :3450, "Scale
@@ -372,6 +372,7 @@ int main(int argc, char* argv[])
 {
 	std::string mapfn, pedfn, genfn, gigimap, gigiped, outfn, deserializefn, tmppath = ".";
 	int COUNT = 3, limit = INDCOUNT;  // :7961-7962
+	bool parse_only = false;  // read the inputs, print what the readers made of them (the dump format of :8157-8192), stop: no GPU needed
 	for (int i = 1; i < argc; i++)
 	{
 		const std::string a = argv[i];
@@ -389,6 +390,7 @@ int main(int argc, char* argv[])
 		else if (a == "--limit") limit = atoi(next().c_str());
 		else if (a == "--tmppath") tmppath = next();
 		else if (a == "--deserialize") deserializefn = next();
+		else if (a == "--parse-only") parse_only = true;
 		else die("unknown option %s (supported: --mapfile --pedfile --genfile --gigimapfile --gigipedfile --count --limit --output --tmppath --deserialize)", a.c_str());
 	}
 	const int rank = getenv("RANK") ? atoi(getenv("RANK")) : 0, world = getenv("WORLD_SIZE") ? atoi(getenv("WORLD_SIZE")) : 1;
@@ -431,6 +433,27 @@ int main(int argc, char* argv[])
 	const int C = (int)chromstarts.size() - 1;
 	if (!M || K < 2 || C < 1) die("no markers or no individuals read");
 	if ((size_t)limit < dous.size()) dous.resize(limit);  // :8122
+	if (parse_only)
+	{
+		FILE* o = outfn.empty() ? stdout : fopen(outfn.c_str(), "w");
+		if (!o) die("cannot open %s", outfn.c_str());
+		fprintf(o, "markers %zu chromosomes %d individuals %zu analysed %zu\n", M, C, K - 1, dous.size());
+		for (int c = 0; c <= C; c++) fprintf(o, "chromstart %u\n", chromstarts[c]);
+		for (size_t i = 1; i < K; i++)
+		{
+			const bool analysed = std::find(dous.begin(), dous.end(), (int)i) != dous.end();
+			fprintf(o, "%zu %s pars %d %d gen %d empty %d prior %d analysed %d\n", i, inds[i].name.c_str(), inds[i].pars[0], inds[i].pars[1], inds[i].gen,
+			        (int)inds[i].empty, (int)inds[i].hasprior, (int)analysed);
+			for (size_t j = 0; j < M; j++)
+			{
+				const size_t x = i * M + j;
+				fprintf(o, "%f\t%d\t%d\t\t%f\t%lf %lf %lf\n", haploweight[x], markerdata[x * 2], markerdata[x * 2 + 1], negshift[x], markersure[x * 2],
+				        markersure[x * 2 + 1], relhaplo[x]);
+			}
+		}
+		if (o != stdout) fclose(o);
+		return 0;
+	}
 
 	// ---- the engine ----
 	cnf2_settings st;
