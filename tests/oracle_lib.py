@@ -10,7 +10,7 @@ _LIB = os.path.join(ROOT, "oracle", "_build", "libcnf2oracle.so")
 
 
 def build_oracle(force=False):
-    srcs = [os.path.join(ROOT, "oracle", f) for f in ("cnf2_oracle.cpp", "cnf2_mstep_oracle.cpp")]
+    srcs = [os.path.join(ROOT, "oracle", f) for f in ("cnf2_oracle.cpp", "cnf2_mstep_oracle.cpp", "cnf2_preprocess_oracle.cpp")]
     if force or not os.path.exists(_LIB) or os.path.getmtime(_LIB) < max(os.path.getmtime(s) for s in srcs):
         os.makedirs(os.path.dirname(_LIB), exist_ok=True)
         subprocess.check_call(["g++", "-std=c++17", "-O2", "-fopenmp", "-fPIC", "-shared", "-o", _LIB] + srcs)
@@ -130,3 +130,19 @@ def oracle_scalefactor(scalefactor, hitnnn, n_dous, oldhitnnn, oldhitnnn2):
     o1, o2 = ctypes.c_int32(int(oldhitnnn)), ctypes.c_int32(int(oldhitnnn2))
     sf = f(ctypes.c_double(scalefactor), ctypes.c_longlong(hitnnn), ctypes.c_int(n_dous), ctypes.byref(o1), ctypes.byref(o2))
     return float(sf), o1.value, o2.value
+
+
+def oracle_preprocess(chromstarts, par, exists, empty, alleles, sure, haploweight):
+    """postmarkerdata (cnF2freq.cpp:3191-3412) on copies of the arrays as the readers left them.  Returns dict(alleles, sure,
+    haploweight, descendants, children, founder, corrections)."""
+    cs = np.ascontiguousarray(chromstarts, np.uint32)
+    par = np.ascontiguousarray(par, np.int32)
+    K, M = par.shape[0], np.asarray(haploweight).shape[1]
+    c = lambda a, dt: np.array(a, dt, order="C", copy=True)
+    al, su, hw = c(alleles, np.uint8), c(sure, np.float64), c(haploweight, np.float64)
+    desc, ch, fo, n = np.zeros(K, np.int32), np.zeros(K, np.int32), np.zeros(K, np.uint8), ctypes.c_int32()
+    rc = lib().cnf2_oracle_preprocess(ctypes.c_int(K), ctypes.c_int(M), ctypes.c_int(len(cs) - 1), _p(cs), _p(par), _p(c(exists, np.uint8)),
+                                      _p(c(empty, np.uint8)), _p(al), _p(su), _p(hw), _p(desc), _p(ch), _p(fo), ctypes.byref(n))
+    assert rc == 0
+    return dict(alleles=al, sure=su, haploweight=hw, descendants=desc, children=ch, founder=fo, corrections=int(n.value),
+                cleared=int(lib().cnf2_oracle_preprocess_cleared()))

@@ -34,10 +34,11 @@ def compare(out, ref, what):
     assert_close(out["loglik"], ref["loglik"], f"{what}:loglik", rtol=RTOL, atol=1e-9)
 
 
-@pytest.mark.parametrize("name", [n for n in GOLDEN_CASES if not n.endswith("iter1")])
+@pytest.mark.parametrize("name", GOLDEN_CASES)
 def test_engine_matches_reference_golden(eng, name):
-    """From the second EM iteration on the reference's sticky founder flags are steady, which is the state
-    the engine works in (include/cnf2_engine.h, cnf2_set_pedigree)."""
+    """The reference's sticky founder flags (fixtrees) are steady from its pre-processing on (postmarkerdata calls fixtrees
+    for every individual, :3377), which is the state the engine works in (include/cnf2_engine.h, cnf2_set_pedigree): the
+    first EM iteration is reproduced like the later ones."""
     g, pb = load_golden(name)
     out = run_engine(eng, pb)
     for k in STATS:

@@ -1,0 +1,76 @@
+"""cnf2_preprocess (row f3: postmarkerdata with its emission scans on the GPU) against the CPU oracle -- which is pinned on
+the reference binary's own post-postmarkerdata state (tests/test_preprocess_oracle.py) -- on random pedigrees as the readers
+would leave them: Mendelian genotypes with missing and half-missing entries, injected impossible genotypes (cleared by
+fixparents, :1432-1437), untyped `empty` individuals, markersure 0.02 / 0, haploweight 0.5."""
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+import randomped
+
+pytestmark = pytest.mark.gpu
+
+
+def raw_inputs(pb, seed, impossible=0.0):
+    """Replaces the random E-step parameters of a randomped problem by reader-like raw data: genotypes dropped down the
+    pedigree from founder alleles, `missing` of them unknown."""
+    rng = np.random.default_rng(seed)
+    K, M = pb.K, pb.M
+    hap = np.zeros((K, M, 2), np.uint8)
+    order = np.argsort(pb.gen, kind="stable")
+    for i in order:
+        if i == 0:
+            continue
+        for s in range(2):
+            p = pb.par[i, s]
+            if p and hap[p].any():
+                pick = rng.integers(0, 2, M)
+                hap[i, :, s] = np.where(pick == 0, hap[p, :, 0], hap[p, :, 1])
+            else:
+                hap[i, :, s] = rng.integers(1, 3, M)
+    al = hap.copy()
+    al[rng.random((K, M)) < 0.25] = 0
+    al[rng.random((K, M, 2)) < 0.05] = 0
+    if impossible:
+        bad = rng.random((K, M)) < impossible
+        al[bad] = 3 - np.where(al[bad] == 0, 1, al[bad])  # flip alleles: some of these contradict the relatives
+    al[pb.empty == 1] = 0
+    al[0] = 0
+    su = np.where(al != 0, 0.02, 0.0)
+    if impossible:
+        su[...] = 0.0  # Gigi-style data (markersure 0, :7497-7498): a Mendelian inconsistency has no admissible interpretation
+    hw = np.full((K, M), 0.5)
+    exists = np.ones(K, np.uint8)
+    exists[0] = 0
+    return exists, al, su, hw
+
+
+@pytest.mark.parametrize("maker,kw,impossible", [
+    ("f2_cross", dict(n_f2=7, n_chrom=2, mpc=11, seed=81), 0.0),
+    ("fullsib", dict(n_fam=2, n_off=3, n_chrom=1, mpc=13, seed=82), 0.0),
+    ("tangled", dict(n_chrom=2, mpc=9, seed=83), 0.0),
+    ("fullsib", dict(n_fam=2, n_off=4, n_chrom=2, mpc=8, seed=84), 0.08),
+    ("tangled", dict(n_chrom=1, mpc=21, seed=85), 0.1),
+])
+def test_preprocess_matches_the_oracle(maker, kw, impossible):
+    from cnf2freq_b200.engine import Engine
+    pb = getattr(randomped, maker)(**kw)
+    exists, al, su, hw = raw_inputs(pb, kw["seed"], impossible)
+    ref = ol.oracle_preprocess(pb.chromstarts, pb.par, exists, pb.empty, al, su, hw)
+    eng = Engine(device=0)
+    try:
+        eng.set_map(pb.markerpos, pb.chromstarts, pb.genrec)
+        a, s, h = al.copy(), su.copy(), hw.copy()
+        lines = []
+        desc, children, founder = eng.preprocess(pb.par, exists, pb.empty, a, s, h, log=lambda st, l: lines.append((st, l)))
+    finally:
+        eng.close()
+    assert np.array_equal(a, ref["alleles"]), np.argwhere(a != ref["alleles"])[:5]
+    assert np.allclose(s, ref["sure"], rtol=1e-12, atol=0, equal_nan=True)  # dosureval(0, .) is NaN in the reference too
+    assert np.array_equal(h, ref["haploweight"]), np.argwhere(h != ref["haploweight"])[:5]
+    assert np.array_equal(desc, ref["descendants"]) and np.array_equal(children, ref["children"]) and np.array_equal(founder, ref["founder"])
+    assert sum(1 for st, l in lines if l.startswith("Correction at")) == ref["corrections"]
+    assert sum(1 for st, l in lines if l.startswith("Fixing point")) == int((h != hw).sum())
+    assert sum(1 for st, l in lines if l.startswith("Clearing")) == ref["cleared"]
+    if impossible:
+        assert ref["cleared"] > 0, "no impossible genotype in this draw"
