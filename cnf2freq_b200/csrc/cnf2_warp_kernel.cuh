@@ -330,6 +330,231 @@ __device__ __forceinline__ void warp_posterior_pairs(WarpSmem& w, const Unit& u,
 	}
 }
 
+// Posterior of the current marker for a unit that rule 2 of ignoreflag2 does not constrain (no individual on both sides:
+// Unit::xmask2 all ones), fully factorised.  Per side the emission of a subtree configuration (m, ma, mb | o, oa, ob) is
+//   E = H(o, m) * X(o, m; first grandparent's orientation and phase index) * Y(o, m; other grandparent's)
+// (post_entry1: nb * [c * gfix(other)] * gfix(first); "first" = the grandparent the parent's meiosis bit m points to), the
+// configurations in use are a product set over the three tree slots (rule 1 pins the orientation of an absent / empty slot,
+// rule 3 the x bit of a homozygous grandparent), and every scatter target of :5556-5575 groups the configurations by a few
+// of these bits.  So nothing is built per configuration: 16 (o, m) rows of factors per side and root orientation
+// (FT: 8 gval evaluations each), sums over the grandparents' orientations where a target does not tell them apart, and one
+// lane per (side, root orientation, phase bit, meiosis bits) CLASS -- 64 classes, two rounds -- that meets the other
+// side's class sums through W (AR / AH, as in the pairwise form) and scatters its ~20 results.  For three-generation
+// outbred pedigrees this replaces 256 table entries + 256 pair-loop items per marker.
+constexpr int FT = 11;  // HE, H1, H2, GY[oo], GXE[of], GX1[of], GX2[of]: gval parts, phase weights W applied by the user
+constexpr int FT_DOUBLES = 16 * FT, CLS_AT = FT_DOUBLES;  // class sums (CLS doubles, layout of class_sums) sit behind the factors
+
+__device__ __forceinline__ void warp_posterior_factored(WarpSmem& w, const Unit& u, int homslot, int gpmust, int t, int lane,
+                                                        double* __restrict__ ft)
+{
+	const unsigned FULL = 0xffffffffu;
+	const double* rc = w.rootc;
+	double* const cls = ft + CLS_AT;
+	const uchar2* A = w.A;
+	const NodeTab* N = w.nt;
+	// ---- factors: lane = (side, f, o, m) * 2 + h; h = the orientation (of the first resp. other grandparent) this lane does ----
+	{
+		const int h = lane & 1, m = (lane >> 1) & 1, o = (lane >> 2) & 1, f = (lane >> 3) & 1, p = lane >> 4;
+		const int sp = 1 + 3 * p;
+		const uchar2 a0 = A[t];
+		const NodeTab& n0 = N[t];
+		const int vroot = p == 0 ? (f ? a0.y : a0.x) : (f ? a0.x : a0.y);
+		const double secroot = p == 0 ? (vroot != UNKNOWN ? n0.RN[f] : 0.0) : n0.SEC[f ^ 1];
+		const bool absent = u.row[sp] < 0, attop = !absent && u.founder[sp];
+		const uchar2 ap = A[sp * WB + t];
+		const NodeTab& np = N[sp * WB + t];
+		const int kf = sp + 1 + m, ko = sp + 1 + (m ^ 1);
+		double H[3], GX[3], GY = 1.0;
+#pragma unroll
+		for (int k = 0; k < 3; k++)
+		{
+			const int v = k == 0 ? vroot : k;
+			const double sec = k == 0 ? secroot : 0.0;
+			if (absent) H[k] = 1.0 + sec, GX[k] = 1.0;
+			else if (attop) H[k] = gval(ap, np, o, v, sec), GX[k] = 1.0;
+			else
+			{
+				const PMsg pm = pmsg(ap, np, o, v, sec);
+				H[k] = pm.nb * (np.S[o ^ 1] != 0 ? 1.0 - np.S[o ^ 1] : 1.0);
+				GX[k] = u.row[kf] < 0 ? 1.0 + pm.up2 : gval(A[kf * WB + t], N[kf * WB + t], h, pm.v2, pm.up2);
+			}
+		}
+		if (!absent && !attop)
+		{
+			const int vo = o ? ap.x : ap.y;
+			const double so = np.SEC[o ^ 1];
+			GY = u.row[ko] < 0 ? 1.0 + so : gval(A[ko * WB + t], N[ko * WB + t], h, vo, so);
+		}
+		double* row = ft + (lane >> 1) * FT;
+		if (h == 0) row[0] = H[0], row[1] = H[1], row[2] = H[2];
+		row[3 + h] = GY;
+		row[5 + h] = GX[0], row[7 + h] = GX[1], row[9 + h] = GX[2];
+	}
+	__syncwarp();
+	// ---- per class (side, f, phase bit, meiosis bits): the factors with the phase weights and the slots' admissible sets ----
+	struct ClassView
+	{
+		double HE, H1, H2, XE[2], X1[2], X2[2], YO[2];  // X / Y: zero where the configuration is not in use
+		int o, m, mF, mO, kF, kO;
+		bool any;
+	};
+	auto view = [&](int p, int f, int ph, int g) -> ClassView {
+		ClassView c;
+		const int sp = 1 + 3 * p;
+		c.m = g & 1;
+		c.o = ph ^ c.m;
+		const int ma = (g >> 1) & 1, mb = (g >> 2) & 1;
+		c.mF = c.m ? mb : ma, c.mO = c.m ? ma : mb;
+		c.kF = sp + 1 + c.m, c.kO = sp + 1 + (c.m ^ 1);
+		const bool leaf = u.row[sp] < 0 || u.founder[sp];  // the subtree ends at the parent: no grandparent is visited
+		const int ign = u.flag2ignore, must = gpmust;
+		c.any = !(((ign >> sp) & 1) && c.o);
+		const double* row = ft + (((p * 2 + f) * 2 + c.o) * 2 + c.m) * FT;
+		c.HE = row[0], c.H1 = row[1], c.H2 = row[2];
+#pragma unroll
+		for (int q = 0; q < 2; q++)  // q: the grandparent's orientation; its x bit (phase index of its weight) is q ^ its meiosis bit
+		{
+			const bool okF = !(((ign >> c.kF) & 1) && q) && !(((must >> c.kF) & 1) && !(q ^ c.mF));
+			const bool okO = !(((ign >> c.kO) & 1) && q) && !(((must >> c.kO) & 1) && !(q ^ c.mO));
+			const double wF = (leaf || u.row[c.kF] < 0) ? 1.0 : N[c.kF * WB + t].W[q ^ c.mF];
+			const double wO = (leaf || u.row[c.kO] < 0) ? 1.0 : N[c.kO * WB + t].W[q ^ c.mO];
+			c.XE[q] = okF ? row[5 + q] * wF : 0.0;
+			c.X1[q] = okF ? row[7 + q] * wF : 0.0;
+			c.X2[q] = okF ? row[9 + q] * wF : 0.0;
+			c.YO[q] = okO ? row[3 + q] * wO : 0.0;
+		}
+		return c;
+	};
+	// class sums of the emissions (and, for parent 1, of the two probing values: homozyg) in class_sums' layout
+#pragma unroll
+	for (int pass = 0; pass < 2; pass++)
+	{
+		const int i = pass * 32 + lane, p = i >> 5, f = (i >> 4) & 1, k = i & 15;
+		const ClassView c = view(p, f, k >> 3, k & 7);
+		const double SY = c.any ? c.YO[0] + c.YO[1] : 0.0;
+		const double sE = c.HE * (c.XE[0] + c.XE[1]) * SY;
+		if (p)
+		{
+			double* o = cls + 32 + (f * 16 + k) * 3;
+			// the probing values only where the configuration's own emission is not zero: a term without posterior mass adds
+			// nothing to homozyg (:5571-5575), whatever its probing value
+			const double e0 = c.HE * c.XE[0], e1 = c.HE * c.XE[1];
+			o[0] = sE;
+			o[1] = c.H1 * ((e0 != 0 ? c.X1[0] : 0.0) + (e1 != 0 ? c.X1[1] : 0.0)) * SY;
+			o[2] = c.H2 * ((e0 != 0 ? c.X2[0] : 0.0) + (e1 != 0 ? c.X2[1] : 0.0)) * SY;
+		}
+		else cls[f * 16 + k] = sE;
+	}
+	__syncwarp();
+	// ---- the other side's class sums through W: lane = side * 16 + meiosis bits * 2 + f (as in the pairwise form) ----
+	const double2* const Ws2 = reinterpret_cast<const double2*>(w.Ws);
+	double AR[4] = { 0, 0, 0, 0 }, AH1[4] = { 0, 0, 0, 0 }, AH2[4] = { 0, 0, 0, 0 };
+	{
+		const int p = lane >> 4, g = (lane >> 1) & 7, f = lane & 1;
+		const int aown = ws_base(g << (p ? 3 : 0));
+		const int kown = p ? 4 : 2, koth = p ? 2 : 4;
+		const double wo0 = rc[12 + (p ^ 1) * 2], wo1 = rc[12 + (p ^ 1) * 2 + 1];
+		const double* C = p ? cls + f * 16 : cls + 32 + f * 48;
+		const int cw = p ? 1 : 3;
+#pragma unroll
+		for (int h = 0; h < 2; h++)
+		{
+			const double qa = h ? wo1 : wo0, qb = h ? wo0 : wo1;
+#pragma unroll 4
+			for (int go = 0; go < 8; go++)
+			{
+				const int a0 = aown ^ (p ? ws_base(go) : ws_base(go << 3));
+				const double* Ck = C + (h * 8 + go) * cw;
+				const double E = Ck[0];
+				const double2 c00 = Ws2[a0 >> 1], cT = Ws2[(a0 ^ koth) >> 1], cO = Ws2[(a0 ^ kown) >> 1], c11 = Ws2[(a0 ^ 6) >> 1];
+				const double ux0 = qa * c00.x + qb * cT.x, uy0 = qa * c00.y + qb * cT.y;
+				const double ux1 = qa * cO.x + qb * c11.x, uy1 = qa * cO.y + qb * c11.y;
+				AR[0] += E * ux0, AR[1] += E * uy0, AR[2] += E * ux1, AR[3] += E * uy1;
+				if (!p)
+				{
+					const double e1 = Ck[1], e2 = Ck[2];
+					AH1[0] += e1 * ux0, AH1[1] += e1 * uy0, AH1[2] += e1 * ux1, AH1[3] += e1 * uy1;
+					AH2[0] += e2 * ux0, AH2[1] += e2 * uy0, AH2[2] += e2 * ux1, AH2[3] += e2 * uy1;
+				}
+			}
+		}
+	}
+	// ---- the classes' own results, scattered into the accumulator columns ----
+	double* const acc = w.acc + (lane & (NCOL - 1)) * NACCP;
+	const int vis = u.vismask, hmask = vis & ~homslot;
+#pragma unroll 1
+	for (int round = 0; round < 2; round++)
+	{
+		const int i = round * 32 + lane, p = i >> 5, f = (i >> 4) & 1, ph = (i >> 3) & 1, g = i & 7;
+		const int sp = 1 + 3 * p;
+		const ClassView c = view(p, f, ph, g);
+		const int src = p * 16 + g * 2 + f;
+		const double Rx0 = __shfl_sync(FULL, AR[0], src), Ry0 = __shfl_sync(FULL, AR[1], src);
+		const double Rx1 = __shfl_sync(FULL, AR[2], src), Ry1 = __shfl_sync(FULL, AR[3], src);
+		const double h10 = __shfl_sync(FULL, AH1[0], src), h11 = __shfl_sync(FULL, AH1[1], src);
+		const double h12 = __shfl_sync(FULL, AH1[2], src), h13 = __shfl_sync(FULL, AH1[3], src);
+		const double h20 = __shfl_sync(FULL, AH2[0], src), h21 = __shfl_sync(FULL, AH2[1], src);
+		const double h22 = __shfl_sync(FULL, AH2[2], src), h23 = __shfl_sync(FULL, AH2[3], src);
+		const double own0 = rc[12 + p * 2 + ph], own1 = rc[12 + p * 2 + (ph ^ 1)];
+		const double rA = rc[2 + f], rB = rc[2 + (f ^ 1)];
+		const double z0 = rA * (own0 * Rx0 + own1 * Rx1), z1 = rB * (own0 * Ry0 + own1 * Ry1);  // root shift bit 0 / 1
+		const double s0 = own0 * (rA * Rx0 + rB * Ry0), s1 = own1 * (rA * Rx1 + rB * Ry1);    // own shift bit 0 / 1
+		const double tS = s0 + s1;
+		const double base = c.any ? rc[f] * c.HE : 0.0;
+		const double SX = c.XE[0] + c.XE[1], SY = c.YO[0] + c.YO[1];
+		const double M = base * SX * SY;
+		const bool live = M * tS > 0;
+		// probing ratios of the GENOS calls (:5517-5538): A_al / (A_1 + A_2) per orientation of the first grandparent
+		const int fq = p ? f ^ 1 : f;
+		double U1[2], U2[2], hz1 = 0, hz2 = 0;
+		const double hzw1 = own0 * (rA * h10 + rB * h11) + own1 * (rA * h12 + rB * h13);
+		const double hzw2 = own0 * (rA * h20 + rB * h21) + own1 * (rA * h22 + rB * h23);
+		const double* row = ft + (((p * 2 + f) * 2 + c.o) * 2 + c.m) * FT;
+#pragma unroll
+		for (int q = 0; q < 2; q++)
+		{
+			const double A1 = rc[4 + fq] * c.H1 * row[7 + q], A2 = rc[6 + fq] * c.H2 * row[9 + q];
+			const double sum = A1 + A2, inv = sum > 0 ? frcp(sum) : 0.0;
+			const double mq = base * c.XE[q] * SY;  // the class's mass with the first grandparent at orientation q
+			U1[q] = mq * tS * (A1 * inv), U2[q] = mq * tS * (A2 * inv);
+			hz1 += mq * (A1 * inv), hz2 += mq * (A2 * inv);
+		}
+		double2 pv[9];
+		int pk[9];
+		bool pe[9];
+		pk[0] = ACC_HAPLOS, pv[0] = f ? make_double2(M * z1, M * z0) : make_double2(M * z0, M * z1), pe[0] = !p && (hmask & 1);
+		pk[1] = ACC_HAPLOS + sp * 2, pv[1] = ph ? make_double2(M * s1, M * s0) : make_double2(M * s0, M * s1), pe[1] = (hmask >> sp) & 1;
+		{
+			// the grandparents' haplos: index = the x bit of the slot = orientation ^ meiosis bit
+			const double f0 = base * tS * c.XE[0] * SY, f1 = base * tS * c.XE[1] * SY, o0 = base * tS * SX * c.YO[0], o1 = base * tS * SX * c.YO[1];
+			pk[2] = ACC_HAPLOS + c.kF * 2, pv[2] = c.mF ? make_double2(f1, f0) : make_double2(f0, f1), pe[2] = (hmask >> c.kF) & 1;
+			pk[3] = ACC_HAPLOS + c.kO * 2, pv[3] = c.mO ? make_double2(o1, o0) : make_double2(o0, o1), pe[3] = (hmask >> c.kO) & 1;
+		}
+		const double2 uu = make_double2(U1[0] + U1[1], U2[0] + U2[1]);
+		pk[4] = ACC_INF + (f ^ p) * 2, pv[4] = uu, pe[4] = true;
+		pk[5] = ACC_INF + (sp * 2 + c.o) * 2, pv[5] = uu, pe[5] = (vis >> sp) & 1;
+		pk[6] = ACC_INF + (c.kF * 2 + 0) * 2, pv[6] = make_double2(U1[0], U2[0]), pe[6] = pe[5] && ((vis >> c.kF) & 1);
+		pk[7] = ACC_INF + (c.kF * 2 + 1) * 2, pv[7] = make_double2(U1[1], U2[1]), pe[7] = pe[6];
+		pk[8] = ACC_HZ, pv[8] = make_double2(hz1 * hzw1 * rc[8 + f], hz2 * hzw2 * rc[10 + f]), pe[8] = !p;
+#pragma unroll 1
+		for (int pass = 0; pass < 32 / NCOL; pass++)
+		{
+			if (live && (lane / NCOL) == pass)
+			{
+#pragma unroll
+				for (int j = 0; j < 9; j++)
+					if (pe[j])
+					{
+						double2* a2 = reinterpret_cast<double2*>(acc + pk[j]);
+						const double2 cur = *a2;
+						*a2 = make_double2(cur.x + pv[j].x, cur.y + pv[j].y);
+					}
+			}
+			__syncwarp();
+		}
+	}
+}
+
 // Transfer of one marker's reduced accumulators into the EM sufficient statistics (cnF2freq.cpp:5875-5904,
 // moveinfprobs :3577-3597, movehaplos :3599-3616; same arithmetic as transfer_stats), one lane per output.
 // transfer_setup fills the per-(unit, chromosome) description of every output once; transfer_out is the
@@ -750,8 +975,10 @@ struct WarpArgs
 	int32_t turns;           // score the phase-inversion turns (HAPLOTYPING && !early && !full, :5668)
 };
 constexpr size_t XBUF_BYTES = 8 * 32 * sizeof(double2);  // warp_w_and_turns' exchange buffer lives in the posterior tables' space
+static_assert((FT_DOUBLES + CLS) * sizeof(double) <= XBUF_BYTES, "the factorised posterior's tables fit the minimum table space");
 __host__ __device__ inline size_t warp_smem_bytes(int cap0, int cap1, int cls)
 {
+	// (the factorised posterior of uncoupled units keeps its factors and class sums, FT_DOUBLES + CLS doubles, in the same space)
 	const size_t tables = ((size_t)cap0 * 2 * T0W + (size_t)cap1 * 2 * T1W + cls) * sizeof(double);
 	return sizeof(WarpSmem) + (tables > XBUF_BYTES ? tables : XBUF_BYTES);
 }
@@ -979,7 +1206,7 @@ __global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wa)
 					}
 					if (m > mb + WB) asm volatile("prefetch.global.L2 [%0];" ::"l"(alpha + (size_t)(m - 1 - WB - mb) * AV + lane * 8));
 					const int gp = w.gpmust[t];
-					if (gp != w.listtag) warp_lists(w, u, gp, lane);
+					if (!agg && gp != w.listtag) warp_lists(w, u, gp, lane);
 					if (lane < 2) root_constants(w.A[t], w.nt[t], lane, w.rootc);
 					else if (lane < 4)
 					{
@@ -990,7 +1217,7 @@ __global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wa)
 					}
 					__syncwarp();
 #ifndef CNF2_X_NOTAB
-					for (int i = lane; i < 2 * w.nE; i += 32)
+					for (int i = lane; !agg && i < 2 * w.nE; i += 32)
 					{
 						const int c = w.el[i >> 1];
 						const int pp = c >> 6, slot = (i >> 1) - (pp ? w.nE0 : 0);
@@ -999,12 +1226,8 @@ __global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wa)
 #endif
 					__syncwarp();
 #ifndef CNF2_X_NOPAIRS
-					if (agg)
-					{
-						class_sums(w, lane, tab0, tab1, cls);
-						__syncwarp();
-					}
-					warp_posterior_pairs<AGG>(w, u, w.homslot[t], lane, tab0, tab1, cls, agg);
+					if (agg) warp_posterior_factored(w, u, w.homslot[t], gp, t, lane, tab0);
+					else warp_posterior_pairs<false>(w, u, w.homslot[t], lane, tab0, tab1, cls, false);
 #endif
 					__syncwarp();
 #ifndef CNF2_X_NOREDUCE
