@@ -610,9 +610,14 @@ extern "C" int cnf2_set_pedigree(cnf2_engine* e, int32_t n_ind, const int32_t* p
 	e->cls = 0;
 	for (const Unit& u : e->units)
 	{
+		// units that rule 2 does not constrain take the factorised posterior: no per-configuration tables for them
+		if ((u.xmask2[0] & u.xmask2[1] & u.xmask2[2] & u.xmask2[3]) == 0xffffffffu)
+		{
+			e->cls = CLS;
+			continue;
+		}
 		e->cap0 = std::max(e->cap0, __builtin_popcountll(u.cfgmask[0]));
 		e->cap1 = std::max(e->cap1, __builtin_popcountll(u.cfgmask[1]));
-		if ((u.xmask2[0] & u.xmask2[1] & u.xmask2[2] & u.xmask2[3]) == 0xffffffffu) e->cls = CLS;
 	}
 	{
 		int per_sm = 0;

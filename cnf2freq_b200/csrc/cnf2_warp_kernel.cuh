@@ -65,7 +65,6 @@ struct __align__(16) WarpSmem
 	unsigned char el[128];         // list of the needed configurations: parent << 6 | cfg; parent 0 first, phase bit 0 first
 	unsigned char vmk[256];        // per (entry, root orientation): bit xo = rule 2 admits the other parent's x = xo
 	unsigned short ainfo[128];     // per entry: ws_base of its meiosis bits at the parent's place | x << 10
-	unsigned char cst[32], ccn[32]; // per (parent, phase bit, meiosis bits) class: first entry and number of entries
 	int listtag;
 	short nE, nE0, nX0, nX1;        // nX0 / nX1: entries of parent 0 / 1 with phase bit x & 1 = 0
 	short ntr, rootmask;            // (sizes kept tight: 12 single-warp CTAs per SM need <= 18,432 B each)
@@ -75,7 +74,7 @@ struct __align__(16) WarpSmem
 	// followed by the posterior tables of the current marker, sized by the host for the pedigree (WarpArgs::cap0/cap1):
 	//   tab0[cap0][f][T0W]: Q(plain), rho0[1], rho0[2];  tab1[cap1][f][T1W]: Q(plain), rho1[1], rho1[2], Q(al,0)/Q(plain)
 	// entry k of a table is the k-th needed configuration of that parent at this marker (its position in el);
-	// then, for pedigrees with a unit that rule 2 does not constrain, CLS doubles of class sums (see class_sums)
+	// (units that rule 2 does not constrain use the same space for their factors and class sums: warp_posterior_factored)
 };
 
 // One (entry, root orientation) pair of the posterior tables of marker t .
@@ -127,39 +126,6 @@ __device__ __forceinline__ void post_entry1(const Unit& u, const uchar2* A, cons
 	}
 }
 
-// Units that rule 2 of ignoreflag2 does not constrain (no individual occupies slots on both sides: Unit::xmask2 is
-// all ones): the other side enters a lane's sums only through its meiosis bits and its phase bit, so its table is
-// first summed per (root orientation, phase bit, meiosis bits) class -- 16 classes instead of up to 64 entries.
-__device__ __forceinline__ void class_sums(const WarpSmem& w, int lane, const double* __restrict__ tab0, const double* __restrict__ tab1,
-                                           double* __restrict__ cls)
-{
-#pragma unroll
-	for (int pass = 0; pass < 2; pass++)
-	{
-		const int i = pass * 32 + lane, p = i >> 5, f = (i >> 4) & 1, k = i & 15;
-		const int j0 = w.cst[p * 16 + k], n = w.ccn[p * 16 + k];
-		double s0 = 0, s1 = 0, s2 = 0;
-		for (int j = j0; j < j0 + n; j++)
-		{
-			if (p)
-			{
-				const double* row = tab1 + ((j - w.nE0) * 2 + f) * T1W;
-				const double E = row[0];
-				s0 += E;
-				s1 += E * row[3];
-				s2 += E * row[4];
-			}
-			else s0 += tab0[(j * 2 + f) * T0W];
-		}
-		if (p)
-		{
-			double* o = cls + 32 + (f * 16 + k) * 3;
-			o[0] = s0, o[1] = s1, o[2] = s2;
-		}
-		else cls[f * 16 + k] = s0;
-	}
-}
-
 // Posterior of the current marker, pairwise form.  A surviving term factorises as
 //   val = rbase[f] * E0[f][cfg0] * E1[f][cfg1] * sum_s Wr[f ^ s0] Wp0[x1 ^ s1] Wp1[x4 ^ s2] W_s[g0 | g1 << 3]
 // and every scatter target of :5556-5575 depends on the term only through (f, cfg0) [root as side 0, parent 0's
@@ -170,53 +136,14 @@ __device__ __forceinline__ void class_sums(const WarpSmem& w, int lane, const do
 // only by the other side's emission and phase weight -- and combined with the lane's own weights after the loop.
 // The unusualstate cut of single terms (val > e^-200, :5414) is not applied here (it removes at most e^-200 of
 // the posterior mass); whole shift modes below it are cut where W is formed.
-template <bool AGG>
 __device__ __forceinline__ void warp_posterior_pairs(WarpSmem& w, const Unit& u, int homslot, int lane, const double* __restrict__ tab0,
-                                                     const double* __restrict__ tab1, const double* __restrict__ cls, bool agg_unit)
+                                                     const double* __restrict__ tab1)
 {
-	const bool agg = AGG && agg_unit;
 	const double* rc = w.rootc;
 	double* const acc = w.acc + (lane & (NCOL - 1)) * NACCP;
 	const int vis = u.vismask, hmask = vis & ~homslot;
 	const int nE = w.nE, nE0 = w.nE0;
 	const double2* const Ws2 = reinterpret_cast<const double2*>(w.Ws);
-	// Class-sum form (agg): a lane's raw sums depend on its entry only through (side, meiosis bits, root orientation),
-	// so lane t = side * 16 + meiosis bits * 2 + f computes them once per marker -- with unit weights of the other
-	// parent's phase (q0, q1 applied per shift bit), for the plain sums (AR) and the two homozyg-weighted ones (AH1, AH2)
-	// -- and the entries' lanes fetch them by shuffle.
-	double AR[4] = { 0, 0, 0, 0 }, AH1[4] = { 0, 0, 0, 0 }, AH2[4] = { 0, 0, 0, 0 };
-	if (agg)
-	{
-		const int p = lane >> 4, g = (lane >> 1) & 7, f = lane & 1;
-		const int aown = ws_base(g << (p ? 3 : 0));
-		const int kown = p ? 4 : 2, koth = p ? 2 : 4;
-		const double wo0 = rc[12 + (p ^ 1) * 2], wo1 = rc[12 + (p ^ 1) * 2 + 1];
-		// the other parent's class sums: parent 0's (E) for a lane of side 1, parent 1's (E, E h1, E h2) for a lane of side 0
-		const double* C = p ? cls + f * 16 : cls + 32 + f * 48;
-		const int cw = p ? 1 : 3;
-#pragma unroll
-		for (int h = 0; h < 2; h++)
-		{
-			const double qa = h ? wo1 : wo0, qb = h ? wo0 : wo1;
-#pragma unroll 4
-			for (int go = 0; go < 8; go++)
-			{
-				const int a0 = aown ^ (p ? ws_base(go) : ws_base(go << 3));
-				const double* Ck = C + (h * 8 + go) * cw;
-				const double E = Ck[0];
-				const double2 c00 = Ws2[a0 >> 1], cT = Ws2[(a0 ^ koth) >> 1], cO = Ws2[(a0 ^ kown) >> 1], c11 = Ws2[(a0 ^ 6) >> 1];
-				const double ux0 = qa * c00.x + qb * cT.x, uy0 = qa * c00.y + qb * cT.y;
-				const double ux1 = qa * cO.x + qb * c11.x, uy1 = qa * cO.y + qb * c11.y;
-				AR[0] += E * ux0, AR[1] += E * uy0, AR[2] += E * ux1, AR[3] += E * uy1;
-				if (!p)
-				{
-					const double e1 = Ck[1], e2 = Ck[2];
-					AH1[0] += e1 * ux0, AH1[1] += e1 * uy0, AH1[2] += e1 * ux1, AH1[3] += e1 * uy1;
-					AH2[0] += e2 * ux0, AH2[1] += e2 * uy0, AH2[2] += e2 * ux1, AH2[3] += e2 * uy1;
-				}
-			}
-		}
-	}
 	for (int ibase = 0; ibase < 2 * nE; ibase += 32)
 	{
 		const int i = ibase + lane;
@@ -260,24 +187,8 @@ __device__ __forceinline__ void warp_posterior_pairs(WarpSmem& w, const Unit& u,
 				}
 			}
 		};
-		if (agg)
-		{
-			const unsigned FULL = 0xffffffffu;
-			const int src = p * 16 + gown * 2 + f;
-			Rx0 = __shfl_sync(FULL, AR[0], src), Ry0 = __shfl_sync(FULL, AR[1], src);
-			Rx1 = __shfl_sync(FULL, AR[2], src), Ry1 = __shfl_sync(FULL, AR[3], src);
-			const double h10 = __shfl_sync(FULL, AH1[0], src), h11 = __shfl_sync(FULL, AH1[1], src);
-			const double h12 = __shfl_sync(FULL, AH1[2], src), h13 = __shfl_sync(FULL, AH1[3], src);
-			const double h20 = __shfl_sync(FULL, AH2[0], src), h21 = __shfl_sync(FULL, AH2[1], src);
-			const double h22 = __shfl_sync(FULL, AH2[2], src), h23 = __shfl_sync(FULL, AH2[3], src);
-			Sx1 = k00 * h10 + k01 * h11 + k10 * h12 + k11 * h13;
-			Sx2 = k00 * h20 + k01 * h21 + k10 * h22 + k11 * h23;
-		}
-		else
-		{
-			run(jlo, jmid, wo0, wo1);
-			run(jmid, jhi, wo1, wo0);
-		}
+		run(jlo, jmid, wo0, wo1);
+		run(jmid, jhi, wo1, wo0);
 		const int slot = ie - (p ? nE0 : 0);
 		const double* To = p ? tab1 + (slot * 2 + f) * T1W : tab0 + (slot * 2 + f) * T0W;
 		const double F = rc[f] * To[0];
@@ -342,7 +253,7 @@ __device__ __forceinline__ void warp_posterior_pairs(WarpSmem& w, const Unit& u,
 // side's class sums through W (AR / AH, as in the pairwise form) and scatters its ~20 results.  For three-generation
 // outbred pedigrees this replaces 256 table entries + 256 pair-loop items per marker.
 constexpr int FT = 11;  // HE, H1, H2, GY[oo], GXE[of], GX1[of], GX2[of]: gval parts, phase weights W applied by the user
-constexpr int FT_DOUBLES = 16 * FT, CLS_AT = FT_DOUBLES;  // class sums (CLS doubles, layout of class_sums) sit behind the factors
+constexpr int FT_DOUBLES = 16 * FT, CLS_AT = FT_DOUBLES;  // class sums (CLS doubles) sit behind the factors
 
 __device__ __forceinline__ void warp_posterior_factored(WarpSmem& w, const Unit& u, int homslot, int gpmust, int t, int lane,
                                                         double* __restrict__ ft)
@@ -425,7 +336,7 @@ __device__ __forceinline__ void warp_posterior_factored(WarpSmem& w, const Unit&
 		}
 		return c;
 	};
-	// class sums of the emissions (and, for parent 1, of the two probing values: homozyg) in class_sums' layout
+	// class sums of the emissions (and, for parent 1, of the two probing values: homozyg) per (root orientation, phase bit, meiosis bits)
 #pragma unroll
 	for (int pass = 0; pass < 2; pass++)
 	{
@@ -927,11 +838,6 @@ __device__ __forceinline__ void warp_lists(WarpSmem& w, const Unit& u, int gpmus
 			w.el[pos] = (unsigned char)(p << 6 | cfg);
 			w.ainfo[pos] = (unsigned short)(ws_base((cfg & 7) << (p ? 3 : 0)) | xc << 10);
 		}
-		if (lane < 4)
-		{
-			w.cst[(p * 2 + xb) * 8 + half * 4 + lane] = (unsigned char)(nE + __popc(mask & ((1u << (8 * lane)) - 1u)));
-			w.ccn[(p * 2 + xb) * 8 + half * 4 + lane] = (unsigned char)__popc((mask >> (8 * lane)) & 0xffu);
-		}
 		nE += __popc(mask);
 		if (!xb) nX[p] += __popc(mask);
 		if (r8 == 3) nE0 = nE;  // entries of parent 0 come first
@@ -983,7 +889,7 @@ __host__ __device__ inline size_t warp_smem_bytes(int cap0, int cap1, int cls)
 	return sizeof(WarpSmem) + (tables > XBUF_BYTES ? tables : XBUF_BYTES);
 }
 
-// AGG: built with the class-sum form for units without rule-2 coupling (picked by the host when the pedigree has any)
+// AGG: built with the factorised posterior for units without rule-2 coupling (picked by the host when the pedigree has any)
 //
 // Memory of the sweeps (row a5): the forward pass keeps alpha only at the start of every segment of `seg` markers (a
 // checkpoint: 4 KB per segment) and, for the chromosome's LAST segment, for every marker in a per-warp ring of `seg`
@@ -997,7 +903,6 @@ __global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wa)
 	WarpSmem& w = *reinterpret_cast<WarpSmem*>(smem_raw);
 	double* const tab0 = reinterpret_cast<double*>(smem_raw + sizeof(WarpSmem));
 	double* const tab1 = tab0 + (size_t)wa.cap0 * 2 * T0W;
-	double* const cls = tab1 + (size_t)wa.cap1 * 2 * T1W;
 	double2* const xbuf = reinterpret_cast<double2*>(tab0);
 	const EstepArgs& a = wa.e;
 	const unsigned FULL = 0xffffffffu;
@@ -1227,7 +1132,7 @@ __global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wa)
 					__syncwarp();
 #ifndef CNF2_X_NOPAIRS
 					if (agg) warp_posterior_factored(w, u, w.homslot[t], gp, t, lane, tab0);
-					else warp_posterior_pairs<false>(w, u, w.homslot[t], lane, tab0, tab1, cls, false);
+					else warp_posterior_pairs(w, u, w.homslot[t], lane, tab0, tab1);
 #endif
 					__syncwarp();
 #ifndef CNF2_X_NOREDUCE
