@@ -252,7 +252,9 @@ __device__ __forceinline__ void warp_posterior_pairs(WarpSmem& w, const Unit& u,
 // lane per (side, root orientation, phase bit, meiosis bits) CLASS -- 64 classes, two rounds -- that meets the other
 // side's class sums through W (AR / AH, as in the pairwise form) and scatters its ~20 results.  For three-generation
 // outbred pedigrees this replaces 256 table entries + 256 pair-loop items per marker.
-constexpr int FT = 11;  // HE, H1, H2, GY[oo], GXE[of], GX1[of], GX2[of]: gval parts, phase weights W applied by the user
+// per (side, f, o, m): H_E, H_1, H_2; X_k[mF][q] (k = E, 1, 2) and Y[mO][q]: the grandparents' values with their phase weight
+// W[q ^ meiosis bit] applied and zero where the slot's admissible set excludes (orientation q, meiosis bit); GX_1[q], GX_2[q] raw
+constexpr int FT = 23, FT_X = 3, FT_Y = 15, FT_G = 19;
 constexpr int FT_DOUBLES = 16 * FT, CLS_AT = FT_DOUBLES;  // class sums (CLS doubles) sit behind the factors
 
 __device__ __forceinline__ void warp_posterior_factored(WarpSmem& w, const Unit& u, int homslot, int gpmust, int t, int lane,
@@ -298,8 +300,20 @@ __device__ __forceinline__ void warp_posterior_factored(WarpSmem& w, const Unit&
 		}
 		double* row = ft + (lane >> 1) * FT;
 		if (h == 0) row[0] = H[0], row[1] = H[1], row[2] = H[2];
-		row[3 + h] = GY;
-		row[5 + h] = GX[0], row[7 + h] = GX[1], row[9 + h] = GX[2];
+		const bool leaf = absent || attop;  // the subtree ends at the parent: no grandparent is visited
+		const int ign = u.flag2ignore;
+#pragma unroll
+		for (int mb = 0; mb < 2; mb++)  // the grandparent's meiosis bit: its x bit (the phase index of its weight) is h ^ mb
+		{
+			const bool okF = !(((ign >> kf) & 1) && h) && !(((gpmust >> kf) & 1) && !(h ^ mb));
+			const bool okO = !(((ign >> ko) & 1) && h) && !(((gpmust >> ko) & 1) && !(h ^ mb));
+			const double wF = (leaf || u.row[kf] < 0) ? 1.0 : N[kf * WB + t].W[h ^ mb];
+			const double wO = (leaf || u.row[ko] < 0) ? 1.0 : N[ko * WB + t].W[h ^ mb];
+#pragma unroll
+			for (int k = 0; k < 3; k++) row[FT_X + (mb * 2 + h) * 3 + k] = okF ? GX[k] * wF : 0.0;
+			row[FT_Y + mb * 2 + h] = okO ? GY * wO : 0.0;
+		}
+		row[FT_G + h] = GX[1], row[FT_G + 2 + h] = GX[2];
 	}
 	__syncwarp();
 	// ---- per class (side, f, phase bit, meiosis bits): the factors with the phase weights and the slots' admissible sets ----
@@ -317,22 +331,15 @@ __device__ __forceinline__ void warp_posterior_factored(WarpSmem& w, const Unit&
 		const int ma = (g >> 1) & 1, mb = (g >> 2) & 1;
 		c.mF = c.m ? mb : ma, c.mO = c.m ? ma : mb;
 		c.kF = sp + 1 + c.m, c.kO = sp + 1 + (c.m ^ 1);
-		const bool leaf = u.row[sp] < 0 || u.founder[sp];  // the subtree ends at the parent: no grandparent is visited
-		const int ign = u.flag2ignore, must = gpmust;
-		c.any = !(((ign >> sp) & 1) && c.o);
+		c.any = !(((u.flag2ignore >> sp) & 1) && c.o);
 		const double* row = ft + (((p * 2 + f) * 2 + c.o) * 2 + c.m) * FT;
 		c.HE = row[0], c.H1 = row[1], c.H2 = row[2];
 #pragma unroll
-		for (int q = 0; q < 2; q++)  // q: the grandparent's orientation; its x bit (phase index of its weight) is q ^ its meiosis bit
+		for (int q = 0; q < 2; q++)  // q: the grandparent's orientation
 		{
-			const bool okF = !(((ign >> c.kF) & 1) && q) && !(((must >> c.kF) & 1) && !(q ^ c.mF));
-			const bool okO = !(((ign >> c.kO) & 1) && q) && !(((must >> c.kO) & 1) && !(q ^ c.mO));
-			const double wF = (leaf || u.row[c.kF] < 0) ? 1.0 : N[c.kF * WB + t].W[q ^ c.mF];
-			const double wO = (leaf || u.row[c.kO] < 0) ? 1.0 : N[c.kO * WB + t].W[q ^ c.mO];
-			c.XE[q] = okF ? row[5 + q] * wF : 0.0;
-			c.X1[q] = okF ? row[7 + q] * wF : 0.0;
-			c.X2[q] = okF ? row[9 + q] * wF : 0.0;
-			c.YO[q] = okO ? row[3 + q] * wO : 0.0;
+			const double* x = row + FT_X + (c.mF * 2 + q) * 3;
+			c.XE[q] = x[0], c.X1[q] = x[1], c.X2[q] = x[2];
+			c.YO[q] = row[FT_Y + c.mO * 2 + q];
 		}
 		return c;
 	};
@@ -367,26 +374,25 @@ __device__ __forceinline__ void warp_posterior_factored(WarpSmem& w, const Unit&
 		const double wo0 = rc[12 + (p ^ 1) * 2], wo1 = rc[12 + (p ^ 1) * 2 + 1];
 		const double* C = p ? cls + f * 16 : cls + 32 + f * 48;
 		const int cw = p ? 1 : 3;
-#pragma unroll
-		for (int h = 0; h < 2; h++)
+		// per meiosis-bits value of the other side: its two phase classes first meet the other parent's phase weights (class h
+		// carries weight wo_h at shift bit 0, wo_(1-h) at shift bit 1), then the W block once
+#pragma unroll 2
+		for (int go = 0; go < 8; go++)
 		{
-			const double qa = h ? wo1 : wo0, qb = h ? wo0 : wo1;
-#pragma unroll 4
-			for (int go = 0; go < 8; go++)
+			const int a0 = aown ^ (p ? ws_base(go) : ws_base(go << 3));
+			const double* C0 = C + go * cw;
+			const double* C1 = C + (8 + go) * cw;
+			const double2 c00 = Ws2[a0 >> 1], cT = Ws2[(a0 ^ koth) >> 1], cO = Ws2[(a0 ^ kown) >> 1], c11 = Ws2[(a0 ^ 6) >> 1];
 			{
-				const int a0 = aown ^ (p ? ws_base(go) : ws_base(go << 3));
-				const double* Ck = C + (h * 8 + go) * cw;
-				const double E = Ck[0];
-				const double2 c00 = Ws2[a0 >> 1], cT = Ws2[(a0 ^ koth) >> 1], cO = Ws2[(a0 ^ kown) >> 1], c11 = Ws2[(a0 ^ 6) >> 1];
-				const double ux0 = qa * c00.x + qb * cT.x, uy0 = qa * c00.y + qb * cT.y;
-				const double ux1 = qa * cO.x + qb * c11.x, uy1 = qa * cO.y + qb * c11.y;
-				AR[0] += E * ux0, AR[1] += E * uy0, AR[2] += E * ux1, AR[3] += E * uy1;
-				if (!p)
-				{
-					const double e1 = Ck[1], e2 = Ck[2];
-					AH1[0] += e1 * ux0, AH1[1] += e1 * uy0, AH1[2] += e1 * ux1, AH1[3] += e1 * uy1;
-					AH2[0] += e2 * ux0, AH2[1] += e2 * uy0, AH2[2] += e2 * ux1, AH2[3] += e2 * uy1;
-				}
+				const double Ea = C0[0] * wo0 + C1[0] * wo1, Eb = C0[0] * wo1 + C1[0] * wo0;
+				AR[0] += Ea * c00.x + Eb * cT.x, AR[1] += Ea * c00.y + Eb * cT.y, AR[2] += Ea * cO.x + Eb * c11.x, AR[3] += Ea * cO.y + Eb * c11.y;
+			}
+			if (!p)
+			{
+				const double Ha = C0[1] * wo0 + C1[1] * wo1, Hb = C0[1] * wo1 + C1[1] * wo0;
+				AH1[0] += Ha * c00.x + Hb * cT.x, AH1[1] += Ha * c00.y + Hb * cT.y, AH1[2] += Ha * cO.x + Hb * c11.x, AH1[3] += Ha * cO.y + Hb * c11.y;
+				const double Ga = C0[2] * wo0 + C1[2] * wo1, Gb = C0[2] * wo1 + C1[2] * wo0;
+				AH2[0] += Ga * c00.x + Gb * cT.x, AH2[1] += Ga * c00.y + Gb * cT.y, AH2[2] += Ga * cO.x + Gb * c11.x, AH2[3] += Ga * cO.y + Gb * c11.y;
 			}
 		}
 	}
@@ -424,7 +430,7 @@ __device__ __forceinline__ void warp_posterior_factored(WarpSmem& w, const Unit&
 #pragma unroll
 		for (int q = 0; q < 2; q++)
 		{
-			const double A1 = rc[4 + fq] * c.H1 * row[7 + q], A2 = rc[6 + fq] * c.H2 * row[9 + q];
+			const double A1 = rc[4 + fq] * c.H1 * row[FT_G + q], A2 = rc[6 + fq] * c.H2 * row[FT_G + 2 + q];
 			const double sum = A1 + A2, inv = sum > 0 ? frcp(sum) : 0.0;
 			const double mq = base * c.XE[q] * SY;  // the class's mass with the first grandparent at orientation q
 			U1[q] = mq * tS * (A1 * inv), U2[q] = mq * tS * (A2 * inv);
