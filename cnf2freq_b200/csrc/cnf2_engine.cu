@@ -110,7 +110,8 @@ struct cnf2_engine
 	int n_ctas_literal = 0;
 	bool literal_only = false;  // debugging / A-B switch: CNF2_LITERAL=1 runs every unit through the literal kernel
 	int seg_override = 0;       // CNF2_SEG: cap on the markers per segment of the warp kernel's alpha ring (experiments, tests)
-	size_t ring_budget = 0;     // CNF2_RING_MB: bytes the ring of one in-flight E-step may take (0: 12 GiB)
+	size_t ring_budget = 0;     // CNF2_RING_MB: bytes the ring of one in-flight E-step may take (0: chosen at the first E-step)
+	size_t ring_budget_auto = 0;
 	DevBuf<Unit> d_units;
 	// M-step (row a6): inputs the E-step does not need, carried haplobase/haplocount, scratch
 	DevBuf<double> d_relhaplo, d_carry_base, d_carry_count, d_ratio, d_fw;
@@ -761,9 +762,18 @@ extern "C" int cnf2_estep(cnf2_engine* e, int32_t chrom)
 	const int n_warps = std::max(1, std::min(e->n_ctas_warp, n_units));
 	const int n_lit = std::max(1, std::min(e->n_ctas_literal, n_units));
 	const size_t ring_per_marker = (size_t)NUMSHIFTS * NUMTYPES * 8 + NUMSHIFTS * 4 + QS * 8;
+	if (!e->ring_budget_auto)
+	{
+		// the rings of all in-flight E-steps together may take a third of what is free when the first E-step comes (parameters
+		// and M-step inputs are resident by then): with one slot a whole chromosome of 5,000 markers fits the ring, with three
+		// slots on an otherwise empty B200 each gets ~19 GB; on a nearly full device the segments get shorter instead
+		size_t free_b = 0, total_b = 0;
+		CU(cudaMemGetInfo(&free_b, &total_b));
+		e->ring_budget_auto = std::max<size_t>((size_t)1 << 30, free_b / 3 / (size_t)e->n_slots);
+	}
 	auto seg_for = [&](int mc) {
 		int sg = ((mc + WB - 1) / WB) * WB;
-		const size_t budget = e->ring_budget ? e->ring_budget : (size_t)12 << 30;
+		const size_t budget = e->ring_budget ? e->ring_budget : e->ring_budget_auto;
 		const size_t fit = budget / ((size_t)n_warps * ring_per_marker);
 		if ((size_t)sg > fit) sg = (int)std::max<size_t>(WB, fit / WB * WB);
 		if (e->seg_override > 0) sg = std::min(sg, std::max(WB, e->seg_override / WB * WB));
