@@ -7,7 +7,7 @@
 // the single shift bit of the root / the parent (it flips the phase-weight index, :1227), so one table serves all
 // 8 shift modes and both sweeps.  With a fixed orientation (the posterior loop, :5406-5583) a subtree value
 // depends on the subtree's local configuration (3 meiosis bits | 3 orientation bits << 3); those tables are
-// built per marker for the configurations in use (post_entry1 in cnf2_warp_kernel.cuh).
+// built per marker for the configurations in use (warp_tables_from_factors in cnf2_warp_kernel.cuh).
 //
 // Validity: markersure in [0,1) and haploweight in [0,1] (then every factor is finite and non-negative and the
 // `if (base)` gates of :1271-1355 only skip zero products); other units go to the literal kernel.

@@ -77,55 +77,6 @@ struct __align__(16) WarpSmem
 	// (units that rule 2 does not constrain use the same space for their factors and class sums: warp_posterior_factored)
 };
 
-// One (entry, root orientation) pair of the posterior tables of marker t .
-__device__ __forceinline__ void post_entry1(const Unit& u, const uchar2* A, const NodeTab* N, const double* __restrict__ rc, int t, int p,
-                                            int cfg, int f, double* __restrict__ e)
-{
-	const int m = cfg & 1, ma = (cfg >> 1) & 1, mb = (cfg >> 2) & 1, o = (cfg >> 3) & 1, oa = (cfg >> 4) & 1, ob = (cfg >> 5) & 1;
-	const int sp = 1 + 3 * p;
-	const uchar2 a0 = A[t];
-	const NodeTab& n0 = N[t];
-	const bool absent = u.row[sp] < 0, attop = !absent && u.founder[sp];
-	const uchar2 ap = A[sp * WB + t];
-	const NodeTab& np = N[sp * WB + t];
-	const int kf = sp + 1 + m, of = m ? ob : oa, wf = of ^ (m ? mb : ma);
-	double pre = 1.0;
-	if (!absent && !attop)
-	{
-		const int ko = sp + 1 + (m ^ 1), oo = m ? oa : ob, wo = oo ^ (m ? ma : mb);
-		if (np.S[o ^ 1] != 0) pre = 1.0 - np.S[o ^ 1];
-		pre *= gfix<WB>(u, A, N, ko, t, o ? ap.x : ap.y, np.SEC[o ^ 1], oo, wo);
-	}
-	auto Q = [&](int v, double sec) -> double {
-		if (absent) return 1.0 + sec;
-		if (attop) return gval(ap, np, o, v, sec);
-		const PMsg pm = pmsg(ap, np, o, v, sec);
-		return pm.nb * pre * gfix<WB>(u, A, N, kf, t, pm.v2, pm.up2, of, wf);
-	};
-	const double P1 = Q(1, 0.0), P2 = Q(2, 0.0);
-	if (p == 0)
-	{
-		const int v = f ? a0.y : a0.x;
-		e[0] = Q(v, v != UNKNOWN ? n0.RN[f] : 0.0);
-		const double A1 = rc[4 + f] * P1, A2 = rc[6 + f] * P2;
-		const double sum = A1 + A2, inv = sum > 0 ? frcp(sum) : 0.0;
-		e[1] = A1 * inv;
-		e[2] = A2 * inv;
-	}
-	else
-	{
-		const int v = f ? a0.x : a0.y;
-		const double E = Q(v, n0.SEC[f ^ 1]);
-		e[0] = E;
-		const double A1 = rc[4 + (f ^ 1)] * P1, A2 = rc[6 + (f ^ 1)] * P2;  // side 1 probes the root at orientation f ^ 1
-		const double sum = A1 + A2, inv = sum > 0 ? frcp(sum) : 0.0, invE = E > 0 ? frcp(E) : 0.0;
-		e[1] = A1 * inv;
-		e[2] = A2 * inv;
-		e[3] = P1 * invE;
-		e[4] = P2 * invE;
-	}
-}
-
 // Posterior of the current marker, pairwise form.  A surviving term factorises as
 //   val = rbase[f] * E0[f][cfg0] * E1[f][cfg1] * sum_s Wr[f ^ s0] Wp0[x1 ^ s1] Wp1[x4 ^ s2] W_s[g0 | g1 << 3]
 // and every scatter target of :5556-5575 depends on the term only through (f, cfg0) [root as side 0, parent 0's
@@ -241,10 +192,106 @@ __device__ __forceinline__ void warp_posterior_pairs(WarpSmem& w, const Unit& u,
 	}
 }
 
+// The posterior tables of the pairwise form, from FACTORS rather than one evaluation per (entry, root orientation): the value
+// of a subtree configuration is H(o, m) * X(first grandparent) * Y(other grandparent) (see warp_posterior_factored), so the
+// 32 lanes evaluate the 16 (side, f, o, m) rows once -- lane = row * 2 + h holds H_E, H_1, H_2 and, for grandparent
+// orientation h, the first grandparent's three values and the other grandparent's one, 4 gval calls instead of 4 per
+// entry -- and every entry's lane fetches its factors by shuffle, applies the grandparents' phase weights and multiplies:
+// nb * [c * gfix(other)] * gfix(first) of the per-entry form, with the same zeros.
+__device__ __forceinline__ void warp_tables_from_factors(const WarpSmem& w, const Unit& u, int t, int lane, double* __restrict__ tab0,
+                                                         double* __restrict__ tab1)
+{
+	const unsigned FULL = 0xffffffffu;
+	const uchar2* A = w.A;
+	const NodeTab* N = w.nt;
+	const double* rc = w.rootc;
+	double H[3], GX[3], GY = 1.0;
+	{
+		const int h = lane & 1, m = (lane >> 1) & 1, o = (lane >> 2) & 1, f = (lane >> 3) & 1, p = lane >> 4;
+		const int sp = 1 + 3 * p;
+		const uchar2 a0 = A[t];
+		const NodeTab& n0 = N[t];
+		const int vroot = p == 0 ? (f ? a0.y : a0.x) : (f ? a0.x : a0.y);
+		const double secroot = p == 0 ? (vroot != UNKNOWN ? n0.RN[f] : 0.0) : n0.SEC[f ^ 1];
+		const bool absent = u.row[sp] < 0, attop = !absent && u.founder[sp];
+		const uchar2 ap = A[sp * WB + t];
+		const NodeTab& np = N[sp * WB + t];
+		const int kf = sp + 1 + m, ko = sp + 1 + (m ^ 1);
+#pragma unroll
+		for (int k = 0; k < 3; k++)
+		{
+			const int v = k == 0 ? vroot : k;
+			const double sec = k == 0 ? secroot : 0.0;
+			if (absent) H[k] = 1.0 + sec, GX[k] = 1.0;
+			else if (attop) H[k] = gval(ap, np, o, v, sec), GX[k] = 1.0;
+			else
+			{
+				const PMsg pm = pmsg(ap, np, o, v, sec);
+				H[k] = pm.nb * (np.S[o ^ 1] != 0 ? 1.0 - np.S[o ^ 1] : 1.0);
+				GX[k] = u.row[kf] < 0 ? 1.0 + pm.up2 : gval(A[kf * WB + t], N[kf * WB + t], h, pm.v2, pm.up2);
+			}
+		}
+		if (!absent && !attop)
+		{
+			const int vo = o ? ap.x : ap.y;
+			const double so = np.SEC[o ^ 1];
+			GY = u.row[ko] < 0 ? 1.0 + so : gval(A[ko * WB + t], N[ko * WB + t], h, vo, so);
+		}
+	}
+	const int nE = w.nE, nE0 = w.nE0;
+	for (int ibase = 0; ibase < 2 * nE; ibase += 32)
+	{
+		const int i = ibase + lane;
+		const bool valid = i < 2 * nE;
+		const int c = w.el[valid ? i >> 1 : 0], f = i & 1;
+		const int p = c >> 6, cfg = c & 63, sp = 1 + 3 * p;
+		const int m = cfg & 1, ma = (cfg >> 1) & 1, mb = (cfg >> 2) & 1, o = (cfg >> 3) & 1, oa = (cfg >> 4) & 1, ob = (cfg >> 5) & 1;
+		const int of = m ? ob : oa, oo = m ? oa : ob, mF = m ? mb : ma, mO = m ? ma : mb;
+		const int kf = sp + 1 + m, ko = sp + 1 + (m ^ 1);
+		const int rowl = ((((p * 2 + f) * 2 + o) * 2 + m) << 1);
+		const double HE = __shfl_sync(FULL, H[0], rowl), H1 = __shfl_sync(FULL, H[1], rowl), H2 = __shfl_sync(FULL, H[2], rowl);
+		double XE = __shfl_sync(FULL, GX[0], rowl | of), X1 = __shfl_sync(FULL, GX[1], rowl | of), X2 = __shfl_sync(FULL, GX[2], rowl | of);
+		double Y = __shfl_sync(FULL, GY, rowl | oo);
+		if (!valid) continue;
+		const bool leaf = u.row[sp] < 0 || u.founder[sp];
+		if (!leaf)
+		{
+			if (u.row[kf] >= 0)
+			{
+				const double wF = N[kf * WB + t].W[of ^ mF];
+				XE *= wF, X1 *= wF, X2 *= wF;
+			}
+			if (u.row[ko] >= 0) Y *= N[ko * WB + t].W[oo ^ mO];
+		}
+		const double E = HE * Y * XE, P1 = H1 * Y * X1, P2 = H2 * Y * X2;
+		const int slot = (i >> 1) - (p ? nE0 : 0);
+		if (p == 0)
+		{
+			double* e = tab0 + (slot * 2 + f) * T0W;
+			e[0] = E;
+			const double A1 = rc[4 + f] * P1, A2 = rc[6 + f] * P2;
+			const double sum = A1 + A2, inv = sum > 0 ? frcp(sum) : 0.0;
+			e[1] = A1 * inv;
+			e[2] = A2 * inv;
+		}
+		else
+		{
+			double* e = tab1 + (slot * 2 + f) * T1W;
+			e[0] = E;
+			const double A1 = rc[4 + (f ^ 1)] * P1, A2 = rc[6 + (f ^ 1)] * P2;  // side 1 probes the root at orientation f ^ 1
+			const double sum = A1 + A2, inv = sum > 0 ? frcp(sum) : 0.0, invE = E > 0 ? frcp(E) : 0.0;
+			e[1] = A1 * inv;
+			e[2] = A2 * inv;
+			e[3] = P1 * invE;
+			e[4] = P2 * invE;
+		}
+	}
+}
+
 // Posterior of the current marker for a unit that rule 2 of ignoreflag2 does not constrain (no individual on both sides:
 // Unit::xmask2 all ones), fully factorised.  Per side the emission of a subtree configuration (m, ma, mb | o, oa, ob) is
 //   E = H(o, m) * X(o, m; first grandparent's orientation and phase index) * Y(o, m; other grandparent's)
-// (post_entry1: nb * [c * gfix(other)] * gfix(first); "first" = the grandparent the parent's meiosis bit m points to), the
+// (warp_tables_from_factors: nb * [c * gfix(other)] * gfix(first); "first" = the grandparent the parent's meiosis bit m points to), the
 // configurations in use are a product set over the three tree slots (rule 1 pins the orientation of an absent / empty slot,
 // rule 3 the x bit of a homozygous grandparent), and every scatter target of :5556-5575 groups the configurations by a few
 // of these bits.  So nothing is built per configuration: 16 (o, m) rows of factors per side and root orientation
@@ -1128,12 +1175,7 @@ __global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wa)
 					}
 					__syncwarp();
 #ifndef CNF2_X_NOTAB
-					for (int i = lane; !agg && i < 2 * w.nE; i += 32)
-					{
-						const int c = w.el[i >> 1];
-						const int pp = c >> 6, slot = (i >> 1) - (pp ? w.nE0 : 0);
-						post_entry1(u, w.A, w.nt, w.rootc, t, pp, c & 63, i & 1, pp ? tab1 + (slot * 2 + (i & 1)) * T1W : tab0 + (slot * 2 + (i & 1)) * T0W);
-					}
+if (!agg) warp_tables_from_factors(w, u, t, lane, tab0, tab1);
 #endif
 					__syncwarp();
 #ifndef CNF2_X_NOPAIRS
