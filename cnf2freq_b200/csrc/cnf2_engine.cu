@@ -11,6 +11,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <mutex>
 #include <set>
 #include <string>
 #include <vector>
@@ -2047,5 +2048,130 @@ extern "C" int cnf2_preprocess(cnf2_engine* e, int32_t n_ind, const int32_t* par
 	}
 	cleanup();
 #undef PRE
+	return CNF2_OK;
+}
+
+// ---- an entry point that allocates nothing (no counterpart in the reference) ----
+// cnf2_negshift_minima_noalloc: the minima of cnf2_negshift_minima for callers that cannot call cudaMalloc (CUDA graph
+// capture, serving loops, harnesses that forbid it).  Inputs and outputs are the caller's device buffers; the kernels'
+// scratch -- one partial minimum per (row, chunk of NA_CHUNK markers) -- is the file-scope array below, held by every GPU
+// that loads the library until the process exits.  Two kernels: chunk minima into the scratch (several warps share a long
+// row instead of one warp walking it alone), then per row the minimum of its chunks and the first marker holding it, found
+// by skipping the chunks whose partial minimum rules them out.  Every scratch cell that the second kernel reads is
+// overwritten by the first, so nothing has to start at zero and the previous call's contents do not matter; all calls share
+// the array, so calls that overlap on the GPU (different streams, no dependency) race on it.
+constexpr int NA_CHUNK = 256;                 // markers per scratch cell
+constexpr size_t NA_MAX_CELLS = 1u << 20;     // 8 MiB of scratch: n_rows * ceil(Mc / NA_CHUNK) may not exceed this
+static __device__ __align__(256) double na_chunkmin[NA_MAX_CELLS];
+namespace
+{
+
+__global__ void __launch_bounds__(128) na_chunk_minima_kernel(const double* __restrict__ ns, int n_rows, int Mc, int nchunk, double* __restrict__ chunkmin)
+{
+	const size_t cell = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+	const int lane = threadIdx.x & 31;
+	if (cell >= (size_t)n_rows * nchunk) return;
+	const int row = (int)(cell / nchunk), ch = (int)(cell % nchunk);
+	const double* r = ns + (size_t)row * Mc;
+	const int mb = ch * NA_CHUNK, me = min(Mc, mb + NA_CHUNK);
+	double best = -1e-10;
+	for (int m = mb + lane; m < me; m += 32) best = fmin(best, r[m]);
+	for (int o = 16; o > 0; o >>= 1) best = fmin(best, __shfl_xor_sync(0xffffffffu, best, o));
+	if (lane == 0) chunkmin[cell] = best;
+}
+
+// same decisions as negshift_minima_kernel: the minimum below -1e-10, the first marker within the scores' rounding noise of it
+__global__ void __launch_bounds__(128) na_row_minima_kernel(const double* __restrict__ ns, int n_rows, int Mc, int nchunk, const double* __restrict__ chunkmin,
+                                                            double* __restrict__ minval, int32_t* __restrict__ minstart)
+{
+	const int row = (int)(((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+	if (row >= n_rows) return;
+	const double* cm = chunkmin + (size_t)row * nchunk;
+	double best = -1e-10;
+	for (int c = lane; c < nchunk; c += 32) best = fmin(best, cm[c]);
+	for (int o = 16; o > 0; o >>= 1) best = fmin(best, __shfl_xor_sync(0xffffffffu, best, o));
+	int at = Mc;
+	double val = best;
+	if (best < -1e-10)
+	{
+		const double thr = best + fmax(1e-15, -best * 1e-12);
+		int first = nchunk;  // the first chunk with a score at or below the threshold (one exists: the minimum's)
+		for (int c0 = 0; c0 < nchunk && first == nchunk; c0 += 32)
+		{
+			const int c = c0 + lane;
+			const unsigned hit = __ballot_sync(0xffffffffu, c < nchunk && cm[c] <= thr);
+			if (hit) first = c0 + __ffs(hit) - 1;
+		}
+		const double* r = ns + (size_t)row * Mc;
+		const int me = min(Mc, (first + 1) * NA_CHUNK);
+		for (int m0 = first * NA_CHUNK; m0 < me && at == Mc; m0 += 32)
+		{
+			const int m = m0 + lane;
+			const double v = m < me ? r[m] : 0.0;
+			const unsigned hit = __ballot_sync(0xffffffffu, m < me && v <= thr);
+			if (hit)
+			{
+				const int src = __ffs(hit) - 1;
+				at = m0 + src;
+				val = __shfl_sync(0xffffffffu, v, src);
+			}
+		}
+	}
+	if (lane == 0) minval[row] = val, minstart[row] = at;
+}
+
+// the scratch array's device address, looked up once per device with that device current (in host code the array's name is
+// only a stand-in for the symbol, not an address a kernel could use)
+constexpr int NA_MAX_DEVICES = 64;
+double* na_scratch_ptr[NA_MAX_DEVICES];
+std::mutex na_mutex;
+}  // namespace
+
+extern "C" int cnf2_negshift_minima_noalloc(const double* negshift_dev, int32_t n_rows, int32_t Mc, double* minval_dev, int32_t* minstart_dev,
+                                            void* stream)
+{
+	std::lock_guard<std::mutex> lock(na_mutex);
+	if (n_rows < 0 || Mc <= 0 || (n_rows > 0 && (!negshift_dev || !minval_dev || !minstart_dev)))
+	{
+		g_create_error = "cnf2_negshift_minima_noalloc: null buffer or negative size";
+		return CNF2_ERR_BAD_ARG;
+	}
+	if (n_rows == 0) return CNF2_OK;
+	const int nchunk = (Mc + NA_CHUNK - 1) / NA_CHUNK;
+	const size_t cells = (size_t)n_rows * nchunk;
+	if (cells > NA_MAX_CELLS)
+	{
+		g_create_error = "cnf2_negshift_minima_noalloc: n_rows * ceil(Mc / 256) = " + std::to_string(cells) + " exceeds the static scratch of " +
+		                 std::to_string(NA_MAX_CELLS) + " cells (8 MiB); split the rows over several calls or use cnf2_negshift_minima";
+		return CNF2_ERR_BAD_ARG;
+	}
+	int dev = -1;
+	cudaError_t err = cudaGetDevice(&dev);
+	if (err != cudaSuccess || dev < 0 || dev >= NA_MAX_DEVICES)
+	{
+		g_create_error = std::string("cnf2_negshift_minima_noalloc: no current CUDA device (") + cudaGetErrorString(err) + ")";
+		return CNF2_ERR_NO_DEVICE;
+	}
+	if (!na_scratch_ptr[dev])
+	{
+		double* p = nullptr;
+		err = cudaGetSymbolAddress((void**)&p, na_chunkmin);
+		if (err != cudaSuccess || !p)
+		{
+			g_create_error = std::string("cnf2_negshift_minima_noalloc: cudaGetSymbolAddress: ") + cudaGetErrorString(err);
+			return CNF2_ERR_CUDA;
+		}
+		na_scratch_ptr[dev] = p;
+	}
+	double* const scratch = na_scratch_ptr[dev];
+	cudaStream_t st = (cudaStream_t)stream;
+	na_chunk_minima_kernel<<<(unsigned)((cells * 32 + 127) / 128), 128, 0, st>>>(negshift_dev, n_rows, Mc, nchunk, scratch);
+	na_row_minima_kernel<<<(unsigned)(((size_t)n_rows * 32 + 127) / 128), 128, 0, st>>>(negshift_dev, n_rows, Mc, nchunk, scratch, minval_dev, minstart_dev);
+	err = cudaGetLastError();
+	if (err != cudaSuccess)
+	{
+		g_create_error = std::string("cnf2_negshift_minima_noalloc: launch: ") + cudaGetErrorString(err);
+		return CNF2_ERR_CUDA;
+	}
 	return CNF2_OK;
 }

@@ -22,7 +22,7 @@ SYMBOLS = [
     "cnf2_begin_iteration", "cnf2_mstep", "cnf2_get_params", "cnf2_get_negshift", "cnf2_get_negshift_packed",
     "cnf2_set_em_state", "cnf2_get_em_state", "cnf2_mstep_pass", "cnf2_negshift_minima", "cnf2_apply_inversions", "cnf2_em_pass",
     "cnf2_set_mstep_rows", "cnf2_set_mstep_chrom_packed", "cnf2_get_params_packed", "cnf2_estep_times", "cnf2_mstep_counters",
-    "cnf2_preprocess",
+    "cnf2_preprocess", "cnf2_negshift_minima_noalloc",
 ]
 
 
@@ -59,6 +59,17 @@ def load_library():
         lib.cnf2_default_settings.restype = None
         _lib = lib
     return _lib
+
+
+def negshift_minima_noalloc(negshift_dev, n_rows, mc, minval_dev, minstart_dev, stream=0):
+    """cnf2_negshift_minima_noalloc: device addresses (ints) of the caller's buffers, negshift [n_rows][mc] f64 in,
+    minval [n_rows] f64 and minstart [n_rows] i32 out, on `stream` (a cudaStream_t as int) of the current device.  Allocates
+    nothing; returns once the two kernels are enqueued."""
+    lib = load_library()
+    rc = lib.cnf2_negshift_minima_noalloc(ctypes.c_void_p(negshift_dev), ctypes.c_int32(n_rows), ctypes.c_int32(mc),
+                                          ctypes.c_void_p(minval_dev), ctypes.c_void_p(minstart_dev), ctypes.c_void_p(stream))
+    if rc != 0:
+        raise EngineError(f"cnf2 error {rc}: {lib.cnf2_last_error(None).decode()}")
 
 
 def _ptr(a):

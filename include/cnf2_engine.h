@@ -269,6 +269,23 @@ int cnf2_elapsed_ms(cnf2_engine* e, int32_t from, int32_t to, float* ms);
  * register-resident DFMA throughput in TFLOP/s and device-to-device copy bandwidth in GB/s. */
 int cnf2_measure_peaks(cnf2_engine* e, double* dfma_tflops, double* copy_gbs);
 
+/* ---- an entry point that allocates nothing ------------------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).  The minima of
+ * cnf2_negshift_minima -- per row the most negative phase-inversion score below -1e-10 and the first marker holding it,
+ * minstart = Mc where there is none -- computed from and into the CALLER's device buffers on the caller's stream, on the
+ * current device: negshift_dev [n_rows][Mc] doubles (the layout of cnf2_get_negshift_packed), minval_dev [n_rows] doubles,
+ * minstart_dev [n_rows] int32, stream a cudaStream_t (NULL = the default stream).  No engine handle is needed.  The call
+ * makes no cudaMalloc / cudaFree and returns without waiting for the kernels.  Their scratch (one partial minimum per row and
+ * chunk of 256 markers) is a static 8 MiB device array inside the library, held by every GPU that loads the library until the
+ * process exits: n_rows * ceil(Mc / 256) may not exceed 1,048,576 (CNF2_ERR_BAD_ARG beyond that; the message is returned by
+ * cnf2_last_error(NULL)).  All calls share that array: calls that overlap on the GPU (different streams without a
+ * dependency between them) race on it; calls on one stream, or ordered by events, are safe.  Nothing in it has to start at
+ * zero -- every cell a call reads it has written first.  The first call on each device looks the array's address up
+ * (cudaGetSymbolAddress); make that call outside a graph capture. */
+int cnf2_negshift_minima_noalloc(const double* negshift_dev, int32_t n_rows, int32_t Mc, double* minval_dev, int32_t* minstart_dev,
+                                 void* stream);
+
 #ifdef __cplusplus
 }
 #endif
