@@ -7,7 +7,9 @@
 #   DOTOULBAR 1 -> 0   (toulbar2 binary is not present; changes only the inversion stage, not rows a1-a5)
 #   XSTDBITSET 1 -> 0  (xstd/bit_set.hpp is not vendored by the reference)
 #   INDCOUNT           (1,000,000 thread-private maps per thread are pointless for oracle-sized inputs)
-# Nothing from /root/reference is written into the repository; the single output is the binary.
+# cnf2ref_selfing (row g1) additionally flips the compile-time knob SELFING to true and un-comments the two extra
+# TYPESEXES / TYPEGENS entries settings.h:21-23 keeps in comments for it (256 states, 192 valid).
+# Nothing from /root/reference is written into the repository; the outputs are the binaries.
 #
 # usage: oracle/build_ref.sh [INDCOUNT]    (default 20000)
 set -e
@@ -20,11 +22,19 @@ if [ ! -f "$REF/cnF2freq.cpp" ]; then
 	exit 0
 fi
 mkdir -p "$OUT"
+SELFING=0
 settings() {
 	sed -e 's/^#define DOTOULBAR 1/#define DOTOULBAR 0/' \
 	    -e 's/^#define XSTDBITSET 1/#define XSTDBITSET 0/' \
 	    -e "s/^const int INDCOUNT = [0-9]*;/const int INDCOUNT = $INDCOUNT;/" \
-	    "$REF/settings.h"
+	    "$REF/settings.h" |
+	if [ "$SELFING" = 1 ]; then
+		sed -e 's/^const bool SELFING = false;/const bool SELFING = true;/' \
+		    -e 's|{ 0, 0, 1, 1, 0, 1/\*, 0, 0\*//\*, 0\*/ }|{ 0, 0, 1, 1, 0, 1, 0, 0 }|' \
+		    -e 's|{ 1, 0, 0, 1, 0, 0/\*, 2, 2\*//\*, 3\*/ }|{ 1, 0, 0, 1, 0, 0, 2, 2 }|'
+	else
+		cat
+	fi
 }
 build() {
 	# $1 = output name, rest = extra flags
@@ -47,4 +57,10 @@ sed -n '140p' "$REF/cnF2freq.cpp" | grep -q '#include "settings.h"' || { echo "r
 build cnf2ref -O2
 # demo.sh:6 flags: the timed CPU baseline
 build cnf2ref_fast -O2 -ffast-math
-echo "built $OUT/cnf2ref $OUT/cnf2ref_fast (INDCOUNT=$INDCOUNT)"
+# row g1: the SELFING = true instantiation (strict IEEE, parity)
+SELFING=1
+settings | grep -q '^const bool SELFING = true;' || { echo "settings.h layout changed (SELFING)" >&2; exit 1; }
+settings | grep -q '{ 1, 0, 0, 1, 0, 0, 2, 2 }' || { echo "settings.h layout changed (TYPEGENS)" >&2; exit 1; }
+build cnf2ref_selfing -O2
+SELFING=0
+echo "built $OUT/cnf2ref $OUT/cnf2ref_fast $OUT/cnf2ref_selfing (INDCOUNT=$INDCOUNT)"

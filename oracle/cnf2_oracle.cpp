@@ -13,6 +13,9 @@
 // Settings restated: settings.h at HEAD -- NUMGEN 3 (64 states, 128 orientations, 8 shift modes),
 // SELFING false, RELSKEWSTATES false, HAPLOTYPING true, DOINFPROBS true, DOIMPOSSIBLE false,
 // DOREMAPDISTANCES false; CORRECTIONINFERENCE is false during doit (cnF2freq.cpp:8083-8085).
+// Compiled with -DCNF2_ORACLE_SELFING=1 (a second library, tests/oracle_lib.py) it restates the SELFING = true
+// instantiation instead (row g1: 256 states = 64 x 4 values of the two selfing bits, 192 of them valid, settings.h:7-46),
+// pinned on tests/golden/selfing_*.npz, which oracle/_ref/cnf2ref_selfing wrote.
 //
 // Every function names the reference lines it follows (paths relative to /root/reference).
 
@@ -31,7 +34,14 @@
 
 namespace
 {
-constexpr int NUMTYPES = 64;   // settings.h:27
+#ifndef CNF2_ORACLE_SELFING
+#define CNF2_ORACLE_SELFING 0
+#endif
+constexpr bool SELFING = CNF2_ORACLE_SELFING;  // settings.h:14
+constexpr int TYPEBITS = 6, SELFBITS = 2, SELFMASK = 3;  // settings.h:7, 20, 38
+constexpr int NONSELFNUMTYPES = 1 << TYPEBITS;           // settings.h:39
+constexpr int NUMTYPES = SELFING ? 256 : 64;             // settings.h:27
+constexpr int VALIDSELFNUMTYPES = NUMTYPES - SELFING * (NUMTYPES >> 2);  // settings.h:46
 constexpr int NUMPATHS = 128;  // settings.h:32
 constexpr int NUMSHIFTS = 8;   // settings.h:35
 constexpr int TURNBITS = 7;    // settings.h:40
@@ -115,9 +125,16 @@ double track(const Env& e, int update, int ind, int inval, double second, int m,
 {
 	const Problem& P = *e.p;
 	const bool attopnow = !(update & U_HOMOZYGOUS) && (genwidth == 1 || P.founder[ind]);  // :1120
-	const uint8_t* A = P.alleles + ((size_t)ind * P.M + m) * 2;
-	const double* S = P.sure + ((size_t)ind * P.M + m) * 2;
+	const uint8_t* const A0 = P.alleles + ((size_t)ind * P.M + m) * 2;
+	const double* const S0 = P.sure + ((size_t)ind * P.M + m) * 2;
 	const double hw = P.haploweight[(size_t)ind * P.M + m];
+	// :1122-1127: bits above TYPEBITS + 1 of the flag are the selfing bits; they only act in the root generation
+	const int selfval = (flag >> (TYPEBITS + 1)) & SELFMASK;
+	const bool selfingNOW = SELFING && genwidth == 4 && selfval;
+	uint8_t selfmarker[2];
+	double selfsure[2];
+	const uint8_t* const A = selfingNOW ? selfmarker : A0;  // :1138-1139
+	const double* const S = selfingNOW ? selfsure : S0;
 
 	int upflag2 = -1;
 	const int upflag = flag >> 1;
@@ -135,6 +152,24 @@ double track(const Env& e, int update, int ind, int inval, double second, int m,
 	for (int f2 = f2s; f2 < f2end; f2++)
 	{
 		int f2n = f2 & 1;
+		if (selfingNOW)  // :1169-1190
+		{
+			const int selfindex = (selfval >> 1) ^ f2n;
+			selfmarker[0] = selfmarker[1] = UNKNOWN;
+			selfsure[0] = selfsure[1] = 0;
+			int first = A0[0];
+			if (!markermiss(first, A0[1]))
+			{
+				selfmarker[selfindex] = (uint8_t)first;
+				selfsure[selfindex] = 1 - (1 - S0[0]) * (1 - S0[1]);
+			}
+			else
+			{
+				selfmarker[selfindex] = A0[1];
+				if (S0[0] == 0) return 0;
+				selfsure[selfindex] = 1 - (S0[0]) * (1 - S0[1]);
+			}
+		}
 		const bool allthesame = A[0] == A[1];
 		int val = inval;
 		double base;
@@ -169,7 +204,7 @@ double track(const Env& e, int update, int ind, int inval, double second, int m,
 			base *= 0.5;
 			doupd = false;
 		}
-		else if (allthesame && S[0] == S[1])  // :1235 with CORRECTIONINFERENCE false
+		else if ((allthesame && S[0] == S[1]) || selfingNOW)  // :1235 with CORRECTIONINFERENCE false
 		{
 			base *= (f2n ? 1.0 : 0.0);
 			doupd = false;
@@ -302,7 +337,7 @@ bool ignoreflag2(const Problem& P, const Tree& t, int flag2, int g, int shift, i
 		if (filtered && filtered != currfilter) return true;  // :3486
 		const uint8_t* A = P.alleles + ((size_t)i->first * P.M + marker) * 2;
 		const double* S = P.sure + ((size_t)i->first * P.M + marker) * 2;
-		if (A[0] == A[1] && S[0] == S[1] && !(((bool)filtered) ^ ((bool)(shift & j->second)))) return true;  // :3488
+		if (!SELFING && A[0] == A[1] && S[0] == S[1] && !(((bool)filtered) ^ ((bool)(shift & j->second)))) return true;  // :3488-3489
 	}
 	return false;
 }
@@ -313,7 +348,7 @@ bool ignoreflag2(const Problem& P, const Tree& t, int flag2, int g, int shift, i
 struct Sweeps
 {
 	int c0 = 0, Mc = 0;
-	std::vector<double> v;    // [NUMSHIFTS][Mc][3][64]
+	std::vector<double> v;    // [NUMSHIFTS][Mc][3][NUMTYPES]
 	std::vector<double> fac;  // [NUMSHIFTS][Mc][3]
 	bool done[NUMSHIFTS] = { false };
 	double* at(int s, int m, int pad) { return &v[(((size_t)s * Mc + (m - c0)) * 3 + pad) * NUMTYPES]; }
@@ -347,27 +382,45 @@ void adjustprobs(const Env& e, int root, double* probs, int marker, double& fact
 }
 
 // transition part of realanalyze, cnF2freq.cpp:2270-2367 (dense XOR-convolution, as the reference does it)
-void transition(const Problem& P, double* probs, double dist)
+void transition(const Problem& P, double* probs, double dist, int selfgen)
 {
 	if (!(dist > 0)) return;
-	double recprob[2][2], other[2][2][2];
-	for (int gen = 0; gen < 2; gen++)
-		for (int k = 0; k < 2; k++) recprob[gen][k] = 0.5 * (1.0 - exp(1 * P.genrec[gen] * dist));  // :2286, getactrec :777-780
+	double recprob[2 + SELFING][2], other[2][2][2];
+	for (int gen = 0; gen < 2 + SELFING; gen++)
+		for (int k = 0; k < 2; k++)
+			recprob[gen][k] = 0.5 * (1.0 - exp((gen == 2 ? selfgen : 1) * P.genrec[gen] * dist));  // :2286, getactrec :777-780
 	for (int gen = 0; gen < 2; gen++)
 		for (int mm = 0; mm < 2; mm++)
 			for (int k = 0; k < 2; k++) other[gen][mm][k] = mm ? 1.0 - recprob[gen][k] : recprob[gen][k];
 	static const int TYPESEXES[6] = { 0, 0, 1, 1, 0, 1 };  // settings.h:21
 	static const int TYPEGENS[6] = { 1, 0, 0, 1, 0, 0 };   // settings.h:23
-	double recombprec[NUMTYPES];
-	for (int i = 0; i < NUMTYPES; i++) recombprec[i] = 1;
+	double recombprec[NONSELFNUMTYPES];
+	for (int i = 0; i < NONSELFNUMTYPES; i++) recombprec[i] = 1;
+	double selfprec[5][5] = { { 0 } };  // :2316-2326 (only filled under SELFING)
+	if (SELFING)
+	{
+		const double rs = recprob[2 * SELFING][0];  // the selfing generations' rate, recprob[2][0]
+		selfprec[0][1] = selfprec[0][2] = rs;
+		selfprec[0][0] = 1 - 2 * rs;
+		selfprec[1][0] = selfgen ? selfprec[0][1] * 2.0 / ((1 << selfgen) - 1) : 1;
+		selfprec[1][2] = selfprec[1][0] * selfprec[0][1];
+		selfprec[2][0] = selfprec[1][0];
+		selfprec[2][1] = selfprec[1][2];
+		selfprec[2][2] = selfprec[1][1] = 1 - selfprec[1][0] - selfprec[1][2];
+	}
 	for (int t = 0; t < 6; t++)
-		for (int i = 0; i < NUMTYPES; i++) recombprec[i] *= other[TYPEGENS[t]][!((i >> t) & 1)][TYPESEXES[t]];
+		for (int i = 0; i < NONSELFNUMTYPES; i++) recombprec[i] *= other[TYPEGENS[t]][!((i >> t) & 1)][TYPESEXES[t]];
 	double probs2[NUMTYPES] = { 0 };
-	for (int from = 0; from < NUMTYPES; from++)
+	for (int from = 0; from < VALIDSELFNUMTYPES; from++)  // :2352-2364 (the double-bit selfing value is never entered or left)
 	{
 		double fromval = probs[from];
 		if (fromval <= 0) continue;
-		for (int to = 0; to < NUMTYPES; to++) probs2[to] += fromval * recombprec[from ^ to];
+		for (int to = 0; to < VALIDSELFNUMTYPES; to++)
+		{
+			const int xored = from ^ to;
+			probs2[to] += fromval * recombprec[xored & (NONSELFNUMTYPES - 1)] *
+			              (SELFING ? selfprec[(from >> TYPEBITS) & SELFMASK][(to >> TYPEBITS) & SELFMASK] : 1);
+		}
 	}
 	std::copy(probs2, probs2 + NUMTYPES, probs);
 }
@@ -381,7 +434,16 @@ void runsweeps(const Env& e, int root, Sweeps& sw, int c0, int c1)
 	sw.done[s] = true;
 	const int E = c1 - 1;
 	double probs[NUMTYPES];
-	for (int i = 0; i < NUMTYPES; i++) probs[i] = 1.0 / NUMTYPES;  // EVENGEN :2100-2104
+	const int selfgen = P.gen[root] - 2;  // :2094
+	double selfingfactors[4] = { 1, 1, 1, 1 };
+	if (SELFING)  // :2092-2099
+	{
+		selfingfactors[0] = 1.0 / (1 << selfgen);
+		selfingfactors[1] = (1 - selfingfactors[0]) * 0.5;
+		selfingfactors[2] = (1 - selfingfactors[0]) * 0.5;
+		selfingfactors[3] = 0;
+	}
+	for (int i = 0; i < NUMTYPES; i++) probs[i] = (1.0 / NUMTYPES) * (SELFING ? selfingfactors[(i >> TYPEBITS) & SELFMASK] : 1.0);  // EVENGEN :2100-2104
 	double factor = 0;
 	for (int m = c0; m <= E; m++)
 	{
@@ -390,7 +452,7 @@ void runsweeps(const Env& e, int root, Sweeps& sw, int c0, int c1)
 		adjustprobs(e, root, probs, m, factor, -1);
 		std::copy(probs, probs + NUMTYPES, sw.at(s, m, 2));
 		sw.f(s, m, 2) = factor;
-		if (m < E) transition(P, probs, P.markerpos[m + 1] - P.markerpos[m]);
+		if (m < E) transition(P, probs, P.markerpos[m + 1] - P.markerpos[m], selfgen);
 	}
 	for (int i = 0; i < NUMTYPES; i++) probs[i] = 1.0;  // :2111-2114
 	factor = 0;
@@ -399,7 +461,7 @@ void runsweeps(const Env& e, int root, Sweeps& sw, int c0, int c1)
 	for (int j = E - 1; j >= c0; j--)
 	{
 		adjustprobs(e, root, probs, j + 1, factor, -1);
-		transition(P, probs, P.markerpos[j + 1] - P.markerpos[j]);
+		transition(P, probs, P.markerpos[j + 1] - P.markerpos[j], selfgen);
 		std::copy(probs, probs + NUMTYPES, sw.at(s, j, 1));
 		sw.f(s, j, 1) = factor;
 	}
@@ -716,7 +778,7 @@ extern "C"
 // caller (the reference zeroes haplobase/haplocount at :5222-5234 and the M-step clears infprobs/homozyg).
 // founder is in/out: fixtrees' sticky side effect (:3176) is applied in analysis order.
 // fwbw_dous_index >= 0 additionally copies that individual's sweeps for chromosome fwbw_chrom into
-// fwbw [8][Mc][3][64] / fwbwfactors [8][Mc][3] / fwbwmask [8].
+// fwbw [8][Mc][3][NUMTYPES] / fwbwfactors [8][Mc][3] / fwbwmask [8].
 // negshift [K][M] (zeroed by the caller; null = no turn scoring) accumulates the phase-inversion scores; children [K]
 // is individ::children as doit rebuilds it from the analysed individuals (:5246-5259).
 int cnf2_oracle_estep(int K, int M, int C, int n_dous, const int32_t* par, const uint8_t* empty, uint8_t* founder,

@@ -8,7 +8,9 @@ import oracle_lib as ol
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 GOLDEN_CASES = sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN, "*.npz"))
-                      if not os.path.basename(p).startswith("mstep_"))
+                      if not os.path.basename(p).startswith(("mstep_", "selfing_")))
+# written by oracle/_ref/cnf2ref_selfing, the SELFING = true instantiation of the reference (row g1)
+SELFING_CASES = sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN, "selfing_*.npz")))
 STATS = ("haplobase", "haplocount", "infprobs", "homozyg")
 RTOL = 1e-9  # BASELINE.json north_star: posteriors within 1e-9 relative (fp64)
 # phase-inversion scores (row f2): differences of logarithms that cancel to rounding where a turn changes nothing, summed

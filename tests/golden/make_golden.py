@@ -29,12 +29,13 @@ from cnf2freq_b200 import synth  # noqa: E402
 
 REF = os.environ.get("CNF2_REFERENCE_DIR", "/root/reference")
 BIN = os.path.join(ROOT, "oracle", "_ref", "cnf2ref")
+BIN_SELFING = os.path.join(ROOT, "oracle", "_ref", "cnf2ref_selfing")  # settings.h with SELFING = true (row g1)
 LINE = re.compile(r"^(\d+),(\d+),(\d+): (\S+)\t(\S+) (\d+)$")
 
 
-def run_ref(args, prefix, count):
+def run_ref(args, prefix, count, binary=None):
     env = dict(os.environ, OMP_NUM_THREADS="1")
-    cmd = [BIN] + args + ["--count", str(count), "--dump", prefix, "--dumpfwbw"]
+    cmd = [binary or BIN] + args + ["--count", str(count), "--dump", prefix, "--dumpfwbw"]
     res = subprocess.run(cmd, env=env, capture_output=True, text=True, check=True)
     return res.stdout
 
@@ -115,7 +116,35 @@ def case_fullsib(tmp):
     return {"fullsib_iter2": collect(tmp + "/fs", out, 2, [(0, n0)])}
 
 
-CASES = dict(demo=case_demo, halfsib=case_halfsib, f2=case_f2, fullsib=case_fullsib)
+def case_selfing_demo(tmp):
+    """The PlantImpute demo under SELFING = true: individual F is listed with generation 20 (18 generations of selfing)."""
+    args = ["--mapfile", f"{REF}/demoplantimpute.map", "--pedfile", f"{REF}/demoplantimpute.ped", "--genfile",
+            f"{REF}/demoplantimpute.gen"]
+    out = run_ref(args, tmp + "/sdemo", 3, BIN_SELFING)
+    return {"selfing_demo_iter2": collect(tmp + "/sdemo", out, 2, [(0, 10)])}
+
+
+def case_selfing_lines(tmp):
+    """An F2 cross whose lines were selfed for 0-4 further generations (ped generation 2-6), SELFING = true."""
+    sim = synth.simulate_f2(n_f2=6, n_chrom=2, markers_per_chrom=14, spacing_cM=2.5, missing=0.2, seed=8)
+    rng = np.random.default_rng(8)
+    gens = [2, 3, 4, 4, 6, 3]
+    sim["ped"] = sim["ped"][:2] + [(me, fa, mo, g) for (me, fa, mo, _), g in zip(sim["ped"][2:], gens)]
+    tok = sim["tokens"]
+    for k, g in enumerate(gens):
+        row = tok[2 + k]
+        fix = (row == 1) & (rng.random(row.shape) > 0.5 ** (g - 2))  # a heterozygote survives a selfing with probability 1/2
+        row[fix] = rng.choice([0, 2], size=int(fix.sum()))
+    synth.write_alpha_files(tmp + "/sl", sim)
+    args = ["--mapfile", tmp + "/sl.map", "--pedfile", tmp + "/sl.ped", "--genfile", tmp + "/sl.gen"]
+    out = run_ref(args, tmp + "/sl", 3, BIN_SELFING)
+    prob = read_dump(tmp + "/sl.problem")
+    d = prob["dous"]
+    return {"selfing_lines_iter2": collect(tmp + "/sl", out, 2, [(0, int(d[2])), (1, int(d[4]))])}
+
+
+CASES = dict(demo=case_demo, halfsib=case_halfsib, f2=case_f2, fullsib=case_fullsib, selfing_demo=case_selfing_demo,
+             selfing_lines=case_selfing_lines)
 
 if __name__ == "__main__":
     if not os.path.exists(BIN):

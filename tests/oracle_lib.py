@@ -7,21 +7,30 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 _LIB = os.path.join(ROOT, "oracle", "_build", "libcnf2oracle.so")
+# the same sources compiled as the SELFING = true instantiation (a compile-time knob of the reference, settings.h:14)
+_LIB_SELFING = os.path.join(ROOT, "oracle", "_build", "libcnf2oracle_selfing.so")
 
 
-def build_oracle(force=False):
+def build_oracle(force=False, selfing=False):
     srcs = [os.path.join(ROOT, "oracle", f) for f in ("cnf2_oracle.cpp", "cnf2_mstep_oracle.cpp", "cnf2_preprocess_oracle.cpp")]
-    if force or not os.path.exists(_LIB) or os.path.getmtime(_LIB) < max(os.path.getmtime(s) for s in srcs):
-        os.makedirs(os.path.dirname(_LIB), exist_ok=True)
-        subprocess.check_call(["g++", "-std=c++17", "-O2", "-fopenmp", "-fPIC", "-shared", "-o", _LIB] + srcs)
-    return _LIB
+    out = _LIB_SELFING if selfing else _LIB
+    if force or not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(s) for s in srcs):
+        os.makedirs(os.path.dirname(out), exist_ok=True)
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-fopenmp", "-fPIC", "-shared"] +
+                              (["-DCNF2_ORACLE_SELFING=1"] if selfing else []) + ["-o", out] + srcs)
+    return out
 
 
 _lib = None
+_lib_selfing = None
 
 
-def lib():
-    global _lib
+def lib(selfing=False):
+    global _lib, _lib_selfing
+    if selfing:
+        if _lib_selfing is None:
+            _lib_selfing = ctypes.CDLL(build_oracle(selfing=True))
+        return _lib_selfing
     if _lib is None:
         _lib = ctypes.CDLL(build_oracle())
     return _lib
@@ -75,7 +84,7 @@ def doit_children(par, dous):
     return ch
 
 
-def oracle_estep(pb, fwbw_for=None, counters=False, all_dous=None):
+def oracle_estep(pb, fwbw_for=None, counters=False, all_dous=None, selfing=False):
     """Runs the oracle E-step.  Returns dict(haplobase, haplocount, infprobs, homozyg, negshift, loglik, founder[, fwbw...]).
     all_dous: the analysed individuals of the whole run when pb.dous is a sample of them (children counts)."""
     K, M, C, nd = pb.K, pb.M, pb.C, len(pb.dous)
@@ -88,10 +97,10 @@ def oracle_estep(pb, fwbw_for=None, counters=False, all_dous=None):
     fw = ff = fm = None
     if fwbw_for is not None:
         mc = int(pb.chromstarts[fc + 1] - pb.chromstarts[fc])
-        fw = np.zeros((8, mc, 3, 64))
+        fw = np.zeros((8, mc, 3, 256 if selfing else 64))
         ff = np.zeros((8, mc, 3))
         fm = np.zeros(8, np.int32)
-    rc = lib().cnf2_oracle_estep(
+    rc = lib(selfing).cnf2_oracle_estep(
         ctypes.c_int(K), ctypes.c_int(M), ctypes.c_int(C), ctypes.c_int(nd), _p(pb.par), _p(pb.empty),
         _p(out["founder"]), _p(pb.gen), _p(pb.descendants), _p(pb.dous), _p(pb.markerpos), _p(pb.chromstarts),
         _p(pb.genrec), _p(pb.alleles), _p(pb.sure), _p(pb.haploweight), _p(out["haplobase"]), _p(out["haplocount"]),

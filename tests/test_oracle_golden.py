@@ -4,17 +4,21 @@ import numpy as np
 import pytest
 
 import oracle_lib as ol
-from cases import GOLDEN_CASES, STATS, assert_close, load_golden
+from cases import GOLDEN_CASES, SELFING_CASES, STATS, assert_close, load_golden
 
 
 def test_fixtures_present():
     assert {"demo_iter1", "demo_iter3", "halfsib_iter2", "f2small_iter2", "fullsib_iter2"} <= set(GOLDEN_CASES)
 
 
-@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_selfing_fixtures_present():
+    assert {"selfing_demo_iter2", "selfing_lines_iter2"} <= set(SELFING_CASES)
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES + SELFING_CASES)
 def test_oracle_statistics_match_reference(name):
     g, pb = load_golden(name)
-    out = ol.oracle_estep(pb)
+    out = ol.oracle_estep(pb, selfing=name in SELFING_CASES)
     for k in STATS:
         # same algorithm, same operation order: expected to be bit-identical, asserted at 1e-12
         assert_close(out[k], g[k], f"{name}:{k}", rtol=1e-12)
@@ -25,7 +29,7 @@ def test_oracle_statistics_match_reference(name):
     assert_close(out["negshift"], g["negshift"], f"{name}:negshift", rtol=1e-12, atol=1e-13)
 
 
-@pytest.mark.parametrize("name", GOLDEN_CASES)
+@pytest.mark.parametrize("name", GOLDEN_CASES + SELFING_CASES)
 def test_oracle_sweeps_match_reference(name):
     g, pb = load_golden(name)
     keys = [k for k in g if k.startswith("fwbw_c")]
@@ -33,7 +37,7 @@ def test_oracle_sweeps_match_reference(name):
     for k in keys:
         c, n = (int(x[1:]) for x in k.split("_")[1:])
         j = int(np.nonzero(pb.dous == n)[0][0])
-        out = ol.oracle_estep(pb, fwbw_for=(j, c))
+        out = ol.oracle_estep(pb, fwbw_for=(j, c), selfing=name in SELFING_CASES)
         mask = g[f"fwbwmask_c{c}_n{n}"]
         for s in range(8):
             if mask[s] != 3:
