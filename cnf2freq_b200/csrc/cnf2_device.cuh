@@ -10,6 +10,9 @@
 namespace cnf2
 {
 constexpr int NUMTYPES = 64;   // settings.h:27
+// SELFING = true (settings.h:7, 14, 27, 38, 46; row g1): two selfing bits above the six meiosis bits, 256 states of which the
+// 192 with selfing value 0..2 are valid; only the literal kernel estep_kernel<true> is instantiated for it
+constexpr int TYPEBITS = 6, SELFMASK = 3, NUMTYPES_SELFING = 256;
 constexpr int NUMPATHS = 128;  // settings.h:32
 constexpr int NUMSHIFTS = 8;   // settings.h:35
 constexpr int NSLOTS = 7;      // TURNBITS, settings.h:40
@@ -51,7 +54,7 @@ struct Unit
 	uint8_t vismask;             // slots trackpossible visits from a non-founder root (pointer chain + founder flags)
 	uint8_t pad0;
 	uint8_t expand[NUMTYPES];    // j -> j deposited into the free state bits
-	uint8_t pad1[4];
+	int32_t selfgen;             // gen - 2: generations of selfing behind the listed pedigree (cnF2freq.cpp:2094, 2280); SELFING only
 	// batched kernel (cnf2_batch_kernel.cuh): x = flag2 ^ (g << 1) values passing rule 2 of ignoreflag2
 	// (bit x of xmask2), and the local configurations (3 meiosis bits | 3 orientation bits << 3) of the two
 	// parents' subtrees that some surviving (x, g) pair uses (bit cfg of cfgmask[p])
@@ -82,7 +85,7 @@ __device__ __forceinline__ int upflagit(int flag, int parnum)
 	return (flag >> (parnum * (GW - 1))) & ((1 << (GW - 1)) - 1);
 }
 
-template <int UPD, int GW>
+template <int UPD, int GW, bool SELF = false>
 __device__ double track(const Ctx& c, int slot, int inval, double second, int t, unsigned flag, int flag99,
                         int localshift, double updateval);
 
@@ -102,14 +105,21 @@ __device__ __forceinline__ double up(const Ctx& c, int slot, int par, int val, d
 // trackpossible<update, zeropropagate = 0>, cnF2freq.cpp:1075-1359: probability of the observed alleles
 // of the focus tree below `slot` given inheritance flag, orientation flag99 (-1 = both) and shift mode;
 // in the update modes it also scatters updateval into the accumulator columns.
-template <int UPD, int GW>
+// SELF: the SELFING = true instantiation; the selfing bits of the flag (above TYPEBITS + 1) act in the root generation only
+// (:1115-1127): a state with selfing value 1 / 2 sees the root's genotype as one known allele -- the agreed one, or the second
+// one of a heterozygote -- on the side the value and the orientation pick, and an unknown one on the other (:1169-1190).
+template <int UPD, int GW, bool SELF>
 __device__ double track(const Ctx& c, int slot, int inval, double second, int t, unsigned flag, int flag99,
                         int localshift, double updateval)
 {
 	const bool attopnow = !(UPD & U_HOMOZYGOUS) && (GW == 1 || c.founder[slot]);  // :1120
-	const uchar2 a = c.A[slot * TILE + t];
-	const double2 s = c.S[slot * TILE + t];
+	uchar2 a = c.A[slot * TILE + t];
+	double2 s = c.S[slot * TILE + t];
 	const double hw = c.HW[slot * TILE + t];
+	const uchar2 a0 = a;
+	const double2 s0 = s;
+	const int selfval = (SELF && GW == 4) ? (int)((flag >> (TYPEBITS + 1)) & SELFMASK) : 0;  // :1122
+	const bool selfingNOW = selfval != 0;                                                       // :1126
 
 	int upflag2 = -1;
 	const int upflag = flag >> 1;
@@ -122,13 +132,45 @@ __device__ double track(const Ctx& c, int slot, int inval, double second, int t,
 		f2end = f2s + 1;
 	}
 	const int firstpar = flag & 1;  // :1156
-	const bool allthesame = a.x == a.y;
+	bool allthesame = a.x == a.y;
 	double ok = 0;
 
 	for (int f2 = f2s; f2 < f2end; f2++)
 	{
 		int f2n = f2;
 		const int realf2n = f2;
+		if constexpr (SELF && GW == 4)
+		{
+			if (selfingNOW)  // :1169-1190
+			{
+				const int selfindex = (selfval >> 1) ^ f2;
+				int first = a0.x;
+				bool miss0;  // markermiss<false>(first, second), :303-316
+				if (first == UNKNOWN)
+				{
+					first = a0.y;
+					miss0 = false;
+				}
+				else if (a0.y == UNKNOWN && first != SEXMARKER) miss0 = false;
+				else miss0 = first != a0.y;
+				int mk;
+				double su;
+				if (!miss0)
+				{
+					mk = first;
+					su = 1.0 - (1.0 - s0.x) * (1.0 - s0.y);
+				}
+				else
+				{
+					mk = a0.y;
+					if (s0.x == 0) return 0;  // :1186
+					su = 1.0 - s0.x * (1.0 - s0.y);
+				}
+				a = selfindex ? make_uchar2(UNKNOWN, (unsigned char)mk) : make_uchar2((unsigned char)mk, UNKNOWN);
+				s = selfindex ? make_double2(0.0, su) : make_double2(su, 0.0);
+				allthesame = a.x == a.y;
+			}
+		}
 		const int Af = f2 ? a.y : a.x, Ao = f2 ? a.x : a.y;
 		const double Sf = f2 ? s.y : s.x, So = f2 ? s.x : s.y;
 		int val = inval;
@@ -162,7 +204,7 @@ __device__ double track(const Ctx& c, int slot, int inval, double second, int t,
 
 		bool doupd = true;
 		f2n ^= (firstpar ^ localshift) & 1;  // :1227
-		if (allthesame && s.x == s.y)        // :1235 (CORRECTIONINFERENCE false inside doit)
+		if ((allthesame && s.x == s.y) || selfingNOW)  // :1235 (CORRECTIONINFERENCE false inside doit)
 		{
 			base *= f2n ? 1.0 : 0.0;
 			doupd = false;

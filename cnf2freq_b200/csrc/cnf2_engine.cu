@@ -109,7 +109,11 @@ struct cnf2_engine
 	int cap0 = 64, cap1 = 64;  // posterior table capacities of the warp kernel for this pedigree
 	int cls = 0;               // CLS when some unit's rule-2 mask is all ones (class sums in use)
 	int n_ctas_literal = 0;
-	bool literal_only = false;  // debugging / A-B switch: CNF2_LITERAL=1 runs every unit through the literal kernel
+	bool literal_only = false;  // debugging / A-B switch: CNF2_LITERAL=1 runs every unit through the literal kernel; always under SELFING
+	bool selfing = false;       // cnf2_settings.selfing (settings.h:14)
+	int n_states = NUMTYPES;    // 64, or 256 under SELFING (settings.h:27)
+	size_t literal_smem = 0;    // dynamic shared memory of the literal kernel's instantiation
+	DevBuf<double> d_dist;      // SELFING: distance to the next marker, laid out like the columns of d_rec's first half
 	int seg_override = 0;       // CNF2_SEG: cap on the markers per segment of the warp kernel's alpha ring (experiments, tests)
 	size_t ring_budget = 0;     // CNF2_RING_MB: bytes the ring of one in-flight E-step may take (0: chosen at the first E-step)
 	size_t ring_budget_auto = 0;
@@ -219,11 +223,11 @@ extern "C" int cnf2_create(cnf2_engine** out, const cnf2_settings* settings)
 		return CNF2_ERR_BAD_ARG;
 	}
 	*out = nullptr;
-	if (settings->numgen != 3 || settings->selfing || settings->relskewstates || !settings->haplotyping ||
-	    !settings->doinfprobs)
+	if (settings->numgen != 3 || (settings->selfing != 0 && settings->selfing != 1) || settings->relskewstates ||
+	    !settings->haplotyping || !settings->doinfprobs)
 	{
 		g_create_error =
-		    "cnf2_create: kernels are built for NUMGEN 3, SELFING false, RELSKEWSTATES false, HAPLOTYPING true, "
+		    "cnf2_create: kernels are built for NUMGEN 3, SELFING false or true, RELSKEWSTATES false, HAPLOTYPING true, "
 		    "DOINFPROBS true";
 		return CNF2_ERR_UNSUPPORTED;
 	}
@@ -266,10 +270,15 @@ extern "C" int cnf2_create(cnf2_engine** out, const cnf2_settings* settings)
 		if ((ce = cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming)) != cudaSuccess) return bail(ce, "cudaEventCreate");
 		if ((ce = cudaEventCreateWithFlags(&sl.tail, cudaEventDisableTiming)) != cudaSuccess) return bail(ce, "cudaEventCreate");
 	}
-	if ((ce = cudaFuncSetAttribute(estep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem))) != cudaSuccess)
+	// SELFING = true (row g1): 256 states; only the literal kernel is instantiated for it, every unit goes through it
+	e->selfing = settings->selfing != 0;
+	e->n_states = e->selfing ? NUMTYPES_SELFING : NUMTYPES;
+	e->literal_smem = e->selfing ? sizeof(SmemSelfing) : sizeof(Smem);
+	const void* const literal_kernel = e->selfing ? (const void*)estep_kernel<true> : (const void*)estep_kernel<false>;
+	if ((ce = cudaFuncSetAttribute(literal_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)e->literal_smem)) != cudaSuccess)
 		return bail(ce, "cudaFuncSetAttribute(estep_kernel)");
 	int per_sm = 0;
-	if ((ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, estep_kernel, NTHREADS, sizeof(Smem))) != cudaSuccess)
+	if ((ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, literal_kernel, NTHREADS, e->literal_smem)) != cudaSuccess)
 		return bail(ce, "occupancy query");
 	if (per_sm < 1) per_sm = 1;
 	if (settings->ctas_per_sm > 0) per_sm = std::min(per_sm, settings->ctas_per_sm);
@@ -282,7 +291,7 @@ extern "C" int cnf2_create(cnf2_engine** out, const cnf2_settings* settings)
 			return bail(ce, "cudaFuncSetAttribute(warp_estep_kernel carveout)");
 	}
 	const char* lit = getenv("CNF2_LITERAL");
-	e->literal_only = lit && lit[0] == '1';
+	e->literal_only = (lit && lit[0] == '1') || e->selfing;
 	if (const char* cp = getenv("CNF2_CTAS_PER_SM")) e->settings.ctas_per_sm = atoi(cp);
 	e->seg_override = settings->segment;
 	if (const char* cp = getenv("CNF2_SEG")) e->seg_override = atoi(cp);
@@ -314,6 +323,7 @@ extern "C" void cnf2_destroy(cnf2_engine* e)
 	e->d_sure.release();
 	e->d_hw.release();
 	e->d_rec.release();
+	e->d_dist.release();
 	for (Slot& sl : e->slots)
 	{
 		if (sl.stream) cudaStreamSynchronize(sl.stream);
@@ -448,6 +458,10 @@ extern "C" int cnf2_set_pedigree(cnf2_engine* e, int32_t n_ind, const int32_t* p
 			for (int lev2 = 0; lev2 < 2; lev2++) ids[base + 1 + lev2] = parents[l1 * 2 + lev2];
 		}
 	};
+	if (e->selfing)
+		for (int j = 0; j < n_dous; j++)
+			if (gen[dous[j]] < 2 || gen[dous[j]] > 32)  // 1 << (gen - 2) of :2095, 2321 in an int
+				return e->fail(CNF2_ERR_BAD_ARG, "cnf2_set_pedigree: SELFING needs generation 2..32 for every analysed individual");
 	for (int j = 0; j < n_dous; j++)
 	{
 		int32_t ids[NSLOTS];
@@ -522,6 +536,7 @@ extern "C" int cnf2_set_pedigree(cnf2_engine* e, int32_t n_ind, const int32_t* p
 		u.flag2ignore = (uint8_t)(flag2ignore ^ (NUMPATHS - 1));
 		u.shiftignore = (uint8_t)(shiftignore ^ (NUMSHIFTS - 1));
 		u.shiftend = (uint8_t)(gen[ind] < 2 ? 2 : NUMSHIFTS);  // :5359
+		u.selfgen = e->selfing ? gen[ind] - 2 : 0;
 		u.out = j;
 		u.descendants = (double)descendants[ind];
 		// updatenegshifts (:3662-3687): who receives a phase-inversion score from this unit, and its weight
@@ -713,6 +728,14 @@ static int set_params_impl(cnf2_engine* e, int32_t chrom, const uint8_t* alleles
 	}
 	CU(e->d_rec.ensure(2 * (e->resident ? M : (size_t)e->max_mc)));
 	CU(cudaMemcpyAsync(e->d_rec.p + 2 * col0, rec.data(), rec.size() * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+	if (e->selfing)
+	{
+		// the selfing generations' rate depends on the unit (:2286: selfgen * genrec[2] * dist): the kernel gets the distances
+		std::vector<double> dist(Mc, 0.0);
+		for (size_t m = 0; m + 1 < Mc; m++) dist[m] = e->markerpos[c0 + m + 1] - e->markerpos[c0 + m];
+		CU(e->d_dist.ensure(e->resident ? M : (size_t)e->max_mc));
+		CU(cudaMemcpyAsync(e->d_dist.p + col0, dist.data(), dist.size() * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+	}
 	CU(cudaEventRecord(e->params_ready, e->stream));
 	// async_params: the copies from page-locked caller buffers are left in flight (the E-step waits for them on the
 	// device); otherwise caller buffers may be reused after return.  rec is pageable: staged before the call returns.
@@ -791,7 +814,7 @@ extern "C" int cnf2_estep(cnf2_engine* e, int32_t chrom)
 		CU(sl.ckalpha.ensure((size_t)n_warps * nseg_max * NUMSHIFTS * NUMTYPES));
 		CU(sl.ckexp.ensure((size_t)n_warps * nseg_max * NUMSHIFTS));
 	}
-	CU(sl.lit_alpha.ensure((size_t)n_lit * e->max_mc * NUMSHIFTS * NUMTYPES));
+	CU(sl.lit_alpha.ensure((size_t)n_lit * e->max_mc * NUMSHIFTS * e->n_states));
 	CU(sl.lit_fac.ensure((size_t)n_lit * e->max_mc * NUMSHIFTS));
 	CU(sl.stats.ensure((size_t)e->n_rows * e->max_mc * STATS_PER_CELL));
 	sl.n_shared = e->n_shared;
@@ -855,7 +878,14 @@ extern "C" int cnf2_estep(cnf2_engine* e, int32_t chrom)
 		}
 		a.alpha = sl.lit_alpha.p;
 		a.alphafac = sl.lit_fac.p;
-		estep_kernel<<<std::max(1, std::min(e->n_ctas_literal, n_units)), NTHREADS, sizeof(Smem), sl.stream>>>(a);
+		const int lit_grid = std::max(1, std::min(e->n_ctas_literal, n_units));
+		if (e->selfing)
+		{
+			a.dist = e->d_dist.p + col0;
+			a.genrec2 = e->genrec[2];
+			estep_kernel<true><<<lit_grid, NTHREADS, e->literal_smem, sl.stream>>>(a);
+		}
+		else estep_kernel<false><<<lit_grid, NTHREADS, e->literal_smem, sl.stream>>>(a);
 		e->n_kernels++;
 		CU(cudaGetLastError());
 		e->last_launches++;

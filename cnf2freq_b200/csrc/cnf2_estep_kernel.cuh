@@ -2,6 +2,12 @@
 // chromosome) units.  One warp per shift mode, two inheritance states per lane (bits 0-4 of the state
 // across lanes, bit 5 inside the thread), so the Kronecker transition R(r)^{(x)6} (cnF2freq.cpp:2270-2367)
 // is five __shfl_xor butterfly stages plus one in-register stage.
+//
+// estep_kernel<true> is the SELFING = true instantiation of the reference (settings.h:14; row g1 of the scope table): 256
+// states = 64 x the value of two selfing bits, eight per lane (state = lane + 32 k: k & 1 is meiosis bit 5, k >> 1 the
+// selfing value), the transition a Kronecker product of the six 2 x 2 matrices with the 3 x 3 selfing matrix selfprec
+// (cnF2freq.cpp:2316-2326, 2352-2364), the prior of :2092-2104, the root's emission of :1169-1190, rule 3 of ignoreflag2 off
+// (:3489).  It is the only kernel built for that setting: every unit goes through it.
 #pragma once
 #include "cnf2_device.cuh"
 
@@ -14,6 +20,8 @@ struct EstepArgs
 	const double* hw;        // [n_rows][ld]
 	const double* rec0;      // [Mc] recombination fraction towards the next marker, genrec[0] (0 = same position)
 	const double* rec1;      // [Mc] same with genrec[1]
+	const double* dist;      // [Mc] SELFING only: distance to the next marker (cM), for the selfing generations' rate (:2286)
+	double genrec2;          // SELFING only: genrec[2] (:7943)
 	const Unit* units;
 	int32_t n_units;
 	int32_t Mc;              // markers of this chromosome
@@ -43,15 +51,16 @@ __host__ __device__ __forceinline__ StatsCell stats_cell(double* base, size_t nr
 	return StatsCell{ base + cell, base + plane + cell, base + 2 * plane + cell * 4, base + 6 * plane + cell * 2, base + 8 * plane + cell };
 }
 
-struct __align__(16) Smem
+template <int NS>  // NS: states (64, or 256 under SELFING)
+struct __align__(16) SmemT
 {
 	double acc[NACC * NTHREADS];
 	double2 S[NSLOTS * TILE];
 	double HW[NSLOTS * TILE];
 	double tot[NACC];
 	double Ls[NUMSHIFTS];
-	double beta[NUMSHIFTS * NUMTYPES];
-	double aplus[NUMSHIFTS * NUMTYPES];     // turn scoring: alpha after the emission at the current marker
+	double beta[NUMSHIFTS * NS];
+	double aplus[NUMSHIFTS * NS];           // turn scoring: alpha after the emission at the current marker
 	double Bs[NUMSHIFTS], Fp[NUMSHIFTS];    // log-factors of beta / alpha+
 	double raw[8 * NUMSHIFTS];              // rawvals[turn][shift], -1 = not scored (:5678-5681)
 	unsigned short queue[NUMSHIFTS * 64];
@@ -59,6 +68,8 @@ struct __align__(16) Smem
 	Unit unit;
 	int32_t unit_index;
 };
+using Smem = SmemT<NUMTYPES>;
+using SmemSelfing = SmemT<NUMTYPES_SELFING>;
 
 __device__ __forceinline__ double warp_sum(double v)
 {
@@ -87,26 +98,55 @@ __device__ __forceinline__ void transition(double& p0, double& p1, double r0, do
 	p1 = n1;
 }
 
+// The same under SELFING (:2276-2364): probs2[to] = sum_from probs[from] recombprec[(from ^ to) & 63] selfprec[sv(from)][sv(to)]
+// over the 192 valid states -- the 64-state product per selfing value, then the 3 x 3 mix of the selfing values; the
+// fourth value is never entered and is zeroed by any transition over a distance (probs2 starts at 0).
+__device__ __forceinline__ void transition_selfing(double (&p)[8], double r0, double r1, double dist, double genrec2, int selfgen)
+{
+	if (!(r0 > 0) && !(r1 > 0)) return;
+#pragma unroll
+	for (int sv = 0; sv < 3; sv++) transition(p[2 * sv], p[2 * sv + 1], r0, r1);
+	const double rs = 0.5 * (1.0 - exp((double)selfgen * genrec2 * dist));  // recprob[2][0], :2286
+	const double s01 = rs, s00 = 1.0 - 2.0 * rs;                   // selfprec, :2319-2325
+	const double s10 = selfgen ? s01 * 2.0 / (double)((1 << selfgen) - 1) : 1.0;
+	const double s12 = s10 * s01, s11 = 1.0 - s10 - s12;
+#pragma unroll
+	for (int h = 0; h < 2; h++)
+	{
+		const double a = p[h], b = p[2 + h], c = p[4 + h];
+		p[h] = a * s00 + b * s10 + c * s10;
+		p[2 + h] = a * s01 + b * s11 + c * s12;
+		p[4 + h] = a * s01 + b * s12 + c * s11;
+		p[6 + h] = 0;
+	}
+}
+
 constexpr double MINFACTOR_D = (double)(float)-1e15;  // settings.h:29, a float constant
 
 // adjustprobs (cnF2freq.cpp:1579-1670) for one warp = one shift mode, all orientations summed (flag2 = -1).
-__device__ __forceinline__ void emit_step(const Ctx& c, int t, int lane, int shift, double& p0, double& p1, double& F)
+template <bool SELF, int NP>  // NP states per lane: state k of the lane is lane + 32 k
+__device__ __forceinline__ void emit_step(const Ctx& c, int t, int lane, int shift, double (&p)[NP], double& F)
 {
-	if (p0 < 1e-300) p0 = 0;
-	else p0 *= track<0, 4>(c, 0, UNKNOWN, 0.0, t, (unsigned)(lane * 2), -1, shift, 0.0);
-	if (p1 < 1e-300) p1 = 0;
-	else p1 *= track<0, 4>(c, 0, UNKNOWN, 0.0, t, (unsigned)((lane + 32) * 2), -1, shift, 0.0);
-	const double sum = warp_sum(p0 + p1);
+	double part = 0;
+#pragma unroll
+	for (int k = 0; k < NP; k++)
+	{
+		if (p[k] < 1e-300) p[k] = 0;
+		else p[k] *= track<0, 4, SELF>(c, 0, UNKNOWN, 0.0, t, (unsigned)((lane + 32 * k) * 2), -1, shift, 0.0);
+		part += p[k];
+	}
+	const double sum = warp_sum(part);
 	if (sum <= 0) F = MINFACTOR_D;
 	else
 	{
-		p0 /= sum;
-		p1 /= sum;
+#pragma unroll
+		for (int k = 0; k < NP; k++) p[k] /= sum;
 		F += log(sum);
 	}
 }
 
-__device__ __forceinline__ void load_tile(Smem& sm, const EstepArgs& a, int m0, int tid)
+template <int NS>
+__device__ __forceinline__ void load_tile(SmemT<NS>& sm, const EstepArgs& a, int m0, int tid)
 {
 	for (int i = tid; i < NSLOTS * TILE; i += NTHREADS)
 	{
@@ -131,6 +171,7 @@ __device__ __forceinline__ void load_tile(Smem& sm, const EstepArgs& a, int m0, 
 
 // ignoreflag2, cnF2freq.cpp:3462-3496, rules 2 and 3 (rule 1 is applied by enumerating only the
 // orientations outside flag2ignore).  hom bit i = relative i is "homozygous with equal sureness" here.
+template <bool SELF>
 __device__ __forceinline__ bool ignored(const Unit& u, int hom, int flag2, int g, int shift)
 {
 	const int x = flag2 ^ (g << 1);
@@ -140,7 +181,7 @@ __device__ __forceinline__ bool ignored(const Unit& u, int hom, int flag2, int g
 		if (!filt) continue;
 		const int filtered = x & filt;
 		if (filtered && filtered != filt) return true;
-		if (((hom >> i) & 1) && !((filtered != 0) ^ ((shift & u.relshift[i]) != 0))) return true;
+		if (!SELF && ((hom >> i) & 1) && !((filtered != 0) ^ ((shift & u.relshift[i]) != 0))) return true;  // rule 3: off under SELFING (:3489)
 	}
 	return false;
 }
@@ -198,6 +239,7 @@ __device__ __forceinline__ void transfer_stats(const EstepArgs& a, const Unit& u
 // One surviving (state g, shift, orientation flag2) term of the posterior loop, cnF2freq.cpp:5464-5577:
 // its weight val = exp(doanalyze(classicstop(marker, g), flag2) - factor) and the scatter of val into the
 // accumulator columns (haplos via updatehaplo, infprobs via the four GENOS calls, homozyg).
+template <bool SELF>
 __device__ __forceinline__ void posterior_term(const Ctx& c, int t, int g, int flag2, int shift, double am, double bm,
                                                double Fm, double B, double factor, float minfactor)
 {
@@ -209,7 +251,7 @@ __device__ __forceinline__ void posterior_term(const Ctx& c, int t, int g, int f
 		double v = 0;
 		if (!(am < 1e-300))
 		{
-			e = track<0, 4>(c, 0, UNKNOWN, 0.0, t, (unsigned)(g * 2), flag2, shift, 0.0);
+			e = track<0, 4, SELF>(c, 0, UNKNOWN, 0.0, t, (unsigned)(g * 2), flag2, shift, 0.0);
 			v = am * e;
 		}
 		lp += (v <= 0) ? MINFACTOR_D : log(v);
@@ -227,31 +269,41 @@ __device__ __forceinline__ void posterior_term(const Ctx& c, int t, int g, int f
 #pragma unroll
 	for (int side = 0; side < 2; side++)  // :5519-5529
 	{
-		sv[side][0] = track<U_GENOSPROBE, 4>(c, 0, 1, 0.0, t, (unsigned)(g * 2 + side), flag2 ^ side, shift, 0.0);
-		sv[side][1] = track<U_GENOSPROBE, 4>(c, 0, 2, 0.0, t, (unsigned)(g * 2 + side), flag2 ^ side, shift, 0.0);
+		sv[side][0] = track<U_GENOSPROBE, 4, SELF>(c, 0, 1, 0.0, t, (unsigned)(g * 2 + side), flag2 ^ side, shift, 0.0);
+		sv[side][1] = track<U_GENOSPROBE, 4, SELF>(c, 0, 2, 0.0, t, (unsigned)(g * 2 + side), flag2 ^ side, shift, 0.0);
 		svs[side] = sv[side][0] + sv[side][1];
 	}
 #pragma unroll
 	for (int al = 0; al < 2; al++)  // :5532-5537
-		hz[al] = track<U_HOMOZYGOUS, 4>(c, 0, al + 1, 0.0, t, (unsigned)(g * 2), flag2, shift, 0.0);
+		hz[al] = track<U_HOMOZYGOUS, 4, SELF>(c, 0, al + 1, 0.0, t, (unsigned)(g * 2), flag2, shift, 0.0);
 	// updatehaplo, :1561-1575 (its first, update-free call is the emission above)
-	if (e != 0) track<U_HAPLOS, 4>(c, 0, UNKNOWN, 0.0, t, (unsigned)(g * 2), flag2, shift, val);
+	if (e != 0) track<U_HAPLOS, 4, SELF>(c, 0, UNKNOWN, 0.0, t, (unsigned)(g * 2), flag2, shift, val);
 #pragma unroll
 	for (int side = 0; side < 2; side++)  // :5560-5568
 #pragma unroll
 		for (int al = 0; al < 2; al++)
-			track<U_GENOS, 4>(c, 0, al + 1, 0.0, t, (unsigned)(g * 2 + side), flag2 ^ side, shift, val * sv[side][al] / svs[side]);
+			track<U_GENOS, 4, SELF>(c, 0, al + 1, 0.0, t, (unsigned)(g * 2 + side), flag2 ^ side, shift, val * sv[side][al] / svs[side]);
 #pragma unroll
 	for (int al = 0; al < 2; al++)  // :5571-5575
 		c.acc[(ACC_HZ + al) * NTHREADS] += val * hz[al] / svs[0];
 }
 
+template <bool SELF, int NP>
+__device__ __forceinline__ void step_over(double (&p)[NP], const EstepArgs& a, int m, int selfgen)
+{
+	if constexpr (SELF) transition_selfing(p, a.rec0[m], a.rec1[m], a.dist[m], a.genrec2, selfgen);
+	else transition(p[0], p[1], a.rec0[m], a.rec1[m]);
+}
+
+template <bool SELF>
 __global__ void __launch_bounds__(NTHREADS, 1) estep_kernel(EstepArgs a)
 {
+	constexpr int NS = SELF ? NUMTYPES_SELFING : NUMTYPES;  // states
+	constexpr int NP = NS / 32;                              // per lane: state k of the lane is lane + 32 k
 	extern __shared__ __align__(16) unsigned char smem_raw[];
-	Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
+	SmemT<NS>& sm = *reinterpret_cast<SmemT<NS>*>(smem_raw);
 	const int tid = threadIdx.x, lane = tid & 31, shift = tid >> 5;
-	double* const alpha = a.alpha + (size_t)blockIdx.x * a.Mc * (NUMSHIFTS * NUMTYPES);
+	double* const alpha = a.alpha + (size_t)blockIdx.x * a.Mc * (NUMSHIFTS * NS);
 	double* const alphafac = a.alphafac + (size_t)blockIdx.x * a.Mc * NUMSHIFTS;
 	Ctx c{ sm.A, sm.S, sm.HW, sm.unit.row, sm.unit.founder, sm.acc + tid };
 	const int Mc = a.Mc, E = Mc - 1;
@@ -277,7 +329,18 @@ __global__ void __launch_bounds__(NTHREADS, 1) estep_kernel(EstepArgs a)
 		const bool active = shift < u.shiftend && !(shift & u.shiftignore);
 
 		// ---- forward sweep: initfwbw + realanalyze<STORE|FORWARD> (cnF2freq.cpp:2086-2107) ----
-		double p0 = 1.0 / NUMTYPES, p1 = 1.0 / NUMTYPES, F = 0;  // EVENGEN, :2100-2104
+		double p[NP], F = 0;
+		const int selfgen = SELF ? u.selfgen : 0;
+#pragma unroll
+		for (int k = 0; k < NP; k++)
+		{
+			p[k] = 1.0 / NS;  // EVENGEN, :2100-2104
+			if constexpr (SELF)  // selfingfactors, :2092-2099
+			{
+				const double f0 = 1.0 / (double)(1 << selfgen);
+				p[k] *= (k >> 1) == 0 ? f0 : (k >> 1) == 3 ? 0.0 : (1.0 - f0) * 0.5;
+			}
+		}
 		double L = 0;
 		for (int tile = 0; tile < ntiles; tile++)
 		{
@@ -289,19 +352,22 @@ __global__ void __launch_bounds__(NTHREADS, 1) estep_kernel(EstepArgs a)
 			for (int t = 0; t < tend; t++)
 			{
 				const int m = tile * TILE + t;
-				double* dst = alpha + ((size_t)m * NUMSHIFTS + shift) * NUMTYPES;
-				dst[lane] = p0;
-				dst[lane + 32] = p1;
+				double* dst = alpha + ((size_t)m * NUMSHIFTS + shift) * NS;
+#pragma unroll
+				for (int k = 0; k < NP; k++) dst[lane + 32 * k] = p[k];
 				if (lane == 0) alphafac[(size_t)m * NUMSHIFTS + shift] = F;
-				emit_step(c, t, lane, shift, p0, p1, F);
-				if (m < E) transition(p0, p1, a.rec0[m], a.rec1[m]);
+				emit_step<SELF>(c, t, lane, shift, p, F);
+				if (m < E) step_over<SELF>(p, a, m, selfgen);
 			}
 		}
 		if (active)
 		{
 			// doanalyze/quickanalyze with NONESTOP (:1984-2018): alpha+ at the last marker against beta = 1
 			L = F;
-			const double sum = warp_sum(p0 + p1);
+			double part = 0;
+#pragma unroll
+			for (int k = 0; k < NP; k++) part += p[k];
+			const double sum = warp_sum(part);
 			if (sum <= 0) L = MINFACTOR_D;
 			else L -= log(1.0 / sum);
 			if (lane == 0) sm.Ls[shift] = L;
@@ -332,7 +398,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) estep_kernel(EstepArgs a)
 		const int allowed = (NUMPATHS - 1) & ~u.flag2ignore;
 
 		// ---- backward sweep fused with the posterior enumeration (cnF2freq.cpp:2109-2116, 5406-5583) ----
-		double b0 = 1.0, b1 = 1.0, B = 0;  // :2111-2114
+		double b[NP], B = 0;  // :2111-2114
+#pragma unroll
+		for (int k = 0; k < NP; k++) b[k] = 1.0;
 		for (int tile = ntiles - 1; tile >= 0; tile--)
 		{
 			__syncthreads();
@@ -342,21 +410,25 @@ __global__ void __launch_bounds__(NTHREADS, 1) estep_kernel(EstepArgs a)
 			for (int t = tend - 1; t >= 0; t--)
 			{
 				const int m = tile * TILE + t;
-				const double* src = alpha + ((size_t)m * NUMSHIFTS + shift) * NUMTYPES;
+				const double* src = alpha + ((size_t)m * NUMSHIFTS + shift) * NS;
 				const double Fm = alphafac[(size_t)m * NUMSHIFTS + shift];
 				// beta of this shift mode, readable by every lane of the warp (and, for the turns, by the other warps)
-				sm.beta[shift * NUMTYPES + lane] = b0;
-				sm.beta[shift * NUMTYPES + lane + 32] = b1;
+#pragma unroll
+				for (int k = 0; k < NP; k++) sm.beta[shift * NS + lane + 32 * k] = b[k];
 				// ---- turn scoring (cnF2freq.cpp:5668-5757, DOTOULBAR 0) and updatenegshifts (:3640-3715) ----
 				{
-					double a0 = 0, a1 = 0, Fp = 0;
+					double ap[NP], Fp = 0;
+#pragma unroll
+					for (int k = 0; k < NP; k++) ap[k] = 0;
 					if (active)
 					{
-						a0 = src[lane], a1 = src[lane + 32], Fp = Fm;
-						emit_step(c, t, lane, shift, a0, a1, Fp);  // alpha+ and its factor: pad 2 of fwbw (:2248-2251)
+#pragma unroll
+						for (int k = 0; k < NP; k++) ap[k] = src[lane + 32 * k];
+						Fp = Fm;
+						emit_step<SELF>(c, t, lane, shift, ap, Fp);  // alpha+ and its factor: pad 2 of fwbw (:2248-2251)
 					}
-					sm.aplus[shift * NUMTYPES + lane] = a0;
-					sm.aplus[shift * NUMTYPES + lane + 32] = a1;
+#pragma unroll
+					for (int k = 0; k < NP; k++) sm.aplus[shift * NS + lane + 32 * k] = ap[k];
 					if (lane == 0) sm.Bs[shift] = B, sm.Fp[shift] = Fp;
 					__syncthreads();
 					const float minfturn = (float)(-50000.0 + factor);
@@ -371,8 +443,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) estep_kernel(EstepArgs a)
 							double fac = sm.Fp[shift];
 							if (!(fac < minfturn))
 							{
-								const double sum = warp_sum(sm.aplus[shift * NUMTYPES + (lane ^ mask)] * sm.beta[s2 * NUMTYPES + lane] +
-								                            sm.aplus[shift * NUMTYPES + ((lane + 32) ^ mask)] * sm.beta[s2 * NUMTYPES + lane + 32]);
+								double part = 0;  // the turn permutes the meiosis bits only (:506, 536: i ^ turn)
+#pragma unroll
+								for (int k = 0; k < NP; k++)
+									part += sm.aplus[shift * NS + ((lane + 32 * k) ^ mask)] * sm.beta[s2 * NS + lane + 32 * k];
+								const double sum = warp_sum(part);
 								fac += sm.Bs[s2];
 								if (sum <= 0) fac = MINFACTOR_D;
 								else fac -= log(1.0 / sum);
@@ -426,17 +501,17 @@ __global__ void __launch_bounds__(NTHREADS, 1) estep_kernel(EstepArgs a)
 					}
 					// The surviving (g, flag2) pairs are sparse and differ from lane to lane, so they are first
 					// compacted into a per-warp queue (ballot + prefix count) and then handed out one per lane.
-					unsigned short* q = sm.queue + shift * 64;
+					unsigned short* q = sm.queue + shift * 64;  // entries: flag2 << 8 | g
 					int cnt = 0;
 					for (int flag2 = allowed;; flag2 = (flag2 - 1) & allowed)
 					{
 #pragma unroll
-						for (int gi = 0; gi < 2; gi++)
+						for (int gi = 0; gi < NP; gi++)
 						{
 							const int g = lane + 32 * gi;
-							const bool ok = !ignored(u, hom, flag2, g, shift);
+							const bool ok = !ignored<SELF>(u, hom, flag2, g, shift);
 							const unsigned mask = __ballot_sync(0xffffffffu, ok);
-							if (ok) q[cnt + __popc(mask & ((1u << lane) - 1u))] = (unsigned short)((flag2 << 6) | g);
+							if (ok) q[cnt + __popc(mask & ((1u << lane) - 1u))] = (unsigned short)((flag2 << 8) | g);
 							cnt += __popc(mask);
 							__syncwarp();
 							if (cnt >= 32)
@@ -444,8 +519,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) estep_kernel(EstepArgs a)
 								cnt -= 32;
 								const int entry = q[cnt + lane];
 								__syncwarp();
-								posterior_term(c, t, entry & 63, entry >> 6, shift, src[entry & 63], sm.beta[shift * NUMTYPES + (entry & 63)],
-								               Fm, B, factor, minfactor);
+								posterior_term<SELF>(c, t, entry & 255, entry >> 8, shift, src[entry & 255], sm.beta[shift * NS + (entry & 255)],
+								                     Fm, B, factor, minfactor);
 							}
 						}
 						if (flag2 == 0) break;
@@ -453,8 +528,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) estep_kernel(EstepArgs a)
 					if (lane < cnt)
 					{
 						const int entry = q[lane];
-						posterior_term(c, t, entry & 63, entry >> 6, shift, src[entry & 63], sm.beta[shift * NUMTYPES + (entry & 63)], Fm,
-						               B, factor, minfactor);
+						posterior_term<SELF>(c, t, entry & 255, entry >> 8, shift, src[entry & 255], sm.beta[shift * NS + (entry & 255)], Fm,
+						                     B, factor, minfactor);
 					}
 					__syncwarp();
 				}
@@ -479,8 +554,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) estep_kernel(EstepArgs a)
 				// beta for the previous marker: adjustprobs at m, then the transition (:2390-2396)
 				if (m > 0)  // every shift mode: a turn pairs alpha+ of one mode with beta of another (initfwbw(..., 2), :1988)
 				{
-					emit_step(c, t, lane, shift, b0, b1, B);
-					transition(b0, b1, a.rec0[m - 1], a.rec1[m - 1]);
+					emit_step<SELF>(c, t, lane, shift, b, B);
+					step_over<SELF>(b, a, m - 1, selfgen);
 				}
 			}
 		}

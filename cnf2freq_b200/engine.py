@@ -90,10 +90,13 @@ def _buf(a, dtype, size, what):
 class Engine:
     """One engine = one GPU (one rank).  Method names follow the C ABI."""
 
-    def __init__(self, device=0, ctas_per_sm=0, async_params=False, in_flight=0, segment=0):
+    def __init__(self, device=0, ctas_per_sm=0, async_params=False, in_flight=0, segment=0, selfing=False):
+        """selfing: the reference's compile-time knob SELFING (settings.h:14) -- 256 states, PlantImpute lines listed with a
+        generation above 2 (demo.sh:18-20); every unit then runs through the literal kernel."""
         self.lib = load_library()
         s = Settings()
         self.lib.cnf2_default_settings(ctypes.byref(s))
+        s.selfing = 1 if selfing else 0
         s.device = device
         s.ctas_per_sm = ctas_per_sm
         s.async_params = 1 if async_params else 0

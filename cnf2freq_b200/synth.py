@@ -48,6 +48,20 @@ def simulate_f2(n_f2, n_chrom, markers_per_chrom, spacing_cM=0.1, missing=0.2, s
     return dict(names=names, ped=ped, tokens=tokens, markerpos=pos, chromstarts=cs)
 
 
+def simulate_selfed_lines(n, n_chrom, markers_per_chrom, spacing_cM, seed, gens, missing=0.2):
+    """PlantImpute lines for the SELFING = true instantiation (demo.sh:18-20): an F2 cross whose line k is listed with pedigree
+    generation gens[k] >= 2, i.e. selfed gens[k] - 2 times behind the listed pedigree; a heterozygous call survives each selfing
+    with probability 1/2."""
+    sim = simulate_f2(n_f2=n, n_chrom=n_chrom, markers_per_chrom=markers_per_chrom, spacing_cM=spacing_cM, missing=missing, seed=seed)
+    rng = np.random.default_rng(seed)
+    sim["ped"] = sim["ped"][:2] + [(me, fa, mo, g) for (me, fa, mo, _), g in zip(sim["ped"][2:], gens)]
+    for k, g in enumerate(gens):
+        row = sim["tokens"][2 + k]
+        fix = (row == 1) & (rng.random(row.shape) > 0.5 ** (g - 2))
+        row[fix] = rng.choice([0, 2], size=int(fix.sum()))
+    return sim
+
+
 def simulate_fullsib(n_fam, n_off, n_chrom, markers_per_chrom, spacing_cM=0.02, missing=0.05, seed=4):
     """cfg4: per family 4 founders (gen 0, i.i.d. alleles), 2 parents (gen 1), n_off offspring (gen 2)."""
     rng = np.random.default_rng(seed)

@@ -18,7 +18,13 @@
 
 namespace
 {
-constexpr int UNKNOWN = 0, SEXMARKER = 9, NUMTYPES = 64, NUMPATHS = 128;
+#ifndef CNF2_ORACLE_SELFING
+#define CNF2_ORACLE_SELFING 0
+#endif
+// -DCNF2_ORACLE_SELFING=1: the SELFING = true instantiation (settings.h:14; row g1), see cnf2_oracle.cpp
+constexpr bool SELFING = CNF2_ORACLE_SELFING;
+constexpr int TYPEBITS = 6, SELFMASK = 3;
+constexpr int UNKNOWN = 0, SEXMARKER = 9, NUMTYPES = SELFING ? 256 : 64, NUMPATHS = 128;
 
 struct Pre
 {
@@ -52,8 +58,12 @@ double track(const Pre& P, int zp, int ind, int inval, double secondval, int m, 
 {
 	const bool rootgen = genwidth == 4;
 	const bool attopnow = genwidth == 1 || P.founder[ind];
-	const int A[2] = { P.al[((size_t)ind * P.M + m) * 2], P.al[((size_t)ind * P.M + m) * 2 + 1] };
-	const double S[2] = { P.su[((size_t)ind * P.M + m) * 2], P.su[((size_t)ind * P.M + m) * 2 + 1] };
+	const int A0[2] = { P.al[((size_t)ind * P.M + m) * 2], P.al[((size_t)ind * P.M + m) * 2 + 1] };
+	const double S0[2] = { P.su[((size_t)ind * P.M + m) * 2], P.su[((size_t)ind * P.M + m) * 2 + 1] };
+	int A[2] = { A0[0], A0[1] };
+	double S[2] = { S0[0], S0[1] };
+	const int selfval = (int)(flag >> (TYPEBITS + 1)) & SELFMASK;  // :1122
+	const bool selfingNOW = SELFING && rootgen && selfval;          // :1126
 	const double hw = P.hw[(size_t)ind * P.M + m];
 	int upflag2 = -1;
 	const int upflag = (int)(flag >> 1), upshift = localshift >> 1;
@@ -70,6 +80,24 @@ double track(const Pre& P, int zp, int ind, int inval, double secondval, int m, 
 	{
 		int f2n = flag2 & 1;
 		const int realf2n = f2n;
+		if (selfingNOW)  // :1169-1190
+		{
+			const int selfindex = (selfval >> 1) ^ f2n;
+			A[0] = A[1] = UNKNOWN;
+			S[0] = S[1] = 0;
+			int first = A0[0];
+			if (!markermiss(0, first, A0[1]))
+			{
+				A[selfindex] = first;
+				S[selfindex] = 1 - (1 - S0[0]) * (1 - S0[1]);
+			}
+			else
+			{
+				A[selfindex] = A0[1];
+				if (S0[0] == 0) return 0;
+				S[selfindex] = 1 - (S0[0]) * (1 - S0[1]);
+			}
+		}
 		const bool allthesame = A[0] == A[1];
 		int markerval = inval;
 		double baseval, mainsecondval = 0;
@@ -92,7 +120,7 @@ double track(const Pre& P, int zp, int ind, int inval, double secondval, int m, 
 		else if (mainsecondval) mainsecondval /= baseval;
 		f2n ^= (firstpar ^ localshift) & 1;
 		if (zp || !genwidth) baseval *= 0.5;
-		else if (allthesame) baseval *= f2n ? 1.0 : 0.0;  // CORRECTIONINFERENCE, :1235
+		else if (allthesame || selfingNOW) baseval *= f2n ? 1.0 : 0.0;  // CORRECTIONINFERENCE, :1235
 		else baseval *= std::fabs((f2n ? 1.0 : 0.0) - hw);
 		if (baseval && !attopnow)
 		{

@@ -4,7 +4,7 @@ lines over the reference's own data structures) and its stdout progress lines, f
 (demo.sh:37, halfsibdemo) and two small synthetic pedigrees.  Single-threaded (deterministic).  Only runs where
 /root/reference exists; the outputs are committed.
 
-usage: python tests/golden/make_host_golden.py
+usage: python tests/golden/make_host_golden.py [selfing]      (selfing: only the SELFING = true run)
 """
 import os
 import subprocess
@@ -18,17 +18,26 @@ from cnf2freq_b200 import synth  # noqa: E402
 
 REF = os.environ.get("CNF2_REFERENCE_DIR", "/root/reference")
 BIN = os.path.join(ROOT, "oracle", "_ref", "cnf2ref")
+BIN_SELFING = os.path.join(ROOT, "oracle", "_ref", "cnf2ref_selfing")  # settings.h with SELFING = true (row g1)
 OUT = os.path.join(HERE, "host")
 
 
-def run(name, args, count):
+def run(name, args, count, binary=BIN):
     env = dict(os.environ, OMP_NUM_THREADS="1")
     sd = os.path.join(OUT, name + ".statedump")
-    r = subprocess.run([BIN] + args + ["--count", str(count), "--statedump", sd, "--quiet"], env=env, capture_output=True, text=True, check=True)
+    r = subprocess.run([binary] + args + ["--count", str(count), "--statedump", sd, "--quiet"], env=env, capture_output=True, text=True, check=True)
     keep = [l for l in r.stdout.splitlines() if l.startswith(("Correction at", "Fixing point", "Inv:", "Scale factor now")) or
             (l[:1].isdigit() and "," in l.split(":")[0])]
     open(os.path.join(OUT, name + ".stdout"), "w").write("\n".join(keep) + "\n")
     print(name, os.path.getsize(sd), "bytes,", len(keep), "progress lines")
+
+
+def main_selfing():
+    """Selfed PlantImpute lines (generation 2-6) through the reference built with SELFING = true."""
+    os.makedirs(OUT, exist_ok=True)
+    prefix = os.path.join(OUT, "selfing")
+    synth.write_alpha_files(prefix, synth.simulate_selfed_lines(6, 2, 14, 2.0, 25, [3, 4, 2, 6, 5, 4]))
+    run("selfing", ["--mapfile", prefix + ".map", "--pedfile", prefix + ".ped", "--genfile", prefix + ".gen"], 4, BIN_SELFING)
 
 
 def main():
@@ -43,4 +52,8 @@ def main():
 
 
 if __name__ == "__main__":
-    main()
+    if sys.argv[1:] == ["selfing"]:
+        main_selfing()
+    else:
+        main()
+        main_selfing()

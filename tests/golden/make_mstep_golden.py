@@ -5,7 +5,7 @@ inversions the reference applied in each pass (its "Inv: <id> <marker>" lines, c
 parameters + step-size scalars after doit().  mstep_demo / mstep_f2 hold iterations without inversions,
 mstep_inv_* iterations with them.  Only runs where /root/reference exists; the fixtures are committed.
 
-usage: python tests/golden/make_mstep_golden.py
+usage: python tests/golden/make_mstep_golden.py [selfing]     (selfing: only mstep_run_selfing, from oracle/_ref/cnf2ref_selfing)
 """
 import os
 import subprocess
@@ -23,6 +23,7 @@ from cnf2freq_b200 import synth  # noqa: E402
 
 REF = os.environ.get("CNF2_REFERENCE_DIR", "/root/reference")
 BIN = os.path.join(ROOT, "oracle", "_ref", "cnf2ref")
+BIN_SELFING = os.path.join(ROOT, "oracle", "_ref", "cnf2ref_selfing")  # settings.h with SELFING = true (row g1)
 
 
 def passes(stdout, C):
@@ -63,6 +64,20 @@ def collect(prefix, iterations, stdout=None, allow_inversions=False, stats=True)
             for k in ("haplobase", "haplocount", "infprobs", "homozyg"):
                 out[f"it{it}_c{c}_{k}"] = st[k]
     return out
+
+
+def main_selfing():
+    """mstep_run_selfing: 8 EM iterations of the SELFING = true build on selfed lines of generation 2-6."""
+    env = dict(os.environ, OMP_NUM_THREADS="1")
+    with tempfile.TemporaryDirectory() as tmp:
+        sim = synth.simulate_selfed_lines(10, 2, 30, 1.2, 23, [2, 3, 4, 5, 6, 3, 4, 2, 5, 4])
+        synth.write_alpha_files(tmp + "/sl", sim)
+        args = ["--mapfile", tmp + "/sl.map", "--pedfile", tmp + "/sl.ped", "--genfile", tmp + "/sl.gen"]
+        r = subprocess.run([BIN_SELFING] + args + ["--count", "9", "--dump", tmp + "/sl"], env=env, capture_output=True, text=True, check=True)
+        g = collect(tmp + "/sl", list(range(1, 9)), r.stdout, True, stats=False)
+        print("inversions per iteration:", [sum(len(g[f"it{it}_c{c}_inv"]) for c in range(2)) for it in range(1, 9)])
+        np.savez_compressed(os.path.join(HERE, "mstep_run_selfing.npz"), **g)
+    print("mstep_run_selfing.npz", os.path.getsize(os.path.join(HERE, "mstep_run_selfing.npz")), "bytes")
 
 
 def main():
@@ -107,4 +122,8 @@ def main():
 
 
 if __name__ == "__main__":
-    main()
+    if sys.argv[1:] == ["selfing"]:
+        main_selfing()
+    else:
+        main()
+        main_selfing()

@@ -141,7 +141,7 @@ def oracle_scalefactor(scalefactor, hitnnn, n_dous, oldhitnnn, oldhitnnn2):
     return float(sf), o1.value, o2.value
 
 
-def oracle_preprocess(chromstarts, par, exists, empty, alleles, sure, haploweight):
+def oracle_preprocess(chromstarts, par, exists, empty, alleles, sure, haploweight, selfing=False):
     """postmarkerdata (cnF2freq.cpp:3191-3412) on copies of the arrays as the readers left them.  Returns dict(alleles, sure,
     haploweight, descendants, children, founder, corrections)."""
     cs = np.ascontiguousarray(chromstarts, np.uint32)
@@ -150,8 +150,8 @@ def oracle_preprocess(chromstarts, par, exists, empty, alleles, sure, haploweigh
     c = lambda a, dt: np.array(a, dt, order="C", copy=True)
     al, su, hw = c(alleles, np.uint8), c(sure, np.float64), c(haploweight, np.float64)
     desc, ch, fo, n = np.zeros(K, np.int32), np.zeros(K, np.int32), np.zeros(K, np.uint8), ctypes.c_int32()
-    rc = lib().cnf2_oracle_preprocess(ctypes.c_int(K), ctypes.c_int(M), ctypes.c_int(len(cs) - 1), _p(cs), _p(par), _p(c(exists, np.uint8)),
+    rc = lib(selfing).cnf2_oracle_preprocess(ctypes.c_int(K), ctypes.c_int(M), ctypes.c_int(len(cs) - 1), _p(cs), _p(par), _p(c(exists, np.uint8)),
                                       _p(c(empty, np.uint8)), _p(al), _p(su), _p(hw), _p(desc), _p(ch), _p(fo), ctypes.byref(n))
     assert rc == 0
     return dict(alleles=al, sure=su, haploweight=hw, descendants=desc, children=ch, founder=fo, corrections=int(n.value),
-                cleared=int(lib().cnf2_oracle_preprocess_cleared()))
+                cleared=int(lib(selfing).cnf2_oracle_preprocess_cleared()))

@@ -38,10 +38,13 @@ def test_unsupported_settings_are_refused():
     lib = engine.load_library()
     s = engine.Settings()
     lib.cnf2_default_settings(ctypes.byref(s))
-    s.selfing = 1
+    s.relskewstates = 1  # (SELFING = true is an instantiation of its own since row g1: tests/test_selfing_gpu.py)
     h = ctypes.c_void_p()
     assert lib.cnf2_create(ctypes.byref(h), ctypes.byref(s)) == -5
-    assert b"SELFING" in lib.cnf2_last_error(None)
+    assert b"RELSKEWSTATES" in lib.cnf2_last_error(None)
+    lib.cnf2_default_settings(ctypes.byref(s))
+    s.numgen = 2
+    assert lib.cnf2_create(ctypes.byref(h), ctypes.byref(s)) == -5
 
 
 def test_no_cpu_fallback():

@@ -42,11 +42,15 @@ def test_oracle_preprocess_reproduces_the_reference_state(name, args):
     assert not np.array_equal(r["haploweight"], hw)  # phases were locked
 
 
-def test_oracle_preprocess_halfsib_dump():
-    cs, par, exists, empty, al, su, hw, inds = arrays(["--gigimapfile", HOST + "/refdata/halfsibdemo.map", "--gigipedfile",
-                                                       HOST + "/refdata/halfsibdemo.ped"])
-    r = ol.oracle_preprocess(cs, par, exists, empty, al, su, hw)
-    lines = [l for l in open(os.path.join(HOST, "halfsib.statedump")).read().splitlines() if l.strip()]
+@pytest.mark.parametrize("name,args,selfing", [
+    ("halfsib", ["--gigimapfile", HOST + "/refdata/halfsibdemo.map", "--gigipedfile", HOST + "/refdata/halfsibdemo.ped"], False),
+    # row g1: selfed lines through the reference built with SELFING = true (fixparents / addvariance then run over 256 states)
+    ("selfing", ["--mapfile", HOST + "/selfing.map", "--pedfile", HOST + "/selfing.ped", "--genfile", HOST + "/selfing.gen"], True),
+])
+def test_oracle_preprocess_against_the_iteration_0_dump(name, args, selfing):
+    cs, par, exists, empty, al, su, hw, inds = arrays(args)
+    r = ol.oracle_preprocess(cs, par, exists, empty, al, su, hw, selfing=selfing)
+    lines = [l for l in open(os.path.join(HOST, name + ".statedump")).read().splitlines() if l.strip()]
     M, k = hw.shape[1], 0
     for n in sorted(inds):
         assert lines[k].split() == [str(n), inds[n]["name"]]
