@@ -1941,7 +1941,8 @@ extern "C" int cnf2_preprocess(cnf2_engine* e, int32_t n_ind, const int32_t* par
 		for (;;)
 		{
 			PRE(upload());
-			pre_okmask_kernel<<<(unsigned)((cells + 127) / 128), 128, 0, e->stream>>>(pa, d_exists.p, d_ok.p);
+			if (e->selfing) pre_okmask_kernel<true><<<(unsigned)((cells + 127) / 128), 128, 0, e->stream>>>(pa, d_exists.p, d_ok.p);
+			else pre_okmask_kernel<false><<<(unsigned)((cells + 127) / 128), 128, 0, e->stream>>>(pa, d_exists.p, d_ok.p);
 			e->n_kernels++;
 			PRE(cudaGetLastError());
 			PRE(cudaMemcpyAsync(okmask.data(), d_ok.p, cells, cudaMemcpyDeviceToHost, e->stream));
@@ -2049,7 +2050,8 @@ extern "C" int cnf2_preprocess(cnf2_engine* e, int32_t n_ind, const int32_t* par
 	PRE(upload());
 	PRE(d_sq.ensure(cells * 8));
 	PRE(d_sum.ensure(cells * 8));
-	pre_variance_kernel<<<(unsigned)((cells * 8 + 127) / 128), 128, 0, e->stream>>>(pa, d_exists.p, d_ign.p, d_sq.p, d_sum.p);
+	if (e->selfing) pre_variance_kernel<true><<<(unsigned)((cells * 8 + 127) / 128), 128, 0, e->stream>>>(pa, d_exists.p, d_ign.p, d_sq.p, d_sum.p);
+	else pre_variance_kernel<false><<<(unsigned)((cells * 8 + 127) / 128), 128, 0, e->stream>>>(pa, d_exists.p, d_ign.p, d_sq.p, d_sum.p);
 	e->n_kernels++;
 	PRE(cudaGetLastError());
 	std::vector<double> psq(cells * 8), psum(cells * 8);

@@ -10,6 +10,8 @@
 // homozygous rule applies whatever the sureness (:1235).  Products and sums are written with the rounding intrinsics so
 // that no multiply-add is fused: addvariance's result decides by `>` which marker's phase is locked (:3058), and the
 // reference binary (x86-64, no FMA contraction) is the yardstick.
+// SELF: the SELFING = true instantiation (row g1): both scans run over 256 states, and the root's emission sees the selfing
+// bits of the flag (:1115-1127, :1169-1190) exactly as track<UPD, GW, true> does in the E-step.
 #pragma once
 #include "cnf2_device.cuh"
 
@@ -43,15 +45,19 @@ __device__ __forceinline__ bool pmiss(int& a, int b)
 
 // founders_upto: individ::founder is false for everybody while fixparents runs and becomes steady[j] when the
 // addvariance loop reaches individual j (its fixtrees call, :3377) -- single-threaded order, individuals by id
-template <int ZP, int GW>
+template <int ZP, int GW, bool SELF = false>
 __device__ double ptrack(const PreArgs& a, int ind, int m, int inval, double second, unsigned flag, int flag99, int localshift, int founders_upto)
 {
 	const bool rootgen = GW == 4;
 	const bool founder = ind <= founders_upto && a.steady[ind];
 	const bool attopnow = GW == 1 || founder;  // :1120
 	const size_t cell = (size_t)ind * a.M + m;
-	const uchar2 A = a.alleles[cell];
-	const double2 S = a.sure[cell];
+	uchar2 A = a.alleles[cell];
+	double2 S = a.sure[cell];
+	const uchar2 A0 = A;
+	const double2 S0 = S;
+	const int selfval = (SELF && GW == 4) ? (int)((flag >> (TYPEBITS + 1)) & SELFMASK) : 0;  // :1122
+	const bool selfingNOW = selfval != 0;                                                       // :1126
 	const double hw = a.hw[cell];
 	const int2 pars = a.par[ind];
 	int upflag2 = -1;
@@ -65,12 +71,36 @@ __device__ double ptrack(const PreArgs& a, int ind, int m, int inval, double sec
 		f2end = f2s + 1;
 	}
 	const int firstpar = flag & 1;
-	const bool allthesame = A.x == A.y;
+	bool allthesame = A.x == A.y;
 	double ok = 0;
 	for (int f2 = f2s; f2 < f2end; f2++)
 	{
 		int f2n = f2;
 		const int realf2n = f2;
+		if constexpr (SELF && GW == 4)
+		{
+			if (selfingNOW)  // :1169-1190
+			{
+				const int selfindex = (selfval >> 1) ^ f2;
+				int first = A0.x;
+				int mk;
+				double su;
+				if (!pmiss<0>(first, A0.y))
+				{
+					mk = first;
+					su = padd(1.0, -pmul(1.0 - S0.x, 1.0 - S0.y));
+				}
+				else
+				{
+					mk = A0.y;
+					if (S0.x == 0) return 0;  // :1186
+					su = padd(1.0, -pmul(S0.x, 1.0 - S0.y));
+				}
+				A = selfindex ? make_uchar2(UNKNOWN, (unsigned char)mk) : make_uchar2((unsigned char)mk, UNKNOWN);
+				S = selfindex ? make_double2(0.0, su) : make_double2(su, 0.0);
+				allthesame = A.x == A.y;
+			}
+		}
 		const int Af = f2 ? A.y : A.x, Ao = f2 ? A.x : A.y;
 		const double Sf = f2 ? S.y : S.x, So = f2 ? S.x : S.y;
 		int val = inval;
@@ -94,7 +124,7 @@ __device__ double ptrack(const PreArgs& a, int ind, int m, int inval, double sec
 		else if (main2 != 0) main2 = main2 / base;
 		f2n ^= (firstpar ^ localshift) & 1;  // :1227
 		if (ZP != 0) base = pmul(base, 0.5);  // :1229-1233 (genwidth is never 0 here)
-		else if (allthesame) base = pmul(base, f2n ? 1.0 : 0.0);  // :1235 with CORRECTIONINFERENCE true
+		else if (allthesame || selfingNOW) base = pmul(base, f2n ? 1.0 : 0.0);  // :1235 with CORRECTIONINFERENCE true
 		else base = pmul(base, fabs((f2n ? 1.0 : 0.0) - hw));    // :1245
 
 		if constexpr (GW > 1)
@@ -129,8 +159,10 @@ __device__ double ptrack(const PreArgs& a, int ind, int m, int inval, double sec
 
 // fixparents' scan (:1413-1430) for every (individual, marker): bit f of okmask = some (state i, orientation flag2 with
 // flag2 & 1 = f) has a non-zero emission at shift mode 0.  One thread per cell; the loops end as the reference's do.
+template <bool SELF>
 __global__ void __launch_bounds__(128) pre_okmask_kernel(PreArgs a, const uint8_t* __restrict__ exists, uint8_t* __restrict__ okmask)
 {
+	constexpr int NS = SELF ? NUMTYPES_SELFING : NUMTYPES;
 	const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (idx >= (size_t)a.K * a.M) return;
 	const int ind = (int)(idx / a.M), m = (int)(idx % a.M);
@@ -140,11 +172,11 @@ __global__ void __launch_bounds__(128) pre_okmask_kernel(PreArgs a, const uint8_
 		return;
 	}
 	bool ok0 = false, ok1 = false;
-	for (int i = 0; i < NUMTYPES && !(ok0 && ok1); i++)
+	for (int i = 0; i < NS && !(ok0 && ok1); i++)
 		for (int flag2 = 0; flag2 < NUMPATHS && !(ok0 && ok1); flag2++)
 		{
 			if ((flag2 & 1) ? ok1 : ok0) continue;
-			const double v = ptrack<0, 4>(a, ind, m, UNKNOWN, 0.0, (unsigned)(i * 2), flag2, 0, -1);
+			const double v = ptrack<0, 4, SELF>(a, ind, m, UNKNOWN, 0.0, (unsigned)(i * 2), flag2, 0, -1);
 			if (!(v != 0)) continue;  // `if (!ok) continue`: a NaN counts as found, as it does there
 			if (flag2 & 1) ok1 = true;
 			else ok0 = true;
@@ -155,9 +187,11 @@ __global__ void __launch_bounds__(128) pre_okmask_kernel(PreArgs a, const uint8_
 // addvariance (:1489-1558) for every (individual, marker): one thread per (cell, shift mode, majori, majorflag2) walks its
 // 64 x 64 (flag, orientation) pairs in the reference's order with the reference's running sums; the eight partial results
 // are combined in that order too.  flag2ignore: what fixtrees returns for the individual (absent / empty slots).
+template <bool SELF>
 __global__ void __launch_bounds__(128) pre_variance_kernel(PreArgs a, const uint8_t* __restrict__ exists, const uint8_t* __restrict__ flag2ignore,
                                                            double* __restrict__ part_sq, double* __restrict__ part_sum)
 {
+	constexpr int NS = SELF ? NUMTYPES_SELFING : NUMTYPES;
 	const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (tid >= (size_t)a.K * a.M * 8) return;
 	const size_t idx = tid >> 3;
@@ -170,13 +204,13 @@ __global__ void __launch_bounds__(128) pre_variance_kernel(PreArgs a, const uint
 		const uchar2 A = a.alleles[cell];
 		const double2 S = a.sure[cell];
 		const int ign = flag2ignore[ind];
-		for (int subi = 0, i = majori; subi < NUMTYPES * 2; subi += 2, i += 2)
+		for (int subi = 0, i = majori; subi < NS * 2; subi += 2, i += 2)
 			for (int flag2 = majorflag2; flag2 < NUMPATHS; flag2 += 2)
 			{
 				if (flag2 & ign) continue;
 				for (int allele = 0; allele < 2; allele++)
 				{
-					const double term = ptrack<-1, 4>(a, ind, m, allele ? A.y : A.x, allele ? S.y : S.x, (unsigned)i, flag2, shift, ind);
+					const double term = ptrack<-1, 4, SELF>(a, ind, m, allele ? A.y : A.x, allele ? S.y : S.x, (unsigned)i, flag2, shift, ind);
 					ok = padd(ok, pmul(term, allele ? 1.0 : -1.0));
 					fullok = padd(fullok, term);
 				}

@@ -5,7 +5,10 @@
 // statements of doit (:5189-6410) that a drop-in has to keep:
 //
 //   cnf2freq_gpu --mapfile M --pedfile P --genfile G [--gigimapfile M --gigipedfile P] --count N [--limit L]
-//                [--output FILE] [--tmppath DIR] [--deserialize FILE] [--parse-only]
+//                [--output FILE] [--tmppath DIR] [--deserialize FILE] [--parse-only] [--selfing]
+//
+// --selfing is the reference's compile-time knob SELFING (settings.h:14; lines listed with a generation above 2 are taken as
+// selfed from generation 2 down, demo.sh:18-20) as a run-time switch: the reference is rebuilt for it, this program is not.
 //
 // --output FILE receives what the reference writes there: the state dump after every iteration (:8157-8192) and the last
 // iteration's per-chromosome report; stdout carries the progress lines (likelihoods :5399-5401, "Inv:" :3450, "Scale
@@ -372,6 +375,7 @@ int main(int argc, char* argv[])
 {
 	std::string mapfn, pedfn, genfn, gigimap, gigiped, outfn, deserializefn, tmppath = ".";
 	int COUNT = 3, limit = INDCOUNT;  // :7961-7962
+	bool selfing = false;     // --selfing: settings.h:14 SELFING as a run-time switch
 	bool parse_only = false;  // read the inputs, print what the readers made of them (the dump format of :8157-8192), stop: no GPU needed
 	for (int i = 1; i < argc; i++)
 	{
@@ -391,7 +395,8 @@ int main(int argc, char* argv[])
 		else if (a == "--tmppath") tmppath = next();
 		else if (a == "--deserialize") deserializefn = next();
 		else if (a == "--parse-only") parse_only = true;
-		else die("unknown option %s (supported: --mapfile --pedfile --genfile --gigimapfile --gigipedfile --count --limit --output --tmppath --deserialize)", a.c_str());
+		else if (a == "--selfing") selfing = true;
+		else die("unknown option %s (supported: --mapfile --pedfile --genfile --gigimapfile --gigipedfile --count --limit --output --tmppath --deserialize --selfing)", a.c_str());
 	}
 	const int rank = getenv("RANK") ? atoi(getenv("RANK")) : 0, world = getenv("WORLD_SIZE") ? atoi(getenv("WORLD_SIZE")) : 1;
 	const int local_rank = getenv("LOCAL_RANK") ? atoi(getenv("LOCAL_RANK")) : rank;
@@ -459,6 +464,7 @@ int main(int argc, char* argv[])
 	cnf2_settings st;
 	cnf2_default_settings(&st);
 	st.device = local_rank;
+	st.selfing = selfing ? 1 : 0;  // settings.h:14
 	st.in_flight = C >= 3 ? 3 : 1;
 	cnf2_engine* eng = nullptr;
 	if (const int rc = cnf2_create(&eng, &st)) die("cnf2_create failed (%d): %s", rc, cnf2_last_error(nullptr));

@@ -60,6 +60,8 @@ CASES = {
     "halfsib": (["--gigimapfile", "halfsibdemo.map", "--gigipedfile", "halfsibdemo.ped"], 4, REFDATA, 1),
     "f2": (["--mapfile", "f2.map", "--pedfile", "f2.ped", "--genfile", "f2.gen"], 4, GOLD, 4),
     "fullsib": (["--mapfile", "fullsib.map", "--pedfile", "fullsib.ped", "--genfile", "fullsib.gen"], 4, GOLD, 1),
+    # row g1: selfed lines (generation 2-6) against the reference built with SELFING = true (oracle/_ref/cnf2ref_selfing)
+    "selfing": (["--mapfile", "selfing.map", "--pedfile", "selfing.ped", "--genfile", "selfing.gen", "--selfing"], 4, GOLD, 4),
 }
 
 
