@@ -44,11 +44,16 @@ typedef enum cnf2_status
 
 /* settings.h knobs that shape the state space (settings.h:3-47).  The kernels are instantiated for the
  * HEAD configuration: NUMGEN 3 (64 states, 128 orientations, 8 shift modes), SELFING false,
- * RELSKEWSTATES false, HAPLOTYPING true, DOINFPROBS true.  Anything else -> CNF2_ERR_UNSUPPORTED. */
+ * RELSKEWSTATES false, HAPLOTYPING true, DOINFPROBS true -- and for SELFING true (settings.h:7, 14, 21-27, 46: 256
+ * states = 64 x the value of two selfing bits, 192 valid; the PlantImpute mode of demo.sh:18-20, lines listed with a
+ * generation above 2).  In the reference SELFING is a compile-time constant; here it is chosen per engine.  Under SELFING
+ * every unit runs through the literal kernel (cnf2::estep_kernel<true>; the warp kernel is built for 64 states), every
+ * analysed individual needs generation 2..32 (1 << (gen - 2) of cnF2freq.cpp:2095, 2321), and cnf2_preprocess scans the
+ * 256 states.  Anything else (NUMGEN != 3, RELSKEWSTATES, !HAPLOTYPING, !DOINFPROBS) -> CNF2_ERR_UNSUPPORTED. */
 typedef struct cnf2_settings
 {
 	int32_t numgen;        /* settings.h:19  NUMGEN */
-	int32_t selfing;       /* settings.h:14  SELFING */
+	int32_t selfing;       /* settings.h:14  SELFING: 0 or 1 */
 	int32_t relskewstates; /* settings.h:16  RELSKEWSTATES */
 	int32_t haplotyping;   /* settings.h:36  HAPLOTYPING */
 	int32_t doinfprobs;    /* settings.h:12  DOINFPROBS */
