@@ -65,7 +65,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="f2", choices=["f2", "fullsib", "cfg5chrom"],
+    ap.add_argument("--workload", default="f2", choices=["f2", "fullsib", "cfg5chrom", "selfing"],
                     help="f2: BASELINE.json configs[2] (the bench workload); fullsib: configs[3]'s pedigree shape (families of 20 "
                          "offspring); cfg5chrom: one chromosome of configs[4]'s shape (biparental F2 families of 200 from 100 lines)")
     ap.add_argument("--individuals", type=int, default=None, help="analysed individuals per GPU")
@@ -83,7 +83,7 @@ def parse():
     return a
 
 
-SHAPES = {"f2": (2000, 10, 1000), "fullsib": (1320, 1, 2000), "cfg5chrom": (20000, 1, 5000)}
+SHAPES = {"f2": (2000, 10, 1000), "fullsib": (1320, 1, 2000), "cfg5chrom": (20000, 1, 5000), "selfing": (296, 1, 500)}
 
 
 def shape_of(a, workload):
@@ -100,6 +100,9 @@ def workload_name(workload, n, c, m):
     if workload == "cfg5chrom":
         return (f"synthetic PlantImpute-shaped chromosome: biparental F2 families of 200 from 100 inbred lines, {n} individuals x "
                 f"{c * m} markers ({c} chromosomes x {m}, 0.02 cM apart) per GPU, 20% missing")
+    if workload == "selfing":
+        return (f"SELFING = true (settings.h:14, 256 states, literal kernel): synthetic F2 lines listed at generation 4 (selfed twice), "
+                f"{n} individuals x {c * m} markers ({c} chromosomes x {m}) per GPU, 20% missing")
     return f"synthetic F2 intercross, {n} individuals x {c * m} markers ({c} chromosomes x {m}) per GPU, 20% missing"
 
 
@@ -413,6 +416,8 @@ def make_workload(a, workload, D, eng, pinned):
             s = synth.F2Shard(total, first, mine, C, mc, spacing_cM=0.02, missing=0.2, seed=5, lines=100, fam_size=200)
         else:
             s = synth.F2Shard(total, first, mine, C, mc, spacing_cM=0.1, missing=0.2, seed=3)
+            if workload == "selfing":  # the same cross, its lines listed two selfings further down (demo.sh:18-20)
+                s.gen[s.all_dous] = 4
         src = dict(par=s.par, empty=s.empty, founder=s.founder, gen=s.gen, descendants=s.descendants, dous=s.dous, all_dous=s.all_dous,
                    shared=s.shared, pos=s.pos, cs=s.cs, genrec=s.genrec, hasprior=s.hasprior, children=s.children)
         params, priors = s.params, s.priors
@@ -443,7 +448,7 @@ def run_workload(a, workload, D, steps, warmup, with_clocks):
     rank, world = D.rank, D.world
     n_chrom = shape_of(a, workload)[1]
     # three E-steps in flight (each with its own scratch and statistics block) once there are chromosomes to overlap
-    eng = Engine(device=D.local_rank, async_params=True, in_flight=3 if n_chrom >= 3 else 1)
+    eng = Engine(device=D.local_rank, async_params=True, in_flight=3 if n_chrom >= 3 else 1, selfing=workload == "selfing")
     w = make_workload(a, workload, D, eng, pinned)
     C, mc, R, P, Q, src = w["C"], w["mc"], w["R"], w["P"], w["Q"], w["src"]
     M = C * mc
@@ -482,7 +487,8 @@ def run_workload(a, workload, D, steps, warmup, with_clocks):
         eng.get_params_packed(c, *Pev[c])
     state = eng.get_em_state()
     ind_markers = w["n"] * M
-    states_per_step = len(src["all_dous"]) * M * NUMTYPES  # the whole job: every rank's analysed individuals
+    # the whole job: every rank's analysed individuals; 256 states under SELFING (settings.h:27)
+    states_per_step = len(src["all_dous"]) * M * (4 * NUMTYPES if workload == "selfing" else NUMTYPES)
 
     # ---- e2e: host buffers; upload of everything once + per iteration the read-back of every chromosome's parameters ----
     D.barrier(eng)
@@ -613,7 +619,7 @@ def ours(a, D):
     res = run_workload(a, a.workload, D, a.steps, a.warmup, True)
     extra = {}
     if world == 1 and not a.no_extra_configs and not a.explicit_shape and a.workload == "f2":
-        for wl in ("fullsib", "cfg5chrom"):
+        for wl in ("fullsib", "cfg5chrom", "selfing"):
             extra[wl] = run_workload(a, wl, D, max(2, min(3, a.steps)), 2, False)
     if rank == 0:
         peaks = measured_peaks()
@@ -634,6 +640,8 @@ def ours(a, D):
                            "e2e": {"value": x["states_per_step"] / x["e2e_s"], "ms_per_step": x["e2e_s"] * 1e3},
                            "frac": rf["frac"], "frac_isolated": rf["frac_isolated"], "launch_ms": rf["launch_ms"],
                            "launch_ms_isolated": rf["launch_ms_isolated"], "mstep_frac": rf["mstep"]["frac"], "inversions": x["inversions"]}
+            if wl == "selfing":  # every unit through the literal kernel estep_kernel<true>: no roofline model is claimed for it
+                configs[wl].update(frac=None, frac_isolated=None, kernel="cnf2::estep_kernel<true> (literal, one CTA per unit, 256 states)")
         line = {
             "metric": METRIC, "value": S / (res["step_ms"] * 1e-3), "unit": UNIT, "n_gpus": world, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": res["step_ms"], "higher_is_better": True, "scaling": "strong" if a.strong else "weak", "vs_baseline": None,

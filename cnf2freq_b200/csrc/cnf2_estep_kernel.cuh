@@ -509,7 +509,12 @@ __global__ void __launch_bounds__(NTHREADS, 1) estep_kernel(EstepArgs a)
 						for (int gi = 0; gi < NP; gi++)
 						{
 							const int g = lane + 32 * gi;
-							const bool ok = !ignored<SELF>(u, hom, flag2, g, shift);
+							// a state without forward or backward mass ends in posterior_term before it scatters anything (v = 0 resp.
+							// bm <= 0 put the term at MINFACTOR, 1e15 below an ordinary factor): not queued.  Under SELFING that is a
+							// quarter of the states at least.  Not so for a unit impossible under every shift mode, whose factor sits at
+							// MINFACTOR itself: there such terms pass the cut and the reference scatters them; they stay queued
+							const bool massless = factor > -1e14 && (src[g] < 1e-300 || !(sm.beta[shift * NS + g] > 0));
+							const bool ok = !massless && !ignored<SELF>(u, hom, flag2, g, shift);
 							const unsigned mask = __ballot_sync(0xffffffffu, ok);
 							if (ok) q[cnt + __popc(mask & ((1u << lane) - 1u))] = (unsigned short)((flag2 << 8) | g);
 							cnt += __popc(mask);

@@ -21,7 +21,18 @@
 
 namespace cnf2
 {
-constexpr int WB = 4;         // markers staged at a time
+// tuning knobs (compile-time; the defaults are the measured best, profiles/r2_summary.md)
+#ifndef CNF2_WB
+#define CNF2_WB 4
+#endif
+#ifndef CNF2_WARPS_PER_SM
+#define CNF2_WARPS_PER_SM 12
+#endif
+#ifndef CNF2_PAIR_UNROLL
+#define CNF2_PAIR_UNROLL 2
+#endif
+constexpr int WB = CNF2_WB;   // markers staged at a time
+constexpr int PAIR_UNROLL = CNF2_PAIR_UNROLL;
 constexpr int T0W = 3, T1W = 5;
 constexpr int NCOL = 8;       // accumulator columns; lanes scatter in 32 / NCOL passes
 constexpr int NACCP = NACC + 2; // column stride of the accumulators (doubles): 16-byte aligned pairs, columns on distinct banks
@@ -119,7 +130,7 @@ __device__ __forceinline__ void warp_posterior_pairs(WarpSmem& w, const Unit& u,
 		double Rx0 = 0, Ry0 = 0, Rx1 = 0, Ry1 = 0, Sx1 = 0, Sx2 = 0;
 		auto run = [&](int ja, int jb, double qa, double qb) {  // qa / qb: the other parent's weight at its shift bit 0 / 1
 			const double* T = Tp + (ja - jlo) * tw;
-#pragma unroll 2
+#pragma unroll PAIR_UNROLL
 			for (int j = ja; j < jb; j++, T += tw)
 			{
 				const int info = w.ainfo[j];
@@ -950,7 +961,7 @@ __host__ __device__ inline size_t warp_smem_bytes(int cap0, int cap1, int cls)
 // forward sweep over it from the checkpoint, filling the ring.  With seg >= Mc that is the plain store-everything
 // schedule (one segment, nothing recomputed); the host picks seg so that the ring fits its budget whatever Mc is.
 template <bool AGG>
-__global__ void __launch_bounds__(32, 12) warp_estep_kernel(WarpArgs wa)
+__global__ void __launch_bounds__(32, CNF2_WARPS_PER_SM) warp_estep_kernel(WarpArgs wa)
 {
 	extern __shared__ __align__(16) unsigned char smem_raw[];
 	WarpSmem& w = *reinterpret_cast<WarpSmem*>(smem_raw);

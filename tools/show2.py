@@ -13,4 +13,5 @@ for p in sys.argv[1:]:
         p, l["value"], l["ms_per_step"], l["e2e"]["value"], l["estep"]["value"], r["launch_ms"], r["launch_ms_isolated"], r["frac"],
         r["frac_isolated"], r["mstep"]["frac"], r["mstep"]["ms_per_iteration_beyond_esteps"]))
     for k, c in (l.get("configs") or {}).items():
-        print("   %s: value %.3e (%.1f ms) estep %.3e frac %.3f" % (k, c["value"], c["ms_per_step"], c["estep"]["value"], c["frac"]))
+        print("   %s: value %.3e (%.1f ms) estep %.3e frac %s" % (k, c["value"], c["ms_per_step"], c["estep"]["value"],
+                                                                 "%.3f" % c["frac"] if c["frac"] is not None else "n/a"))
