@@ -114,6 +114,7 @@ struct cnf2_engine
 	int n_states = NUMTYPES;    // 64, or 256 under SELFING (settings.h:27)
 	size_t literal_smem = 0;    // dynamic shared memory of the literal kernel's instantiation
 	DevBuf<double> d_dist;      // SELFING: distance to the next marker, laid out like the columns of d_rec's first half
+	size_t pre_literal_cells = 0;  // cnf2_preprocess: (individual, marker) cells whose addvariance sums the literal kernel evaluated
 	int seg_override = 0;       // CNF2_SEG: cap on the markers per segment of the warp kernel's alpha ring (experiments, tests)
 	size_t ring_budget = 0;     // CNF2_RING_MB: bytes the ring of one in-flight E-step may take (0: chosen at the first E-step)
 	size_t ring_budget_auto = 0;
@@ -2048,17 +2049,105 @@ extern "C" int cnf2_preprocess(cnf2_engine* e, int32_t n_ind, const int32_t* par
 	// lockhaplos (:3045-3079): the phase is locked at the marker of largest variance of each chromosome
 	for (size_t i = 1; i < K; i++) founder[i] = exists[i] ? steady[i] : 0;
 	PRE(upload());
-	PRE(d_sq.ensure(cells * 8));
-	PRE(d_sum.ensure(cells * 8));
-	if (e->selfing) pre_variance_kernel<true><<<(unsigned)((cells * 8 + 127) / 128), 128, 0, e->stream>>>(pa, d_exists.p, d_ign.p, d_sq.p, d_sum.p);
-	else pre_variance_kernel<false><<<(unsigned)((cells * 8 + 127) / 128), 128, 0, e->stream>>>(pa, d_exists.p, d_ign.p, d_sq.p, d_sum.p);
-	e->n_kernels++;
-	PRE(cudaGetLastError());
-	std::vector<double> psq(cells * 8), psum(cells * 8);
-	PRE(cudaMemcpyAsync(psq.data(), d_sq.p, cells * 8 * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
-	PRE(cudaMemcpyAsync(psum.data(), d_sum.p, cells * 8 * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
-	PRE(cudaStreamSynchronize(e->stream));
 	const size_t C = e->chromstarts.size() - 1;
+	// Which cells the literal sums are needed for.  SELFING: all of them (the factorised form is written for 64 states).
+	// Otherwise pre_variance_fast_kernel ranks the markers of every (individual, chromosome); only a marker within 1e-9 of the
+	// largest value can hold lockhaplos' strict maximum (the two forms differ by rounding, ~1e-15), and among markers with the
+	// same genotypes and sureness in the whole focus tree (equal signatures: bit-identical literal sums) only the first can.
+	// CNF2_PRE_LITERAL=1 forces the literal kernel everywhere (A/B switch of the tests).
+	const char* force_lit = getenv("CNF2_PRE_LITERAL");
+	const bool all_literal = e->selfing || (force_lit && force_lit[0] == '1');
+	std::vector<unsigned long long> list;
+	if (!all_literal)
+	{
+		DevBuf<double> d_rank;
+		DevBuf<unsigned long long> d_sig;
+		auto drop = [&]() { d_rank.release(), d_sig.release(); };
+		int rc = e->cuda(d_rank.ensure(cells), "cudaMalloc(rank)");
+		if (!rc) rc = e->cuda(d_sig.ensure(cells), "cudaMalloc(signatures)");
+		if (!rc)
+		{
+			pre_variance_fast_kernel<<<(unsigned)((cells + 127) / 128), 128, 0, e->stream>>>(pa, d_exists.p, d_ign.p, d_rank.p, d_sig.p);
+			e->n_kernels++;
+			rc = e->cuda(cudaGetLastError(), "pre_variance_fast_kernel");
+		}
+		std::vector<double> rank(cells);
+		std::vector<unsigned long long> sig(cells);
+		if (!rc) rc = e->cuda(cudaMemcpyAsync(rank.data(), d_rank.p, cells * sizeof(double), cudaMemcpyDeviceToHost, e->stream), "cudaMemcpy(rank)");
+		if (!rc) rc = e->cuda(cudaMemcpyAsync(sig.data(), d_sig.p, cells * sizeof(unsigned long long), cudaMemcpyDeviceToHost, e->stream), "cudaMemcpy(signatures)");
+		if (!rc) rc = e->cuda(cudaStreamSynchronize(e->stream), "cudaStreamSynchronize");
+		drop();
+		if (rc)
+		{
+			cleanup();
+			return rc;
+		}
+		std::vector<unsigned long long> seen;
+		for (size_t i = 1; i < K; i++)
+		{
+			if (!exists[i]) continue;
+			for (size_t c = 0; c < C; c++)
+			{
+				const size_t j0 = e->chromstarts[c], j1 = e->chromstarts[c + 1];
+				double best = 0;
+				bool noisy = false;
+				for (size_t j = j0; j < j1; j++)
+				{
+					const double v = std::fabs(rank[i * M + j]);
+					if (v > best) best = v, noisy = rank[i * M + j] < 0;
+				}
+				if (!(best > 0)) continue;  // every marker's two alleles give the same sums: no variance anywhere, nothing is locked
+				// a largest value at rounding-noise level ranks nothing: every marker with any variance is then evaluated literally
+				const double thr = noisy ? 0.0 : best * (1.0 - 1e-9);
+				seen.clear();
+				for (size_t j = j0; j < j1; j++)
+				{
+					const double v = std::fabs(rank[i * M + j]);
+					if (!(v > 0) || v < thr) continue;
+					const unsigned long long h = sig[i * M + j];
+					if (std::find(seen.begin(), seen.end(), h) != seen.end()) continue;
+					seen.push_back(h);
+					list.push_back((unsigned long long)(i * M + j));
+				}
+			}
+		}
+	}
+	const size_t n_eval = all_literal ? cells : list.size();
+	DevBuf<unsigned long long> d_list;
+	std::vector<double> psq(n_eval * 8), psum(n_eval * 8);
+	if (n_eval > 0)
+	{
+		PRE(d_sq.ensure(n_eval * 8));
+		PRE(d_sum.ensure(n_eval * 8));
+		if (!all_literal)
+		{
+			int rc = e->cuda(d_list.ensure(n_eval), "cudaMalloc(list)");
+			if (!rc) rc = e->cuda(cudaMemcpyAsync(d_list.p, list.data(), n_eval * sizeof(unsigned long long), cudaMemcpyHostToDevice, e->stream), "cudaMemcpy(list)");
+			if (rc)
+			{
+				d_list.release();
+				cleanup();
+				return rc;
+			}
+		}
+		const unsigned grid = (unsigned)((n_eval * 8 + 127) / 128);
+		if (e->selfing) pre_variance_kernel<true><<<grid, 128, 0, e->stream>>>(pa, d_exists.p, d_ign.p, d_sq.p, d_sum.p, nullptr, 0);
+		else pre_variance_kernel<false><<<grid, 128, 0, e->stream>>>(pa, d_exists.p, d_ign.p, d_sq.p, d_sum.p, all_literal ? nullptr : d_list.p, n_eval);
+		e->n_kernels++;
+		int rc = e->cuda(cudaGetLastError(), "pre_variance_kernel");
+		if (!rc) rc = e->cuda(cudaMemcpyAsync(psq.data(), d_sq.p, n_eval * 8 * sizeof(double), cudaMemcpyDeviceToHost, e->stream), "cudaMemcpy(sq)");
+		if (!rc) rc = e->cuda(cudaMemcpyAsync(psum.data(), d_sum.p, n_eval * 8 * sizeof(double), cudaMemcpyDeviceToHost, e->stream), "cudaMemcpy(sum)");
+		if (!rc) rc = e->cuda(cudaStreamSynchronize(e->stream), "cudaStreamSynchronize");
+		d_list.release();
+		if (rc)
+		{
+			cleanup();
+			return rc;
+		}
+	}
+	e->pre_literal_cells = n_eval;
+	// lockhaplos (:3045-3079): the first marker holding the strict maximum of the literal variances
+	size_t at = 0;  // position in list (ascending in (individual, marker))
 	for (size_t i = 1; i < K; i++)
 	{
 		if (!exists[i]) continue;
@@ -2066,13 +2155,16 @@ extern "C" int cnf2_preprocess(cnf2_engine* e, int32_t n_ind, const int32_t* par
 		{
 			long bestpos = -1;
 			double bestvar = 0;
-			for (size_t j = e->chromstarts[c]; j != e->chromstarts[c + 1]; j++)
-			{
+			auto consider = [&](size_t j, size_t slot) {
 				double sum = 0, sqsum = 0;
-				for (int k = 0; k < 8; k++) sum += psum[(i * M + j) * 8 + k], sqsum += psq[(i * M + j) * 8 + k];
+				for (int k = 0; k < 8; k++) sum += psum[slot * 8 + k], sqsum += psq[slot * 8 + k];
 				const double variance = sum ? sqsum : 0.0;  // `if (!sum) return` leaves the vector's zero (:1553)
 				if (variance > bestvar) bestpos = (long)j, bestvar = variance;
-			}
+			};
+			if (all_literal)
+				for (size_t j = e->chromstarts[c]; j != e->chromstarts[c + 1]; j++) consider(j, i * M + j);
+			else
+				for (; at < list.size() && list[at] < (unsigned long long)(i * M + e->chromstarts[c + 1]); at++) consider((size_t)(list[at] - i * M), at);
 			if (bestpos == -1) continue;
 			say(0, "Fixing point: %d %d %d\n", (int)i, (int)c + 1, (int)bestpos);
 			haploweight[i * M + bestpos] = haploweight[i * M + bestpos] <= 0.5 ? 0 : 1;
@@ -2081,6 +2173,11 @@ extern "C" int cnf2_preprocess(cnf2_engine* e, int32_t n_ind, const int32_t* par
 	cleanup();
 #undef PRE
 	return CNF2_OK;
+}
+
+extern "C" int64_t cnf2_preprocess_literal_cells(const cnf2_engine* e)
+{
+	return e ? (int64_t)e->pre_literal_cells : -1;
 }
 
 // ---- an entry point that allocates nothing (no counterpart in the reference) ----

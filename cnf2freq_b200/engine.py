@@ -22,7 +22,7 @@ SYMBOLS = [
     "cnf2_begin_iteration", "cnf2_mstep", "cnf2_get_params", "cnf2_get_negshift", "cnf2_get_negshift_packed",
     "cnf2_set_em_state", "cnf2_get_em_state", "cnf2_mstep_pass", "cnf2_negshift_minima", "cnf2_apply_inversions", "cnf2_em_pass",
     "cnf2_set_mstep_rows", "cnf2_set_mstep_chrom_packed", "cnf2_get_params_packed", "cnf2_estep_times", "cnf2_mstep_counters",
-    "cnf2_preprocess", "cnf2_negshift_minima_noalloc",
+    "cnf2_preprocess", "cnf2_negshift_minima_noalloc", "cnf2_preprocess_literal_cells",
 ]
 
 
@@ -239,6 +239,12 @@ class Engine:
             _buf(alleles, np.uint8, 2 * km, "preprocess alleles"), _buf(sure, np.float64, 2 * km, "preprocess sure"),
             _buf(haploweight, np.float64, km, "preprocess haploweight"), _ptr(desc), _ptr(children), _ptr(founder), cb, None))
         return desc, children, founder
+
+    def preprocess_literal_cells(self):
+        """(individual, marker) cells whose addvariance sums the last preprocess() walked term by term (cnf2_preprocess_literal_cells)."""
+        f = self.lib.cnf2_preprocess_literal_cells
+        f.restype = ctypes.c_int64
+        return int(f(self.h))
 
     # -- M-step on the device (rows a6 / f1) ---------------------------------------------------------
     def set_mstep_inputs(self, relhaplo, prioralleles, priorsure, hasprior, children, empty, descendants):

@@ -247,6 +247,14 @@ typedef void (*cnf2_log_fn)(void* ctx, int32_t stream, const char* line);
 int cnf2_preprocess(cnf2_engine* e, int32_t n_ind, const int32_t* parents, const uint8_t* exists, const uint8_t* empty,
                     uint8_t* alleles, double* sure, double* haploweight, int32_t* descendants, int32_t* children,
                     uint8_t* founder, cnf2_log_fn log, void* log_ctx);
+/* addvariance's 65,536 emission walks per (individual, marker) feed one decision only: which marker of a chromosome holds the
+ * largest variance (lockhaplos :3058, a strict `>`).  With SELFING false cnf2_preprocess therefore ranks the markers with the
+ * factorised form of those sums (~500 node evaluations per cell, equal up to rounding) and walks the literal sums, in the
+ * reference's order of operations, only for the markers that can hold the maximum: those within 1e-9 of the largest ranked
+ * value, one per distinct set of genotypes in the focus tree -- the decision is the literal one.  This returns how many
+ * (individual, marker) cells the last cnf2_preprocess evaluated literally (all of them under SELFING or with
+ * CNF2_PRE_LITERAL=1 in the environment); -1 for a NULL engine.  Replaces nothing in the reference (a diagnostic). */
+int64_t cnf2_preprocess_literal_cells(const cnf2_engine* e);
 
 /* Block until everything enqueued by this engine has finished; returns the first asynchronous error. */
 int cnf2_sync(cnf2_engine* e);

@@ -79,3 +79,41 @@ def test_preprocess_matches_the_oracle(maker, kw, impossible, selfing):
     assert sum(1 for st, l in lines if l.startswith("Clearing")) == ref["cleared"]
     if impossible:
         assert ref["cleared"] > 0, "no impossible genotype in this draw"
+
+
+@pytest.mark.parametrize("maker,kw,impossible", [
+    ("fullsib", dict(n_fam=3, n_off=4, n_chrom=2, mpc=40, seed=91), 0.0),
+    ("f2_cross", dict(n_f2=12, n_chrom=3, mpc=50, seed=92), 0.0),   # few distinct genotype patterns: many exact ties per chromosome
+    ("tangled", dict(n_chrom=2, mpc=35, seed=93), 0.05),
+])
+def test_factorised_ranking_gives_the_literal_decisions(monkeypatch, maker, kw, impossible):
+    """addvariance's sums only decide where lockhaplos locks the phase: cnf2_preprocess ranks the markers with the factorised
+    form and walks the literal sums for the few markers that can hold the maximum (include/cnf2_engine.h,
+    cnf2_preprocess_literal_cells).  Same locks, same lines as with the literal kernel on every cell (CNF2_PRE_LITERAL=1)."""
+    from cnf2freq_b200.engine import Engine
+    pb = getattr(randomped, maker)(**kw)
+    exists, al, su, hw = raw_inputs(pb, kw["seed"], impossible)
+    runs = {}
+    for mode in ("ranked", "literal"):
+        if mode == "literal":
+            monkeypatch.setenv("CNF2_PRE_LITERAL", "1")
+        else:
+            monkeypatch.delenv("CNF2_PRE_LITERAL", raising=False)
+        eng = Engine(device=0)
+        try:
+            eng.set_map(pb.markerpos, pb.chromstarts, pb.genrec)
+            a, s, h = al.copy(), su.copy(), hw.copy()
+            lines = []
+            out = eng.preprocess(pb.par, exists, pb.empty, a, s, h, log=lambda st, l: lines.append((st, l)))
+            runs[mode] = (a, s, h, out, lines, eng.preprocess_literal_cells())
+        finally:
+            eng.close()
+    r, l = runs["ranked"], runs["literal"]
+    assert np.array_equal(r[0], l[0]) and np.array_equal(r[1], l[1], equal_nan=True) and np.array_equal(r[2], l[2])
+    assert all(np.array_equal(x, y) for x, y in zip(r[3], l[3]))
+    assert r[4] == l[4]
+    assert sum(1 for st, line in r[4] if line.startswith("Fixing point")) > 0
+    cells = pb.K * pb.M
+    assert l[5] == cells
+    print(f"{maker}: literal sums walked for {r[5]} of {cells} cells")
+    assert 0 < r[5] <= 0.2 * cells
