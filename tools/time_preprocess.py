@@ -4,6 +4,7 @@ usage: python tools/time_preprocess.py N_F2 N_CHROM MARKERS_PER_CHROM [literal]"
 import os
 import sys
 import time
+import zlib
 
 import numpy as np
 
@@ -56,5 +57,6 @@ def log(st, line):
 eng.preprocess(par, exists, empty, al, su, hw, log=log)
 dt = time.perf_counter() - t0
 print(f"{'literal' if os.environ.get('CNF2_PRE_LITERAL') == '1' else 'ranked'}: {K} individuals x {M} markers ({C} x {mpc}): cnf2_preprocess {dt:.2f} s, "
-      f"literal sums for {eng.preprocess_literal_cells()} of {K * M} cells, {nfix[0]} phases locked")
+      f"literal sums for {eng.preprocess_literal_cells()} of {K * M} cells, {nfix[0]} phases locked, "
+      f"checksum of the locked phases {zlib.crc32(hw.tobytes()):08x}, of the genotypes {zlib.crc32(al.tobytes()):08x}")
 eng.close()
