@@ -95,3 +95,19 @@ def test_selfing_em_iterations_teacher_forced(eng):
 
 def test_selfing_em_pass_makes_the_reference_decisions(eng):
     eml.test_em_pass_makes_the_reference_decisions(eng, "mstep_run_selfing")
+
+
+def test_selfing_shards_sum_to_the_whole(eng):
+    """Two shards of the analysed individuals (what two ranks hold) add up to the unsharded statistics under SELFING too."""
+    pb = selfed(randomped.f2_cross(n_f2=6, n_chrom=1, mpc=17, seed=38), 38)
+    whole = run_engine(eng, pb)
+    keys = STATS + ("negshift",)
+    acc = {k: np.zeros_like(whole[k]) for k in keys}
+    for r in range(2):
+        engine_problem(eng, pb, dous=pb.dous[r::2], all_dous=pb.dous, shared=[1, 2])
+        part = eng.estep_all(pb.alleles, pb.sure, pb.haploweight)
+        for k in keys:
+            acc[k] += part[k]
+        assert_close(part["loglik"], whole["loglik"][r::2], "selfing shard loglik", rtol=1e-12)
+    for k in keys:
+        assert_close(acc[k], whole[k], f"selfing sharded:{k}", rtol=1e-12, atol=ATOL)
