@@ -240,9 +240,13 @@ class Dist:
             import torch.distributed as dist
             dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
             self.dist = dist
+            # a communicator of its own for the engine's control stream (include/cnf2_engine.h, cnf2_set_allreduce): the
+            # passes' one-double sums do not queue behind the statistics of the E-steps issued ahead
+            self.control_group = dist.new_group(backend="nccl")
 
-    def hook(self):
+    def hook(self, eng):
         torch, dist, dev = self.torch, self.dist, self.local_rank
+        control_stream, control_group = eng.control_stream(), self.control_group
 
         class DevBuf:  # zero-copy view of an engine buffer for torch.distributed
             def __init__(self, ptr, n):
@@ -251,7 +255,7 @@ class Dist:
         def allreduce(ptr, count, stream):
             with torch.cuda.stream(torch.cuda.ExternalStream(stream)):
                 t = torch.as_tensor(DevBuf(ptr, count), device=torch.device("cuda", dev))
-                dist.all_reduce(t, op=dist.ReduceOp.SUM)
+                dist.all_reduce(t, op=dist.ReduceOp.SUM, group=control_group if stream == control_stream else None)
         return allreduce
 
     def barrier(self, eng=None):
@@ -310,7 +314,7 @@ def parity_check(D):
         rows = np.array(mine, np.int64)
         eng = Engine(device=D.local_rank)
         if D.world > 1:
-            eng.set_allreduce(D.hook())
+            eng.set_allreduce(D.hook(eng))
         eng.set_map(pb.markerpos, pb.chromstarts, pb.genrec)
         eng.set_shared_rows(shared)
         eng.set_pedigree(pb.par, pb.empty, pb.founder, pb.gen, pb.descendants, shards[D.rank], pb.dous)
@@ -424,7 +428,7 @@ def make_workload(a, workload, D, eng, pinned):
     eng.set_map(src["pos"], src["cs"], src["genrec"])
     eng.set_shared_rows(src["shared"])
     if world > 1:
-        eng.set_allreduce(D.hook())
+        eng.set_allreduce(D.hook(eng))
     eng.set_pedigree(src["par"], src["empty"], src["founder"], src["gen"], src["descendants"], src["dous"], src["all_dous"])
     ids = eng.row_ids()
     R = len(ids)

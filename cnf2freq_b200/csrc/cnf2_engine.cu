@@ -73,7 +73,8 @@ struct cnf2_engine
 	cnf2_settings settings{};
 	std::string error;
 	cudaStream_t stream = nullptr;  // copies of parameters, marks, microbenchmarks
-	cudaStream_t comm = nullptr;    // the all-reduce hook runs here, in call order
+	cudaStream_t comm = nullptr;
+	cudaStream_t comm2 = nullptr;  // control stream: the small collectives of the M-step passes (hitnnn, phase-inversion minima)    // the all-reduce hook runs here, in call order
 	cudaStream_t side = nullptr;    // M-step: the relskew chains of a pass run here, beside processinfprobs
 	cudaEvent_t ms_fork = nullptr, ms_join = nullptr;
 	// M-step passes and phase inversions update parameters of several chromosomes from different streams: each waits for
@@ -254,6 +255,7 @@ extern "C" int cnf2_create(cnf2_engine** out, const cnf2_settings* settings)
 	e->n_sm = prop.multiProcessorCount;
 	if ((ce = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(ce, "cudaStreamCreate");
 	if ((ce = cudaStreamCreateWithFlags(&e->comm, cudaStreamNonBlocking)) != cudaSuccess) return bail(ce, "cudaStreamCreate");
+	if ((ce = cudaStreamCreateWithFlags(&e->comm2, cudaStreamNonBlocking)) != cudaSuccess) return bail(ce, "cudaStreamCreate");
 	if ((ce = cudaEventCreateWithFlags(&e->params_ready, cudaEventDisableTiming)) != cudaSuccess) return bail(ce, "cudaEventCreate");
 	{
 		int lo_prio = 0, hi_prio = 0;
@@ -338,6 +340,7 @@ extern "C" void cnf2_destroy(cnf2_engine* e)
 		if (sl.stream) cudaStreamDestroy(sl.stream);
 	}
 	if (e->comm) cudaStreamSynchronize(e->comm), cudaStreamDestroy(e->comm);
+	if (e->comm2) cudaStreamSynchronize(e->comm2), cudaStreamDestroy(e->comm2);
 	if (e->side) cudaStreamSynchronize(e->side), cudaStreamDestroy(e->side);
 	if (e->ms_fork) cudaEventDestroy(e->ms_fork);
 	if (e->ms_join) cudaEventDestroy(e->ms_join);
@@ -1150,10 +1153,12 @@ static int enqueue_pass(cnf2_engine* e, int32_t chrom, int any, int set, double 
 		ms_pack_kernel<<<1, 1, 0, sl.stream>>>(e->d_ctl.p);
 		e->n_kernels++;
 		CU(cudaEventRecord(sl.tail, sl.stream));
-		CU(cudaStreamWaitEvent(e->comm, sl.tail, 0));
-		const int rc = e->allreduce(e->allreduce_ctx, &e->d_ctl.p->hit_local_d, 1, (void*)e->comm);
+		// on the control stream: behind the statistics all-reduces of the E-steps issued ahead (e->comm) this one-double sum
+		// would wait for those E-steps to finish, and the next pass with it
+		CU(cudaStreamWaitEvent(e->comm2, sl.tail, 0));
+		const int rc = e->allreduce(e->allreduce_ctx, &e->d_ctl.p->hit_local_d, 1, (void*)e->comm2);
 		if (rc) return e->fail(CNF2_ERR_CUDA, "cnf2_mstep_pass: all-reduce hook failed");
-		CU(cudaEventRecord(sl.done, e->comm));
+		CU(cudaEventRecord(sl.done, e->comm2));
 		CU(cudaStreamWaitEvent(sl.stream, sl.done, 0));
 		reduced = 1;
 	}
@@ -1390,10 +1395,11 @@ extern "C" int cnf2_em_pass(cnf2_engine* e, int32_t chrom, int32_t* inv_ids, int
 		{
 			// rows only one rank holds: everybody else contributes zeros to the sum; shared rows are identical everywhere
 			CU(e->d_gmin.ensure(g.size()));
-			CU(cudaMemcpyAsync(e->d_gmin.p, g.data(), g.size() * sizeof(double), cudaMemcpyHostToDevice, e->comm));
-			if (e->allreduce(e->allreduce_ctx, e->d_gmin.p, g.size(), (void*)e->comm)) return e->fail(CNF2_ERR_CUDA, "cnf2_em_pass: all-reduce hook failed");
-			CU(cudaMemcpyAsync(g.data(), e->d_gmin.p, g.size() * sizeof(double), cudaMemcpyDeviceToHost, e->comm));
-			CU(cudaStreamSynchronize(e->comm));
+			// on the control stream (see cnf2_mstep_pass): the host waits for this exchange, not for the E-steps issued ahead
+			CU(cudaMemcpyAsync(e->d_gmin.p, g.data(), g.size() * sizeof(double), cudaMemcpyHostToDevice, e->comm2));
+			if (e->allreduce(e->allreduce_ctx, e->d_gmin.p, g.size(), (void*)e->comm2)) return e->fail(CNF2_ERR_CUDA, "cnf2_em_pass: all-reduce hook failed");
+			CU(cudaMemcpyAsync(g.data(), e->d_gmin.p, g.size() * sizeof(double), cudaMemcpyDeviceToHost, e->comm2));
+			CU(cudaStreamSynchronize(e->comm2));
 			for (int r = 0; r < e->n_shared; r++)
 				g[(size_t)e->rowid[r] * 2] = mv[r], g[(size_t)e->rowid[r] * 2 + 1] = (double)(Mc - ms[r]);
 		}
@@ -1655,6 +1661,11 @@ extern "C" int cnf2_elapsed_ms(cnf2_engine* e, int32_t from, int32_t to, float* 
 	CU(cudaEventSynchronize(e->marks[to]));
 	CU(cudaEventElapsedTime(ms, e->marks[from], e->marks[to]));
 	return CNF2_OK;
+}
+
+extern "C" void* cnf2_control_stream(cnf2_engine* e)
+{
+	return e ? (void*)e->comm2 : nullptr;
 }
 
 extern "C" void* cnf2_stream(cnf2_engine* e)

@@ -22,7 +22,7 @@ SYMBOLS = [
     "cnf2_begin_iteration", "cnf2_mstep", "cnf2_get_params", "cnf2_get_negshift", "cnf2_get_negshift_packed",
     "cnf2_set_em_state", "cnf2_get_em_state", "cnf2_mstep_pass", "cnf2_negshift_minima", "cnf2_apply_inversions", "cnf2_em_pass",
     "cnf2_set_mstep_rows", "cnf2_set_mstep_chrom_packed", "cnf2_get_params_packed", "cnf2_estep_times", "cnf2_mstep_counters",
-    "cnf2_preprocess", "cnf2_negshift_minima_noalloc", "cnf2_preprocess_literal_cells",
+    "cnf2_preprocess", "cnf2_negshift_minima_noalloc", "cnf2_preprocess_literal_cells", "cnf2_control_stream",
 ]
 
 
@@ -54,6 +54,8 @@ def load_library():
         lib.cnf2_last_error.argtypes = [ctypes.c_void_p]
         lib.cnf2_stream.restype = ctypes.c_void_p
         lib.cnf2_stream.argtypes = [ctypes.c_void_p]
+        lib.cnf2_control_stream.restype = ctypes.c_void_p
+        lib.cnf2_control_stream.argtypes = [ctypes.c_void_p]
         lib.cnf2_destroy.restype = None
         lib.cnf2_destroy.argtypes = [ctypes.c_void_p]
         lib.cnf2_default_settings.restype = None
@@ -150,6 +152,11 @@ class Engine:
         cb = ALLREDUCE_FN(tramp)
         self._keep.append(cb)
         self._check(self.lib.cnf2_set_allreduce(self.h, cb, None))
+
+    def control_stream(self):
+        """The cudaStream_t (int) the hook is called with for the M-step passes' small collectives (cnf2_control_stream): a
+        binding gives it a communicator of its own."""
+        return int(self.lib.cnf2_control_stream(self.h) or 0)
 
     def set_pedigree(self, parents, empty, founder, gen, descendants, dous, all_dous=None):
         parents = np.ascontiguousarray(parents, np.int32)

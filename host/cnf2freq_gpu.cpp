@@ -342,10 +342,12 @@ void log_line(void*, int32_t stream, const char* line)
 	} while (0)
 
 #ifdef CNF2_WITH_NCCL
-ncclComm_t g_comm;
+ncclComm_t g_comm, g_comm_control;  // one communicator per stream the engine calls the hook with (include/cnf2_engine.h)
+void* g_control_stream = nullptr;
 int nccl_hook(void*, double* buf, size_t count, void* stream)
 {
-	return ncclAllReduce(buf, buf, count, ncclDouble, ncclSum, g_comm, (cudaStream_t)stream) == ncclSuccess ? 0 : 1;
+	ncclComm_t comm = stream == g_control_stream ? g_comm_control : g_comm;
+	return ncclAllReduce(buf, buf, count, ncclDouble, ncclSum, comm, (cudaStream_t)stream) == ncclSuccess ? 0 : 1;
 }
 #endif
 
@@ -540,12 +542,12 @@ int main(int argc, char* argv[])
 #ifdef CNF2_WITH_NCCL
 		cudaSetDevice(local_rank);
 		const std::string idfile = getenv("CNF2_NCCL_ID_FILE") ? getenv("CNF2_NCCL_ID_FILE") : tmppath + "/cnf2_nccl_id";
-		ncclUniqueId id;
+		ncclUniqueId id[2];  // statistics communicator, control communicator
 		if (rank == 0)
 		{
-			if (ncclGetUniqueId(&id) != ncclSuccess) die("ncclGetUniqueId failed");
+			if (ncclGetUniqueId(&id[0]) != ncclSuccess || ncclGetUniqueId(&id[1]) != ncclSuccess) die("ncclGetUniqueId failed");
 			FILE* f = fopen((idfile + ".tmp").c_str(), "wb");
-			if (!f || fwrite(&id, sizeof(id), 1, f) != 1) die("cannot write %s", idfile.c_str());
+			if (!f || fwrite(id, sizeof(id), 1, f) != 1) die("cannot write %s", idfile.c_str());
 			fclose(f);
 			rename((idfile + ".tmp").c_str(), idfile.c_str());
 		}
@@ -553,11 +555,13 @@ int main(int argc, char* argv[])
 		{
 			FILE* f = nullptr;
 			for (int tries = 0; tries < 600 && !(f = fopen(idfile.c_str(), "rb")); tries++) usleep(100000);
-			if (!f || fread(&id, sizeof(id), 1, f) != 1) die("cannot read the NCCL id from %s", idfile.c_str());
+			if (!f || fread(id, sizeof(id), 1, f) != 1) die("cannot read the NCCL id from %s", idfile.c_str());
 			fclose(f);
 		}
-		if (ncclCommInitRank(&g_comm, world, id, rank) != ncclSuccess) die("ncclCommInitRank failed");
+		if (ncclCommInitRank(&g_comm, world, id[0], rank) != ncclSuccess) die("ncclCommInitRank failed");
+		if (ncclCommInitRank(&g_comm_control, world, id[1], rank) != ncclSuccess) die("ncclCommInitRank (control) failed");
 		if (rank == 0) remove(idfile.c_str());
+		g_control_stream = cnf2_control_stream(eng);
 		CK(cnf2_set_allreduce(eng, nccl_hook, nullptr));
 #else
 		die("built without NCCL (make -C host NCCL=1): WORLD_SIZE must be 1");

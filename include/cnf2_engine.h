@@ -120,9 +120,19 @@ int cnf2_estep(cnf2_engine* e, int32_t chrom);
  * individuals listed in cnf2_set_shared_rows (9 doubles per (row, marker): haplobase, haplocount,
  * infprobs[0][1], [0][2], [1][1], [1][2], homozyg[0], homozyg[1], negshift).  The hook must enqueue a sum-all-reduce
  * over `count` doubles in place on `cuda_stream` (e.g. ncclAllReduce / torch.distributed.all_reduce).  The
- * engine passes one and the same stream for every call, so collectives are issued in cnf2_estep call order. */
+ * engine passes one of two streams.  The statistics stream carries every E-step's all-reduce, in cnf2_estep call order.
+ * The control stream (cnf2_control_stream) carries the small sums of the block behind a chromosome -- hitnnn of
+ * cnf2_mstep_pass (one double), the phase-inversion minima of cnf2_em_pass (two doubles per individual) -- in call order
+ * as well.  The two are independent on purpose: behind the statistics of the E-steps issued ahead, a pass's one-double sum
+ * (and the host, in cnf2_em_pass) would wait for those E-steps to finish.  A binding therefore uses ONE COMMUNICATOR PER
+ * STREAM (a second ncclComm_t / torch.distributed.new_group for the control stream); with a single communicator the
+ * collectives of the two streams must be serialised by the binding (torch.distributed does that by itself), which is
+ * correct and only gives the overlap away.  Every rank calls the engine in the same order, so each communicator sees its
+ * collectives in the same order on every rank. */
 typedef int (*cnf2_allreduce_fn)(void* ctx, double* device_buf, size_t count, void* cuda_stream);
 int cnf2_set_allreduce(cnf2_engine* e, cnf2_allreduce_fn fn, void* ctx);
+/* The control stream the hook is called with for the M-step passes' collectives (a cudaStream_t); see above. */
+void* cnf2_control_stream(cnf2_engine* e);
 /* Individuals whose statistics rows receive contributions from more than one rank (e.g. the founders of
  * an F2 cross).  Must be the same list, in the same order, on every rank.  Call before cnf2_set_pedigree. */
 int cnf2_set_shared_rows(cnf2_engine* e, const int32_t* ids, int32_t n_ids);
