@@ -74,6 +74,7 @@ struct cnf2_engine
 	std::string error;
 	cudaStream_t stream = nullptr;  // copies of parameters, marks, microbenchmarks
 	cudaStream_t comm = nullptr;
+	cudaStream_t copy = nullptr;   // cnf2_get_params_packed_async: read-backs beside the kernels
 	cudaStream_t comm2 = nullptr;  // control stream: the small collectives of the M-step passes (hitnnn, phase-inversion minima)    // the all-reduce hook runs here, in call order
 	cudaStream_t side = nullptr;    // M-step: the relskew chains of a pass run here, beside processinfprobs
 	cudaEvent_t ms_fork = nullptr, ms_join = nullptr;
@@ -256,6 +257,7 @@ extern "C" int cnf2_create(cnf2_engine** out, const cnf2_settings* settings)
 	if ((ce = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(ce, "cudaStreamCreate");
 	if ((ce = cudaStreamCreateWithFlags(&e->comm, cudaStreamNonBlocking)) != cudaSuccess) return bail(ce, "cudaStreamCreate");
 	if ((ce = cudaStreamCreateWithFlags(&e->comm2, cudaStreamNonBlocking)) != cudaSuccess) return bail(ce, "cudaStreamCreate");
+	if ((ce = cudaStreamCreateWithFlags(&e->copy, cudaStreamNonBlocking)) != cudaSuccess) return bail(ce, "cudaStreamCreate");
 	if ((ce = cudaEventCreateWithFlags(&e->params_ready, cudaEventDisableTiming)) != cudaSuccess) return bail(ce, "cudaEventCreate");
 	{
 		int lo_prio = 0, hi_prio = 0;
@@ -341,6 +343,7 @@ extern "C" void cnf2_destroy(cnf2_engine* e)
 	}
 	if (e->comm) cudaStreamSynchronize(e->comm), cudaStreamDestroy(e->comm);
 	if (e->comm2) cudaStreamSynchronize(e->comm2), cudaStreamDestroy(e->comm2);
+	if (e->copy) cudaStreamSynchronize(e->copy), cudaStreamDestroy(e->copy);
 	if (e->side) cudaStreamSynchronize(e->side), cudaStreamDestroy(e->side);
 	if (e->ms_fork) cudaEventDestroy(e->ms_fork);
 	if (e->ms_join) cudaEventDestroy(e->ms_join);
@@ -914,8 +917,10 @@ extern "C" int cnf2_sync(cnf2_engine* e)
 	cudaSetDevice(e->settings.device);
 	for (Slot& sl : e->slots) CU(cudaStreamSynchronize(sl.stream));
 	CU(cudaStreamSynchronize(e->comm));
+	CU(cudaStreamSynchronize(e->comm2));
 	CU(cudaStreamSynchronize(e->side));
 	CU(cudaStreamSynchronize(e->stream));
+	CU(cudaStreamSynchronize(e->copy));
 	CU(cudaGetLastError());
 	return CNF2_OK;
 }
@@ -1618,6 +1623,22 @@ extern "C" int cnf2_get_params_packed(cnf2_engine* e, int32_t chrom, uint8_t* al
 	if (sure) CU(cudaMemcpyAsync(sure, e->d_sure.p + blk, n * 16, cudaMemcpyDeviceToHost, e->stream));
 	if (haploweight) CU(cudaMemcpyAsync(haploweight, e->d_hw.p + blk, n * 8, cudaMemcpyDeviceToHost, e->stream));
 	CU(cudaStreamSynchronize(e->stream));
+	return CNF2_OK;
+}
+
+extern "C" int cnf2_get_params_packed_async(cnf2_engine* e, int32_t chrom, uint8_t* alleles, double* sure, double* haploweight)
+{
+	if (!e) return CNF2_ERR_BAD_ARG;
+	if (chrom < 0 || chrom >= (int)e->have_params.size() || !e->have_params[chrom])
+		return e->fail(CNF2_ERR_STATE, "cnf2_get_params_packed_async: no parameters of this chromosome on the device");
+	cudaSetDevice(e->settings.device);
+	const size_t c0 = e->chromstarts[chrom], Mc = e->mc(chrom), n = (size_t)e->n_rows * Mc;
+	const size_t blk = (size_t)e->n_rows * (e->resident ? c0 : 0);
+	// behind the last pass / inversion enqueued so far (what it wrote is what is read), beside whatever is enqueued later
+	if (int rc = e->wait_chain(e->copy)) return rc;
+	if (alleles) CU(cudaMemcpyAsync(alleles, e->d_alleles.p + blk, n * 2, cudaMemcpyDeviceToHost, e->copy));
+	if (sure) CU(cudaMemcpyAsync(sure, e->d_sure.p + blk, n * 16, cudaMemcpyDeviceToHost, e->copy));
+	if (haploweight) CU(cudaMemcpyAsync(haploweight, e->d_hw.p + blk, n * 8, cudaMemcpyDeviceToHost, e->copy));
 	return CNF2_OK;
 }
 

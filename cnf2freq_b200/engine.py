@@ -23,6 +23,7 @@ SYMBOLS = [
     "cnf2_set_em_state", "cnf2_get_em_state", "cnf2_mstep_pass", "cnf2_negshift_minima", "cnf2_apply_inversions", "cnf2_em_pass",
     "cnf2_set_mstep_rows", "cnf2_set_mstep_chrom_packed", "cnf2_get_params_packed", "cnf2_estep_times", "cnf2_mstep_counters",
     "cnf2_preprocess", "cnf2_negshift_minima_noalloc", "cnf2_preprocess_literal_cells", "cnf2_control_stream",
+    "cnf2_get_params_packed_async",
 ]
 
 
@@ -338,6 +339,13 @@ class Engine:
         self._check(self.lib.cnf2_get_params_packed(self.h, ctypes.c_int32(chrom), _buf(alleles, np.uint8, 2 * n, "get_params_packed alleles"),
                                                     _buf(sure, np.float64, 2 * n, "get_params_packed sure"),
                                                     _buf(haploweight, np.float64, n, "get_params_packed haploweight")))
+
+    def get_params_packed_async(self, chrom, alleles=None, sure=None, haploweight=None):
+        """cnf2_get_params_packed_async: enqueues the read-back (page-locked buffers) and returns; sync() waits for it."""
+        n = self.n_rows() * self.mc(chrom)
+        self._check(self.lib.cnf2_get_params_packed_async(
+            self.h, ctypes.c_int32(chrom), _buf(alleles, np.uint8, 2 * n, "get_params_packed_async alleles"),
+            _buf(sure, np.float64, 2 * n, "get_params_packed_async sure"), _buf(haploweight, np.float64, n, "get_params_packed_async haploweight")))
 
     def estep_times(self, reset=False):
         """(summed device ms of the E-step kernels, their launches, kernels of any kind launched) since the last reset."""

@@ -205,6 +205,13 @@ int cnf2_get_params(cnf2_engine* e, int32_t chrom, uint8_t* alleles, double* sur
 /* The chromosome's parameters in the engine's row order: alleles [n_rows][Mc][2], sure [n_rows][Mc][2], haploweight
  * [n_rows][Mc] -- what the per-iteration dump (cnF2freq.cpp:8157-8192) prints, as three unstrided device -> host copies. */
 int cnf2_get_params_packed(cnf2_engine* e, int32_t chrom, uint8_t* alleles, double* sure, double* haploweight);
+/* The same without waiting: the copies (into page-locked caller buffers; any pointer may be NULL) are enqueued behind the last
+ * cnf2_mstep_pass / cnf2_em_pass / cnf2_apply_inversions issued so far and run beside whatever is issued later; cnf2_sync
+ * waits for them.  What a host that writes the per-iteration dump (:8157-8192) uses to take a chromosome's alleles and
+ * markersure as soon as its own pass is through -- processinfprobs writes them in that pass only (:6356-6367), later passes
+ * and inversions of the iteration touch haploweight alone (:3437-3459, :4533-4734) -- and the haploweights at the
+ * iteration's end, so that most of the read-back hides behind the remaining chromosomes' kernels. */
+int cnf2_get_params_packed_async(cnf2_engine* e, int32_t chrom, uint8_t* alleles, double* sure, double* haploweight);
 
 /* ---- the EM loop without host round trips (rows a6 / f1 / f2) ---------------------------------------------------
  * The reference's step-size control (cnF2freq.cpp:6333-6392: scalefactor /= 1.1 on a bad pass, *= 1.21 on a good one,

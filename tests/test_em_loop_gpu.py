@@ -208,3 +208,31 @@ def test_free_running_em_loop(eng, name):
         assert d_al == 0, f"{name}: {d_al} imputed calls differ after iteration {it}"
         assert d_su <= 1e-9 and d_hw <= 1e-9, f"{name}: drift after iteration {it}: {d_su:.2e} / {d_hw:.2e}"
         assert abs(sf - rsf) <= 1e-12 * abs(rsf), f"{name}: scalefactor after iteration {it}"
+
+
+def test_async_readback_equals_the_final_state(eng):
+    """cnf2_get_params_packed_async as bench.py's e2e loop and a dumping host use it: alleles and markersure of a chromosome
+    right behind its own pass (later passes and inversions of the iteration leave them alone), the haploweights at the
+    iteration's end; after cnf2_sync the buffers hold what cnf2_get_params_packed returns."""
+    g = dict(np.load(os.path.join(GOLDEN, "mstep_run_f2.npz")))
+    cs = g["chromstarts"].astype(np.int64)
+    C = len(cs) - 1
+    ctypes.CDLL(None).srand(1)
+    setup_iteration(eng, g, 7, first=True)  # the reference inverts ten phases per pass in this iteration
+    R = len(eng.row_ids())
+    mk = lambda: [(np.zeros((R, int(cs[c + 1] - cs[c]), 2), np.uint8), np.zeros((R, int(cs[c + 1] - cs[c]), 2)), np.zeros((R, int(cs[c + 1] - cs[c]))))
+                  for c in range(C)]
+    back, ref = mk(), mk()
+    n_inv = 0
+    for c in range(C):
+        eng.estep(c)
+        n_inv += len(eng.em_pass(c))
+        eng.get_params_packed_async(c, back[c][0], back[c][1], None)
+    for c in range(C):
+        eng.get_params_packed_async(c, None, None, back[c][2])
+    eng.sync()
+    for c in range(C):
+        eng.get_params_packed(c, *ref[c])
+        for a, b in zip(back[c], ref[c]):
+            assert np.array_equal(a, b)
+    print(f"async read-back: {n_inv} inversions applied in the iteration")
